@@ -1,0 +1,134 @@
+"""ctypes binding of libbrush_b200.so -- the same C ABI a Rust `brush-b200-sys` crate would bind
+(include/brush_b200.h).  There is NO fallback: if the library is missing or a call fails, this raises."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "lib", "libbrush_b200.so")
+
+BRUSH_OK, BRUSH_E_INVALID, BRUSH_E_CAPACITY, BRUSH_E_CUDA = 0, -1, -2, -3
+STAGE_NAMES = ["ProjectSplats", "DepthSort", "ProjectVisible", "PrefixSum", "MapGaussiansToIntersect", "TileSort",
+               "GetTileBinEdges", "Rasterize", "RasterizeBackwards", "GatherProjectBackwards"]
+
+
+class BrushUniforms(C.Structure):
+    """helpers.wgsl:7-30"""
+
+    _fields_ = [("viewmat", C.c_float * 16), ("focal", C.c_float * 2), ("img_size", C.c_uint32 * 2),
+                ("tile_bounds", C.c_uint32 * 2), ("pixel_center", C.c_float * 2), ("sh_degree", C.c_uint32),
+                ("num_visible", C.c_uint32), ("total_splats", C.c_uint32), ("padding", C.c_uint32)]
+
+
+class BrushAux(C.Structure):
+    """lib.rs:20-33 as raw device pointers"""
+
+    _fields_ = [("projected_splats", C.c_void_p), ("uniforms_buffer", C.c_void_p),
+                ("num_intersections", C.c_void_p), ("num_visible", C.c_void_p), ("final_index", C.c_void_p),
+                ("cum_tiles_hit", C.c_void_p), ("tile_bins", C.c_void_p), ("compact_gid_from_isect", C.c_void_p),
+                ("global_from_compact_gid", C.c_void_p), ("tile_id_from_isect", C.c_void_p),
+                ("isect_capacity", C.c_uint64)]
+
+
+assert C.sizeof(BrushUniforms) == 112
+
+
+class BrushError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"brush_b200 error {code}: {msg}")
+        self.code = code
+
+
+class CapacityError(BrushError):
+    pass
+
+
+_lib = None
+
+_SIGS = {
+    "brush_ctx_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
+    "brush_ctx_destroy": (None, [C.c_void_p]),
+    "brush_last_error": (C.c_char_p, [C.c_void_p]),
+    "brush_version": (C.c_char_p, []),
+    "brush_ctx_set_sort_mode": (C.c_int, [C.c_void_p, C.c_int]),
+    "brush_ctx_set_timing": (C.c_int, [C.c_void_p, C.c_int]),
+    "brush_stage_times_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.c_int, C.c_void_p]),
+    "brush_ctx_check": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "brush_render_forward": (C.c_int, [C.c_void_p, C.POINTER(BrushUniforms), C.c_uint32, C.c_uint32] +
+                             [C.c_void_p] * 5 + [C.c_int, C.c_void_p, C.POINTER(BrushAux), C.c_void_p]),
+    "brush_render_backward": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32] + [C.c_void_p] * 6 +
+                              [C.POINTER(BrushAux)] + [C.c_void_p] * 6 + [C.c_void_p]),
+    "brush_radix_argsort_u32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32,
+                                          C.c_void_p, C.c_void_p, C.c_void_p]),
+    "brush_radix_argsort_u64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32,
+                                          C.c_void_p, C.c_void_p, C.c_void_p]),
+    "brush_prefix_sum_u32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]),
+    "brush_render_forward_host": (C.c_int, [C.c_void_p, C.POINTER(BrushUniforms), C.c_uint32, C.c_uint32] +
+                                  [C.c_void_p] * 5 + [C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
+}
+
+
+def lib():
+    """Loads the CUDA library.  Raises (never falls back) if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise RuntimeError(f"{SO_PATH} not found: run `python -m brush_b200.build` (needs nvcc). "
+                               "brush_b200 has no CPU or PyTorch fallback.")
+        l = C.CDLL(SO_PATH)
+        for name, (res, args) in _SIGS.items():
+            fn = getattr(l, name)  # AttributeError if the .so does not export the ABI
+            fn.restype, fn.argtypes = res, args
+        _lib = l
+    return _lib
+
+
+def exported_symbols():
+    return sorted(_SIGS)
+
+
+class Context:
+    """One brush_ctx per (device); owns only scratch."""
+
+    def __init__(self, device: int = 0):
+        self._h = C.c_void_p()
+        rc = lib().brush_ctx_create(int(device), C.byref(self._h))
+        if rc != 0:
+            raise BrushError(rc, "brush_ctx_create failed (is a CUDA device present?)")
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib().brush_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def handle(self):
+        return self._h
+
+    def check(self, rc: int):
+        if rc != 0:
+            msg = lib().brush_last_error(self._h).decode()
+            raise (CapacityError if rc == BRUSH_E_CAPACITY else BrushError)(rc, msg)
+
+    def set_sort_mode(self, fused64: bool):
+        self.check(lib().brush_ctx_set_sort_mode(self._h, int(fused64)))
+
+    def set_timing(self, enabled: bool):
+        self.check(lib().brush_ctx_set_timing(self._h, int(enabled)))
+
+    def stage_times_ms(self, stream=0):
+        arr = (C.c_float * len(STAGE_NAMES))()
+        self.check(lib().brush_stage_times_ms(self._h, arr, len(STAGE_NAMES), C.c_void_p(stream)))
+        return dict(zip(STAGE_NAMES, list(arr)))
+
+    def sync_check(self, stream=0):
+        """Synchronises and raises CapacityError if any forward since the last check overflowed."""
+        self.check(lib().brush_ctx_check(self._h, C.c_void_p(stream)))

@@ -1,0 +1,487 @@
+// C ABI of libbrush_b200.so (include/brush_b200.h): context, scratch management and the host-side
+// sequencing of the forward chain (== render_forward, crates/brush-render/src/render.rs:55-323) and the
+// backward chain (== RenderBackwards::backward, render.rs:468-625).
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "internal.h"
+
+using namespace brush;
+
+struct Buf {
+    void* p = nullptr;
+    size_t bytes = 0;
+};
+
+struct brush_ctx {
+    int device = 0;
+    std::string err;
+    int fused64 = 0;
+    int timing = 0;
+    // scratch, grown on demand (growth synchronises; steady state never allocates)
+    Buf control, presort_gid, depth_bits, depth_sorted, num_tiles_hit, keys_tmp, vals_tmp, hist, lb, tickets,
+        tile_ids_unsorted, cg_unsorted, tile_ids_sorted, v_projected, sticky;
+    // host-staged path
+    Buf h_means, h_lscales, h_quats, h_sh, h_opac, h_img, h_aux[9];
+    cudaEvent_t ev[BRUSH_STAGE_COUNT + 1][2];
+    bool ev_used[BRUSH_STAGE_COUNT];
+    bool ev_ready = false;
+    // host copies of the uniforms written by recent forwards, keyed by aux.uniforms_buffer, so the backward
+    // needs no device readback (a forward's uniforms are part of the autodiff state, render.rs:436-446)
+    std::vector<std::pair<const void*, BrushUniforms>> uni_cache;
+};
+
+static int fail(brush_ctx* c, int code, const std::string& msg) {
+    if (c) c->err = msg;
+    return code;
+}
+static int cuda_fail(brush_ctx* c, cudaError_t e, const char* where) {
+    return fail(c, BRUSH_E_CUDA, std::string(where) + ": " + cudaGetErrorString(e));
+}
+#define CU(call)                                                     \
+    do {                                                             \
+        cudaError_t e__ = (call);                                    \
+        if (e__ != cudaSuccess) return cuda_fail(ctx, e__, #call);   \
+    } while (0)
+
+static int ensure(brush_ctx* ctx, Buf& b, size_t bytes) {
+    if (bytes <= b.bytes) return BRUSH_OK;
+    if (b.p) CU(cudaFree(b.p));
+    b.p = nullptr;
+    b.bytes = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    CU(cudaMalloc(&b.p, want));
+    b.bytes = want;
+    return BRUSH_OK;
+}
+#define ENSURE(buf, bytes)                         \
+    do {                                           \
+        int r__ = ensure(ctx, ctx->buf, (bytes));  \
+        if (r__ != BRUSH_OK) return r__;           \
+    } while (0)
+
+struct StageTimer {
+    brush_ctx* c;
+    cudaStream_t st;
+    int stage;
+    StageTimer(brush_ctx* c_, cudaStream_t s, int stage_) : c(c_), st(s), stage(stage_) {
+        if (c->timing) {
+            cudaEventRecord(c->ev[stage][0], st);
+            c->ev_used[stage] = true;
+        }
+    }
+    ~StageTimer() {
+        if (c->timing) cudaEventRecord(c->ev[stage][1], st);
+    }
+};
+
+__global__ void write_uniforms_kernel(const __grid_constant__ BrushUniforms u, int32_t* dst) {
+    const int32_t* src = reinterpret_cast<const int32_t*>(&u);
+    if (threadIdx.x < 28) dst[threadIdx.x] = src[threadIdx.x];
+}
+
+static bool valid_k(uint32_t K) { return K == 1 || K == 4 || K == 9 || K == 16 || K == 25; }
+static uint32_t degree_of(uint32_t K) { return K == 1 ? 0 : K == 4 ? 1 : K == 9 ? 2 : K == 16 ? 3 : 4; }
+static uint32_t bits_for(uint32_t num_tiles) {  // render.rs:227
+    uint32_t b = 0;
+    while (b < 32 && (num_tiles >> b)) b++;
+    return b;
+}
+
+// Layout of the control buffer (zeroed per forward): [Control][lb_project u64 x ..][lb_scan u64 x ..]
+struct ControlLayout {
+    size_t lb_project_off, lb_scan_off, total;
+};
+static ControlLayout control_layout(uint32_t N) {
+    ControlLayout l;
+    l.lb_project_off = sizeof(Control);
+    size_t project_tiles = ((size_t)N + 255) / 256 + 1;
+    l.lb_scan_off = l.lb_project_off + project_tiles * 8;
+    l.total = l.lb_scan_off + scan_status_words(N) * 8;
+    return l;
+}
+
+extern "C" {
+#pragma GCC visibility push(default)
+
+const char* brush_version(void) { return "brush_b200 0.1 (sm_100a)"; }
+
+int brush_ctx_create(int device, brush_ctx** out) {
+    if (!out) return BRUSH_E_INVALID;
+    *out = nullptr;
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return BRUSH_E_CUDA;
+    brush_ctx* ctx = new brush_ctx();
+    ctx->device = device;
+    for (int i = 0; i < BRUSH_STAGE_COUNT; i++) {
+        cudaEventCreate(&ctx->ev[i][0]);
+        cudaEventCreate(&ctx->ev[i][1]);
+        ctx->ev_used[i] = false;
+    }
+    ctx->ev_ready = true;
+    if (cudaMalloc(&ctx->sticky.p, 256) != cudaSuccess || cudaMemset(ctx->sticky.p, 0, 256) != cudaSuccess) {
+        delete ctx;
+        return BRUSH_E_CUDA;
+    }
+    ctx->sticky.bytes = 256;
+    *out = ctx;
+    return BRUSH_OK;
+}
+
+void brush_ctx_destroy(brush_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    Buf* bufs[] = {&ctx->control, &ctx->presort_gid, &ctx->depth_bits, &ctx->depth_sorted, &ctx->num_tiles_hit,
+                   &ctx->keys_tmp, &ctx->vals_tmp, &ctx->hist, &ctx->lb, &ctx->tickets, &ctx->tile_ids_unsorted,
+                   &ctx->cg_unsorted, &ctx->tile_ids_sorted, &ctx->v_projected, &ctx->sticky, &ctx->h_means, &ctx->h_lscales,
+                   &ctx->h_quats, &ctx->h_sh, &ctx->h_opac, &ctx->h_img};
+    for (Buf* b : bufs)
+        if (b->p) cudaFree(b->p);
+    for (Buf& b : ctx->h_aux)
+        if (b.p) cudaFree(b.p);
+    if (ctx->ev_ready)
+        for (int i = 0; i < BRUSH_STAGE_COUNT; i++) {
+            cudaEventDestroy(ctx->ev[i][0]);
+            cudaEventDestroy(ctx->ev[i][1]);
+        }
+    delete ctx;
+}
+
+const char* brush_last_error(brush_ctx* ctx) { return ctx ? ctx->err.c_str() : "null ctx"; }
+
+int brush_ctx_set_sort_mode(brush_ctx* ctx, int fused64) {
+    if (!ctx) return BRUSH_E_INVALID;
+    ctx->fused64 = fused64 ? 1 : 0;
+    return BRUSH_OK;
+}
+int brush_ctx_set_timing(brush_ctx* ctx, int enabled) {
+    if (!ctx) return BRUSH_E_INVALID;
+    ctx->timing = enabled ? 1 : 0;
+    return BRUSH_OK;
+}
+
+int brush_stage_times_ms(brush_ctx* ctx, float* out_host, int n, void* stream) {
+    if (!ctx || !out_host) return BRUSH_E_INVALID;
+    CU(cudaStreamSynchronize((cudaStream_t)stream));
+    for (int i = 0; i < n && i < BRUSH_STAGE_COUNT; i++) {
+        out_host[i] = 0.f;
+        if (ctx->ev_used[i]) cudaEventElapsedTime(&out_host[i], ctx->ev[i][0], ctx->ev[i][1]);
+    }
+    return BRUSH_OK;
+}
+
+int brush_ctx_check(brush_ctx* ctx, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    CU(cudaStreamSynchronize((cudaStream_t)stream));
+    uint32_t sticky = 0;
+    uint32_t* dev = reinterpret_cast<uint32_t*>(ctx->sticky.p);
+    CU(cudaMemcpy(&sticky, dev, 4, cudaMemcpyDeviceToHost));
+    if (sticky) {
+        CU(cudaMemset(dev, 0, 4));
+        if (sticky & 1u)
+            return fail(ctx, BRUSH_E_CAPACITY, "intersection count exceeded isect_capacity; lists were truncated");
+    }
+    return BRUSH_OK;
+}
+
+static int sort_scratch(brush_ctx* ctx, uint32_t max_n, int key_bytes, uint32_t bits, SortScratch* s) {
+    uint32_t rb = ((bits + 3) / 4) * 4;
+    uint32_t passes = (rb + 7) / 8;
+    size_t tiles = sort_tiles(max_n, key_bytes);
+    ENSURE(keys_tmp, (size_t)max_n * key_bytes);
+    ENSURE(vals_tmp, (size_t)max_n * 4);
+    ENSURE(hist, 8 * 256 * 4);
+    ENSURE(lb, (size_t)(passes ? passes : 1) * tiles * 256 * 4);
+    ENSURE(tickets, 64);
+    s->keys_tmp = ctx->keys_tmp.p;
+    s->vals_tmp = (uint32_t*)ctx->vals_tmp.p;
+    s->hist = (uint32_t*)ctx->hist.p;
+    s->lb = (uint32_t*)ctx->lb.p;
+    s->tickets = (uint32_t*)ctx->tickets.p;
+    return BRUSH_OK;
+}
+
+int brush_render_forward(brush_ctx* ctx, const BrushUniforms* uniforms_host, uint32_t N, uint32_t K,
+                         const float* means, const float* log_scales, const float* quats, const float* sh_coeffs,
+                         const float* raw_opacity, int raster_u32, void* out_img, const BrushAux* aux, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (!uniforms_host || !aux || !out_img) return fail(ctx, BRUSH_E_INVALID, "null argument");
+    if (!valid_k(K)) return fail(ctx, BRUSH_E_INVALID, "Invalid nr. of sh bases " + std::to_string(K));  // render.rs:51
+    if (N > 0 && (!means || !log_scales || !quats || !sh_coeffs || !raw_opacity))
+        return fail(ctx, BRUSH_E_INVALID, "null parameter array");
+    if (!aux->uniforms_buffer || !aux->num_intersections || !aux->num_visible || !aux->tile_bins ||
+        (!raster_u32 && !aux->final_index) ||
+        (N > 0 && (!aux->projected_splats || !aux->cum_tiles_hit || !aux->global_from_compact_gid)) ||
+        (aux->isect_capacity > 0 && !aux->compact_gid_from_isect))
+        return fail(ctx, BRUSH_E_INVALID, "null aux buffer");
+    if (N >= (1u << 30) || aux->isect_capacity >= (1ull << 30))
+        return fail(ctx, BRUSH_E_INVALID, "N and isect_capacity must be < 2^30");
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(ctx->device));
+
+    BrushUniforms u = *uniforms_host;
+    u.tile_bounds[0] = (u.img_size[0] + TILE_WIDTH - 1) / TILE_WIDTH;  // render.rs:82-85
+    u.tile_bounds[1] = (u.img_size[1] + TILE_WIDTH - 1) / TILE_WIDTH;
+    u.sh_degree = degree_of(K);
+    u.total_splats = N;
+    u.num_visible = 0;
+    u.padding = 0;
+    const Cam cam = make_cam(u);
+    const uint32_t num_tiles = u.tile_bounds[0] * u.tile_bounds[1];
+    const uint64_t cap = aux->isect_capacity;
+    const uint32_t cap32 = (uint32_t)cap;
+    const int fused = ctx->fused64;
+
+    const ControlLayout cl = control_layout(N);
+    ENSURE(control, cl.total);
+    ENSURE(presort_gid, (size_t)N * 4);
+    ENSURE(depth_bits, (size_t)N * 4);
+    ENSURE(depth_sorted, (size_t)N * 4);
+    ENSURE(num_tiles_hit, (size_t)N * 4);
+    ENSURE(tile_ids_unsorted, (size_t)cap * (fused ? 8 : 4));
+    ENSURE(cg_unsorted, (size_t)cap * 4);
+    if (fused || !aux->tile_id_from_isect) ENSURE(tile_ids_sorted, (size_t)cap * (fused ? 8 : 4));
+    const uint32_t tile_bits = bits_for(num_tiles);
+    SortScratch ss;
+    {
+        uint32_t mx = N > cap32 ? N : cap32;
+        int r = sort_scratch(ctx, mx, fused ? 8 : 4, fused ? 32 + tile_bits : 32, &ss);
+        if (r != BRUSH_OK) return r;
+    }
+    for (int i = 0; i <= BRUSH_STAGE_RASTERIZE; i++) ctx->ev_used[i] = false;
+
+    char* ctl = (char*)ctx->control.p;
+    Control* control = (Control*)ctl;
+    uint64_t* lb_project = (uint64_t*)(ctl + cl.lb_project_off);
+    uint64_t* lb_scan = (uint64_t*)(ctl + cl.lb_scan_off);
+    uint32_t* sticky = (uint32_t*)ctx->sticky.p;
+    uint32_t* gfc = (uint32_t*)aux->global_from_compact_gid;
+
+    {
+        bool found = false;
+        for (auto& e : ctx->uni_cache)
+            if (e.first == aux->uniforms_buffer) { e.second = u; found = true; }
+        if (!found) {
+            if (ctx->uni_cache.size() >= 256) ctx->uni_cache.erase(ctx->uni_cache.begin());
+            ctx->uni_cache.emplace_back(aux->uniforms_buffer, u);
+        }
+    }
+    CU(cudaMemsetAsync(ctl, 0, cl.total, st));
+    write_uniforms_kernel<<<1, 32, 0, st>>>(u, aux->uniforms_buffer);
+    CU(cudaMemsetAsync(aux->num_visible, 0, 4, st));
+    CU(cudaMemsetAsync(aux->num_intersections, 0, 4, st));
+    if (N) CU(cudaMemsetAsync(gfc, 0, (size_t)N * 4, st));  // int_zeros, render.rs:124
+
+    {   // render.rs:127-142
+        StageTimer t(ctx, st, BRUSH_STAGE_PROJECT_SPLATS);
+        launch_project_forward(cam, N, means, log_scales, quats, (uint32_t*)ctx->presort_gid.p,
+                               (uint32_t*)ctx->depth_bits.p, lb_project, &control->ticket[0], aux->uniforms_buffer,
+                               aux->num_visible, st);
+    }
+    {   // render.rs:151-156
+        StageTimer t(ctx, st, BRUSH_STAGE_DEPTH_SORT);
+        launch_radix_sort_u32((uint32_t*)ctx->depth_bits.p, (uint32_t*)ctx->presort_gid.p, aux->num_visible, N, 32,
+                              (uint32_t*)ctx->depth_sorted.p, gfc, ss, st);
+    }
+    {   // render.rs:168-184
+        StageTimer t(ctx, st, BRUSH_STAGE_PROJECT_VISIBLE);
+        launch_project_visible(cam, N, K, means, log_scales, quats, sh_coeffs, raw_opacity, gfc, aux->num_visible,
+                               aux->projected_splats, (uint32_t*)ctx->num_tiles_hit.p, st);
+    }
+    {   // render.rs:186-192
+        StageTimer t(ctx, st, BRUSH_STAGE_PREFIX_SUM);
+        launch_inclusive_scan((uint32_t*)ctx->num_tiles_hit.p, N, (uint32_t*)aux->cum_tiles_hit, lb_scan,
+                              &control->ticket[1], aux->num_intersections, cap, sticky, st);
+    }
+    uint32_t* tid_unsorted = (uint32_t*)ctx->tile_ids_unsorted.p;
+    uint32_t* tid_sorted = aux->tile_id_from_isect && !fused ? (uint32_t*)aux->tile_id_from_isect
+                                                             : (uint32_t*)ctx->tile_ids_sorted.p;
+    {   // render.rs:211-223
+        StageTimer t(ctx, st, BRUSH_STAGE_MAP_INTERSECTS);
+        launch_map_intersects(cam, N, aux->projected_splats, (uint32_t*)aux->cum_tiles_hit, aux->num_visible, cap,
+                              fused ? nullptr : tid_unsorted, (uint32_t*)ctx->cg_unsorted.p,
+                              (uint32_t*)ctx->depth_sorted.p, fused ? (uint64_t*)tid_unsorted : nullptr, sticky, st);
+    }
+    {   // render.rs:227-237
+        StageTimer t(ctx, st, BRUSH_STAGE_TILE_SORT);
+        if (cap32) {
+            if (fused)
+                launch_radix_sort_u64((uint64_t*)tid_unsorted, (uint32_t*)ctx->cg_unsorted.p, aux->num_intersections,
+                                      cap32, 32 + tile_bits, (uint64_t*)tid_sorted,
+                                      (uint32_t*)aux->compact_gid_from_isect, ss, st);
+            else
+                launch_radix_sort_u32(tid_unsorted, (uint32_t*)ctx->cg_unsorted.p, aux->num_intersections, cap32,
+                                      tile_bits, tid_sorted, (uint32_t*)aux->compact_gid_from_isect, ss, st);
+        }
+    }
+    {   // render.rs:239-262
+        StageTimer t(ctx, st, BRUSH_STAGE_TILE_BINS);
+        launch_tile_bins(fused ? nullptr : tid_sorted, fused ? (uint64_t*)tid_sorted : nullptr,
+                         aux->num_intersections, cap, num_tiles, (uint32_t*)aux->tile_bins, st);
+    }
+    {   // render.rs:267-307
+        StageTimer t(ctx, st, BRUSH_STAGE_RASTERIZE);
+        launch_rasterize(cam, (uint32_t*)aux->compact_gid_from_isect, (uint32_t*)aux->tile_bins,
+                         aux->projected_splats, raster_u32, out_img, (uint32_t*)aux->final_index, st);
+    }
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
+
+int brush_render_backward(brush_ctx* ctx, uint32_t N, uint32_t K, const float* means, const float* log_scales,
+                          const float* quats, const float* raw_opacity, const float* out_img,
+                          const float* v_out_img, const BrushAux* aux, float* v_means, float* v_xy,
+                          float* v_log_scales, float* v_quats, float* v_sh_coeffs, float* v_raw_opacity,
+                          void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (!valid_k(K)) return fail(ctx, BRUSH_E_INVALID, "Invalid nr. of sh bases " + std::to_string(K));
+    if (!aux || !out_img || !v_out_img || !v_means || !v_xy || !v_log_scales || !v_quats || !v_sh_coeffs ||
+        !v_raw_opacity)
+        return fail(ctx, BRUSH_E_INVALID, "null argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(ctx->device));
+    BrushUniforms u;
+    bool cached = false;
+    for (auto& e : ctx->uni_cache)
+        if (e.first == aux->uniforms_buffer) { u = e.second; cached = true; }
+    if (!cached) {  // aux from another ctx / process: read the 112 bytes back (synchronises)
+        CU(cudaMemcpyAsync(&u, aux->uniforms_buffer, sizeof(u), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+    }
+    if (u.total_splats != N || u.sh_degree != degree_of(K))
+        return fail(ctx, BRUSH_E_INVALID, "aux.uniforms_buffer does not match N / K");
+    const Cam cam = make_cam(u);
+    ENSURE(v_projected, (size_t)N * 9 * 4 + 16);
+    ctx->ev_used[BRUSH_STAGE_RASTERIZE_BWD] = ctx->ev_used[BRUSH_STAGE_GATHER_PROJECT_BWD] = false;
+    if (N) {
+        // zero-init is a contract of the reference too (render.rs:505-507,539-540,547,573-575)
+        CU(cudaMemsetAsync(ctx->v_projected.p, 0, (size_t)N * 9 * 4, st));
+        CU(cudaMemsetAsync(v_means, 0, (size_t)N * 3 * 4, st));
+        CU(cudaMemsetAsync(v_xy, 0, (size_t)N * 2 * 4, st));
+        CU(cudaMemsetAsync(v_log_scales, 0, (size_t)N * 3 * 4, st));
+        CU(cudaMemsetAsync(v_quats, 0, (size_t)N * 4 * 4, st));
+        CU(cudaMemsetAsync(v_sh_coeffs, 0, (size_t)N * K * 3 * 4, st));
+        CU(cudaMemsetAsync(v_raw_opacity, 0, (size_t)N * 4, st));
+    }
+    {   // render.rs:515-532
+        StageTimer t(ctx, st, BRUSH_STAGE_RASTERIZE_BWD);
+        launch_rasterize_backward(cam, (uint32_t*)aux->compact_gid_from_isect, (uint32_t*)aux->tile_bins,
+                                  aux->projected_splats, (uint32_t*)aux->final_index, out_img, v_out_img,
+                                  (float*)ctx->v_projected.p, st);
+    }
+    {   // render.rs:542-594
+        StageTimer t(ctx, st, BRUSH_STAGE_GATHER_PROJECT_BWD);
+        launch_gather_project_backward(cam, N, K, means, log_scales, quats, raw_opacity,
+                                       (uint32_t*)aux->global_from_compact_gid, aux->num_visible,
+                                       (float*)ctx->v_projected.p, v_means, v_xy, v_log_scales, v_quats, v_sh_coeffs,
+                                       v_raw_opacity, st);
+    }
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
+
+int brush_radix_argsort_u32(brush_ctx* ctx, const uint32_t* keys, const uint32_t* values, const int32_t* n_dev,
+                            uint32_t max_n, uint32_t bits, uint32_t* keys_out, uint32_t* values_out, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (bits > 32) return fail(ctx, BRUSH_E_INVALID, "sorting_bits must be <= 32");  // brush-sort/src/lib.rs:39
+    if (max_n >= (1u << 30)) return fail(ctx, BRUSH_E_INVALID, "max_n must be < 2^30");
+    if (max_n && (!keys || !values || !n_dev || !keys_out || !values_out))
+        return fail(ctx, BRUSH_E_INVALID, "null argument");
+    CU(cudaSetDevice(ctx->device));
+    SortScratch ss;
+    int r = sort_scratch(ctx, max_n, 4, bits, &ss);
+    if (r != BRUSH_OK) return r;
+    launch_radix_sort_u32(keys, values, n_dev, max_n, bits, keys_out, values_out, ss, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
+
+int brush_radix_argsort_u64(brush_ctx* ctx, const uint64_t* keys, const uint32_t* values, const int32_t* n_dev,
+                            uint32_t max_n, uint32_t bits, uint64_t* keys_out, uint32_t* values_out, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (bits > 64) return fail(ctx, BRUSH_E_INVALID, "sorting_bits must be <= 64");
+    if (max_n >= (1u << 30)) return fail(ctx, BRUSH_E_INVALID, "max_n must be < 2^30");
+    if (max_n && (!keys || !values || !n_dev || !keys_out || !values_out))
+        return fail(ctx, BRUSH_E_INVALID, "null argument");
+    CU(cudaSetDevice(ctx->device));
+    SortScratch ss;
+    int r = sort_scratch(ctx, max_n, 8, bits, &ss);
+    if (r != BRUSH_OK) return r;
+    launch_radix_sort_u64(keys, values, n_dev, max_n, bits, keys_out, values_out, ss, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
+
+int brush_prefix_sum_u32(brush_ctx* ctx, const uint32_t* in, uint32_t n, uint32_t* out, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (n && (!in || !out)) return fail(ctx, BRUSH_E_INVALID, "null argument");
+    if (n == 0) return BRUSH_OK;
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    size_t bytes = 64 + scan_status_words(n) * 8;
+    ENSURE(control, bytes);
+    CU(cudaMemsetAsync(ctx->control.p, 0, bytes, st));
+    launch_inclusive_scan(in, n, out, (uint64_t*)((char*)ctx->control.p + 64), (uint32_t*)ctx->control.p, nullptr,
+                          ~0ull, nullptr, st);
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
+
+int brush_render_forward_host(brush_ctx* ctx, const BrushUniforms* uniforms_host, uint32_t N, uint32_t K,
+                              const float* means_host, const float* log_scales_host, const float* quats_host,
+                              const float* sh_coeffs_host, const float* raw_opacity_host, uint64_t isect_capacity,
+                              float* out_img_host, uint32_t* num_visible_host, uint32_t* num_intersections_host) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (!uniforms_host || !out_img_host) return fail(ctx, BRUSH_E_INVALID, "null argument");
+    if (!valid_k(K)) return fail(ctx, BRUSH_E_INVALID, "Invalid nr. of sh bases " + std::to_string(K));
+    CU(cudaSetDevice(ctx->device));
+    const uint32_t W = uniforms_host->img_size[0], H = uniforms_host->img_size[1];
+    const uint32_t tx = (W + 15) / 16, ty = (H + 15) / 16;
+    const size_t n1 = N ? N : 1;
+    ENSURE(h_means, n1 * 12);
+    ENSURE(h_lscales, n1 * 12);
+    ENSURE(h_quats, n1 * 16);
+    ENSURE(h_sh, n1 * K * 12);
+    ENSURE(h_opac, n1 * 4);
+    ENSURE(h_img, (size_t)W * H * 16 + 16);
+    const size_t aux_bytes[9] = {n1 * 36, 128, 16, 16, (size_t)W * H * 4 + 16, n1 * 4, (size_t)tx * ty * 8 + 16,
+                                 (size_t)(isect_capacity ? isect_capacity : 1) * 4, n1 * 4};
+    for (int i = 0; i < 9; i++) {
+        int r = ensure(ctx, ctx->h_aux[i], aux_bytes[i]);
+        if (r != BRUSH_OK) return r;
+    }
+    cudaStream_t st = 0;
+    if (N) {
+        CU(cudaMemcpyAsync(ctx->h_means.p, means_host, (size_t)N * 12, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(ctx->h_lscales.p, log_scales_host, (size_t)N * 12, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(ctx->h_quats.p, quats_host, (size_t)N * 16, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(ctx->h_sh.p, sh_coeffs_host, (size_t)N * K * 12, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(ctx->h_opac.p, raw_opacity_host, (size_t)N * 4, cudaMemcpyHostToDevice, st));
+    }
+    BrushAux aux;
+    aux.projected_splats = (float*)ctx->h_aux[0].p;
+    aux.uniforms_buffer = (int32_t*)ctx->h_aux[1].p;
+    aux.num_intersections = (int32_t*)ctx->h_aux[2].p;
+    aux.num_visible = (int32_t*)ctx->h_aux[3].p;
+    aux.final_index = (int32_t*)ctx->h_aux[4].p;
+    aux.cum_tiles_hit = (int32_t*)ctx->h_aux[5].p;
+    aux.tile_bins = (int32_t*)ctx->h_aux[6].p;
+    aux.compact_gid_from_isect = (int32_t*)ctx->h_aux[7].p;
+    aux.global_from_compact_gid = (int32_t*)ctx->h_aux[8].p;
+    aux.tile_id_from_isect = nullptr;
+    aux.isect_capacity = isect_capacity;
+    int r = brush_render_forward(ctx, uniforms_host, N, K, (float*)ctx->h_means.p, (float*)ctx->h_lscales.p,
+                                 (float*)ctx->h_quats.p, (float*)ctx->h_sh.p, (float*)ctx->h_opac.p, 0,
+                                 ctx->h_img.p, &aux, st);
+    if (r != BRUSH_OK) return r;
+    CU(cudaMemcpyAsync(out_img_host, ctx->h_img.p, (size_t)W * H * 16, cudaMemcpyDeviceToHost, st));
+    if (num_visible_host) CU(cudaMemcpyAsync(num_visible_host, aux.num_visible, 4, cudaMemcpyDeviceToHost, st));
+    if (num_intersections_host)
+        CU(cudaMemcpyAsync(num_intersections_host, aux.num_intersections, 4, cudaMemcpyDeviceToHost, st));
+    return brush_ctx_check(ctx, st);
+}
+
+#pragma GCC visibility pop
+}  // extern "C"

@@ -1,0 +1,78 @@
+// Internal launch interface between the translation units of libbrush_b200.so.
+// Each function enqueues kernels on `st` and returns; no synchronisation.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "brush_math.cuh"
+
+namespace brush {
+
+// Word offsets inside the device copy of RenderUniforms (i32[28]).
+constexpr int UNI_NUM_VISIBLE_WORD = 25;  // render.rs:145-149
+
+// Device control block, zeroed by one memset at the start of every forward.
+struct Control {
+    uint32_t ticket[8];        // dynamic tile tickets (one per look-back kernel in the chain)
+    uint32_t status;           // sticky error bits (1 = intersection capacity overflow)
+    uint32_t num_visible;
+    uint32_t num_intersections;
+    uint32_t pad[5];
+};
+
+// ---- project.cu (-fmad=false) ----
+void launch_project_forward(const Cam& cam, uint32_t N, const float* means, const float* log_scales,
+                            const float* quats, uint32_t* presort_gid, uint32_t* depth_bits,
+                            uint64_t* lb_status, uint32_t* ticket, int32_t* uniforms_dev, int32_t* num_visible_out,
+                            cudaStream_t st);
+void launch_project_visible(const Cam& cam, uint32_t N, uint32_t K, const float* means, const float* log_scales,
+                            const float* quats, const float* coeffs, const float* raw_opac,
+                            const uint32_t* global_from_compact, const int32_t* num_visible_dev, float* projected,
+                            uint32_t* num_tiles_hit, cudaStream_t st);
+void launch_map_intersects(const Cam& cam, uint32_t N, const float* projected, const uint32_t* cum_tiles_hit,
+                           const int32_t* num_visible_dev, uint64_t capacity, uint32_t* tile_id_from_isect,
+                           uint32_t* compact_gid_from_isect, const uint32_t* depth_sorted_bits,
+                           uint64_t* key64_from_isect, uint32_t* status_word, cudaStream_t st);
+
+// ---- scan.cu ----
+// Inclusive scan of in[0..n) -> out. If total_out != nullptr, also writes the grand total (min(total,cap)) there
+// and sets bit 0 of *status_word when total > cap.
+void launch_inclusive_scan(const uint32_t* in, uint32_t n, uint32_t* out, uint64_t* lb_status, uint32_t* ticket,
+                           int32_t* total_out, uint64_t cap, uint32_t* status_word, cudaStream_t st);
+size_t scan_status_words(uint32_t n);
+
+// ---- sort.cu ----
+struct SortScratch {
+    void* keys_tmp;        // max_n keys (u32 or u64)
+    uint32_t* vals_tmp;    // max_n
+    uint32_t* hist;        // passes * 256
+    uint32_t* lb;          // passes * tiles * 256 status words
+    uint32_t* tickets;     // passes
+};
+size_t sort_tiles(uint32_t max_n, int key_bytes);
+// Zeroes what the sort needs (hist, lb, tickets) itself.  Result lands in keys_out/vals_out.
+void launch_radix_sort_u32(const uint32_t* keys, const uint32_t* vals, const int32_t* n_dev, uint32_t max_n,
+                           uint32_t bits, uint32_t* keys_out, uint32_t* vals_out, const SortScratch& s,
+                           cudaStream_t st);
+void launch_radix_sort_u64(const uint64_t* keys, const uint32_t* vals, const int32_t* n_dev, uint32_t max_n,
+                           uint32_t bits, uint64_t* keys_out, uint32_t* vals_out, const SortScratch& s,
+                           cudaStream_t st);
+
+// ---- raster.cu ----
+void launch_tile_bins(const uint32_t* sorted_tile_ids, const uint64_t* sorted_keys64, const int32_t* n_isect_dev,
+                      uint64_t capacity, uint32_t num_tiles, uint32_t* tile_bins, cudaStream_t st);
+void launch_rasterize(const Cam& cam, const uint32_t* compact_gid_from_isect, const uint32_t* tile_bins,
+                      const float* projected, int raster_u32, void* out_img, uint32_t* final_index,
+                      cudaStream_t st);
+void launch_rasterize_backward(const Cam& cam, const uint32_t* compact_gid_from_isect, const uint32_t* tile_bins,
+                               const float* projected, const uint32_t* final_index, const float* out_img,
+                               const float* v_out_img, float* v_projected /* [N,9] zeroed */, cudaStream_t st);
+
+// ---- backward.cu ----
+void launch_gather_project_backward(const Cam& cam, uint32_t N, uint32_t K, const float* means,
+                                    const float* log_scales, const float* quats, const float* raw_opac,
+                                    const uint32_t* global_from_compact, const int32_t* num_visible_dev,
+                                    const float* v_projected, float* v_means, float* v_xy, float* v_log_scales,
+                                    float* v_quats, float* v_coeffs, float* v_raw_opac, cudaStream_t st);
+
+}  // namespace brush

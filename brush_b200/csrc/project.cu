@@ -1,0 +1,239 @@
+// Projection stages of the forward chain.  Compiled with -fmad=false: these kernels decide the
+// integer outputs (visibility, depth order, tile lists), which are bit-exact against the oracle.
+//   project_forward   == crates/brush-render/src/shaders/project_forward.wgsl:15-68
+//   project_visible   == crates/brush-render/src/shaders/project_visible.wgsl:163-258
+//   map_intersects    == crates/brush-render/src/shaders/map_gaussian_to_intersects.wgsl:10-48
+#include "internal.h"
+#include "lookback.cuh"
+
+namespace brush {
+
+constexpr int PF_THREADS = 256;
+
+// Stage a block's packed vec3 rows (12-byte stride) through shared memory with 16-byte loads.
+// Rows [first, first+256) -> smem[3*i .. 3*i+2].
+__device__ __forceinline__ void stage_vec3_rows(const float* __restrict__ src, uint32_t first, uint32_t n_total,
+                                                float* smem) {
+    const uint32_t tid = threadIdx.x;
+    if (first + PF_THREADS <= n_total) {
+        // 256 rows * 12 B = 3072 B = 192 float4, block base is 3072-byte aligned.
+        if (tid < 192) {
+            float4 v = __ldg(reinterpret_cast<const float4*>(src + (size_t)first * 3) + tid);
+            reinterpret_cast<float4*>(smem)[tid] = v;
+        }
+    } else {
+        uint32_t rows = n_total - first;
+        for (uint32_t i = tid; i < rows * 3; i += PF_THREADS) smem[i] = __ldg(src + (size_t)first * 3 + i);
+    }
+}
+
+__global__ void __launch_bounds__(PF_THREADS)
+project_forward_kernel(const __grid_constant__ Cam cam, const float* __restrict__ means,
+                       const float* __restrict__ log_scales, const float* __restrict__ quats,
+                       uint32_t* __restrict__ presort_gid, uint32_t* __restrict__ depth_bits, uint64_t* lb_status,
+                       uint32_t* ticket, int32_t* uniforms_dev, int32_t* num_visible_out) {
+    __shared__ __align__(16) float s_mean[PF_THREADS * 3];
+    __shared__ __align__(16) float s_lscale[PF_THREADS * 3];
+    __shared__ uint32_t s_warp_tot[PF_THREADS / 32];
+    __shared__ uint32_t s_tile, s_base;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const uint32_t N = cam.total_splats;
+    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t first = tile * PF_THREADS;
+    stage_vec3_rows(means, first, N, s_mean);
+    stage_vec3_rows(log_scales, first, N, s_lscale);
+    __syncthreads();
+
+    const uint32_t g = first + tid;
+    bool visible = false;
+    float depth = 0.0f;
+    if (g < N) {
+        V3 mean = {s_mean[3 * tid], s_mean[3 * tid + 1], s_mean[3 * tid + 2]};
+        V3 p_view = mul(cam.W, mean) + cam.t;
+        if (!(p_view.z <= 0.01f)) {
+            V3 scale = exp3(V3{s_lscale[3 * tid], s_lscale[3 * tid + 1], s_lscale[3 * tid + 2]});
+            float4 q4 = __ldg(reinterpret_cast<const float4*>(quats) + g);
+            V3 cov2d = calc_cov2d(cam, p_view, scale, V4{q4.x, q4.y, q4.z, q4.w});
+            float det = cov2d.x * cov2d.z - cov2d.y * cov2d.y;
+            if (!(det == 0.0f)) {
+                V3 conic = cov_to_conic(cov2d);
+                V2 xy = project_pix(cam, p_view);
+                uint32_t radius = radius_from_conic(conic);
+                TileBox b = get_tile_bbox(xy, radius, cam.tiles_x, cam.tiles_y);
+                visible = !((b.maxx - b.minx) == 0u || (b.maxy - b.miny) == 0u);
+                depth = p_view.z;
+            }
+        }
+    }
+    // Deterministic compaction: ballot -> warp offsets -> block scan -> chained look-back across tiles.
+    const uint32_t ballot = __ballot_sync(0xffffffffu, visible);
+    const uint32_t in_warp = __popc(ballot & ((1u << lane) - 1u));
+    if (lane == 0) s_warp_tot[warp] = __popc(ballot);
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t v = lane < PF_THREADS / 32 ? s_warp_tot[lane] : 0u;
+        uint32_t incl = v;
+#pragma unroll
+        for (int o = 1; o < PF_THREADS / 32; o <<= 1) {
+            uint32_t n = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= (uint32_t)o) incl += n;
+        }
+        uint32_t block_total = __shfl_sync(0xffffffffu, incl, PF_THREADS / 32 - 1);
+        if (lane < PF_THREADS / 32) s_warp_tot[lane] = incl - v;  // exclusive warp offsets
+        uint32_t excl = lookback_exclusive(lb_status, tile, block_total);
+        if (lane == 0) {
+            s_base = excl;
+            if (first + PF_THREADS >= N) {  // last tile: the inclusive total is num_visible
+                uniforms_dev[UNI_NUM_VISIBLE_WORD] = (int32_t)(excl + block_total);
+                *num_visible_out = (int32_t)(excl + block_total);
+            }
+        }
+    }
+    __syncthreads();
+    if (visible) {
+        uint32_t w = s_base + s_warp_tot[warp] + in_warp;
+        presort_gid[w] = g;
+        depth_bits[w] = __float_as_uint(depth);  // positive floats sort as u32 (render.rs:153-155)
+    }
+}
+
+void launch_project_forward(const Cam& cam, uint32_t N, const float* means, const float* log_scales,
+                            const float* quats, uint32_t* presort_gid, uint32_t* depth_bits, uint64_t* lb_status,
+                            uint32_t* ticket, int32_t* uniforms_dev, int32_t* num_visible_out, cudaStream_t st) {
+    if (N == 0) return;
+    uint32_t tiles = (N + PF_THREADS - 1) / PF_THREADS;
+    project_forward_kernel<<<tiles, PF_THREADS, 0, st>>>(cam, means, log_scales, quats, presort_gid, depth_bits,
+                                                         lb_status, ticket, uniforms_dev, num_visible_out);
+}
+
+// ---------------------------------------------------------------------------------------------
+template <int K>
+__device__ __forceinline__ V3 eval_sh_color(uint32_t degree, V3 viewdir, const float* __restrict__ coeffs,
+                                            uint32_t g) {
+    float c[3 * K];
+    const float* base = coeffs + (size_t)g * (3 * K);
+    if ((3 * K) % 4 == 0) {
+#pragma unroll
+        for (int j = 0; j < (3 * K) / 4; j++) {
+            float4 v = __ldg(reinterpret_cast<const float4*>(base) + j);
+            c[4 * j] = v.x; c[4 * j + 1] = v.y; c[4 * j + 2] = v.z; c[4 * j + 3] = v.w;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < 3 * K; j++) c[j] = __ldg(base + j);
+    }
+    float b[K];
+    sh_basis<K>(degree, viewdir, b);
+    V3 col = {0.f, 0.f, 0.f};
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        col.x += b[k] * c[3 * k];
+        col.y += b[k] * c[3 * k + 1];
+        col.z += b[k] * c[3 * k + 2];
+    }
+    return col;
+}
+
+template <int K>
+__global__ void __launch_bounds__(256)
+project_visible_kernel(const __grid_constant__ Cam cam, const float* __restrict__ means,
+                       const float* __restrict__ log_scales, const float* __restrict__ quats,
+                       const float* __restrict__ coeffs, const float* __restrict__ raw_opac,
+                       const uint32_t* __restrict__ global_from_compact, const int32_t* __restrict__ num_visible_dev,
+                       float* __restrict__ projected, uint32_t* __restrict__ num_tiles_hit) {
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cam.total_splats) return;
+    const uint32_t V = (uint32_t)*num_visible_dev;
+    if (c >= V) {
+        num_tiles_hit[c] = 0u;  // the scan runs over all N (render.rs:164-165,187)
+        return;
+    }
+    const uint32_t g = global_from_compact[c];
+    V3 mean = {__ldg(means + 3 * (size_t)g), __ldg(means + 3 * (size_t)g + 1), __ldg(means + 3 * (size_t)g + 2)};
+    V3 ls = {__ldg(log_scales + 3 * (size_t)g), __ldg(log_scales + 3 * (size_t)g + 1),
+             __ldg(log_scales + 3 * (size_t)g + 2)};
+    float4 q4 = __ldg(reinterpret_cast<const float4*>(quats) + g);
+    V3 scale = exp3(ls);
+    float opac = sigmoid_det(__ldg(raw_opac + g));
+    V3 p_view = mul(cam.W, mean) + cam.t;
+    V3 cov2d = calc_cov2d(cam, p_view, scale, V4{q4.x, q4.y, q4.z, q4.w});
+    V3 conic = cov_to_conic(cov2d);
+    V2 xy = project_pix(cam, p_view);
+    V3 viewdir = normalize3(mean - cam.t);  // project_visible.wgsl:232-233
+    V3 color = eval_sh_color<K>(cam.sh_degree, viewdir, coeffs, g);
+    color = {color.x + 0.5f, color.y + 0.5f, color.z + 0.5f};
+
+    uint32_t radius = radius_from_conic(conic);
+    TileBox b = get_tile_bbox(xy, radius, cam.tiles_x, cam.tiles_y);
+    VisTest vt = make_vis_test(xy, conic, opac);
+    uint32_t area = 0;
+    for (uint32_t ty = b.miny; ty < b.maxy; ty++)
+        for (uint32_t tx = b.minx; tx < b.maxx; tx++) area += can_be_visible(vt, tx, ty) ? 1u : 0u;
+
+    float* p = projected + (size_t)c * 9;
+    p[0] = xy.x; p[1] = xy.y; p[2] = conic.x; p[3] = conic.y; p[4] = conic.z;
+    p[5] = color.x; p[6] = color.y; p[7] = color.z; p[8] = opac;
+    num_tiles_hit[c] = area;
+}
+
+void launch_project_visible(const Cam& cam, uint32_t N, uint32_t K, const float* means, const float* log_scales,
+                            const float* quats, const float* coeffs, const float* raw_opac,
+                            const uint32_t* global_from_compact, const int32_t* num_visible_dev, float* projected,
+                            uint32_t* num_tiles_hit, cudaStream_t st) {
+    if (N == 0) return;
+    dim3 grid((N + 255) / 256), block(256);
+#define PV_ARGS cam, means, log_scales, quats, coeffs, raw_opac, global_from_compact, num_visible_dev, projected, \
+                num_tiles_hit
+    switch (K) {
+        case 1: project_visible_kernel<1><<<grid, block, 0, st>>>(PV_ARGS); break;
+        case 4: project_visible_kernel<4><<<grid, block, 0, st>>>(PV_ARGS); break;
+        case 9: project_visible_kernel<9><<<grid, block, 0, st>>>(PV_ARGS); break;
+        case 16: project_visible_kernel<16><<<grid, block, 0, st>>>(PV_ARGS); break;
+        case 25: project_visible_kernel<25><<<grid, block, 0, st>>>(PV_ARGS); break;
+    }
+#undef PV_ARGS
+}
+
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+map_intersects_kernel(const __grid_constant__ Cam cam, const float* __restrict__ projected,
+                      const uint32_t* __restrict__ cum_tiles_hit, const int32_t* __restrict__ num_visible_dev,
+                      uint64_t capacity, uint32_t* __restrict__ tile_id_from_isect,
+                      uint32_t* __restrict__ compact_gid_from_isect, const uint32_t* __restrict__ depth_sorted_bits,
+                      uint64_t* __restrict__ key64_from_isect) {
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t V = (uint32_t)*num_visible_dev;
+    if (c >= V) return;
+    const float* p = projected + (size_t)c * 9;
+    V2 xy = {p[0], p[1]};
+    V3 conic = {p[2], p[3], p[4]};
+    float opac = p[8];
+    uint32_t radius = radius_from_conic(conic);
+    TileBox b = get_tile_bbox(xy, radius, cam.tiles_x, cam.tiles_y);
+    VisTest vt = make_vis_test(xy, conic, opac);
+    uint64_t isect = c > 0 ? cum_tiles_hit[c - 1] : 0u;
+    const uint64_t depth_lo = key64_from_isect ? (uint64_t)depth_sorted_bits[c] : 0ull;
+    for (uint32_t ty = b.miny; ty < b.maxy; ty++)
+        for (uint32_t tx = b.minx; tx < b.maxx; tx++)
+            if (can_be_visible(vt, tx, ty) && isect < capacity) {
+                uint32_t tile_id = tx + ty * cam.tiles_x;
+                if (key64_from_isect) key64_from_isect[isect] = ((uint64_t)tile_id << 32) | depth_lo;
+                else tile_id_from_isect[isect] = tile_id;
+                compact_gid_from_isect[isect] = c;
+                isect++;
+            }
+}
+
+void launch_map_intersects(const Cam& cam, uint32_t N, const float* projected, const uint32_t* cum_tiles_hit,
+                           const int32_t* num_visible_dev, uint64_t capacity, uint32_t* tile_id_from_isect,
+                           uint32_t* compact_gid_from_isect, const uint32_t* depth_sorted_bits,
+                           uint64_t* key64_from_isect, uint32_t* /*status_word*/, cudaStream_t st) {
+    if (N == 0) return;
+    map_intersects_kernel<<<(N + 255) / 256, 256, 0, st>>>(cam, projected, cum_tiles_hit, num_visible_dev, capacity,
+                                                           tile_id_from_isect, compact_gid_from_isect,
+                                                           depth_sorted_bits, key64_from_isect);
+}
+
+}  // namespace brush

@@ -1,0 +1,258 @@
+// Tile binning and the per-tile alpha compositor, forward and backward.
+//   tile_bins          == crates/brush-render/src/shaders/get_tile_bin_edges.wgsl:15-42
+//   rasterize          == crates/brush-render/src/shaders/rasterize.wgsl:20-115
+//   rasterize_backward == crates/brush-render/src/shaders/rasterize_backwards.wgsl:140-304
+// FP32/MUFU-bound stages: compiled with FMA contraction on and ex2.approx for exp(-sigma); parity is
+// the 1e-5 absolute image tolerance / 1e-3 relative gradient tolerance, not bit equality.
+#include "internal.h"
+
+namespace brush {
+
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+tile_bins_kernel(const uint32_t* __restrict__ tile_ids, const uint64_t* __restrict__ keys64,
+                 const int32_t* __restrict__ n_dev, uint64_t capacity, uint32_t* __restrict__ tile_bins) {
+    const uint32_t n = (uint32_t)min((uint64_t)max(*n_dev, 0), capacity);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t cur = keys64 ? (uint32_t)(keys64[i] >> 32) : tile_ids[i];
+        if (i == n - 1) tile_bins[cur * 2 + 1] = n;
+        if (i == 0) {
+            tile_bins[cur * 2] = 0u;
+        } else {
+            const uint32_t prev = keys64 ? (uint32_t)(keys64[i - 1] >> 32) : tile_ids[i - 1];
+            if (prev != cur) {
+                tile_bins[prev * 2 + 1] = i;
+                tile_bins[cur * 2] = i;
+            }
+        }
+    }
+}
+
+void launch_tile_bins(const uint32_t* sorted_tile_ids, const uint64_t* sorted_keys64, const int32_t* n_isect_dev,
+                      uint64_t capacity, uint32_t num_tiles, uint32_t* tile_bins, cudaStream_t st) {
+    cudaMemsetAsync(tile_bins, 0, (size_t)num_tiles * 2 * sizeof(uint32_t), st);  // render.rs:241-244
+    if (capacity == 0) return;
+    uint64_t blocks = (capacity + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    tile_bins_kernel<<<(uint32_t)blocks, 256, 0, st>>>(sorted_tile_ids, sorted_keys64, n_isect_dev, capacity,
+                                                       tile_bins);
+}
+
+// ---------------------------------------------------------------------------------------------
+// One CTA per 16x16 tile, one thread per pixel.  The tile's depth-sorted splats are staged through
+// shared memory in batches of 256 (rasterize.wgsl:57-71); every thread then reads the same splat at
+// the same time (shared-memory broadcast, conflict free).
+struct SplatSmem {
+    float4 g0[TILE_SIZE];  // x, y, conic.x, conic.y
+    float2 g1[TILE_SIZE];  // conic.z, opacity
+    float4 col[TILE_SIZE]; // r, g, b, -
+};
+
+__device__ __forceinline__ void stage_splat(SplatSmem& s, uint32_t slot, const float* __restrict__ projected,
+                                            uint32_t cg) {
+    const float* p = projected + (size_t)cg * 9;
+    s.g0[slot] = make_float4(__ldg(p), __ldg(p + 1), __ldg(p + 2), __ldg(p + 3));
+    s.g1[slot] = make_float2(__ldg(p + 4), __ldg(p + 8));
+    s.col[slot] = make_float4(__ldg(p + 5), __ldg(p + 6), __ldg(p + 7), 0.f);
+}
+
+template <bool RASTER_U32>
+__global__ void __launch_bounds__(TILE_SIZE)
+rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ compact_gid_from_isect,
+                 const uint32_t* __restrict__ tile_bins, const float* __restrict__ projected,
+                 void* __restrict__ out_img, uint32_t* __restrict__ final_index) {
+    __shared__ SplatSmem s;
+    const uint32_t tid = threadIdx.x;
+    const uint32_t tile_id = blockIdx.x + blockIdx.y * cam.tiles_x;
+    const uint32_t px = blockIdx.x * TILE_WIDTH + (tid % TILE_WIDTH);
+    const uint32_t py = blockIdx.y * TILE_WIDTH + (tid / TILE_WIDTH);
+    const bool inside = px < cam.img_w && py < cam.img_h;
+    const float pcx = (float)px + 0.5f, pcy = (float)py + 0.5f;
+    bool done = !inside;
+
+    const uint2 range = __ldg(reinterpret_cast<const uint2*>(tile_bins) + tile_id);
+    const uint32_t num_batches = (range.y - range.x + TILE_SIZE - 1) / TILE_SIZE;
+    float T = 1.0f;
+    float pr = 0.f, pg = 0.f, pb = 0.f;
+    uint32_t final_idx = 0;
+
+    for (uint32_t b = 0; b < num_batches; b++) {
+        // barrier before the batch buffer is overwritten + whole-tile early exit (the reference keeps
+        // finished threads spinning through every batch)
+        if (__syncthreads_and(done)) break;
+        const uint32_t batch_start = range.x + b * TILE_SIZE;
+        const uint32_t remaining = min(TILE_SIZE, range.y - batch_start);
+        if (tid < remaining) stage_splat(s, tid, projected, __ldg(compact_gid_from_isect + batch_start + tid));
+        __syncthreads();
+        if (!done) {
+            for (uint32_t t = 0; t < remaining; t++) {
+                const float4 g0 = s.g0[t];
+                const float2 g1 = s.g1[t];
+                const float dx = g0.x - pcx, dy = g0.y - pcy;
+                const float sigma = 0.5f * (g0.z * dx * dx + g1.x * dy * dy) + g0.w * dx * dy;
+                const float vis = __expf(-sigma);
+                const float alpha = fminf(0.999f, g1.y * vis);
+                if (sigma >= 0.0f && alpha >= 1.0f / 255.0f) {
+                    const float next_T = T * (1.0f - alpha);
+                    if (next_T <= 1e-4f) {
+                        done = true;
+                        break;
+                    }
+                    const float fac = alpha * T;
+                    const float4 c = s.col[t];
+                    pr += c.x * fac; pg += c.y * fac; pb += c.z * fac;
+                    T = next_T;
+                    final_idx = batch_start + t;
+                }
+            }
+        }
+    }
+    if (inside) {
+        const size_t pix_id = (size_t)px + (size_t)py * cam.img_w;
+        const float a = 1.0f - T;
+        if (RASTER_U32) {  // rasterize.wgsl:106-109
+            uint32_t r8 = __float2uint_rz(fminf(fmaxf(pr * 255.0f, 0.f), 255.f));
+            uint32_t g8 = __float2uint_rz(fminf(fmaxf(pg * 255.0f, 0.f), 255.f));
+            uint32_t b8 = __float2uint_rz(fminf(fmaxf(pb * 255.0f, 0.f), 255.f));
+            uint32_t a8 = __float2uint_rz(fminf(fmaxf(a * 255.0f, 0.f), 255.f));
+            reinterpret_cast<uint32_t*>(out_img)[pix_id] = r8 | (g8 << 8) | (b8 << 16) | (a8 << 24);
+        } else {
+            reinterpret_cast<float4*>(out_img)[pix_id] = make_float4(pr, pg, pb, a);
+            final_index[pix_id] = final_idx;
+        }
+    }
+}
+
+void launch_rasterize(const Cam& cam, const uint32_t* compact_gid_from_isect, const uint32_t* tile_bins,
+                      const float* projected, int raster_u32, void* out_img, uint32_t* final_index,
+                      cudaStream_t st) {
+    if (cam.tiles_x == 0 || cam.tiles_y == 0) return;
+    dim3 grid(cam.tiles_x, cam.tiles_y);
+    if (raster_u32)
+        rasterize_kernel<true><<<grid, TILE_SIZE, 0, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
+                                                           out_img, final_index);
+    else
+        rasterize_kernel<false><<<grid, TILE_SIZE, 0, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
+                                                            out_img, final_index);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Backward.  Per pixel, back to front (rasterize_backwards.wgsl:194-272).  The nine per-splat
+// gradient terms are summed over the warp with a butterfly that halves the live values at each
+// exchange (12 shuffles instead of 9*5), then added with one predicated red.global.add.f32 -- the
+// native replacement for the reference's CAS loops (rasterize_backwards.wgsl:79-133).
+__device__ __forceinline__ float warp_reduce9(float v0, float v1, float v2, float v3, float v4, float v5, float v6,
+                                              float v7, float v8, uint32_t lane) {
+    const uint32_t F = 0xffffffffu;
+    const bool h16 = lane & 16u, h8 = lane & 8u, h4 = lane & 4u, h2 = lane & 2u;
+    float a0 = (h16 ? v4 : v0) + __shfl_xor_sync(F, h16 ? v0 : v4, 16);
+    float a1 = (h16 ? v5 : v1) + __shfl_xor_sync(F, h16 ? v1 : v5, 16);
+    float a2 = (h16 ? v6 : v2) + __shfl_xor_sync(F, h16 ? v2 : v6, 16);
+    float a3 = (h16 ? v7 : v3) + __shfl_xor_sync(F, h16 ? v3 : v7, 16);
+    float b0 = (h8 ? a2 : a0) + __shfl_xor_sync(F, h8 ? a0 : a2, 8);
+    float b1 = (h8 ? a3 : a1) + __shfl_xor_sync(F, h8 ? a1 : a3, 8);
+    float c = (h4 ? b1 : b0) + __shfl_xor_sync(F, h4 ? b0 : b1, 4);
+    float w = v8;
+    w += __shfl_xor_sync(F, w, 16);
+    w += __shfl_xor_sync(F, w, 8);
+    w += __shfl_xor_sync(F, w, 4);
+    float x = (h2 ? w : c) + __shfl_xor_sync(F, h2 ? c : w, 2);
+    x += __shfl_xor_sync(F, x, 1);
+    // lanes with (lane & 3) == 0 hold the total of value (lane >> 2); lanes with bit 1 set hold value 8
+    return x;
+}
+
+__global__ void __launch_bounds__(TILE_SIZE)
+rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ compact_gid_from_isect,
+                          const uint32_t* __restrict__ tile_bins, const float* __restrict__ projected,
+                          const uint32_t* __restrict__ final_index, const float* __restrict__ out_img,
+                          const float* __restrict__ v_out_img, float* __restrict__ v_projected) {
+    __shared__ SplatSmem s;
+    __shared__ uint32_t s_id[TILE_SIZE];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u;
+    const uint32_t tile_id = blockIdx.x;
+    const uint32_t tile_x = tile_id % cam.tiles_x, tile_y = tile_id / cam.tiles_x;
+    const uint32_t px = tile_x * TILE_WIDTH + (tid % TILE_WIDTH);
+    const uint32_t py = tile_y * TILE_WIDTH + (tid / TILE_WIDTH);
+    const bool inside = px < cam.img_w && py < cam.img_h;
+    const float pcx = (float)px + 0.5f, pcy = (float)py + 0.5f;
+
+    const uint2 range = __ldg(reinterpret_cast<const uint2*>(tile_bins) + tile_id);
+    if (range.y <= range.x) return;
+
+    float T_final = 1.0f;
+    float4 v_out = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint32_t final_isect = 0;
+    if (inside) {
+        const size_t pix_id = (size_t)px + (size_t)py * cam.img_w;
+        T_final = 1.0f - __ldg(out_img + pix_id * 4 + 3);
+        final_isect = __ldg(final_index + pix_id);
+        v_out = __ldg(reinterpret_cast<const float4*>(v_out_img) + pix_id);
+    }
+    float T = T_final;
+    float br = 0.f, bg = 0.f, bb = 0.f;
+    // Splats behind every pixel's last contributor are skipped warp-wide.
+    const uint32_t warp_final = __reduce_max_sync(0xffffffffu, inside ? final_isect : 0u);
+    const bool warp_any_inside = __any_sync(0xffffffffu, inside);
+
+    const uint32_t num_batches = (range.y - range.x + TILE_SIZE - 1) / TILE_SIZE;
+    for (uint32_t b = 0; b < num_batches; b++) {
+        __syncthreads();
+        const uint32_t batch_end = range.y - b * TILE_SIZE;
+        const uint32_t remaining = min(TILE_SIZE, batch_end - range.x);
+        if (tid < remaining) {
+            const uint32_t cg = __ldg(compact_gid_from_isect + batch_end - 1u - tid);
+            s_id[tid] = cg;
+            stage_splat(s, tid, projected, cg);
+        }
+        __syncthreads();
+        if (!warp_any_inside) continue;
+        for (uint32_t t = 0; t < remaining; t++) {
+            const uint32_t isect = batch_end - 1u - t;
+            if (isect > warp_final) continue;  // warp-uniform
+            const float4 g0 = s.g0[t];
+            const float2 g1 = s.g1[t];
+            const float dx = g0.x - pcx, dy = g0.y - pcy;
+            const float sigma = 0.5f * (g0.z * dx * dx + g1.x * dy * dy) + g0.w * dx * dy;
+            const float vis = __expf(-sigma);
+            const float alpha = fminf(0.99f, g1.y * vis);  // 0.99 here, 0.999 forward (reference quirk)
+            const bool active = inside && isect <= final_isect && sigma >= 0.0f && alpha >= 1.0f / 255.0f;
+            if (!__any_sync(0xffffffffu, active)) continue;
+            float v_x = 0.f, v_y = 0.f, v_cxx = 0.f, v_cxy = 0.f, v_cyy = 0.f, v_r = 0.f, v_g = 0.f, v_b = 0.f,
+                  v_a = 0.f;
+            if (active) {
+                const float4 c = s.col[t];
+                const float ra = __frcp_rn(1.0f - alpha);
+                T *= ra;
+                const float fac = alpha * T;
+                float v_alpha = (c.x * T - br * ra) * v_out.x + (c.y * T - bg * ra) * v_out.y +
+                                (c.z * T - bb * ra) * v_out.z;
+                v_alpha += T_final * ra * v_out.w;
+                br += c.x * fac; bg += c.y * fac; bb += c.z * fac;
+                const float v_sigma = -g1.y * vis * v_alpha;
+                v_x = v_sigma * (g0.z * dx + g0.w * dy);
+                v_y = v_sigma * (g0.w * dx + g1.x * dy);
+                v_cxx = 0.5f * v_sigma * dx * dx;
+                v_cxy = v_sigma * dx * dy;
+                v_cyy = 0.5f * v_sigma * dy * dy;
+                v_r = fac * v_out.x; v_g = fac * v_out.y; v_b = fac * v_out.z;
+                v_a = vis * v_alpha;
+            }
+            const float x = warp_reduce9(v_x, v_y, v_cxx, v_cxy, v_cyy, v_r, v_g, v_b, v_a, lane);
+            float* dst = v_projected + (size_t)s_id[t] * 9;
+            if ((lane & 3u) == 0u) atomicAdd(dst + (lane >> 2), x);
+            else if (lane == 2u) atomicAdd(dst + 8, x);
+        }
+    }
+}
+
+void launch_rasterize_backward(const Cam& cam, const uint32_t* compact_gid_from_isect, const uint32_t* tile_bins,
+                               const float* projected, const uint32_t* final_index, const float* out_img,
+                               const float* v_out_img, float* v_projected, cudaStream_t st) {
+    const uint32_t tiles = cam.tiles_x * cam.tiles_y;
+    if (tiles == 0) return;
+    rasterize_backward_kernel<<<tiles, TILE_SIZE, 0, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
+                                                           final_index, out_img, v_out_img, v_projected);
+}
+
+}  // namespace brush

@@ -1,0 +1,270 @@
+// Onesweep least-significant-digit radix sort (Adinets & Merrill 2022), key-value, stable, 8-bit digits.
+// == brush_sort::radix_argsort (brush-sort/src/lib.rs:32-147), which runs 5 kernels per 4-bit pass
+// (count / reduce / scan / scan_add / scatter: 40 launches for 32 bits).  Here: one histogram launch
+// for all passes + ONE launch per 8-bit pass; each pass reads and writes every key/value once and
+// resolves the cross-tile digit offsets with decoupled look-back instead of a global scan.
+//
+// The element count lives on the device (*n_dev), as in the reference (indirect dispatch): the grid
+// is sized for max_n and tiles past *n_dev exit at once.
+// Sort order contract: stable, ascending on the low 4*ceil(bits/4) key bits (exactly the bits the
+// reference's ceil(bits/4) passes look at).
+#include "internal.h"
+
+namespace brush {
+
+constexpr int RS_THREADS = 256;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_RADIX = 256;
+constexpr int RS_MAX_PASSES = 8;
+
+template <typename KeyT> struct SortCfg;
+template <> struct SortCfg<uint32_t> { static constexpr int ITEMS = 16; };
+template <> struct SortCfg<uint64_t> { static constexpr int ITEMS = 8; };
+
+size_t sort_tiles(uint32_t max_n, int key_bytes) {
+    uint32_t tile = RS_THREADS * (key_bytes == 8 ? SortCfg<uint64_t>::ITEMS : SortCfg<uint32_t>::ITEMS);
+    return ((size_t)max_n + tile - 1) / tile;
+}
+
+struct PassPlan {
+    uint32_t passes;
+    uint32_t shift[RS_MAX_PASSES];
+    uint32_t mask[RS_MAX_PASSES];
+};
+
+static PassPlan make_plan(uint32_t bits) {
+    PassPlan p{};
+    uint32_t rb = ((bits + 3) / 4) * 4;  // bits the reference's 4-bit passes cover
+    p.passes = (rb + 7) / 8;
+    for (uint32_t i = 0; i < p.passes; i++) {
+        uint32_t nb = rb - 8 * i < 8 ? rb - 8 * i : 8;
+        p.shift[i] = 8 * i;
+        p.mask[i] = (1u << nb) - 1u;
+    }
+    return p;
+}
+
+// ---- histogram of every pass's digit, one read of the keys ----
+template <typename KeyT>
+__global__ void __launch_bounds__(RS_THREADS)
+radix_hist_kernel(const KeyT* __restrict__ keys, const int32_t* __restrict__ n_dev, uint32_t max_n,
+                  const __grid_constant__ PassPlan plan, uint32_t* __restrict__ hist) {
+    __shared__ uint32_t s_hist[RS_MAX_PASSES * RS_RADIX];
+    const uint32_t n = min((uint32_t)max(*n_dev, 0), max_n);
+    for (uint32_t i = threadIdx.x; i < plan.passes * RS_RADIX; i += RS_THREADS) s_hist[i] = 0;
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31u;
+    // warp-uniform loop bound so match_any always sees the whole warp
+    const uint32_t stride = gridDim.x * RS_THREADS;
+    for (uint32_t base = blockIdx.x * RS_THREADS; base < n; base += stride) {
+        const uint32_t i = base + threadIdx.x;
+        const bool valid = i < n;
+        const KeyT k = valid ? keys[i] : (KeyT)0;
+        for (uint32_t p = 0; p < plan.passes; p++) {
+            const uint32_t d = (uint32_t)(k >> plan.shift[p]) & plan.mask[p];
+            // warp-aggregated shared atomics: clustered keys (tile ids, depth exponents) would
+            // otherwise serialise 32-way on one bank.
+            const uint32_t peers = __match_any_sync(0xffffffffu, valid ? d : (RS_RADIX + lane));
+            if (valid && lane == (uint32_t)(31 - __clz(peers))) atomicAdd(&s_hist[p * RS_RADIX + d], __popc(peers));
+        }
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < plan.passes * RS_RADIX; i += RS_THREADS)
+        if (s_hist[i]) atomicAdd(&hist[i], s_hist[i]);
+}
+
+// ---- one onesweep pass ----
+template <typename KeyT>
+__global__ void __launch_bounds__(RS_THREADS)
+onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, KeyT* __restrict__ keys_out,
+                uint32_t* __restrict__ vals_out, const int32_t* __restrict__ n_dev, uint32_t max_n, uint32_t shift,
+                uint32_t mask, const uint32_t* __restrict__ hist, uint32_t* lb, uint32_t* ticket) {
+    constexpr int ITEMS = SortCfg<KeyT>::ITEMS;
+    constexpr int TILE = RS_THREADS * ITEMS;
+    __shared__ KeyT s_keys[TILE];
+    __shared__ uint32_t s_vals[TILE];
+    __shared__ uint32_t s_whist[RS_WARPS][RS_RADIX];
+    __shared__ uint32_t s_local_base[RS_RADIX];  // exclusive digit offsets inside the tile
+    __shared__ uint32_t s_goff[RS_RADIX];        // global destination of the tile's first key of each digit
+    __shared__ uint32_t s_scan[RS_WARPS];
+    __shared__ uint32_t s_tile;
+
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; w++) s_whist[w][tid] = 0;
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t n = min((uint32_t)max(*n_dev, 0), max_n);
+    const uint64_t tile_start = (uint64_t)tile * TILE;
+    if (tile_start >= n) return;
+    const uint32_t count = (uint32_t)min((uint64_t)TILE, (uint64_t)n - tile_start);
+
+    // global exclusive digit base = exclusive scan of this pass's histogram (thread d <-> digit d)
+    uint32_t bin_base;
+    {
+        uint32_t h = hist[tid];
+        uint32_t incl = h;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= (uint32_t)o) incl += t;
+        }
+        if (lane == 31) s_scan[warp] = incl;
+        __syncthreads();
+        uint32_t woff = 0;
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; w++) woff += (w < (int)warp) ? s_scan[w] : 0u;
+        bin_base = woff + incl - h;
+    }
+
+    // warp-striped load: warp w owns [w*ITEMS*32, (w+1)*ITEMS*32), item i of lane l = chunk[i*32 + l]
+    KeyT key[ITEMS];
+    uint32_t rank[ITEMS];
+    const uint32_t chunk = warp * (ITEMS * 32);
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        uint32_t idx = chunk + i * 32 + lane;
+        key[i] = idx < count ? keys_in[tile_start + idx] : (KeyT)0;
+    }
+    // stable per-warp multisplit: match_any groups equal digits, the group leader bumps the warp counter
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        const bool valid = chunk + i * 32 + lane < count;
+        const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
+        const uint32_t peers = __match_any_sync(0xffffffffu, valid ? d : (RS_RADIX + lane));
+        const uint32_t leader = 31 - __clz(peers);
+        uint32_t pre = 0;
+        if (valid && lane == leader) {
+            pre = s_whist[warp][d];
+            s_whist[warp][d] = pre + __popc(peers);
+        }
+        pre = __shfl_sync(0xffffffffu, pre, leader);
+        rank[i] = pre + __popc(peers & ((1u << lane) - 1u));
+        __syncwarp();
+    }
+    __syncthreads();
+
+    // thread d: exclusive scan of digit d's count over the warps -> tile count of digit d
+    uint32_t tile_count = 0;
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; w++) {
+        uint32_t t = s_whist[w][tid];
+        s_whist[w][tid] = tile_count;
+        tile_count += t;
+    }
+    // decoupled look-back per digit: status word = flag[31:30] | count[29:0]
+    {
+        volatile uint32_t* vlb = lb;
+        const uint32_t me = tile * RS_RADIX + tid;
+        uint32_t excl = 0;
+        if (tile == 0) {
+            vlb[me] = (2u << 30) | tile_count;
+        } else {
+            vlb[me] = (1u << 30) | tile_count;
+            int t = (int)tile - 1;
+            while (true) {
+                uint32_t s;
+                do { s = vlb[(uint32_t)t * RS_RADIX + tid]; } while ((s >> 30) == 0u);
+                excl += s & 0x3fffffffu;
+                if ((s >> 30) == 2u) break;
+                t--;
+            }
+            vlb[me] = (2u << 30) | (excl + tile_count);
+        }
+        s_goff[tid] = bin_base + excl;
+    }
+    // exclusive scan of tile_count over digits -> position of each digit's run inside the tile
+    {
+        uint32_t incl = tile_count;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= (uint32_t)o) incl += t;
+        }
+        __syncthreads();  // s_scan reuse
+        if (lane == 31) s_scan[warp] = incl;
+        __syncthreads();
+        uint32_t woff = 0;
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; w++) woff += (w < (int)warp) ? s_scan[w] : 0u;
+        s_local_base[tid] = woff + incl - tile_count;
+    }
+    __syncthreads();
+
+    // scatter into shared memory in sorted order, then stream out digit runs (coalesced)
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        uint32_t idx = chunk + i * 32 + lane;
+        if (idx < count) {
+            const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
+            const uint32_t pos = s_local_base[d] + s_whist[warp][d] + rank[i];
+            s_keys[pos] = key[i];
+            s_vals[pos] = vals_in[tile_start + idx];
+        }
+    }
+    __syncthreads();
+    for (uint32_t j = tid; j < count; j += RS_THREADS) {
+        const KeyT k = s_keys[j];
+        const uint32_t d = (uint32_t)(k >> shift) & mask;
+        const uint32_t dst = s_goff[d] + (j - s_local_base[d]);
+        keys_out[dst] = k;
+        vals_out[dst] = s_vals[j];
+    }
+}
+
+template <typename KeyT>
+__global__ void copy_first_n_kernel(const KeyT* __restrict__ k, const uint32_t* __restrict__ v,
+                                    const int32_t* __restrict__ n_dev, uint32_t max_n, KeyT* __restrict__ ko,
+                                    uint32_t* __restrict__ vo) {
+    const uint32_t n = min((uint32_t)max(*n_dev, 0), max_n);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        ko[i] = k[i];
+        vo[i] = v[i];
+    }
+}
+
+template <typename KeyT>
+static void radix_sort_impl(const KeyT* keys, const uint32_t* vals, const int32_t* n_dev, uint32_t max_n,
+                            uint32_t bits, KeyT* keys_out, uint32_t* vals_out, const SortScratch& s,
+                            cudaStream_t st) {
+    if (max_n == 0) return;
+    const PassPlan plan = make_plan(bits);
+    if (plan.passes == 0) {
+        copy_first_n_kernel<KeyT><<<296, 256, 0, st>>>(keys, vals, n_dev, max_n, keys_out, vals_out);
+        return;
+    }
+    const uint32_t tiles = (uint32_t)sort_tiles(max_n, sizeof(KeyT));
+    cudaMemsetAsync(s.hist, 0, (size_t)plan.passes * RS_RADIX * 4, st);
+    cudaMemsetAsync(s.lb, 0, (size_t)plan.passes * tiles * RS_RADIX * 4, st);
+    cudaMemsetAsync(s.tickets, 0, RS_MAX_PASSES * 4, st);
+    uint32_t hist_blocks = (max_n + RS_THREADS - 1) / RS_THREADS;
+    if (hist_blocks > 148 * 8) hist_blocks = 148 * 8;
+    radix_hist_kernel<KeyT><<<hist_blocks, RS_THREADS, 0, st>>>(keys, n_dev, max_n, plan, s.hist);
+    const KeyT* src_k = keys;
+    const uint32_t* src_v = vals;
+    KeyT* tmp_k = reinterpret_cast<KeyT*>(s.keys_tmp);
+    for (uint32_t p = 0; p < plan.passes; p++) {
+        const bool to_out = ((plan.passes - 1 - p) % 2) == 0;
+        KeyT* dst_k = to_out ? keys_out : tmp_k;
+        uint32_t* dst_v = to_out ? vals_out : s.vals_tmp;
+        onesweep_kernel<KeyT><<<tiles, RS_THREADS, 0, st>>>(src_k, src_v, dst_k, dst_v, n_dev, max_n, plan.shift[p],
+                                                           plan.mask[p], s.hist + p * RS_RADIX,
+                                                           s.lb + (size_t)p * tiles * RS_RADIX, s.tickets + p);
+        src_k = dst_k;
+        src_v = dst_v;
+    }
+}
+
+void launch_radix_sort_u32(const uint32_t* keys, const uint32_t* vals, const int32_t* n_dev, uint32_t max_n,
+                           uint32_t bits, uint32_t* keys_out, uint32_t* vals_out, const SortScratch& s,
+                           cudaStream_t st) {
+    radix_sort_impl<uint32_t>(keys, vals, n_dev, max_n, bits, keys_out, vals_out, s, st);
+}
+void launch_radix_sort_u64(const uint64_t* keys, const uint32_t* vals, const int32_t* n_dev, uint32_t max_n,
+                           uint32_t bits, uint64_t* keys_out, uint32_t* vals_out, const SortScratch& s,
+                           cudaStream_t st) {
+    radix_sort_impl<uint64_t>(keys, vals, n_dev, max_n, bits, keys_out, vals_out, s, st);
+}
+
+}  // namespace brush

@@ -1,0 +1,144 @@
+/* brush_b200.h -- C ABI of the B200-native differentiable splat pipeline.
+ *
+ * Drop-in boundary for ONE path of wartron/brush: brush_render::Backend::render_splats
+ * (crates/brush-render/src/lib.rs:66-86), its autodiff backward
+ * (crates/brush-render/src/render.rs:465-626) and the two primitives it is built on
+ * (brush-sort/src/lib.rs:32, brush-prefix-sum/src/lib.rs:17).  Plain pointers and sizes only;
+ * every pointer is a DEVICE pointer unless its name ends in `_host`.  `stream` is a
+ * cudaStream_t passed as void* so a Rust/ctypes binding needs no CUDA headers.
+ *
+ * All calls enqueue work on `stream` and return; none synchronises unless stated.
+ * Return value: 0 = ok, <0 = error (see BRUSH_E_*); brush_last_error() gives the text.
+ * A ctx is bound to one device, owns only scratch memory, and is not thread-safe.
+ */
+#ifndef BRUSH_B200_H
+#define BRUSH_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BRUSH_OK 0
+#define BRUSH_E_INVALID (-1)   /* bad argument (DimCheck / sh_degree_from_coeffs panics in the reference) */
+#define BRUSH_E_CAPACITY (-2)  /* intersection buffer too small (the reference truncates silently) */
+#define BRUSH_E_CUDA (-3)      /* CUDA runtime error */
+
+#define BRUSH_TILE_WIDTH 16u   /* helpers.wgsl:1 */
+#define BRUSH_PROJECTED_FLOATS 9u /* helpers.wgsl:33-43 ProjectedSplat */
+
+/* == shaders::helpers::RenderUniforms, crates/brush-render/src/shaders/helpers.wgsl:7-30 (112 bytes).
+ * Filled by the caller as render.rs:102-116 does; tile_bounds, sh_degree, num_visible and total_splats
+ * are (re)computed by brush_render_forward.  viewmat is column-major world->camera. */
+typedef struct BrushUniforms {
+    float viewmat[16];
+    float focal[2];
+    uint32_t img_size[2];
+    uint32_t tile_bounds[2];
+    float pixel_center[2];
+    uint32_t sh_degree;
+    uint32_t num_visible;
+    uint32_t total_splats;
+    uint32_t padding;
+} BrushUniforms;
+
+/* == brush_render::RenderAux, crates/brush-render/src/lib.rs:20-33.  Caller-allocated device buffers:
+ *   projected_splats        f32[N,9]      rows >= num_visible are unspecified
+ *   uniforms_buffer         i32[28]       the 112-byte RenderUniforms; word 25 = num_visible
+ *   num_intersections       i32[1]
+ *   num_visible             i32[1]
+ *   final_index             i32[H,W]      (not written when raster_u32)
+ *   cum_tiles_hit           i32[N]        inclusive scan; entries >= num_visible equal num_intersections
+ *   tile_bins               i32[Ty,Tx,2]
+ *   compact_gid_from_isect  i32[isect_capacity]
+ *   global_from_compact_gid i32[N]        entries >= num_visible are 0
+ *   tile_id_from_isect      i32[isect_capacity] or NULL (sorted tile ids; kept for tests, not in RenderAux)
+ * isect_capacity replaces the reference's hard-coded min(N*tiles, 128*65535) (render.rs:204-206). */
+typedef struct BrushAux {
+    float* projected_splats;
+    int32_t* uniforms_buffer;
+    int32_t* num_intersections;
+    int32_t* num_visible;
+    int32_t* final_index;
+    int32_t* cum_tiles_hit;
+    int32_t* tile_bins;
+    int32_t* compact_gid_from_isect;
+    int32_t* global_from_compact_gid;
+    int32_t* tile_id_from_isect;
+    uint64_t isect_capacity;
+} BrushAux;
+
+typedef struct brush_ctx brush_ctx;
+
+/* Stage indices for brush_stage_times_ms (== the reference's tracing spans, render.rs:127-267,515-577). */
+enum {
+    BRUSH_STAGE_PROJECT_SPLATS = 0,
+    BRUSH_STAGE_DEPTH_SORT,
+    BRUSH_STAGE_PROJECT_VISIBLE,
+    BRUSH_STAGE_PREFIX_SUM,
+    BRUSH_STAGE_MAP_INTERSECTS,
+    BRUSH_STAGE_TILE_SORT,
+    BRUSH_STAGE_TILE_BINS,
+    BRUSH_STAGE_RASTERIZE,
+    BRUSH_STAGE_RASTERIZE_BWD,
+    BRUSH_STAGE_GATHER_PROJECT_BWD,
+    BRUSH_STAGE_COUNT
+};
+
+int brush_ctx_create(int device, brush_ctx** out);
+void brush_ctx_destroy(brush_ctx* ctx);
+const char* brush_last_error(brush_ctx* ctx);
+const char* brush_version(void);
+
+/* Tile-sort strategy: 0 = two-stage (depth sort, then stable sort by tile id: the reference's structure,
+ * render.rs:151-156,225-237), 1 = single fused 64-bit (tile<<32 | depth_bits) key sort.  Same output. */
+int brush_ctx_set_sort_mode(brush_ctx* ctx, int fused64);
+/* Per-stage CUDA-event timing (the sync-span equivalent, crates/sync-span/src/lib.rs:26-41). Off by default. */
+int brush_ctx_set_timing(brush_ctx* ctx, int enabled);
+/* Synchronises `stream`, then fills out[0..n) with the last call's stage times in ms. */
+int brush_stage_times_ms(brush_ctx* ctx, float* out_host, int n, void* stream);
+/* Synchronises `stream` and returns the sticky device status: BRUSH_OK or BRUSH_E_CAPACITY; clears it. */
+int brush_ctx_check(brush_ctx* ctx, void* stream);
+
+/* == render_forward, crates/brush-render/src/render.rs:55-323.
+ * means f32[N,3], log_scales f32[N,3], quats f32[N,4] (normalised, w first), sh_coeffs f32[N,K,3],
+ * raw_opacity f32[N]; K in {1,4,9,16,25}.  out_img: f32[H,W,4], or u32[H,W] packed RGBA8 if raster_u32. */
+int brush_render_forward(brush_ctx* ctx, const BrushUniforms* uniforms_host, uint32_t N, uint32_t K,
+                         const float* means, const float* log_scales, const float* quats, const float* sh_coeffs,
+                         const float* raw_opacity, int raster_u32, void* out_img, const BrushAux* aux, void* stream);
+
+/* == RenderBackwards::backward, crates/brush-render/src/render.rs:468-625.
+ * Inputs: the checkpointed parameters, the forward's out_img and aux, and v_out_img f32[H,W,4].
+ * Outputs (dense, fully written; zero for non-visible splats): v_means f32[N,3], v_xy f32[N,2] (the xy_dummy
+ * gradient), v_log_scales f32[N,3], v_quats f32[N,4], v_sh_coeffs f32[N,K,3], v_raw_opacity f32[N]. */
+int brush_render_backward(brush_ctx* ctx, uint32_t N, uint32_t K, const float* means, const float* log_scales,
+                          const float* quats, const float* raw_opacity, const float* out_img,
+                          const float* v_out_img, const BrushAux* aux, float* v_means, float* v_xy,
+                          float* v_log_scales, float* v_quats, float* v_sh_coeffs, float* v_raw_opacity,
+                          void* stream);
+
+/* == brush_sort::radix_argsort, brush-sort/src/lib.rs:32-37.  Stable ascending key-value sort of the first
+ * *n_dev entries (device-side count) on the low 4*ceil(bits/4) key bits; entries >= *n_dev of the outputs are
+ * unspecified.  max_n = allocated length of all four arrays. */
+int brush_radix_argsort_u32(brush_ctx* ctx, const uint32_t* keys, const uint32_t* values, const int32_t* n_dev,
+                            uint32_t max_n, uint32_t bits, uint32_t* keys_out, uint32_t* values_out, void* stream);
+/* 64-bit-key variant used by the fused (tile | depth) sort. */
+int brush_radix_argsort_u64(brush_ctx* ctx, const uint64_t* keys, const uint32_t* values, const int32_t* n_dev,
+                            uint32_t max_n, uint32_t bits, uint64_t* keys_out, uint32_t* values_out, void* stream);
+
+/* == brush_prefix_sum::prefix_sum, brush-prefix-sum/src/lib.rs:17.  Inclusive u32 scan of n elements. */
+int brush_prefix_sum_u32(brush_ctx* ctx, const uint32_t* in, uint32_t n, uint32_t* out, void* stream);
+
+/* Host-staged convenience for FFI callers that hold HOST buffers (bench e2e leg, smoke tests): copies the five
+ * parameter arrays H2D, renders, copies out_img (f32[H,W,4]) and the two counters back, synchronises. */
+int brush_render_forward_host(brush_ctx* ctx, const BrushUniforms* uniforms_host, uint32_t N, uint32_t K,
+                              const float* means_host, const float* log_scales_host, const float* quats_host,
+                              const float* sh_coeffs_host, const float* raw_opacity_host, uint64_t isect_capacity,
+                              float* out_img_host, uint32_t* num_visible_host, uint32_t* num_intersections_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BRUSH_B200_H */

@@ -1,0 +1,291 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle and the reference's golden vectors.
+
+Bars (BASELINE.json north_star): intersection lists / tile offsets / sort order bit-exact (canonical form,
+SURVEY.md 8a note vi); image within 1e-5 absolute; gradients within 1e-3 relative."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import all_close, crab, load_case, reference_camera
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+
+
+def T(a, dtype=torch.float32):
+    return torch.as_tensor(np.ascontiguousarray(a), device=DEV).to(dtype)
+
+
+def grads_close(a, b, name):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    scale = np.abs(b).max() + 1e-30
+    bad = np.abs(a - b) > 1e-3 * np.abs(b) + 2e-5 * scale
+    assert not bad.any(), f"{name}: {bad.sum()} / {bad.size} outside 1e-3 rel; max abs diff {np.abs(a - b).max():.3e}, scale {scale:.3e}"
+
+
+# ------------------------------------------------------------------------------------------------ primitives
+def test_sorting_reference_vectors(oracle):
+    """brush-sort/src/lib.rs:164-217"""
+    from brush_b200 import radix_argsort
+    from test_oracle_golden import sort_vectors
+
+    for keys in sort_vectors():
+        vals = keys * 2 + 5
+        n = torch.tensor([len(keys)], dtype=torch.int32, device=DEV)
+        ko, vo = radix_argsort(T(keys.astype(np.int64), torch.int64).to(torch.int32), T(vals.astype(np.int64), torch.int64).to(torch.int32), n, 32)
+        idx = np.argsort(keys, kind="stable")
+        assert np.array_equal(ko.cpu().numpy().view(np.uint32), keys[idx])
+        assert np.array_equal(vo.cpu().numpy().view(np.uint32), vals[idx])
+
+
+@pytest.mark.parametrize("n,bits", [(1, 32), (255, 32), (4096, 32), (4097, 8), (100_003, 13), (1_200_000, 32),
+                                    (3_000_000, 16)])
+def test_sorting_big_vs_oracle(oracle, n, bits):
+    """brush-sort/src/lib.rs:219-265 shape (clustered keys); payload = index, so stability is checked."""
+    from brush_b200 import radix_argsort
+
+    rng = np.random.default_rng(n)
+    if bits == 32:
+        keys = (rng.integers(0, 250, n) + np.arange(n) // 3).astype(np.uint32)
+        keys[::7] = rng.integers(0, 2 ** 32, len(keys[::7]), dtype=np.uint64).astype(np.uint32)
+    else:
+        keys = rng.integers(0, 2 ** bits, n).astype(np.uint32)
+    vals = np.arange(n, dtype=np.uint32)
+    n_sort = max(1, n - n // 5)  # only the first n_sort entries take part; arrays are longer
+    ko, vo = radix_argsort(T(keys.view(np.int32), torch.int32), T(vals.view(np.int32), torch.int32),
+                           torch.tensor([n_sort], dtype=torch.int32, device=DEV), bits)
+    rk, rv = oracle.radix_argsort_u32(keys, vals, n=n_sort, bits=bits)
+    assert np.array_equal(ko.cpu().numpy().view(np.uint32)[:n_sort], rk[:n_sort])
+    assert np.array_equal(vo.cpu().numpy().view(np.uint32)[:n_sort], rv[:n_sort])
+
+
+def test_sorting_u64_fused_key(oracle):
+    from brush_b200 import radix_argsort
+
+    rng = np.random.default_rng(5)
+    n = 700_001
+    keys = (rng.integers(0, 8160, n).astype(np.uint64) << np.uint64(32)) | rng.integers(0, 2 ** 32, n).astype(np.uint64)
+    keys[1000:2000] = keys[999]  # ties
+    vals = np.arange(n, dtype=np.uint32)
+    ko, vo = radix_argsort(T(keys.view(np.int64), torch.int64), T(vals.view(np.int32), torch.int32),
+                           torch.tensor([n], dtype=torch.int32, device=DEV), 45)
+    rk, rv = oracle.radix_argsort_u64(keys, vals, bits=45)
+    assert np.array_equal(ko.cpu().numpy().view(np.uint64), rk)
+    assert np.array_equal(vo.cpu().numpy().view(np.uint32), rv)
+
+
+def test_prefix_sum_reference_vectors(oracle):
+    """brush-prefix-sum/src/lib.rs:110-175"""
+    from brush_b200 import prefix_sum
+
+    cases = [np.array([1, 1, 1, 1]), 90 + np.arange(1024)]
+    it = np.arange(512 * 16 + 123)
+    cases.append(np.stack([2 + it, 0 * it, 32 + 0 * it, 512 + 0 * it, 30965 + 0 * it], 1).reshape(-1))
+    rng = np.random.default_rng(1)
+    cases.append(rng.integers(0, 40, 1_000_003))
+    cases.append(rng.integers(0, 40, 1023))
+    for d in cases:
+        d = d.astype(np.uint32)
+        got = prefix_sum(T(d.view(np.int32), torch.int32)).cpu().numpy().view(np.uint32)
+        assert np.array_equal(got, oracle.prefix_sum_u32(d))
+
+
+# ------------------------------------------------------------------------------------------------ golden vectors
+@pytest.mark.parametrize("name", ["tiny_case", "basic_case"])
+def test_reference_golden(name):
+    """test_reference, crates/brush-render/src/render.rs:695-833, same tolerances."""
+    from brush_b200 import Camera, Splats, fov_to_focal, focal_to_fov
+
+    d = load_case(name)
+    h, w, _ = d["out_img"].shape
+    focal = fov_to_focal(math.pi * 0.5, w)
+    cam = Camera((0.0, 0.0, -8.0), (0, 0, 0, 1), focal_to_fov(focal, w), focal_to_fov(focal, h))
+    splats = Splats.from_safetensors(d, DEV)
+    out, aux = splats.render(cam, (w, h), False)
+    V = aux.read_num_visible()
+    perm = aux.global_from_compact_gid[:V].cpu().numpy()
+    proj = aux.projected_splats.cpu().numpy()
+    assert all_close(proj[:V, 0:2], d["xys"][perm], 1e-4, 1e-10)
+    assert all_close(proj[:V, 2:5], d["conics"][perm], 1e-4, 5e-7)
+    out_rgb = out[..., :3]
+    assert all_close(out_rgb.detach().cpu().numpy(), d["out_img"], 1e-4, 1e-9)
+    loss = ((out_rgb - T(crab())) ** 2).mean()
+    loss.backward()
+    g = lambda t: t.grad.cpu().numpy()
+    assert all_close(g(splats.xys_dummy), d["v_xy"], 1e-4, 1e-9)
+    assert all_close(g(splats.raw_opacity), d["v_opacities"], 1e-4, 1e-10)
+    assert all_close(g(splats.sh_coeffs), d["v_coeffs"], 1e-4, 1e-9)
+    assert all_close(g(splats.log_scales), d["v_scales"], 1e-4, 1e-9)
+    assert all_close(g(splats.means), d["v_means"], 1e-4, 1e-9)
+    assert all_close(g(splats.rotation), d["v_quats"], 1e-1, 1e-1)
+
+
+def test_renders_at_all():
+    """render.rs:652-693"""
+    from brush_b200 import Camera, render_splats
+
+    cam = Camera((0, 0, 0), (0, 0, 0, 1), 0.5, 0.5)
+    n = 8
+    f = dict(device=DEV, dtype=torch.float32)
+    quats = torch.tensor([[0.0, 0.0, 0.0, 1.0]], **f).repeat(n, 1)
+    out, aux = render_splats(cam, (32, 32), torch.zeros(n, 3, **f).requires_grad_(), torch.zeros(n, 2, **f),
+                             torch.ones(n, 3, **f) * 2.0, quats, torch.ones(n, 1, 3, **f), torch.zeros(n, **f), False)
+    assert abs(float(out[..., :3].mean())) < 1e-5
+    assert float(out[..., 3].mean()) == 0.0
+    assert aux.read_num_visible() == 0 and aux.read_num_intersections() == 0
+
+
+# ------------------------------------------------------------------------------------------------ oracle parity
+def _run_both(oracle, sc, w, h, capacity=None, fused=False, v_out=None, seed=0):
+    from brush_b200 import get_context, make_uniforms, render_backward, render_forward
+
+    vm, focal, center = reference_camera(w, h)
+    ou = oracle.make_uniforms(vm, focal, (w, h), center)
+    ref_img, ref_aux = oracle.render_forward(ou, sc.means, sc.log_scales, sc.quats, sc.sh_coeffs, sc.raw_opacity,
+                                             capacity=capacity)
+    u = make_uniforms(vm, focal, (w, h), center)
+    ctx = get_context(DEV)
+    ctx.set_sort_mode(fused)
+    tm, tl, tq, ts, to = T(sc.means), T(sc.log_scales), T(sc.quats), T(sc.sh_coeffs), T(sc.raw_opacity)
+    img, aux = render_forward(u, tm, tl, tq, ts, to, False, isect_capacity=capacity, keep_tile_ids=True)
+    ctx.set_sort_mode(False)
+    grads = ref_grads = None
+    if v_out is not None:
+        grads = render_backward(aux, tm, tl, tq, ts.shape, to, img, T(v_out))
+        ref_grads = oracle.render_backward(ref_aux, sc.means, sc.log_scales, sc.quats, sc.raw_opacity,
+                                           sc.sh_coeffs.shape[1], ref_img, v_out)
+    return img, aux, ref_img, ref_aux, grads, ref_grads
+
+
+def _check_forward(img, aux, ref_img, ref_aux, fused=False):
+    V, I = aux.read_num_visible(), aux.read_num_intersections()
+    assert V == ref_aux.num_visible and I == ref_aux.num_intersections
+    u = aux.uniforms_buffer.cpu().numpy()
+    assert u[25] == V and u[26] == ref_aux.uniforms.total_splats and u[24] == ref_aux.uniforms.sh_degree
+    gfc = aux.global_from_compact_gid.cpu().numpy().view(np.uint32)
+    assert np.array_equal(gfc, ref_aux.global_from_compact_gid)           # depth order incl. zero tail
+    assert np.array_equal(aux.cum_tiles_hit.cpu().numpy().view(np.uint32), ref_aux.cum_tiles_hit)
+    assert np.array_equal(aux.tile_bins.cpu().numpy().view(np.uint32), ref_aux.tile_bins)
+    cg = aux.compact_gid_from_isect.cpu().numpy().view(np.uint32)[:I]
+    assert np.array_equal(cg, ref_aux.compact_gid_from_isect[:I])         # the intersection list itself
+    if not fused:
+        tid = aux.tile_id_from_isect.cpu().numpy().view(np.uint32)[:I]
+        assert np.array_equal(tid, ref_aux.tile_id_from_isect[:I])
+    proj = aux.projected_splats.cpu().numpy()[:V]
+    rp = ref_aux.projected_splats[:V]
+    assert np.array_equal(proj[:, [0, 1, 2, 3, 4, 8]], rp[:, [0, 1, 2, 3, 4, 8]])  # xy, conic, opac: bit-exact
+    assert np.abs(proj[:, 5:8] - rp[:, 5:8]).max() < 2e-6                           # SH colour: float order only
+    out = img.cpu().numpy()
+    assert np.abs(out - ref_img).max() < 1e-5
+    fi = aux.final_index.cpu().numpy().view(np.uint32)
+    assert (fi != ref_aux.final_index).mean() < 1e-3  # decided by exp() rounding at the 1/255 threshold
+
+
+@pytest.mark.parametrize("n,w,h,deg,seed", [(16_384, 256, 256, 0, 1001), (20_000, 333, 200, 3, 7),
+                                            (3_000, 64, 48, 4, 9), (5_000, 130, 70, 1, 11), (5_000, 96, 96, 2, 13)])
+def test_forward_backward_vs_oracle(oracle, n, w, h, deg, seed):
+    from brush_b200 import scene
+
+    sc = scene.make_scene(n, w, h, deg, seed)
+    rng = np.random.default_rng(seed)
+    target = rng.uniform(0, 1, (h, w, 3)).astype(np.float32)
+    # MSE against a seeded random target, as render.rs:786-789; alpha gets a gradient too so v_out.a is exercised
+    vm, focal, center = reference_camera(w, h)
+    ou = oracle.make_uniforms(vm, focal, (w, h), center)
+    ref_img, _ = oracle.render_forward(ou, sc.means, sc.log_scales, sc.quats, sc.sh_coeffs, sc.raw_opacity)
+    v_out = np.zeros((h, w, 4), np.float32)
+    v_out[..., :3] = 2.0 * (ref_img[..., :3] - target) / (h * w * 3)
+    v_out[..., 3] = rng.uniform(-1, 1, (h, w)).astype(np.float32) / (h * w)
+    img, aux, ref_img, ref_aux, grads, ref_grads = _run_both(oracle, sc, w, h, v_out=v_out)
+    _check_forward(img, aux, ref_img, ref_aux)
+    names = ["v_means", "v_xy", "v_log_scales", "v_quats", "v_coeffs", "v_raw_opac"]
+    for gname, gt in zip(names, grads):
+        grads_close(gt.cpu().numpy(), ref_grads[gname], gname)
+    # dense gradients: exactly zero for non-visible splats (render.rs:571-575)
+    V = aux.read_num_visible()
+    vis = np.zeros(n, bool)
+    vis[aux.global_from_compact_gid.cpu().numpy()[:V]] = True
+    for gt in grads:
+        assert not gt.cpu().numpy()[~vis].any()
+
+
+def test_fused64_sort_mode_identical(oracle):
+    from brush_b200 import scene
+
+    sc = scene.make_scene(30_000, 400, 300, 0, 21)
+    img, aux, ref_img, ref_aux, _, _ = _run_both(oracle, sc, 400, 300, fused=True)
+    _check_forward(img, aux, ref_img, ref_aux, fused=True)
+
+
+def test_many_splats_per_tile_and_depth_ties(oracle):
+    """> 256 splats in one tile (multi-batch staging) and exact depth ties (order must fall back to gid)."""
+    from brush_b200 import scene
+
+    sc = scene.make_scene(6_000, 48, 32, 0, 33, sigma_px=(2.0, 6.0))
+    sc.means[:, 2] = np.round(sc.means[:, 2] * 4) / 4  # many equal depths
+    rng = np.random.default_rng(1)
+    v_out = rng.uniform(-1, 1, (32, 48, 4)).astype(np.float32) / (32 * 48)
+    img, aux, ref_img, ref_aux, grads, ref_grads = _run_both(oracle, sc, 48, 32, v_out=v_out)
+    assert (ref_aux.tile_bins[..., 1] - ref_aux.tile_bins[..., 0]).max() > 256
+    _check_forward(img, aux, ref_img, ref_aux)
+    for gname, gt in zip(["v_means", "v_xy", "v_log_scales", "v_quats", "v_coeffs", "v_raw_opac"], grads):
+        grads_close(gt.cpu().numpy(), ref_grads[gname], gname)
+
+
+def test_raster_u32(oracle):
+    """Packed RGBA8 output (rasterize.wgsl:106-109): equal up to 1 LSB per channel (exp rounding)."""
+    from brush_b200 import make_uniforms, render_forward, scene
+
+    w, h = 200, 120
+    sc = scene.make_scene(8_000, w, h, 0, 5)
+    vm, focal, center = reference_camera(w, h)
+    ref, _ = oracle.render_forward(oracle.make_uniforms(vm, focal, (w, h), center), sc.means, sc.log_scales, sc.quats,
+                                   sc.sh_coeffs, sc.raw_opacity, raster_u32=True)
+    out, _ = render_forward(make_uniforms(vm, focal, (w, h), center), T(sc.means), T(sc.log_scales), T(sc.quats),
+                            T(sc.sh_coeffs), T(sc.raw_opacity), True)
+    got = out.cpu().numpy().view(np.uint32).reshape(h, w)
+    for sh in (0, 8, 16, 24):
+        a, b = (got >> sh) & 255, (ref >> sh) & 255
+        assert np.abs(a.astype(int) - b.astype(int)).max() <= 1
+    assert (got != ref).mean() < 0.02
+
+
+def test_capacity_overflow_is_reported(oracle):
+    from brush_b200 import get_context, make_uniforms, render_forward, scene
+    from brush_b200._lib import CapacityError
+
+    w, h = 128, 128
+    sc = scene.make_scene(4_000, w, h, 0, 3)
+    vm, focal, center = reference_camera(w, h)
+    u = make_uniforms(vm, focal, (w, h), center)
+    args = [T(sc.means), T(sc.log_scales), T(sc.quats), T(sc.sh_coeffs), T(sc.raw_opacity)]
+    _, aux = render_forward(u, *args, False, isect_capacity=1000)
+    with pytest.raises(CapacityError):
+        get_context(DEV).sync_check()
+    assert aux.read_num_intersections() == 1000
+    # same truncation as the oracle / map_gaussian_to_intersects.wgsl:40
+    ref_img, ref_aux = oracle.render_forward(oracle.make_uniforms(vm, focal, (w, h), center), sc.means, sc.log_scales,
+                                             sc.quats, sc.sh_coeffs, sc.raw_opacity, capacity=1000)
+    assert ref_aux.status == -2
+    assert np.array_equal(aux.compact_gid_from_isect.cpu().numpy().view(np.uint32)[:1000],
+                          ref_aux.compact_gid_from_isect[:1000])
+    _, aux = render_forward(u, *args, False)  # default capacity is fine again
+    get_context(DEV).sync_check()
+
+
+def test_empty_and_single():
+    from brush_b200 import make_uniforms, render_forward
+
+    vm, focal, center = reference_camera(40, 24)
+    u = make_uniforms(vm, focal, (40, 24), center)
+    f = dict(device=DEV, dtype=torch.float32)
+    out, aux = render_forward(u, torch.zeros(0, 3, **f), torch.zeros(0, 3, **f), torch.zeros(0, 4, **f),
+                              torch.zeros(0, 1, 3, **f), torch.zeros(0, **f), False)
+    assert float(out.abs().max()) == 0.0 and aux.read_num_visible() == 0
+    q = torch.tensor([[1.0, 0, 0, 0]], **f)
+    out, aux = render_forward(u, torch.zeros(1, 3, **f), torch.zeros(1, 3, **f), q, torch.ones(1, 1, 3, **f),
+                              torch.ones(1, **f) * 2, False)
+    assert aux.read_num_visible() == 1 and float(out[..., 3].max()) > 0.5
