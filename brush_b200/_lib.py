@@ -31,6 +31,12 @@ class BrushAux(C.Structure):
                 ("isect_capacity", C.c_uint64)]
 
 
+class BrushAdamGroup(C.Structure):
+    _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p),
+                ("count", C.c_uint64), ("lr", C.c_float), ("sh_coeffs_per_channel", C.c_uint32),
+                ("sh_rest_lr_scale", C.c_float)]
+
+
 assert C.sizeof(BrushUniforms) == 112
 
 
@@ -64,6 +70,15 @@ _SIGS = {
     "brush_radix_argsort_u64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32,
                                           C.c_void_p, C.c_void_p, C.c_void_p]),
     "brush_prefix_sum_u32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]),
+    "brush_l1_loss_backward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
+                                         C.c_void_p, C.c_void_p, C.c_void_p]),
+    "brush_adam_step": (C.c_int, [C.c_void_p, C.POINTER(BrushAdamGroup), C.c_int, C.c_float, C.c_float, C.c_float,
+                                  C.c_uint32, C.c_float, C.c_void_p]),
+    "brush_launch_count": (C.c_uint64, []),
+    "brush_quat_normalize": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]),
+    "brush_quat_normalize_vjp": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]),
+    "brush_xy_grad_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(BrushAux), C.c_uint32, C.c_uint32,
+                                      C.c_uint32, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "brush_render_forward_host": (C.c_int, [C.c_void_p, C.POINTER(BrushUniforms), C.c_uint32, C.c_uint32] +
                                   [C.c_void_p] * 5 + [C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
 }

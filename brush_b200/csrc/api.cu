@@ -1,6 +1,7 @@
 // C ABI of libbrush_b200.so (include/brush_b200.h): context, scratch management and the host-side
 // sequencing of the forward chain (== render_forward, crates/brush-render/src/render.rs:55-323) and the
 // backward chain (== RenderBackwards::backward, render.rs:468-625).
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -269,6 +270,7 @@ int brush_render_forward(brush_ctx* ctx, const BrushUniforms* uniforms_host, uin
         }
     }
     CU(cudaMemsetAsync(ctl, 0, cl.total, st));
+    g_launch_count++;
     write_uniforms_kernel<<<1, 32, 0, st>>>(u, aux->uniforms_buffer);
     CU(cudaMemsetAsync(aux->num_visible, 0, 4, st));
     CU(cudaMemsetAsync(aux->num_intersections, 0, 4, st));
@@ -483,5 +485,68 @@ int brush_render_forward_host(brush_ctx* ctx, const BrushUniforms* uniforms_host
     return brush_ctx_check(ctx, st);
 }
 
+
+uint64_t brush_launch_count(void) { return g_launch_count.load(); }
+
+int brush_quat_normalize(brush_ctx* ctx, const float* quats, uint32_t n, float* out, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (n && (!quats || !out)) return fail(ctx, BRUSH_E_INVALID, "null argument");
+    CU(cudaSetDevice(ctx->device));
+    launch_quat_normalize(quats, n, out, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
+int brush_quat_normalize_vjp(brush_ctx* ctx, const float* quats, uint32_t n, float* v_inout, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (n && (!quats || !v_inout)) return fail(ctx, BRUSH_E_INVALID, "null argument");
+    CU(cudaSetDevice(ctx->device));
+    launch_quat_normalize_vjp(quats, n, v_inout, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
+int brush_xy_grad_stats(brush_ctx* ctx, const float* v_xy, const BrushAux* aux, uint32_t n, uint32_t width,
+                        uint32_t height, int accumulate, float* grad_norm, float* visible, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (!aux || (n && (!v_xy || !grad_norm || !visible))) return fail(ctx, BRUSH_E_INVALID, "null argument");
+    CU(cudaSetDevice(ctx->device));
+    launch_xy_grad_stats(v_xy, (const uint32_t*)aux->global_from_compact_gid, aux->num_visible, n, 0.5f * width,
+                         0.5f * height, accumulate, grad_norm, visible, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
+
+int brush_l1_loss_backward(brush_ctx* ctx, const float* pred, const float* gt, uint32_t height, uint32_t width,
+                           uint32_t gt_channels, float* v_out_img, float* loss_out, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (!pred || !gt || !v_out_img || !loss_out) return fail(ctx, BRUSH_E_INVALID, "null argument");
+    if (gt_channels != 3 && gt_channels != 4) return fail(ctx, BRUSH_E_INVALID, "gt_channels must be 3 or 4");
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaMemsetAsync(loss_out, 0, 4, st));
+    launch_l1_loss_backward(pred, gt, height * width, gt_channels, v_out_img, loss_out, st);
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
+
+int brush_adam_step(brush_ctx* ctx, const BrushAdamGroup* groups_host, int n_groups, float beta1, float beta2,
+                    float eps, uint32_t step, float grad_scale, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (!groups_host || n_groups < 1 || n_groups > 8 || step < 1)
+        return fail(ctx, BRUSH_E_INVALID, "adam: 1..8 groups, step >= 1");
+    CU(cudaSetDevice(ctx->device));
+    AdamLaunch L{};
+    L.n_groups = n_groups;
+    for (int i = 0; i < n_groups; i++) {
+        const BrushAdamGroup& g = groups_host[i];
+        if (g.count && (!g.param || !g.grad || !g.m || !g.v)) return fail(ctx, BRUSH_E_INVALID, "adam: null group buffer");
+        L.seg[i] = AdamSeg{g.param, g.grad, g.m, g.v, g.count, g.lr, g.sh_coeffs_per_channel, g.sh_rest_lr_scale, 0};
+    }
+    L.beta1 = beta1; L.beta2 = beta2; L.eps = eps; L.grad_scale = grad_scale;
+    L.inv_bc1 = (float)(1.0 / (1.0 - std::pow((double)beta1, (double)step)));
+    L.inv_bc2 = (float)(1.0 / (1.0 - std::pow((double)beta2, (double)step)));
+    launch_adam(L, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
 #pragma GCC visibility pop
 }  // extern "C"

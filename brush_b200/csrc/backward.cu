@@ -137,6 +137,7 @@ void launch_gather_project_backward(const Cam& cam, uint32_t N, uint32_t K, cons
                                     float* v_quats, float* v_coeffs, float* v_raw_opac, cudaStream_t st) {
     if (N == 0) return;
     dim3 grid((N + 255) / 256), block(256);
+    g_launch_count++;
 #define GB_ARGS cam, means, log_scales, quats, raw_opac, global_from_compact, num_visible_dev, v_projected, v_means, \
                 v_xy, v_log_scales, v_quats, v_coeffs, v_raw_opac
     switch (K) {

@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 #include "brush_math.cuh"
 
 namespace brush {
@@ -74,5 +76,32 @@ void launch_gather_project_backward(const Cam& cam, uint32_t N, uint32_t K, cons
                                     const uint32_t* global_from_compact, const int32_t* num_visible_dev,
                                     const float* v_projected, float* v_means, float* v_xy, float* v_log_scales,
                                     float* v_quats, float* v_coeffs, float* v_raw_opac, cudaStream_t st);
+
+// ---- optim.cu ----
+extern std::atomic<uint64_t> g_launch_count;  // kernels launched by this library (bench.py's gpu_launches)
+struct AdamSeg {
+    float* param;
+    const float* grad;
+    float* m;
+    float* v;
+    uint64_t count;
+    float lr;
+    uint32_t sh_k;
+    float sh_rest_scale;
+    uint32_t pad;
+};
+struct AdamLaunch {
+    AdamSeg seg[8];
+    int n_groups;
+    float beta1, beta2, eps, inv_bc1, inv_bc2, grad_scale;
+};
+void launch_l1_loss_backward(const float* pred, const float* gt, uint32_t P, uint32_t C, float* v_out,
+                             float* loss_out, cudaStream_t st);
+void launch_adam(const AdamLaunch& L, cudaStream_t st);
+void launch_quat_normalize(const float* q, uint32_t n, float* out, cudaStream_t st);
+void launch_quat_normalize_vjp(const float* q, uint32_t n, float* v_inout, cudaStream_t st);
+void launch_xy_grad_stats(const float* v_xy, const uint32_t* gfc, const int32_t* num_visible_dev, uint32_t n,
+                          float half_w, float half_h, int accumulate, float* grad_norm, float* visible,
+                          cudaStream_t st);
 
 }  // namespace brush

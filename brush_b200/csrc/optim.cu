@@ -1,0 +1,159 @@
+// Train-step kernels either side of the render path: the L1 image loss that produces
+// v_out_img directly, and a fused multi-tensor Adam over the five parameter groups.
+//   loss  == (pred_compare - gt).abs().mean()                  crates/brush-train/src/train.rs:255
+//   Adam  == AdamConfig::new().with_epsilon(1e-15) (Burn 0.16) crates/brush-train/src/train.rs:184,318-359
+#include "internal.h"
+
+namespace brush {
+
+std::atomic<uint64_t> g_launch_count{0};
+
+// pred f32[P,4]; gt f32[P,C] (C = 3: RGB compare, C = 4: RGBA compare).  v_out[P,4] = d mean|pred-gt| / d pred.
+// loss_out[0] += sum |pred-gt| / (P*C)   (must be zeroed by the caller; one atomic per CTA)
+__global__ void __launch_bounds__(256)
+l1_loss_backward_kernel(const float4* __restrict__ pred, const float* __restrict__ gt, uint32_t P, uint32_t Cc,
+                        float4* __restrict__ v_out, float* __restrict__ loss_out) {
+    __shared__ float s_part[8];
+    const float inv = 1.0f / ((float)P * (float)Cc);
+    float acc = 0.f;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < P; i += gridDim.x * blockDim.x) {
+        const float4 p = pred[i];
+        float d[4] = {0.f, 0.f, 0.f, 0.f};
+        if (Cc == 4) {
+            const float4 g = __ldg(reinterpret_cast<const float4*>(gt) + i);
+            d[0] = p.x - g.x; d[1] = p.y - g.y; d[2] = p.z - g.z; d[3] = p.w - g.w;
+        } else {
+            d[0] = p.x - __ldg(gt + 3 * (size_t)i);
+            d[1] = p.y - __ldg(gt + 3 * (size_t)i + 1);
+            d[2] = p.z - __ldg(gt + 3 * (size_t)i + 2);
+        }
+        float4 v;
+        v.x = d[0] > 0.f ? inv : (d[0] < 0.f ? -inv : 0.f);
+        v.y = d[1] > 0.f ? inv : (d[1] < 0.f ? -inv : 0.f);
+        v.z = d[2] > 0.f ? inv : (d[2] < 0.f ? -inv : 0.f);
+        v.w = Cc == 4 ? (d[3] > 0.f ? inv : (d[3] < 0.f ? -inv : 0.f)) : 0.f;
+        v_out[i] = v;
+        acc += fabsf(d[0]) + fabsf(d[1]) + fabsf(d[2]) + fabsf(d[3]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 8) {
+        float v = s_part[threadIdx.x];
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) v += __shfl_xor_sync(0xffu, v, o);
+        if (threadIdx.x == 0) atomicAdd(loss_out, v * inv);
+    }
+}
+
+void launch_l1_loss_backward(const float* pred, const float* gt, uint32_t P, uint32_t C, float* v_out,
+                             float* loss_out, cudaStream_t st) {
+    if (P == 0) return;
+    uint32_t blocks = (P + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    g_launch_count++;
+    l1_loss_backward_kernel<<<blocks, 256, 0, st>>>(reinterpret_cast<const float4*>(pred), gt, P, C,
+                                                    reinterpret_cast<float4*>(v_out), loss_out);
+}
+
+// One launch for all parameter groups.  Element e of group s: lr = s.lr, except SH coefficients k > 0 which
+// use lr * sh_rest_scale (the reference's 1/lr_coeffs_sh_scale lerp, train.rs:334-348; Adam's update is linear
+// in lr so the lerp is exactly a smaller lr).
+__global__ void __launch_bounds__(256)
+adam_kernel(const __grid_constant__ AdamLaunch L) {
+    const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (int s = 0; s < L.n_groups; s++) {
+        const AdamSeg& g = L.seg[s];
+        for (uint64_t e = gid; e < g.count; e += stride) {
+            const float grad = g.grad[e] * L.grad_scale;
+            const float m = L.beta1 * g.m[e] + (1.0f - L.beta1) * grad;
+            const float v = L.beta2 * g.v[e] + (1.0f - L.beta2) * grad * grad;
+            g.m[e] = m;
+            g.v[e] = v;
+            float lr = g.lr;
+            if (g.sh_k > 1 && ((e / 3) % g.sh_k) != 0) lr *= g.sh_rest_scale;
+            const float update = (m * L.inv_bc1) / (sqrtf(v * L.inv_bc2) + L.eps);
+            g.param[e] -= lr * update;
+        }
+    }
+}
+
+void launch_adam(const AdamLaunch& L, cudaStream_t st) {
+    uint64_t mx = 0;
+    for (int s = 0; s < L.n_groups; s++) mx = L.seg[s].count > mx ? L.seg[s].count : mx;
+    if (mx == 0) return;
+    uint64_t blocks = (mx + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    g_launch_count++;
+    adam_kernel<<<(uint32_t)blocks, 256, 0, st>>>(L);
+}
+
+
+// ---- rotation normalisation either side of the operator (gaussian_splats.rs:174-175; the reference leaves
+// both directions to Burn's elementwise ops + autodiff) ----
+__global__ void __launch_bounds__(256)
+quat_normalize_kernel(const float4* __restrict__ q, uint32_t n, float4* __restrict__ out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 v = q[i];
+    const float inv = 1.0f / sqrtf(v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w);
+    out[i] = make_float4(v.x * inv, v.y * inv, v.z * inv, v.w * inv);
+}
+// v_q = (v_qhat - qhat * dot(qhat, v_qhat)) / |q|, in place on the gradient
+__global__ void __launch_bounds__(256)
+quat_normalize_vjp_kernel(const float4* __restrict__ q, uint32_t n, float4* __restrict__ v_inout) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 a = q[i];
+    const float inv = 1.0f / sqrtf(a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w);
+    const float4 h = make_float4(a.x * inv, a.y * inv, a.z * inv, a.w * inv);
+    const float4 g = v_inout[i];
+    const float d = h.x * g.x + h.y * g.y + h.z * g.z + h.w * g.w;
+    v_inout[i] = make_float4((g.x - h.x * d) * inv, (g.y - h.y * d) * inv, (g.z - h.z * d) * inv,
+                             (g.w - h.w * d) * inv);
+}
+// Refine statistics of one view (train.rs:284-316): grad_norm[g] (+)= |v_xy[g] * (w/2, h/2)|,
+// visible[g] (+)= 1 for the view's visible splats.  accumulate = 0 overwrites (first view of a batch).
+__global__ void __launch_bounds__(256)
+xy_grad_stats_kernel(const float2* __restrict__ v_xy, const uint32_t* __restrict__ global_from_compact,
+                     const int32_t* __restrict__ num_visible_dev, uint32_t n, float half_w, float half_h,
+                     int accumulate, float* __restrict__ grad_norm, float* __restrict__ visible) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float2 g = v_xy[i];
+    const float gx = g.x * half_w, gy = g.y * half_h;
+    const float nrm = sqrtf(gx * gx + gy * gy);
+    grad_norm[i] = accumulate ? grad_norm[i] + nrm : nrm;
+    if (!accumulate) visible[i] = 0.f;
+}
+__global__ void __launch_bounds__(256)
+visible_flags_kernel(const uint32_t* __restrict__ global_from_compact, const int32_t* __restrict__ num_visible_dev,
+                     float* __restrict__ visible) {
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= (uint32_t)*num_visible_dev) return;
+    visible[global_from_compact[c]] += 1.0f;  // compact ids are unique: no race
+}
+
+void launch_quat_normalize(const float* q, uint32_t n, float* out, cudaStream_t st) {
+    if (!n) return;
+    g_launch_count++;
+    quat_normalize_kernel<<<(n + 255) / 256, 256, 0, st>>>((const float4*)q, n, (float4*)out);
+}
+void launch_quat_normalize_vjp(const float* q, uint32_t n, float* v_inout, cudaStream_t st) {
+    if (!n) return;
+    g_launch_count++;
+    quat_normalize_vjp_kernel<<<(n + 255) / 256, 256, 0, st>>>((const float4*)q, n, (float4*)v_inout);
+}
+void launch_xy_grad_stats(const float* v_xy, const uint32_t* gfc, const int32_t* num_visible_dev, uint32_t n,
+                          float half_w, float half_h, int accumulate, float* grad_norm, float* visible,
+                          cudaStream_t st) {
+    if (!n) return;
+    g_launch_count += 2;
+    xy_grad_stats_kernel<<<(n + 255) / 256, 256, 0, st>>>((const float2*)v_xy, gfc, num_visible_dev, n, half_w,
+                                                          half_h, accumulate, grad_norm, visible);
+    visible_flags_kernel<<<(n + 255) / 256, 256, 0, st>>>(gfc, num_visible_dev, visible);
+}
+
+}  // namespace brush

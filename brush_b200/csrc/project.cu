@@ -104,6 +104,7 @@ void launch_project_forward(const Cam& cam, uint32_t N, const float* means, cons
                             uint32_t* ticket, int32_t* uniforms_dev, int32_t* num_visible_out, cudaStream_t st) {
     if (N == 0) return;
     uint32_t tiles = (N + PF_THREADS - 1) / PF_THREADS;
+    g_launch_count++;
     project_forward_kernel<<<tiles, PF_THREADS, 0, st>>>(cam, means, log_scales, quats, presort_gid, depth_bits,
                                                          lb_status, ticket, uniforms_dev, num_visible_out);
 }
@@ -184,6 +185,7 @@ void launch_project_visible(const Cam& cam, uint32_t N, uint32_t K, const float*
                             uint32_t* num_tiles_hit, cudaStream_t st) {
     if (N == 0) return;
     dim3 grid((N + 255) / 256), block(256);
+    g_launch_count++;
 #define PV_ARGS cam, means, log_scales, quats, coeffs, raw_opac, global_from_compact, num_visible_dev, projected, \
                 num_tiles_hit
     switch (K) {
@@ -231,6 +233,7 @@ void launch_map_intersects(const Cam& cam, uint32_t N, const float* projected, c
                            uint32_t* compact_gid_from_isect, const uint32_t* depth_sorted_bits,
                            uint64_t* key64_from_isect, uint32_t* /*status_word*/, cudaStream_t st) {
     if (N == 0) return;
+    g_launch_count++;
     map_intersects_kernel<<<(N + 255) / 256, 256, 0, st>>>(cam, projected, cum_tiles_hit, num_visible_dev, capacity,
                                                            tile_id_from_isect, compact_gid_from_isect,
                                                            depth_sorted_bits, key64_from_isect);

@@ -34,6 +34,7 @@ void launch_tile_bins(const uint32_t* sorted_tile_ids, const uint64_t* sorted_ke
     if (capacity == 0) return;
     uint64_t blocks = (capacity + 255) / 256;
     if (blocks > 148 * 16) blocks = 148 * 16;
+    g_launch_count++;
     tile_bins_kernel<<<(uint32_t)blocks, 256, 0, st>>>(sorted_tile_ids, sorted_keys64, n_isect_dev, capacity,
                                                        tile_bins);
 }
@@ -128,6 +129,7 @@ void launch_rasterize(const Cam& cam, const uint32_t* compact_gid_from_isect, co
                       cudaStream_t st) {
     if (cam.tiles_x == 0 || cam.tiles_y == 0) return;
     dim3 grid(cam.tiles_x, cam.tiles_y);
+    g_launch_count++;
     if (raster_u32)
         rasterize_kernel<true><<<grid, TILE_SIZE, 0, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
                                                            out_img, final_index);
@@ -251,6 +253,7 @@ void launch_rasterize_backward(const Cam& cam, const uint32_t* compact_gid_from_
                                const float* v_out_img, float* v_projected, cudaStream_t st) {
     const uint32_t tiles = cam.tiles_x * cam.tiles_y;
     if (tiles == 0) return;
+    g_launch_count++;
     rasterize_backward_kernel<<<tiles, TILE_SIZE, 0, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
                                                            final_index, out_img, v_out_img, v_projected);
 }

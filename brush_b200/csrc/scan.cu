@@ -78,6 +78,7 @@ void launch_inclusive_scan(const uint32_t* in, uint32_t n, uint32_t* out, uint64
                            int32_t* total_out, uint64_t cap, uint32_t* status_word, cudaStream_t st) {
     if (n == 0) return;
     uint32_t tiles = (n + SC_TILE - 1) / SC_TILE;
+    g_launch_count++;
     inclusive_scan_kernel<<<tiles, SC_THREADS, 0, st>>>(in, n, out, lb_status, ticket, total_out, cap, status_word);
 }
 

@@ -231,6 +231,7 @@ static void radix_sort_impl(const KeyT* keys, const uint32_t* vals, const int32_
     if (max_n == 0) return;
     const PassPlan plan = make_plan(bits);
     if (plan.passes == 0) {
+        g_launch_count++;
         copy_first_n_kernel<KeyT><<<296, 256, 0, st>>>(keys, vals, n_dev, max_n, keys_out, vals_out);
         return;
     }
@@ -240,6 +241,7 @@ static void radix_sort_impl(const KeyT* keys, const uint32_t* vals, const int32_
     cudaMemsetAsync(s.tickets, 0, RS_MAX_PASSES * 4, st);
     uint32_t hist_blocks = (max_n + RS_THREADS - 1) / RS_THREADS;
     if (hist_blocks > 148 * 8) hist_blocks = 148 * 8;
+    g_launch_count += 1 + plan.passes;
     radix_hist_kernel<KeyT><<<hist_blocks, RS_THREADS, 0, st>>>(keys, n_dev, max_n, plan, s.hist);
     const KeyT* src_k = keys;
     const uint32_t* src_v = vals;

@@ -211,19 +211,22 @@ def render_forward(uniforms: BrushUniforms, means, log_scales, quats, sh_coeffs,
 
 
 def render_backward(aux: RenderAux, means, log_scales, quats, sh_coeffs_shape, raw_opacity, out_img, v_out_img,
-                    ctx: Optional[Context] = None):
+                    ctx: Optional[Context] = None, out=None):
     """render.rs:468-625 through brush_render_backward.  Returns the six dense gradients in the reference's
     registration order: means, xy_dummy, log_scales, quats, sh_coeffs, raw_opacity."""
     dev = means.device
     ctx = ctx or get_context(dev)
     N, K = means.shape[0], sh_coeffs_shape[1]
     f32 = dict(dtype=torch.float32, device=dev)
-    v_means = torch.empty((N, 3), **f32)
-    v_xy = torch.empty((N, 2), **f32)
-    v_scales = torch.empty((N, 3), **f32)
-    v_quats = torch.empty((N, 4), **f32)
-    v_sh = torch.empty((N, K, 3), **f32)
-    v_opac = torch.empty((N,), **f32)
+    if out is not None:  # caller-owned (e.g. views into one flat all-reduce buffer)
+        v_means, v_xy, v_scales, v_quats, v_sh, v_opac = out
+    else:
+        v_means = torch.empty((N, 3), **f32)
+        v_xy = torch.empty((N, 2), **f32)
+        v_scales = torch.empty((N, 3), **f32)
+        v_quats = torch.empty((N, 4), **f32)
+        v_sh = torch.empty((N, K, 3), **f32)
+        v_opac = torch.empty((N,), **f32)
     v_out_img = v_out_img.contiguous()
     caux = aux._c()
     with torch.cuda.device(dev):

@@ -138,6 +138,45 @@ int brush_render_forward_host(brush_ctx* ctx, const BrushUniforms* uniforms_host
                               const float* sh_coeffs_host, const float* raw_opacity_host, uint64_t isect_capacity,
                               float* out_img_host, uint32_t* num_visible_host, uint32_t* num_intersections_host);
 
+/* ---- train-step kernels either side of the path ---- */
+
+/* == (pred_compare - gt).abs().mean() and its gradient, crates/brush-train/src/train.rs:255.
+ * pred f32[H,W,4]; gt f32[H,W,C], C = 3 (compare RGB) or 4 (compare RGBA, train.rs:249-253).
+ * Writes v_out_img f32[H,W,4] = d loss / d pred and loss_out f32[1] = the mean. */
+int brush_l1_loss_backward(brush_ctx* ctx, const float* pred, const float* gt, uint32_t height, uint32_t width,
+                           uint32_t gt_channels, float* v_out_img, float* loss_out, void* stream);
+
+/* == the five optim.step calls of SplatTrainer::step, crates/brush-train/src/train.rs:318-359, as ONE launch.
+ * Burn Adam: m = b1 m + (1-b1) g; v = b2 v + (1-b2) g^2; p -= lr * (m/(1-b1^t)) / (sqrt(v/(1-b2^t)) + eps).
+ * sh_coeffs_per_channel > 1 marks the SH group [N,K,3]: coefficients k > 0 use lr * sh_rest_lr_scale
+ * (the 1/lr_coeffs_sh_scale lerp of train.rs:334-348).  grad_scale multiplies every gradient (1/world for DP). */
+typedef struct BrushAdamGroup {
+    float* param;
+    const float* grad;
+    float* m;
+    float* v;
+    uint64_t count;
+    float lr;
+    uint32_t sh_coeffs_per_channel;
+    float sh_rest_lr_scale;
+} BrushAdamGroup;
+int brush_adam_step(brush_ctx* ctx, const BrushAdamGroup* groups_host, int n_groups, float beta1, float beta2,
+                    float eps, uint32_t step, float grad_scale, void* stream);
+
+/* == the rotation normalisation Splats::render applies before the operator and its VJP (Burn elementwise ops +
+ * autodiff in the reference, crates/brush-render/src/gaussian_splats.rs:174-175).  quats f32[n,4]. */
+int brush_quat_normalize(brush_ctx* ctx, const float* quats, uint32_t n, float* out, void* stream);
+int brush_quat_normalize_vjp(brush_ctx* ctx, const float* quats, uint32_t n, float* v_inout, void* stream);
+
+/* == the xy-gradient refine statistics of one view, crates/brush-train/src/train.rs:284-316:
+ * grad_norm[g] (+)= |v_xy[g] * (w/2, h/2)|, visible[g] (+)= 1 for the view's visible splats; accumulate = 0
+ * overwrites both (first view of a batch). */
+int brush_xy_grad_stats(brush_ctx* ctx, const float* v_xy, const BrushAux* aux, uint32_t n, uint32_t width,
+                        uint32_t height, int accumulate, float* grad_norm, float* visible, void* stream);
+
+/* Number of kernels this library has launched in this process (all contexts). */
+uint64_t brush_launch_count(void);
+
 #ifdef __cplusplus
 }
 #endif
