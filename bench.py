@@ -1,0 +1,372 @@
+#!/usr/bin/env python
+"""bench.py -- fwd+bwd training iterations/s of the splat path (BASELINE.json metric).
+
+    python bench.py [--gpus N --steps K --warmup W]            our arm: B200 kernels through the C ABI
+    python bench.py --impl reference [--steps K --warmup W]    the reference's CPU path (oracle port), host cores
+
+One "step" = one complete training iteration of brush_b200.train.SplatTrainer.step on one view per GPU:
+rotation normalise -> render forward -> L1 loss + d loss/d image -> render backward -> refine statistics
+-> (N > 1: one NCCL all-reduce of the flat dense gradient) -> normalisation VJP -> fused Adam.
+Workload = BASELINE.json configs[3]: 1M random Gaussians, SH degree 3, 1920x1080 (synthetic, seeded;
+generator in brush_b200/scene.py).  `value` times steps whose ground-truth view is already in HBM; `e2e`
+times the same steps with the view's image coming from pinned host memory (H2D inside the timed region)
+and the loss read back to the host every step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "fwd+bwd train it/s at 1M Gaussians 1080p"
+UNIT = "it/s"
+WORKLOAD = "cfg4_1m_1080p"
+N_VIEWS = 16
+ISECT_CAPACITY = 16 * 1024 * 1024
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return float(p.get("hbm_gbs", 6650.0)), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def view_cameras(width, height):
+    """16 training views: the reference bench camera (benches/render_bench.rs:163-174) plus small yaw steps on
+    the radius-8 ring around the origin, so every view sees about the same number of splats."""
+    from brush_b200 import Camera
+    from brush_b200.scene import ring_camera_params
+
+    cams = []
+    for k in range(N_VIEWS):
+        j = (k + 1) // 2 * (1 if k % 2 else -1)  # 0, +1, -1, +2, -2 ...
+        ang_steps = 2.0 * np.pi / 0.02
+        pos, rot, fx, fy = ring_camera_params(width, height, j, ang_steps)
+        cams.append(Camera(pos, rot, fx, fy))
+    return cams
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            c = [x.strip() for x in r.split(",")]
+            if len(c) < 7:
+                continue
+            try:
+                sm.append(float(c[0]))
+                mx = float(c[1])
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        busy = [x for x in sm if mx and x > 0.5 * mx] or sm
+        return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def algorithmic_bytes(stage, N, V, I, P, T, K):
+    """algorithmic bytes per launch of each stage."""
+    return {
+        "ProjectSplats": 40 * N + 8 * V,
+        "DepthSort": 68 * V,
+        "ProjectVisible": (48 + 12 * K) * V + 40 * V,
+        "PrefixSum": 8 * V,
+        "MapGaussiansToIntersect": 40 * V + 8 * I,
+        "TileSort": 36 * I,
+        "GetTileBinEdges": 4 * I + 8 * T,
+        "Rasterize": 40 * I + 20 * P,
+        "RasterizeBackwards": 40 * I + 36 * P + 36 * V,
+        "GatherProjectBackwards": (84 + 52 + 12 * K) * V + (52 + 12 * K) * N,
+    }[stage]
+
+
+def run_ours(args):
+    import torch
+
+    from brush_b200 import Splats, _lib, get_context, scene
+    from brush_b200.train import SceneBatch, SplatTrainer, TrainConfig
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback "
+                         "(use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    pg = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=dev)
+        pg = dist.group.WORLD
+    if args.gpus != world and rank == 0:
+        print(f"[bench] note: --gpus {args.gpus} but WORLD_SIZE={world}; using WORLD_SIZE", file=sys.stderr)
+
+    sc = scene.make_config_scene(args.workload, args.n_override)
+    W, H, N, K = sc.width, sc.height, sc.means.shape[0], sc.sh_coeffs.shape[1]
+    P, T = W * H, ((W + 15) // 16) * ((H + 15) // 16)
+    t = lambda a: torch.as_tensor(a, device=dev)
+    splats = Splats(t(sc.means), t(sc.sh_coeffs), t(sc.quats), t(sc.raw_opacity), t(sc.log_scales))
+    cams = view_cameras(W, H)
+    rng = np.random.default_rng(4242)
+    gt_host = torch.from_numpy(rng.uniform(0, 1, (N_VIEWS, H, W, 3)).astype(np.float32)).pin_memory()
+    gt_dev = gt_host.to(dev)
+    ctx = get_context(dev)
+    trainer = SplatTrainer(N, TrainConfig(), dev, sh_coeffs_per_channel=K, process_group=pg,
+                           isect_capacity=args.capacity, optimize=not args.no_optim)
+    loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
+
+    def one_step(step_idx, host_inputs):
+        v = (step_idx * world + rank) % N_VIEWS
+        src = gt_host if host_inputs else gt_dev
+        batch = SceneBatch(src[v:v + 1], [cams[v]], 1.0)
+        _, stats = trainer.step(batch, splats)
+        if host_inputs:
+            loss_host.copy_(stats.loss, non_blocking=True)
+            torch.cuda.current_stream().synchronize()  # the user reads the loss every step
+        return stats
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    def timed(n_steps, host_inputs, first_idx):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = _lib.lib().brush_launch_count()
+        e0.record()
+        for s in range(n_steps):
+            one_step(first_idx + s, host_inputs)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        launches = _lib.lib().brush_launch_count() - l0
+        if world > 1:
+            tt = torch.tensor([ms], device=dev)
+            torch.distributed.all_reduce(tt, op=torch.distributed.ReduceOp.MAX)
+            ms = float(tt.item())
+        return ms, launches
+
+    # ---- warm-up, then the device-resident timed region ----
+    for s in range(args.warmup):
+        one_step(s, False)
+    ctx.sync_check()  # raises if the intersection capacity was too small
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ms_total, launches = timed(args.steps, False, args.warmup)
+    clocks = sampler.stop() if rank == 0 else None
+    ms_step = ms_total / args.steps
+    # ---- the same steps end to end: view image from pinned host memory, loss read back each step ----
+    for s in range(2):
+        one_step(s, True)
+    ms_e2e, _ = timed(args.steps, True, args.warmup + args.steps)
+    ms_e2e_step = ms_e2e / args.steps
+    ctx.sync_check()
+
+    # ---- per-stage device times (CUDA events around each stage, on the launching stream) ----
+    stage_ms, counts = {}, None
+    if rank == 0:
+        ctx.set_timing(True)
+        acc = {}
+        reps = max(3, min(args.steps, 10))
+        for s in range(reps):
+            stats = one_step(1000 + s, False)
+            tm = ctx.stage_times_ms(torch.cuda.current_stream().cuda_stream)
+            for k_, v_ in tm.items():
+                acc[k_] = acc.get(k_, 0.0) + v_ / reps
+        ctx.set_timing(False)
+        stage_ms = acc
+        aux = stats.auxes[0]
+        counts = (aux.read_num_visible(), aux.read_num_intersections())
+    if world > 1:
+        barrier()
+
+    if rank != 0:
+        if world > 1:
+            torch.distributed.destroy_process_group()
+        return
+    V, I = counts
+    peak, peak_src = load_peaks()
+    stages = []
+    for name, ms in stage_ms.items():
+        b = algorithmic_bytes(name, N, V, I, P, T, K)
+        stages.append({"stage": name, "ms": round(ms, 4), "alg_bytes": b,
+                       "gbs": round(b / (ms * 1e-3) / 1e9, 1) if ms > 0 else None,
+                       "frac_hbm": round(b / (ms * 1e-3) / 1e9 / peak, 4) if ms > 0 else None})
+    dom = max(stages, key=lambda s_: s_["ms"])
+    out = {
+        "metric": METRIC, "value": round(world * 1000.0 / ms_step, 3), "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: {N} random Gaussians, SH degree {sc.sh_degree}, {W}x{H}, one view per "
+                               f"GPU per step, L1 loss, {'fused Adam' if not args.no_optim else 'no optimizer'}, "
+                               f"{'NCCL all-reduce of the flat dense gradient' if world > 1 else 'single GPU'}",
+                   "num_visible": V, "num_intersections": I, "views": N_VIEWS, "isect_capacity": args.capacity,
+                   "l2": "inputs larger than L2 (236 MB of parameters + 244 MB of gradients per step vs 126 MB L2)"},
+        "e2e": {"value": round(world * 1000.0 / ms_e2e_step, 3), "unit": UNIT, "ms_per_step": round(ms_e2e_step, 4),
+                "h2d_bytes_per_step": int(gt_host[0].numel() * 4 + 112), "d2h_bytes_per_step": 4},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"kernel": dom["stage"], "bound": "hbm", "achieved": dom["gbs"], "peak": peak, "unit": "GB/s",
+                     "frac": dom["frac_hbm"], "traffic": None, "peak_source": peak_src,
+                     "note": "dominant kernel by time; it is FP32/MUFU/atomic-bound (SURVEY 8d), so the HBM fraction "
+                             "of its algorithmic bytes is a floor, not its ceiling; see stages[] and profiles/"},
+        "stages": stages,
+    }
+    if not args.no_cpu_baseline and world == 1:
+        out["cpu_baseline"] = cpu_baseline_sample(args, sc, 1)
+    print(json.dumps(out))
+    if world > 1:
+        torch.distributed.destroy_process_group()
+
+
+def _oracle_iteration(O, u, sc, v_out, capacity):
+    """One fwd+bwd of the reference's CPU path: render.rs:55-323 then render.rs:468-625 (oracle restatement)."""
+    img, aux = O.render_forward(u, sc.means, sc.log_scales, sc.quats, sc.sh_coeffs, sc.raw_opacity,
+                                capacity=capacity)
+    O.render_backward(aux, sc.means, sc.log_scales, sc.quats, sc.raw_opacity, sc.sh_coeffs.shape[1], img, v_out)
+    return aux
+
+
+def _oracle_setup(args, sc):
+    from oracle import pyoracle as O  # the ONLY place bench.py touches oracle/: the CPU baseline legs
+
+    O.build()
+    threads = O.max_threads()
+    O.set_threads(threads)
+    W, H = sc.width, sc.height
+    vm = np.eye(4, dtype=np.float32)
+    vm[2, 3] = 8.0  # bench camera (0,0,-8), identity (benches/render_bench.rs:163-174)
+    u = O.make_uniforms(vm, (0.5 * W, 0.5 * W), (W, H), (0.5 * W, 0.5 * H))
+    v_out = np.full((H, W, 4), 1.0 / (4 * H * W), np.float32)  # loss = mean(out) (render_bench.rs:180)
+    return O, u, v_out, threads
+
+
+def cpu_baseline_sample(args, sc, iters):
+    O, u, v_out, threads = _oracle_setup(args, sc)
+    _oracle_iteration(O, u, sc, v_out, args.capacity)  # warm (page-in, allocator)
+    t0 = time.perf_counter()
+    for _ in range(iters):
+        _oracle_iteration(O, u, sc, v_out, args.capacity)
+    dt = (time.perf_counter() - t0) / iters
+    return {"value": round(1.0 / dt, 4), "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"{iters} full fwd+bwd iteration(s) of the whole workload ({sc.means.shape[0]} Gaussians, "
+                      f"{sc.width}x{sc.height}, bench camera, v_out = 1/(4P)) by the C++ oracle with OpenMP on "
+                      f"{threads} threads; {dt:.2f} s per iteration"}
+
+
+def run_reference(args):
+    """The reference arm: the reference's own implementation of the path is WGSL through wgpu, which cannot run on
+    this box (no Rust toolchain, no graphics stack), so this times the oracle port of it on all host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from brush_b200 import scene
+
+    sc = scene.make_config_scene(args.workload, args.n_override)
+    O, u, v_out, threads = _oracle_setup(args, sc)
+    # bounded sample: keep the whole run within a few minutes whatever K and W are
+    t0 = time.perf_counter()
+    _oracle_iteration(O, u, sc, v_out, args.capacity)
+    probe = time.perf_counter() - t0
+    budget = float(os.environ.get("BRUSH_REF_BUDGET_S", "240"))
+    stride = 1
+    while probe / stride * (args.steps + args.warmup) > budget and stride < 64:
+        stride *= 2
+    if stride > 1:  # every stride-th Gaussian: fewer splats at the same resolution; value is it/s ON THAT SAMPLE
+        sc.means, sc.log_scales, sc.quats = sc.means[::stride].copy(), sc.log_scales[::stride].copy(), sc.quats[::stride].copy()
+        sc.sh_coeffs, sc.raw_opacity = sc.sh_coeffs[::stride].copy(), sc.raw_opacity[::stride].copy()
+    for _ in range(max(args.warmup - 1, 0)):
+        _oracle_iteration(O, u, sc, v_out, args.capacity)
+    t0 = time.perf_counter()
+    aux = None
+    for _ in range(args.steps):
+        aux = _oracle_iteration(O, u, sc, v_out, args.capacity)
+    dt = (time.perf_counter() - t0) / args.steps
+    val = round(1.0 / dt, 4)
+    N, K = sc.means.shape[0], sc.sh_coeffs.shape[1]
+    out = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(dt * 1e3, 2), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: {N} random Gaussians, SH degree {sc.sh_degree}, {sc.width}x"
+                               f"{sc.height}, fwd+bwd of one view per step on the host CPU (no optimizer; the "
+                               "reference bench shape, benches/render_bench.rs:176-184)",
+                   "num_visible": aux.num_visible, "num_intersections": aux.num_intersections},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": (f"every step = one full fwd+bwd of the whole workload by the C++ oracle (OpenMP, "
+                                    f"{threads} threads); the reference's wgpu path is unavailable on this box"
+                                    + (f"; SUBSAMPLED to every {stride}th Gaussian to fit the time budget" if stride > 1
+                                       else ""))},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(out))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--workload", default=WORKLOAD)
+    ap.add_argument("--n-override", type=int, default=None, help="debug: fewer Gaussians (not a bench number)")
+    ap.add_argument("--capacity", type=int, default=ISECT_CAPACITY)
+    ap.add_argument("--no-optim", action="store_true", help="skip Adam (pure fwd+bwd, the reference bench shape)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -170,8 +170,11 @@ def _stream_ptr(device) -> int:
 
 
 def render_forward(uniforms: BrushUniforms, means, log_scales, quats, sh_coeffs, raw_opacity, raster_u32: bool,
-                   isect_capacity: Optional[int] = None, keep_tile_ids: bool = False, ctx: Optional[Context] = None):
-    """render.rs:55-323 through brush_render_forward.  Returns (out_img, RenderAux).  Async on the current stream."""
+                   isect_capacity: Optional[int] = None, keep_tile_ids: bool = False, ctx: Optional[Context] = None,
+                   reuse=None):
+    """render.rs:55-323 through brush_render_forward.  Returns (out_img, RenderAux).  Async on the current stream.
+    `reuse` = an (out_img, RenderAux) pair from an earlier call with the same shapes: its buffers are overwritten
+    instead of allocating new ones (steady-state training loops)."""
     _check_dims(means, log_scales, quats, sh_coeffs, raw_opacity)
     dev = means.device
     ctx = ctx or get_context(dev)
@@ -184,6 +187,19 @@ def render_forward(uniforms: BrushUniforms, means, log_scales, quats, sh_coeffs,
         isect_capacity = min(N * tx * ty, REFERENCE_MAX_INTERSECTS)  # render.rs:204-206
     cap = max(int(isect_capacity), 1)
     i32 = dict(dtype=torch.int32, device=dev)
+    if reuse is not None:
+        out, aux = reuse
+        if (aux.projected_splats.shape[0] != N or aux.final_index.shape != (H, W)
+                or aux.compact_gid_from_isect.numel() != cap or out.shape[-1] != (1 if raster_u32 else 4)):
+            raise ValueError("render_forward: `reuse` buffers do not match this call's shapes")
+        caux = aux._c()
+        with torch.cuda.device(dev):
+            rc = _lib.lib().brush_render_forward(
+                ctx.handle, C.byref(uniforms), N, K, means.data_ptr(), log_scales.data_ptr(), quats.data_ptr(),
+                sh_coeffs.data_ptr(), raw_opacity.data_ptr(), int(raster_u32), out.data_ptr(), C.byref(caux),
+                C.c_void_p(_stream_ptr(dev)))
+        ctx.check(rc)
+        return out, aux
     aux = RenderAux(
         projected_splats=torch.empty((N, 9), dtype=torch.float32, device=dev),
         uniforms_buffer=torch.empty(28, **i32),
