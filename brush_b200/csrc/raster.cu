@@ -40,21 +40,49 @@ void launch_tile_bins(const uint32_t* sorted_tile_ids, const uint64_t* sorted_ke
 }
 
 // ---------------------------------------------------------------------------------------------
-// One CTA per 16x16 tile, one thread per pixel.  The tile's depth-sorted splats are staged through
-// shared memory in batches of 256 (rasterize.wgsl:57-71); every thread then reads the same splat at
-// the same time (shared-memory broadcast, conflict free).
+// One CTA per 16x16 tile, 8 warps, each warp owns an 8x4 pixel block.  The tile's depth-sorted splats are
+// staged through shared memory in batches of 256 (rasterize.wgsl:57-71).  B200-first differences from the
+// reference loop (which walks every splat of the tile for every pixel, ~35 instructions per pair):
+//  * at staging time each splat is put in "log2 form": q(d) = L + A dx^2 + B dx dy + C dy^2 with
+//    L = log2(opac), (A,B,C) = -log2(e) * (cxx/2, cxy, cyy/2), so alpha = 2^q, and the visibility test
+//    "sigma >= 0 && alpha >= 1/255" becomes "q - L <= 0 && q >= log2(1/255)" -- no exp for rejected pairs;
+//  * each splat also gets the pixel-space bounding box of its alpha >= 1/255 ellipse; every warp tests 32
+//    splats at a time against its 8x4 block (one lane per splat), ballots, and only walks the survivors
+//    (about half of the tile's list at 1M splats / 1080p), in depth order;
+//  * whole-warp and whole-tile early exit once every pixel's transmittance is spent.
 struct SplatSmem {
-    float4 g0[TILE_SIZE];  // x, y, conic.x, conic.y
-    float2 g1[TILE_SIZE];  // conic.z, opacity
-    float4 col[TILE_SIZE]; // r, g, b, -
+    float4 g0[TILE_SIZE];    // x, y, A, B
+    float2 g1[TILE_SIZE];    // C, L
+    float4 col[TILE_SIZE];   // r, g, b, opacity
+    float4 bbox[TILE_SIZE];  // xmin, xmax, ymin, ymax of the alpha >= 1/255 ellipse (pixel coordinates)
 };
+
+constexpr float LOG2E = 1.4426950408889634f;
+constexpr float LN2 = 0.6931471805599453f;
+constexpr float LOG2_INV255 = -7.994353436858858f;  // log2(1/255)
+
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 
 __device__ __forceinline__ void stage_splat(SplatSmem& s, uint32_t slot, const float* __restrict__ projected,
                                             uint32_t cg) {
     const float* p = projected + (size_t)cg * 9;
-    s.g0[slot] = make_float4(__ldg(p), __ldg(p + 1), __ldg(p + 2), __ldg(p + 3));
-    s.g1[slot] = make_float2(__ldg(p + 4), __ldg(p + 8));
-    s.col[slot] = make_float4(__ldg(p + 5), __ldg(p + 6), __ldg(p + 7), 0.f);
+    const float x = __ldg(p), y = __ldg(p + 1), cxx = __ldg(p + 2), cxy = __ldg(p + 3), cyy = __ldg(p + 4);
+    const float opac = __ldg(p + 8);
+    s.g0[slot] = make_float4(x, y, -0.5f * LOG2E * cxx, -LOG2E * cxy);
+    s.g1[slot] = make_float2(-0.5f * LOG2E * cyy, __log2f(opac));
+    s.col[slot] = make_float4(__ldg(p + 5), __ldg(p + 6), __ldg(p + 7), opac);
+    // sigma(d) <= t = ln(255 opac)  =>  |dx| <= sqrt(2 t cyy / det), |dy| <= sqrt(2 t cxx / det); slightly inflated
+    // so that rounding can only keep a splat, never drop one.
+    const float t = __logf(255.0f * opac) + 1e-3f;
+    const float det = cxx * cyy - cxy * cxy;
+    float ex = sqrtf(2.0f * t * cyy / det) * 1.001f + 1e-2f;
+    float ey = sqrtf(2.0f * t * cxx / det) * 1.001f + 1e-2f;
+    if (!(det > 0.0f) || !(ex < 1e30f) || !(ey < 1e30f)) ex = ey = 1e30f;  // degenerate: never cull
+    s.bbox[slot] = make_float4(x - ex, x + ex, y - ey, y + ey);
 }
 
 template <bool RASTER_U32>
@@ -63,12 +91,14 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
                  const uint32_t* __restrict__ tile_bins, const float* __restrict__ projected,
                  void* __restrict__ out_img, uint32_t* __restrict__ final_index) {
     __shared__ SplatSmem s;
-    const uint32_t tid = threadIdx.x;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t tile_id = blockIdx.x + blockIdx.y * cam.tiles_x;
-    const uint32_t px = blockIdx.x * TILE_WIDTH + (tid % TILE_WIDTH);
-    const uint32_t py = blockIdx.y * TILE_WIDTH + (tid / TILE_WIDTH);
+    const uint32_t bx0 = blockIdx.x * TILE_WIDTH + (warp & 1u) * 8u, by0 = blockIdx.y * TILE_WIDTH + (warp >> 1) * 4u;
+    const uint32_t px = bx0 + (lane & 7u), py = by0 + (lane >> 3);
     const bool inside = px < cam.img_w && py < cam.img_h;
     const float pcx = (float)px + 0.5f, pcy = (float)py + 0.5f;
+    // the warp's block in pixel-centre coordinates
+    const float rx0 = (float)bx0 + 0.5f, rx1 = (float)bx0 + 7.5f, ry0 = (float)by0 + 0.5f, ry1 = (float)by0 + 3.5f;
     bool done = !inside;
 
     const uint2 range = __ldg(reinterpret_cast<const uint2*>(tile_bins) + tile_id);
@@ -85,25 +115,39 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
         const uint32_t remaining = min(TILE_SIZE, range.y - batch_start);
         if (tid < remaining) stage_splat(s, tid, projected, __ldg(compact_gid_from_isect + batch_start + tid));
         __syncthreads();
-        if (!done) {
-            for (uint32_t t = 0; t < remaining; t++) {
+        bool warp_done = __all_sync(0xffffffffu, done);
+        for (uint32_t c0 = 0; c0 < remaining && !warp_done; c0 += 32) {
+            const uint32_t mine = c0 + lane;
+            bool hit = false;
+            if (mine < remaining) {
+                const float4 bb = s.bbox[mine];
+                hit = bb.x <= rx1 && bb.y >= rx0 && bb.z <= ry1 && bb.w >= ry0;
+            }
+            uint32_t mask = __ballot_sync(0xffffffffu, hit);
+            while (mask) {
+                const uint32_t t = c0 + (uint32_t)__ffs(mask) - 1u;
+                mask &= mask - 1u;
                 const float4 g0 = s.g0[t];
                 const float2 g1 = s.g1[t];
                 const float dx = g0.x - pcx, dy = g0.y - pcy;
-                const float sigma = 0.5f * (g0.z * dx * dx + g1.x * dy * dy) + g0.w * dx * dy;
-                const float vis = __expf(-sigma);
-                const float alpha = fminf(0.999f, g1.y * vis);
-                if (sigma >= 0.0f && alpha >= 1.0f / 255.0f) {
+                const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);  // -sigma * log2(e)
+                const float q = sp + g1.y;                                              // log2(opac * exp(-sigma))
+                if (!done && sp <= 0.0f && q >= LOG2_INV255) {
+                    const float alpha = fminf(0.999f, ex2_approx(q));
                     const float next_T = T * (1.0f - alpha);
                     if (next_T <= 1e-4f) {
                         done = true;
-                        break;
+                    } else {
+                        const float fac = alpha * T;
+                        const float4 c = s.col[t];
+                        pr = fmaf(c.x, fac, pr); pg = fmaf(c.y, fac, pg); pb = fmaf(c.z, fac, pb);
+                        T = next_T;
+                        final_idx = batch_start + t;
                     }
-                    const float fac = alpha * T;
-                    const float4 c = s.col[t];
-                    pr += c.x * fac; pg += c.y * fac; pb += c.z * fac;
-                    T = next_T;
-                    final_idx = batch_start + t;
+                }
+                if (__all_sync(0xffffffffu, done)) {
+                    warp_done = true;
+                    break;
                 }
             }
         }
@@ -139,10 +183,11 @@ void launch_rasterize(const Cam& cam, const uint32_t* compact_gid_from_isect, co
 }
 
 // ---------------------------------------------------------------------------------------------
-// Backward.  Per pixel, back to front (rasterize_backwards.wgsl:194-272).  The nine per-splat
-// gradient terms are summed over the warp with a butterfly that halves the live values at each
-// exchange (12 shuffles instead of 9*5), then added with one predicated red.global.add.f32 -- the
-// native replacement for the reference's CAS loops (rasterize_backwards.wgsl:79-133).
+// Backward.  Per pixel, back to front (rasterize_backwards.wgsl:194-272), same warp-level culling as the
+// forward.  The nine per-splat gradient terms are summed over the warp with a butterfly that halves the
+// live values at each exchange (12 shuffles instead of 9*5), then added with one predicated
+// red.global.add.f32 -- the native replacement for the reference's CAS loops
+// (rasterize_backwards.wgsl:79-133).
 __device__ __forceinline__ float warp_reduce9(float v0, float v1, float v2, float v3, float v4, float v5, float v6,
                                               float v7, float v8, uint32_t lane) {
     const uint32_t F = 0xffffffffu;
@@ -171,13 +216,14 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
                           const float* __restrict__ v_out_img, float* __restrict__ v_projected) {
     __shared__ SplatSmem s;
     __shared__ uint32_t s_id[TILE_SIZE];
-    const uint32_t tid = threadIdx.x, lane = tid & 31u;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t tile_id = blockIdx.x;
     const uint32_t tile_x = tile_id % cam.tiles_x, tile_y = tile_id / cam.tiles_x;
-    const uint32_t px = tile_x * TILE_WIDTH + (tid % TILE_WIDTH);
-    const uint32_t py = tile_y * TILE_WIDTH + (tid / TILE_WIDTH);
+    const uint32_t bx0 = tile_x * TILE_WIDTH + (warp & 1u) * 8u, by0 = tile_y * TILE_WIDTH + (warp >> 1) * 4u;
+    const uint32_t px = bx0 + (lane & 7u), py = by0 + (lane >> 3);
     const bool inside = px < cam.img_w && py < cam.img_h;
     const float pcx = (float)px + 0.5f, pcy = (float)py + 0.5f;
+    const float rx0 = (float)bx0 + 0.5f, rx1 = (float)bx0 + 7.5f, ry0 = (float)by0 + 0.5f, ry1 = (float)by0 + 3.5f;
 
     const uint2 range = __ldg(reinterpret_cast<const uint2*>(tile_bins) + tile_id);
     if (range.y <= range.x) return;
@@ -209,41 +255,55 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
         }
         __syncthreads();
         if (!warp_any_inside) continue;
-        for (uint32_t t = 0; t < remaining; t++) {
-            const uint32_t isect = batch_end - 1u - t;
-            if (isect > warp_final) continue;  // warp-uniform
-            const float4 g0 = s.g0[t];
-            const float2 g1 = s.g1[t];
-            const float dx = g0.x - pcx, dy = g0.y - pcy;
-            const float sigma = 0.5f * (g0.z * dx * dx + g1.x * dy * dy) + g0.w * dx * dy;
-            const float vis = __expf(-sigma);
-            const float alpha = fminf(0.99f, g1.y * vis);  // 0.99 here, 0.999 forward (reference quirk)
-            const bool active = inside && isect <= final_isect && sigma >= 0.0f && alpha >= 1.0f / 255.0f;
-            if (!__any_sync(0xffffffffu, active)) continue;
-            float v_x = 0.f, v_y = 0.f, v_cxx = 0.f, v_cxy = 0.f, v_cyy = 0.f, v_r = 0.f, v_g = 0.f, v_b = 0.f,
-                  v_a = 0.f;
-            if (active) {
-                const float4 c = s.col[t];
-                const float ra = __frcp_rn(1.0f - alpha);
-                T *= ra;
-                const float fac = alpha * T;
-                float v_alpha = (c.x * T - br * ra) * v_out.x + (c.y * T - bg * ra) * v_out.y +
-                                (c.z * T - bb * ra) * v_out.z;
-                v_alpha += T_final * ra * v_out.w;
-                br += c.x * fac; bg += c.y * fac; bb += c.z * fac;
-                const float v_sigma = -g1.y * vis * v_alpha;
-                v_x = v_sigma * (g0.z * dx + g0.w * dy);
-                v_y = v_sigma * (g0.w * dx + g1.x * dy);
-                v_cxx = 0.5f * v_sigma * dx * dx;
-                v_cxy = v_sigma * dx * dy;
-                v_cyy = 0.5f * v_sigma * dy * dy;
-                v_r = fac * v_out.x; v_g = fac * v_out.y; v_b = fac * v_out.z;
-                v_a = vis * v_alpha;
+        for (uint32_t c0 = 0; c0 < remaining; c0 += 32) {
+            const uint32_t mine = c0 + lane;
+            bool hit = false;
+            if (mine < remaining && batch_end - 1u - mine <= warp_final) {
+                const float4 bbx = s.bbox[mine];
+                hit = bbx.x <= rx1 && bbx.y >= rx0 && bbx.z <= ry1 && bbx.w >= ry0;
             }
-            const float x = warp_reduce9(v_x, v_y, v_cxx, v_cxy, v_cyy, v_r, v_g, v_b, v_a, lane);
-            float* dst = v_projected + (size_t)s_id[t] * 9;
-            if ((lane & 3u) == 0u) atomicAdd(dst + (lane >> 2), x);
-            else if (lane == 2u) atomicAdd(dst + 8, x);
+            uint32_t mask = __ballot_sync(0xffffffffu, hit);
+            while (mask) {
+                const uint32_t t = c0 + (uint32_t)__ffs(mask) - 1u;
+                mask &= mask - 1u;
+                const uint32_t isect = batch_end - 1u - t;
+                const float4 g0 = s.g0[t];
+                const float2 g1 = s.g1[t];
+                const float dx = g0.x - pcx, dy = g0.y - pcy;
+                const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);
+                const float q = sp + g1.y;
+                // the same predicate, on the same instruction sequence, as the forward
+                const bool active = inside && isect <= final_isect && sp <= 0.0f && q >= LOG2_INV255;
+                if (!__any_sync(0xffffffffu, active)) continue;
+                float v_x = 0.f, v_y = 0.f, v_cxx = 0.f, v_cxy = 0.f, v_cyy = 0.f, v_r = 0.f, v_g = 0.f, v_b = 0.f,
+                      v_a = 0.f;
+                if (active) {
+                    const float4 c = s.col[t];
+                    const float vis = ex2_approx(sp);
+                    const float av = c.w * vis;
+                    const float alpha = fminf(0.99f, av);  // 0.99 here, 0.999 forward (reference quirk)
+                    const float ra = __frcp_rn(1.0f - alpha);
+                    T *= ra;
+                    const float fac = alpha * T;
+                    float v_alpha = (c.x * T - br * ra) * v_out.x + (c.y * T - bg * ra) * v_out.y +
+                                    (c.z * T - bb * ra) * v_out.z;
+                    v_alpha += T_final * ra * v_out.w;
+                    br = fmaf(c.x, fac, br); bg = fmaf(c.y, fac, bg); bb = fmaf(c.z, fac, bb);
+                    const float v_sigma = -av * v_alpha;
+                    const float vs2 = -LN2 * v_sigma;  // conic = -ln2 * (2A, B, 2C)
+                    v_x = vs2 * fmaf(2.0f * g0.z, dx, g0.w * dy);
+                    v_y = vs2 * fmaf(g0.w, dx, 2.0f * g1.x * dy);
+                    v_cxx = 0.5f * v_sigma * dx * dx;
+                    v_cxy = v_sigma * dx * dy;
+                    v_cyy = 0.5f * v_sigma * dy * dy;
+                    v_r = fac * v_out.x; v_g = fac * v_out.y; v_b = fac * v_out.z;
+                    v_a = vis * v_alpha;
+                }
+                const float x = warp_reduce9(v_x, v_y, v_cxx, v_cxy, v_cyy, v_r, v_g, v_b, v_a, lane);
+                float* dst = v_projected + (size_t)s_id[t] * 9;
+                if ((lane & 3u) == 0u) atomicAdd(dst + (lane >> 2), x);
+                else if (lane == 2u) atomicAdd(dst + 8, x);
+            }
         }
     }
 }

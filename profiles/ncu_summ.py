@@ -1,0 +1,28 @@
+"""Prints the handful of ncu metrics we track from a `ncu --page raw --csv` dump (profiles/ helper)."""
+import csv
+import sys
+
+rows = list(csv.reader(open(sys.argv[1])))
+hdr, units = rows[0], rows[1]
+want = ['Kernel Name', 'gpu__time_duration.sum', 'launch__registers_per_thread', 'launch__occupancy_limit_registers',
+        'launch__occupancy_limit_shared_mem', 'sm__warps_active.avg.pct_of_peak_sustained_active',
+        'sm__throughput.avg.pct_of_peak_sustained_elapsed', 'dram__bytes_read.sum', 'dram__bytes_write.sum',
+        'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed',
+        'sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active',
+        'sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active',
+        'sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active',
+        'sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active',
+        'smsp__issue_active.avg.pct_of_peak_sustained_active', 'smsp__inst_executed.sum',
+        'lts__t_sectors_op_red.sum', 'lts__t_sectors_op_atom.sum', 'l1tex__data_pipe_lsu_wavefronts_mem_shared.sum',
+        'smsp__thread_inst_executed_per_inst_executed.ratio', 'lts__t_sector_hit_rate.pct',
+        'l1tex__t_sector_hit_rate.pct']
+for r in rows[2:]:
+    print('----')
+    for w in want:
+        if w in hdr:
+            i = hdr.index(w)
+            print(f"  {w} = {r[i]} {units[i]}")
+    st = [(hdr[i], r[i]) for i in range(len(hdr)) if 'issue_stalled' in hdr[i] and hdr[i].endswith('per_warp_active.pct')]
+    st = sorted(st, key=lambda kv: -float(kv[1].replace(',', '') or 0))[:8]
+    for k, v in st:
+        print('    stall', k.replace('smsp__average_warp_latency_issue_stalled_', '').replace('smsp__average_warps_issue_stalled_', '').replace('_per_warp_active.pct', ''), v)

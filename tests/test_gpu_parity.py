@@ -178,8 +178,12 @@ def _check_forward(img, aux, ref_img, ref_aux, fused=False):
     rp = ref_aux.projected_splats[:V]
     assert np.array_equal(proj[:, [0, 1, 2, 3, 4, 8]], rp[:, [0, 1, 2, 3, 4, 8]])  # xy, conic, opac: bit-exact
     assert np.abs(proj[:, 5:8] - rp[:, 5:8]).max() < 2e-6                           # SH colour: float order only
-    out = img.cpu().numpy()
-    assert np.abs(out - ref_img).max() < 1e-5
+    # image: 1e-5 absolute, except isolated pixels where some splat's alpha lies within float rounding of the 1/255
+    # cut-off and exp() rounds differently on the two machines (the pair is then kept on one side only: an error of
+    # at most alpha * T <= 1/255 on that pixel).  Those pixels are counted and bounded, never ignored.
+    err = np.abs(img.cpu().numpy() - ref_img).max(axis=2)
+    assert (err > 1e-5).sum() <= max(2, 2e-5 * err.size), f"{(err > 1e-5).sum()} pixels over 1e-5"
+    assert err.max() < 1.0 / 255.0 + 1e-4 and np.median(err) < 1e-6
     fi = aux.final_index.cpu().numpy().view(np.uint32)
     assert (fi != ref_aux.final_index).mean() < 1e-3  # decided by exp() rounding at the 1/255 threshold
 
@@ -289,3 +293,34 @@ def test_empty_and_single():
     out, aux = render_forward(u, torch.zeros(1, 3, **f), torch.zeros(1, 3, **f), q, torch.ones(1, 1, 3, **f),
                               torch.ones(1, **f) * 2, False)
     assert aux.read_num_visible() == 1 and float(out[..., 3].max()) > 0.5
+
+
+def test_full_size_config4_vs_oracle(oracle):
+    """BASELINE.json configs[3] at full size: 1M Gaussians, SH3, 1920x1080.  Integer outputs bit-exact; image within
+    1e-5 except for the (counted) pixels where a splat sits exactly on the alpha = 1/255 threshold and exp() rounding
+    decides differently on the two machines; gradients within 1e-3 relative."""
+    from brush_b200 import scene
+
+    oracle.set_threads(oracle.max_threads())
+    try:
+        sc = scene.make_config_scene("cfg4_1m_1080p")
+        w, h = sc.width, sc.height
+        v_out = np.full((h, w, 4), 1.0 / (4 * h * w), np.float32)
+        img, aux, ref_img, ref_aux, grads, ref_grads = _run_both(oracle, sc, w, h, capacity=16 << 20, v_out=v_out)
+    finally:
+        oracle.set_threads(1)
+    V, I = aux.read_num_visible(), aux.read_num_intersections()
+    assert V == ref_aux.num_visible and I == ref_aux.num_intersections
+    assert np.array_equal(aux.global_from_compact_gid.cpu().numpy().view(np.uint32), ref_aux.global_from_compact_gid)
+    assert np.array_equal(aux.cum_tiles_hit.cpu().numpy().view(np.uint32), ref_aux.cum_tiles_hit)
+    assert np.array_equal(aux.tile_bins.cpu().numpy().view(np.uint32), ref_aux.tile_bins)
+    assert np.array_equal(aux.compact_gid_from_isect.cpu().numpy().view(np.uint32)[:I], ref_aux.compact_gid_from_isect[:I])
+    assert np.array_equal(aux.tile_id_from_isect.cpu().numpy().view(np.uint32)[:I], ref_aux.tile_id_from_isect[:I])
+    err = np.abs(img.cpu().numpy() - ref_img).max(axis=2)
+    flips = int((err > 1e-5).sum())
+    print(f"full size: V={V} I={I} max err {err.max():.2e}, pixels over 1e-5: {flips} of {err.size}")
+    assert flips <= 1e-4 * err.size and err.max() < 1.0 / 255.0 + 1e-4
+    for gname, gt in zip(["v_means", "v_xy", "v_log_scales", "v_quats", "v_coeffs", "v_raw_opac"], grads):
+        a, b = gt.cpu().numpy().astype(np.float64), ref_grads[gname].astype(np.float64)
+        bad = np.abs(a - b) > 1e-3 * np.abs(b) + 2e-5 * np.abs(b).max()
+        assert bad.mean() < 1e-5, f"{gname}: {bad.sum()} of {bad.size}"
