@@ -52,9 +52,10 @@ void launch_tile_bins(const uint32_t* sorted_tile_ids, const uint64_t* sorted_ke
 //  * whole-warp and whole-tile early exit once every pixel's transmittance is spent.
 struct SplatSmem {
     float4 g0[TILE_SIZE];    // x, y, A, B
-    float2 g1[TILE_SIZE];    // C, L
-    float4 col[TILE_SIZE];   // r, g, b, opacity
+    float4 g1[TILE_SIZE];    // C, L, opacity, -      (g1 sits exactly 4096 bytes after g0: one offset serves both)
+    float4 col[TILE_SIZE];   // r, g, b, -
     float4 bbox[TILE_SIZE];  // xmin, xmax, ymin, ymax of the alpha >= 1/255 ellipse (pixel coordinates)
+    uint16_t list[TILE_SIZE / 32][TILE_SIZE];  // per warp: byte offsets (slot * 16) of the splats that survive culling
 };
 
 constexpr float LOG2E = 1.4426950408889634f;
@@ -73,8 +74,8 @@ __device__ __forceinline__ void stage_splat(SplatSmem& s, uint32_t slot, const f
     const float x = __ldg(p), y = __ldg(p + 1), cxx = __ldg(p + 2), cxy = __ldg(p + 3), cyy = __ldg(p + 4);
     const float opac = __ldg(p + 8);
     s.g0[slot] = make_float4(x, y, -0.5f * LOG2E * cxx, -LOG2E * cxy);
-    s.g1[slot] = make_float2(-0.5f * LOG2E * cyy, __log2f(opac));
-    s.col[slot] = make_float4(__ldg(p + 5), __ldg(p + 6), __ldg(p + 7), opac);
+    s.g1[slot] = make_float4(-0.5f * LOG2E * cyy, __log2f(opac), opac, 0.f);
+    s.col[slot] = make_float4(__ldg(p + 5), __ldg(p + 6), __ldg(p + 7), 0.f);
     // sigma(d) <= t = ln(255 opac)  =>  |dx| <= sqrt(2 t cyy / det), |dy| <= sqrt(2 t cxx / det); slightly inflated
     // so that rounding can only keep a splat, never drop one.
     const float t = __logf(255.0f * opac) + 1e-3f;
@@ -115,41 +116,44 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
         const uint32_t remaining = min(TILE_SIZE, range.y - batch_start);
         if (tid < remaining) stage_splat(s, tid, projected, __ldg(compact_gid_from_isect + batch_start + tid));
         __syncthreads();
-        bool warp_done = __all_sync(0xffffffffu, done);
-        for (uint32_t c0 = 0; c0 < remaining && !warp_done; c0 += 32) {
+        if (__all_sync(0xffffffffu, done)) continue;
+        // cull: one lane per splat against this warp's 8x4 block; survivors go to the warp's list in depth order
+        uint32_t n_list = 0;
+        for (uint32_t c0 = 0; c0 < remaining; c0 += 32) {
             const uint32_t mine = c0 + lane;
             bool hit = false;
             if (mine < remaining) {
                 const float4 bb = s.bbox[mine];
                 hit = bb.x <= rx1 && bb.y >= rx0 && bb.z <= ry1 && bb.w >= ry0;
             }
-            uint32_t mask = __ballot_sync(0xffffffffu, hit);
-            while (mask) {
-                const uint32_t t = c0 + (uint32_t)__ffs(mask) - 1u;
-                mask &= mask - 1u;
-                const float4 g0 = s.g0[t];
-                const float2 g1 = s.g1[t];
-                const float dx = g0.x - pcx, dy = g0.y - pcy;
-                const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);  // -sigma * log2(e)
-                const float q = sp + g1.y;                                              // log2(opac * exp(-sigma))
-                if (!done && sp <= 0.0f && q >= LOG2_INV255) {
-                    const float alpha = fminf(0.999f, ex2_approx(q));
-                    const float next_T = T * (1.0f - alpha);
-                    if (next_T <= 1e-4f) {
-                        done = true;
-                    } else {
-                        const float fac = alpha * T;
-                        const float4 c = s.col[t];
-                        pr = fmaf(c.x, fac, pr); pg = fmaf(c.y, fac, pg); pb = fmaf(c.z, fac, pb);
-                        T = next_T;
-                        final_idx = batch_start + t;
-                    }
-                }
-                if (__all_sync(0xffffffffu, done)) {
-                    warp_done = true;
-                    break;
+            const uint32_t mask = __ballot_sync(0xffffffffu, hit);
+            if (hit) s.list[warp][n_list + __popc(mask & ((1u << lane) - 1u))] = (uint16_t)(mine * 16u);
+            n_list += __popc(mask);
+        }
+        __syncwarp();
+        const char* sbase = reinterpret_cast<const char*>(&s.g0[0]);
+        const uint16_t* list = s.list[warp];
+        for (uint32_t i = 0; i < n_list; i++) {
+            const uint32_t off = list[i];
+            const float4 g0 = *reinterpret_cast<const float4*>(sbase + off);
+            const float4 g1 = *reinterpret_cast<const float4*>(sbase + sizeof(float4) * TILE_SIZE + off);
+            const float dx = g0.x - pcx, dy = g0.y - pcy;
+            const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);  // -sigma * log2(e)
+            const float q = sp + g1.y;                                              // log2(opac * exp(-sigma))
+            if (!done && sp <= 0.0f && q >= LOG2_INV255) {
+                const float alpha = fminf(0.999f, ex2_approx(q));
+                const float next_T = T * (1.0f - alpha);
+                if (next_T <= 1e-4f) {
+                    done = true;
+                } else {
+                    const float fac = alpha * T;
+                    const float4 c = *reinterpret_cast<const float4*>(sbase + 2 * sizeof(float4) * TILE_SIZE + off);
+                    pr = fmaf(c.x, fac, pr); pg = fmaf(c.y, fac, pg); pb = fmaf(c.z, fac, pb);
+                    T = next_T;
+                    final_idx = batch_start + (off >> 4);
                 }
             }
+            if ((i & 31u) == 31u && __all_sync(0xffffffffu, done)) break;
         }
     }
     if (inside) {
@@ -255,6 +259,7 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
         }
         __syncthreads();
         if (!warp_any_inside) continue;
+        uint32_t n_list = 0;
         for (uint32_t c0 = 0; c0 < remaining; c0 += 32) {
             const uint32_t mine = c0 + lane;
             bool hit = false;
@@ -262,48 +267,53 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
                 const float4 bbx = s.bbox[mine];
                 hit = bbx.x <= rx1 && bbx.y >= rx0 && bbx.z <= ry1 && bbx.w >= ry0;
             }
-            uint32_t mask = __ballot_sync(0xffffffffu, hit);
-            while (mask) {
-                const uint32_t t = c0 + (uint32_t)__ffs(mask) - 1u;
-                mask &= mask - 1u;
-                const uint32_t isect = batch_end - 1u - t;
-                const float4 g0 = s.g0[t];
-                const float2 g1 = s.g1[t];
-                const float dx = g0.x - pcx, dy = g0.y - pcy;
-                const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);
-                const float q = sp + g1.y;
-                // the same predicate, on the same instruction sequence, as the forward
-                const bool active = inside && isect <= final_isect && sp <= 0.0f && q >= LOG2_INV255;
-                if (!__any_sync(0xffffffffu, active)) continue;
-                float v_x = 0.f, v_y = 0.f, v_cxx = 0.f, v_cxy = 0.f, v_cyy = 0.f, v_r = 0.f, v_g = 0.f, v_b = 0.f,
-                      v_a = 0.f;
-                if (active) {
-                    const float4 c = s.col[t];
-                    const float vis = ex2_approx(sp);
-                    const float av = c.w * vis;
-                    const float alpha = fminf(0.99f, av);  // 0.99 here, 0.999 forward (reference quirk)
-                    const float ra = __frcp_rn(1.0f - alpha);
-                    T *= ra;
-                    const float fac = alpha * T;
-                    float v_alpha = (c.x * T - br * ra) * v_out.x + (c.y * T - bg * ra) * v_out.y +
-                                    (c.z * T - bb * ra) * v_out.z;
-                    v_alpha += T_final * ra * v_out.w;
-                    br = fmaf(c.x, fac, br); bg = fmaf(c.y, fac, bg); bb = fmaf(c.z, fac, bb);
-                    const float v_sigma = -av * v_alpha;
-                    const float vs2 = -LN2 * v_sigma;  // conic = -ln2 * (2A, B, 2C)
-                    v_x = vs2 * fmaf(2.0f * g0.z, dx, g0.w * dy);
-                    v_y = vs2 * fmaf(g0.w, dx, 2.0f * g1.x * dy);
-                    v_cxx = 0.5f * v_sigma * dx * dx;
-                    v_cxy = v_sigma * dx * dy;
-                    v_cyy = 0.5f * v_sigma * dy * dy;
-                    v_r = fac * v_out.x; v_g = fac * v_out.y; v_b = fac * v_out.z;
-                    v_a = vis * v_alpha;
-                }
-                const float x = warp_reduce9(v_x, v_y, v_cxx, v_cxy, v_cyy, v_r, v_g, v_b, v_a, lane);
-                float* dst = v_projected + (size_t)s_id[t] * 9;
-                if ((lane & 3u) == 0u) atomicAdd(dst + (lane >> 2), x);
-                else if (lane == 2u) atomicAdd(dst + 8, x);
+            const uint32_t mask = __ballot_sync(0xffffffffu, hit);
+            if (hit) s.list[warp][n_list + __popc(mask & ((1u << lane) - 1u))] = (uint16_t)(mine * 16u);
+            n_list += __popc(mask);
+        }
+        __syncwarp();
+        const char* sbase = reinterpret_cast<const char*>(&s.g0[0]);
+        const uint16_t* list = s.list[warp];
+        for (uint32_t i = 0; i < n_list; i++) {
+            const uint32_t off = list[i];
+            const uint32_t t = off >> 4;
+            const uint32_t isect = batch_end - 1u - t;
+            const float4 g0 = *reinterpret_cast<const float4*>(sbase + off);
+            const float4 g1 = *reinterpret_cast<const float4*>(sbase + sizeof(float4) * TILE_SIZE + off);
+            const float dx = g0.x - pcx, dy = g0.y - pcy;
+            const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);
+            const float q = sp + g1.y;
+            // the same predicate, on the same instruction sequence, as the forward
+            const bool active = inside && isect <= final_isect && sp <= 0.0f && q >= LOG2_INV255;
+            if (!__any_sync(0xffffffffu, active)) continue;
+            float v_x = 0.f, v_y = 0.f, v_cxx = 0.f, v_cxy = 0.f, v_cyy = 0.f, v_r = 0.f, v_g = 0.f, v_b = 0.f,
+                  v_a = 0.f;
+            if (active) {
+                const float4 c = *reinterpret_cast<const float4*>(sbase + 2 * sizeof(float4) * TILE_SIZE + off);
+                const float vis = ex2_approx(sp);
+                const float av = g1.z * vis;
+                const float alpha = fminf(0.99f, av);  // 0.99 here, 0.999 forward (reference quirk)
+                const float ra = __frcp_rn(1.0f - alpha);
+                T *= ra;
+                const float fac = alpha * T;
+                float v_alpha = (c.x * T - br * ra) * v_out.x + (c.y * T - bg * ra) * v_out.y +
+                                (c.z * T - bb * ra) * v_out.z;
+                v_alpha += T_final * ra * v_out.w;
+                br = fmaf(c.x, fac, br); bg = fmaf(c.y, fac, bg); bb = fmaf(c.z, fac, bb);
+                const float v_sigma = -av * v_alpha;
+                const float vs2 = -LN2 * v_sigma;  // conic = -ln2 * (2A, B, 2C)
+                v_x = vs2 * fmaf(2.0f * g0.z, dx, g0.w * dy);
+                v_y = vs2 * fmaf(g0.w, dx, 2.0f * g1.x * dy);
+                v_cxx = 0.5f * v_sigma * dx * dx;
+                v_cxy = v_sigma * dx * dy;
+                v_cyy = 0.5f * v_sigma * dy * dy;
+                v_r = fac * v_out.x; v_g = fac * v_out.y; v_b = fac * v_out.z;
+                v_a = vis * v_alpha;
             }
+            const float x = warp_reduce9(v_x, v_y, v_cxx, v_cxy, v_cyy, v_r, v_g, v_b, v_a, lane);
+            float* dst = v_projected + (size_t)s_id[t] * 9;
+            if ((lane & 3u) == 0u) atomicAdd(dst + (lane >> 2), x);
+            else if (lane == 2u) atomicAdd(dst + 8, x);
         }
     }
 }
