@@ -50,13 +50,14 @@ void launch_tile_bins(const uint32_t* sorted_tile_ids, const uint64_t* sorted_ke
 //    splats at a time against its 8x4 block (one lane per splat), ballots, and only walks the survivors
 //    (about half of the tile's list at 1M splats / 1080p), in depth order;
 //  * whole-warp and whole-tile early exit once every pixel's transmittance is spent.
-struct SplatSmem {
-    float4 g0[TILE_SIZE];    // x, y, A, B
-    float4 g1[TILE_SIZE];    // C, L, opacity, -      (g1 sits exactly 4096 bytes after g0: one offset serves both)
-    float4 col[TILE_SIZE];   // r, g, b, -
-    float4 bbox[TILE_SIZE];  // xmin, xmax, ymin, ymax of the alpha >= 1/255 ellipse (pixel coordinates)
-    uint16_t list[TILE_SIZE / 32][TILE_SIZE];  // per warp: byte offsets (slot * 16) of the splats that survive culling
-};
+// Shared-memory layout of one CTA (byte offsets from the CTA's shared window; accessed with explicit
+// ld.shared so the inner loops carry one 32-bit address register and no generic->shared conversions).
+constexpr uint32_t SM_G0 = 0;                       // float4[256]: x, y, A, B
+constexpr uint32_t SM_G1 = SM_G0 + 16 * TILE_SIZE;  // float4[256]: C, L, opacity, compact gid (bits)
+constexpr uint32_t SM_COL = SM_G1 + 16 * TILE_SIZE; // float4[256]: r, g, b, -
+constexpr uint32_t SM_BBOX = SM_COL + 16 * TILE_SIZE; // float4[256]: xmin, xmax, ymin, ymax of the alpha>=1/255 ellipse
+constexpr uint32_t SM_LIST = SM_BBOX + 16 * TILE_SIZE; // u16[8][256]: per warp, byte offsets (slot*16) of survivors
+constexpr uint32_t SM_BYTES = SM_LIST + 2 * TILE_SIZE * (TILE_SIZE / 32);
 
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
@@ -67,23 +68,67 @@ __device__ __forceinline__ float ex2_approx(float x) {
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+__device__ __forceinline__ float rcp_approx(float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float4 lds128(uint32_t a) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds_u16(uint32_t a) {
+    uint32_t v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts128(uint32_t a, float4 v) {
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void sts_u16(uint32_t a, uint32_t v) {
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
 
-__device__ __forceinline__ void stage_splat(SplatSmem& s, uint32_t slot, const float* __restrict__ projected,
+// Put one splat of the tile's list into shared memory in "log2 form" (see the kernel comment).
+__device__ __forceinline__ void stage_splat(uint32_t sbase, uint32_t slot, const float* __restrict__ projected,
                                             uint32_t cg) {
     const float* p = projected + (size_t)cg * 9;
     const float x = __ldg(p), y = __ldg(p + 1), cxx = __ldg(p + 2), cxy = __ldg(p + 3), cyy = __ldg(p + 4);
     const float opac = __ldg(p + 8);
-    s.g0[slot] = make_float4(x, y, -0.5f * LOG2E * cxx, -LOG2E * cxy);
-    s.g1[slot] = make_float4(-0.5f * LOG2E * cyy, __log2f(opac), opac, 0.f);
-    s.col[slot] = make_float4(__ldg(p + 5), __ldg(p + 6), __ldg(p + 7), 0.f);
+    sts128(sbase + SM_G0 + slot * 16, make_float4(x, y, -0.5f * LOG2E * cxx, -LOG2E * cxy));
+    sts128(sbase + SM_G1 + slot * 16, make_float4(-0.5f * LOG2E * cyy, __log2f(opac), opac, __uint_as_float(cg)));
+    sts128(sbase + SM_COL + slot * 16, make_float4(__ldg(p + 5), __ldg(p + 6), __ldg(p + 7), 0.f));
     // sigma(d) <= t = ln(255 opac)  =>  |dx| <= sqrt(2 t cyy / det), |dy| <= sqrt(2 t cxx / det); slightly inflated
     // so that rounding can only keep a splat, never drop one.
     const float t = __logf(255.0f * opac) + 1e-3f;
     const float det = cxx * cyy - cxy * cxy;
-    float ex = sqrtf(2.0f * t * cyy / det) * 1.001f + 1e-2f;
-    float ey = sqrtf(2.0f * t * cxx / det) * 1.001f + 1e-2f;
+    const float k = 2.0f * t * rcp_approx(det);
+    float ex = sqrtf(k * cyy) * 1.001f + 1e-2f;
+    float ey = sqrtf(k * cxx) * 1.001f + 1e-2f;
     if (!(det > 0.0f) || !(ex < 1e30f) || !(ey < 1e30f)) ex = ey = 1e30f;  // degenerate: never cull
-    s.bbox[slot] = make_float4(x - ex, x + ex, y - ey, y + ey);
+    sts128(sbase + SM_BBOX + slot * 16, make_float4(x - ex, x + ex, y - ey, y + ey));
+}
+
+// Cull pass of one warp over the staged batch: one lane per splat against the warp's pixel block; the byte
+// offsets of the survivors are appended, in depth order, to the warp's list.  Returns the list length.
+// Only slots in [t_lo, t_max) take part.
+__device__ __forceinline__ uint32_t cull_to_list(uint32_t sbase, uint32_t list_addr, uint32_t lane, uint32_t t_lo,
+                                                 uint32_t t_max, float rx0, float rx1, float ry0, float ry1) {
+    uint32_t n_list = 0;
+    for (uint32_t c0 = t_lo & ~31u; c0 < t_max; c0 += 32) {
+        const uint32_t mine = c0 + lane;
+        bool hit = false;
+        if (mine >= t_lo && mine < t_max) {
+            const float4 bb = lds128(sbase + SM_BBOX + mine * 16);
+            hit = bb.x <= rx1 && bb.y >= rx0 && bb.z <= ry1 && bb.w >= ry0;
+        }
+        const uint32_t mask = __ballot_sync(0xffffffffu, hit);
+        if (hit) sts_u16(list_addr + 2u * (n_list + __popc(mask & ((1u << lane) - 1u))), mine * 16u);
+        n_list += __popc(mask);
+    }
+    __syncwarp();
+    return n_list;
 }
 
 template <bool RASTER_U32>
@@ -91,8 +136,10 @@ __global__ void __launch_bounds__(TILE_SIZE)
 rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ compact_gid_from_isect,
                  const uint32_t* __restrict__ tile_bins, const float* __restrict__ projected,
                  void* __restrict__ out_img, uint32_t* __restrict__ final_index) {
-    __shared__ SplatSmem s;
+    __shared__ __align__(16) unsigned char smem[SM_BYTES];
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(smem);
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const uint32_t list_addr = sbase + SM_LIST + warp * (2u * TILE_SIZE);
     const uint32_t tile_id = blockIdx.x + blockIdx.y * cam.tiles_x;
     const uint32_t bx0 = blockIdx.x * TILE_WIDTH + (warp & 1u) * 8u, by0 = blockIdx.y * TILE_WIDTH + (warp >> 1) * 4u;
     const uint32_t px = bx0 + (lane & 7u), py = by0 + (lane >> 3);
@@ -114,46 +161,34 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
         if (__syncthreads_and(done)) break;
         const uint32_t batch_start = range.x + b * TILE_SIZE;
         const uint32_t remaining = min(TILE_SIZE, range.y - batch_start);
-        if (tid < remaining) stage_splat(s, tid, projected, __ldg(compact_gid_from_isect + batch_start + tid));
+        if (tid < remaining) stage_splat(sbase, tid, projected, __ldg(compact_gid_from_isect + batch_start + tid));
         __syncthreads();
         if (__all_sync(0xffffffffu, done)) continue;
-        // cull: one lane per splat against this warp's 8x4 block; survivors go to the warp's list in depth order
-        uint32_t n_list = 0;
-        for (uint32_t c0 = 0; c0 < remaining; c0 += 32) {
-            const uint32_t mine = c0 + lane;
-            bool hit = false;
-            if (mine < remaining) {
-                const float4 bb = s.bbox[mine];
-                hit = bb.x <= rx1 && bb.y >= rx0 && bb.z <= ry1 && bb.w >= ry0;
-            }
-            const uint32_t mask = __ballot_sync(0xffffffffu, hit);
-            if (hit) s.list[warp][n_list + __popc(mask & ((1u << lane) - 1u))] = (uint16_t)(mine * 16u);
-            n_list += __popc(mask);
-        }
-        __syncwarp();
-        const char* sbase = reinterpret_cast<const char*>(&s.g0[0]);
-        const uint16_t* list = s.list[warp];
-        for (uint32_t i = 0; i < n_list; i++) {
-            const uint32_t off = list[i];
-            const float4 g0 = *reinterpret_cast<const float4*>(sbase + off);
-            const float4 g1 = *reinterpret_cast<const float4*>(sbase + sizeof(float4) * TILE_SIZE + off);
-            const float dx = g0.x - pcx, dy = g0.y - pcy;
-            const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);  // -sigma * log2(e)
-            const float q = sp + g1.y;                                              // log2(opac * exp(-sigma))
-            if (!done && sp <= 0.0f && q >= LOG2_INV255) {
-                const float alpha = fminf(0.999f, ex2_approx(q));
-                const float next_T = T * (1.0f - alpha);
-                if (next_T <= 1e-4f) {
-                    done = true;
-                } else {
-                    const float fac = alpha * T;
-                    const float4 c = *reinterpret_cast<const float4*>(sbase + 2 * sizeof(float4) * TILE_SIZE + off);
-                    pr = fmaf(c.x, fac, pr); pg = fmaf(c.y, fac, pg); pb = fmaf(c.z, fac, pb);
-                    T = next_T;
-                    final_idx = batch_start + (off >> 4);
+        const uint32_t n_list = cull_to_list(sbase, list_addr, lane, 0u, remaining, rx0, rx1, ry0, ry1);
+        for (uint32_t i0 = 0; i0 < n_list; i0 += 32) {
+            const uint32_t i1 = min(i0 + 32u, n_list);
+            for (uint32_t i = i0; i < i1; i++) {
+                const uint32_t a = sbase + lds_u16(list_addr + 2u * i);
+                const float4 g0 = lds128(a + SM_G0);
+                const float4 g1 = lds128(a + SM_G1);
+                const float dx = g0.x - pcx, dy = g0.y - pcy;
+                const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);  // -sigma * log2(e)
+                const float q = sp + g1.y;                                              // log2(opac * exp(-sigma))
+                if (!done && sp <= 0.0f && q >= LOG2_INV255) {
+                    const float alpha = fminf(0.999f, ex2_approx(q));
+                    const float next_T = T * (1.0f - alpha);
+                    if (next_T <= 1e-4f) {
+                        done = true;
+                    } else {
+                        const float fac = alpha * T;
+                        const float4 c = lds128(a + SM_COL);
+                        pr = fmaf(c.x, fac, pr); pg = fmaf(c.y, fac, pg); pb = fmaf(c.z, fac, pb);
+                        T = next_T;
+                        final_idx = batch_start + ((a - sbase) >> 4);
+                    }
                 }
             }
-            if ((i & 31u) == 31u && __all_sync(0xffffffffu, done)) break;
+            if (__all_sync(0xffffffffu, done)) break;
         }
     }
     if (inside) {
@@ -218,9 +253,10 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
                           const uint32_t* __restrict__ tile_bins, const float* __restrict__ projected,
                           const uint32_t* __restrict__ final_index, const float* __restrict__ out_img,
                           const float* __restrict__ v_out_img, float* __restrict__ v_projected) {
-    __shared__ SplatSmem s;
-    __shared__ uint32_t s_id[TILE_SIZE];
+    __shared__ __align__(16) unsigned char smem[SM_BYTES];
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(smem);
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const uint32_t list_addr = sbase + SM_LIST + warp * (2u * TILE_SIZE);
     const uint32_t tile_id = blockIdx.x;
     const uint32_t tile_x = tile_id % cam.tiles_x, tile_y = tile_id / cam.tiles_x;
     const uint32_t bx0 = tile_x * TILE_WIDTH + (warp & 1u) * 8u, by0 = tile_y * TILE_WIDTH + (warp >> 1) * 4u;
@@ -246,74 +282,61 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
     // Splats behind every pixel's last contributor are skipped warp-wide.
     const uint32_t warp_final = __reduce_max_sync(0xffffffffu, inside ? final_isect : 0u);
     const bool warp_any_inside = __any_sync(0xffffffffu, inside);
+    // after the butterfly, lane 4j holds gradient term j (j < 8) and lane 2 holds term 8
+    const bool red_lane = (lane & 3u) == 0u || lane == 2u;
+    const uint32_t red_term = (lane & 3u) == 0u ? (lane >> 2) : 8u;
 
     const uint32_t num_batches = (range.y - range.x + TILE_SIZE - 1) / TILE_SIZE;
     for (uint32_t b = 0; b < num_batches; b++) {
         __syncthreads();
-        const uint32_t batch_end = range.y - b * TILE_SIZE;
+        const uint32_t batch_end = range.y - b * TILE_SIZE;  // slot t of this batch <-> isect batch_end-1-t
         const uint32_t remaining = min(TILE_SIZE, batch_end - range.x);
-        if (tid < remaining) {
-            const uint32_t cg = __ldg(compact_gid_from_isect + batch_end - 1u - tid);
-            s_id[tid] = cg;
-            stage_splat(s, tid, projected, cg);
-        }
+        if (tid < remaining) stage_splat(sbase, tid, projected, __ldg(compact_gid_from_isect + batch_end - 1u - tid));
         __syncthreads();
-        if (!warp_any_inside) continue;
-        uint32_t n_list = 0;
-        for (uint32_t c0 = 0; c0 < remaining; c0 += 32) {
-            const uint32_t mine = c0 + lane;
-            bool hit = false;
-            if (mine < remaining && batch_end - 1u - mine <= warp_final) {
-                const float4 bbx = s.bbox[mine];
-                hit = bbx.x <= rx1 && bbx.y >= rx0 && bbx.z <= ry1 && bbx.w >= ry0;
-            }
-            const uint32_t mask = __ballot_sync(0xffffffffu, hit);
-            if (hit) s.list[warp][n_list + __popc(mask & ((1u << lane) - 1u))] = (uint16_t)(mine * 16u);
-            n_list += __popc(mask);
-        }
-        __syncwarp();
-        const char* sbase = reinterpret_cast<const char*>(&s.g0[0]);
-        const uint16_t* list = s.list[warp];
+        if (!warp_any_inside || batch_end - remaining > warp_final) continue;
+        // isect <= final  <=>  t >= batch_end-1-final; as byte offsets (slot*16) so the loop compares directly
+        const uint32_t t_lo_warp = batch_end - 1u > warp_final ? batch_end - 1u - warp_final : 0u;
+        const uint32_t off_lo = !inside ? 0xffffffffu
+                                        : (batch_end - 1u > final_isect ? (batch_end - 1u - final_isect) * 16u : 0u);
+        const uint32_t n_list = cull_to_list(sbase, list_addr, lane, t_lo_warp, remaining, rx0, rx1, ry0, ry1);
         for (uint32_t i = 0; i < n_list; i++) {
-            const uint32_t off = list[i];
-            const uint32_t t = off >> 4;
-            const uint32_t isect = batch_end - 1u - t;
-            const float4 g0 = *reinterpret_cast<const float4*>(sbase + off);
-            const float4 g1 = *reinterpret_cast<const float4*>(sbase + sizeof(float4) * TILE_SIZE + off);
+            const uint32_t off = lds_u16(list_addr + 2u * i);
+            const uint32_t a = sbase + off;
+            const float4 g0 = lds128(a + SM_G0);
+            const float4 g1 = lds128(a + SM_G1);
             const float dx = g0.x - pcx, dy = g0.y - pcy;
             const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);
             const float q = sp + g1.y;
             // the same predicate, on the same instruction sequence, as the forward
-            const bool active = inside && isect <= final_isect && sp <= 0.0f && q >= LOG2_INV255;
+            const bool active = off >= off_lo && sp <= 0.0f && q >= LOG2_INV255;
             if (!__any_sync(0xffffffffu, active)) continue;
             float v_x = 0.f, v_y = 0.f, v_cxx = 0.f, v_cxy = 0.f, v_cyy = 0.f, v_r = 0.f, v_g = 0.f, v_b = 0.f,
                   v_a = 0.f;
             if (active) {
-                const float4 c = *reinterpret_cast<const float4*>(sbase + 2 * sizeof(float4) * TILE_SIZE + off);
+                const float4 c = lds128(a + SM_COL);
                 const float vis = ex2_approx(sp);
                 const float av = g1.z * vis;
                 const float alpha = fminf(0.99f, av);  // 0.99 here, 0.999 forward (reference quirk)
-                const float ra = __frcp_rn(1.0f - alpha);
+                const float ra = rcp_approx(1.0f - alpha);
                 T *= ra;
                 const float fac = alpha * T;
                 float v_alpha = (c.x * T - br * ra) * v_out.x + (c.y * T - bg * ra) * v_out.y +
                                 (c.z * T - bb * ra) * v_out.z;
-                v_alpha += T_final * ra * v_out.w;
+                v_alpha = fmaf(T_final * ra, v_out.w, v_alpha);
                 br = fmaf(c.x, fac, br); bg = fmaf(c.y, fac, bg); bb = fmaf(c.z, fac, bb);
                 const float v_sigma = -av * v_alpha;
                 const float vs2 = -LN2 * v_sigma;  // conic = -ln2 * (2A, B, 2C)
                 v_x = vs2 * fmaf(2.0f * g0.z, dx, g0.w * dy);
                 v_y = vs2 * fmaf(g0.w, dx, 2.0f * g1.x * dy);
-                v_cxx = 0.5f * v_sigma * dx * dx;
+                const float hs = 0.5f * v_sigma;
+                v_cxx = hs * dx * dx;
                 v_cxy = v_sigma * dx * dy;
-                v_cyy = 0.5f * v_sigma * dy * dy;
+                v_cyy = hs * dy * dy;
                 v_r = fac * v_out.x; v_g = fac * v_out.y; v_b = fac * v_out.z;
                 v_a = vis * v_alpha;
             }
             const float x = warp_reduce9(v_x, v_y, v_cxx, v_cxy, v_cyy, v_r, v_g, v_b, v_a, lane);
-            float* dst = v_projected + (size_t)s_id[t] * 9;
-            if ((lane & 3u) == 0u) atomicAdd(dst + (lane >> 2), x);
-            else if (lane == 2u) atomicAdd(dst + 8, x);
+            if (red_lane) atomicAdd(v_projected + (size_t)__float_as_uint(g1.w) * 9 + red_term, x);
         }
     }
 }
