@@ -19,6 +19,7 @@ from typing import List, Optional
 import torch
 
 from . import _lib
+from .parallel import FlatGradLayout, allreduce_flat, global_grad_scale
 from .render import Camera, RenderAux, Splats, _stream_ptr, get_context, make_uniforms, render_backward, render_forward
 
 
@@ -79,13 +80,10 @@ class SplatTrainer:
     def _alloc(self, n: int, k: int):
         f = dict(dtype=torch.float32, device=self.device)
         self.n, self.k = n, k
-        sizes = [3 * n, 2 * n, 3 * n, 4 * n, 3 * k * n, n, n, n]
-        self.flat_grad = torch.zeros(sum(sizes), **f)
-        views = torch.split(self.flat_grad, sizes)
-        self.g_means, self.g_xy, self.g_scales, self.g_quats = (views[0].view(n, 3), views[1].view(n, 2),
-                                                                views[2].view(n, 3), views[3].view(n, 4))
-        self.g_sh, self.g_opac = views[4].view(n, k, 3), views[5]
-        self.stat_grad_norm, self.stat_visible = views[6], views[7]
+        self.layout = FlatGradLayout(n, k)
+        self.flat_grad = self.layout.alloc(self.device)
+        (self.g_means, self.g_xy, self.g_scales, self.g_quats, self.g_sh, self.g_opac, self.stat_grad_norm,
+         self.stat_visible) = self.layout.views(self.flat_grad)
         self.tmp = None  # second gradient set, only for batches of more than one view per rank
         self.grad_2d_accum = torch.zeros(n, **f)   # train.rs:195-196
         self.xy_grad_counts = torch.zeros(n, **f)
@@ -155,9 +153,9 @@ class SplatTrainer:
                 preds.append(pred)
                 auxes.append(aux)
             if self.pg is not None and world > 1:
-                torch.distributed.all_reduce(self.flat_grad, group=self.pg)  # NCCL over NVLink
-                torch.distributed.all_reduce(self.loss_total, group=self.pg)
-            grad_scale = 1.0 / (B * world)  # the loss is a mean over the global batch (train.rs:255)
+                allreduce_flat(self.flat_grad, self.pg)  # ONE NCCL all-reduce over NVLink
+                allreduce_flat(self.loss_total, self.pg)
+            grad_scale = global_grad_scale(B, world)
             # VJP of the rotation normalisation (Burn autodiff in the reference), linear so it commutes with the sum
             ctx.check(L.brush_quat_normalize_vjp(ctx.handle, p_rot.data_ptr(), self.n, self.g_quats.data_ptr(), st))
             if self.iter > cfg.warmup_steps:  # train.rs:286-316
