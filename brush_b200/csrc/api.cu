@@ -355,11 +355,11 @@ int brush_render_backward(brush_ctx* ctx, uint32_t N, uint32_t K, const float* m
     if (u.total_splats != N || u.sh_degree != degree_of(K))
         return fail(ctx, BRUSH_E_INVALID, "aux.uniforms_buffer does not match N / K");
     const Cam cam = make_cam(u);
-    ENSURE(v_projected, (size_t)N * 9 * 4 + 16);
+    ENSURE(v_projected, (size_t)N * VP_STRIDE * 4 + 16);
     ctx->ev_used[BRUSH_STAGE_RASTERIZE_BWD] = ctx->ev_used[BRUSH_STAGE_GATHER_PROJECT_BWD] = false;
     if (N) {
         // zero-init is a contract of the reference too (render.rs:505-507,539-540,547,573-575)
-        CU(cudaMemsetAsync(ctx->v_projected.p, 0, (size_t)N * 9 * 4, st));
+        CU(cudaMemsetAsync(ctx->v_projected.p, 0, (size_t)N * VP_STRIDE * 4, st));
         CU(cudaMemsetAsync(v_means, 0, (size_t)N * 3 * 4, st));
         CU(cudaMemsetAsync(v_xy, 0, (size_t)N * 2 * 4, st));
         CU(cudaMemsetAsync(v_log_scales, 0, (size_t)N * 3 * 4, st));

@@ -2,7 +2,7 @@
 //   == crates/brush-render/src/shaders/gather_grads.wgsl:165-232       (SH VJP, opacity VJP, xy scatter)
 //   == crates/brush-render/src/shaders/project_backwards.wgsl:75-227   (conic/cov2d/J/W/R/S VJP chain)
 // The reference runs these as two kernels over three intermediate buffers; fusing them reads the
-// rasterizer's nine accumulated sums (v_projected[c, 0..9)) once and writes each dense gradient once.
+// rasterizer's nine accumulated sums (v_projected[c][0..9), row stride VP_STRIDE) once and writes each dense gradient once.
 #include "internal.h"
 
 namespace brush {
@@ -48,11 +48,12 @@ gather_project_backward_kernel(const __grid_constant__ Cam cam, const float* __r
     const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= (uint32_t)*num_visible_dev) return;
     const uint32_t g = global_from_compact[c];
-    const float* vp = v_projected + (size_t)c * 9;
-    const V2 v_xy = {vp[0], vp[1]};
-    const V3 v_conic = {vp[2], vp[3], vp[4]};
-    const V3 v_rgb = {vp[5], vp[6], vp[7]};
-    const float v_alpha = vp[8];
+    const float4* vp = reinterpret_cast<const float4*>(v_projected + (size_t)c * VP_STRIDE);
+    const float4 vp0 = vp[0], vp1 = vp[1];
+    const V2 v_xy = {vp0.x, vp0.y};
+    const V3 v_conic = {vp0.z, vp0.w, vp1.x};
+    const V3 v_rgb = {vp1.y, vp1.z, vp1.w};
+    const float v_alpha = reinterpret_cast<const float*>(vp)[8];
 
     const V3 mean = {__ldg(means + 3 * (size_t)g), __ldg(means + 3 * (size_t)g + 1), __ldg(means + 3 * (size_t)g + 2)};
     const V3 scale = {__expf(__ldg(log_scales + 3 * (size_t)g)), __expf(__ldg(log_scales + 3 * (size_t)g + 1)),

@@ -12,6 +12,9 @@ namespace brush {
 
 // Word offsets inside the device copy of RenderUniforms (i32[28]).
 constexpr int UNI_NUM_VISIBLE_WORD = 25;  // render.rs:145-149
+// Row stride (floats) of the rasterize_backwards accumulator v_projected[N][VP_STRIDE]:
+// (v_x, v_y, v_cxx, v_cxy | v_cyy, v_r, v_g, v_b | v_a, -, -, -); 48-byte rows keep red.global.add.v4.f32 aligned.
+constexpr uint32_t VP_STRIDE = 12;
 
 // Device control block, zeroed by one memset at the start of every forward.
 struct Control {
@@ -68,7 +71,7 @@ void launch_rasterize(const Cam& cam, const uint32_t* compact_gid_from_isect, co
                       cudaStream_t st);
 void launch_rasterize_backward(const Cam& cam, const uint32_t* compact_gid_from_isect, const uint32_t* tile_bins,
                                const float* projected, const uint32_t* final_index, const float* out_img,
-                               const float* v_out_img, float* v_projected /* [N,9] zeroed */, cudaStream_t st);
+                               const float* v_out_img, float* v_projected /* [N,VP_STRIDE] zeroed */, cudaStream_t st);
 
 // ---- backward.cu ----
 void launch_gather_project_backward(const Cam& cam, uint32_t N, uint32_t K, const float* means,

@@ -52,12 +52,15 @@ void launch_tile_bins(const uint32_t* sorted_tile_ids, const uint64_t* sorted_ke
 //  * whole-warp and whole-tile early exit once every pixel's transmittance is spent.
 // Shared-memory layout of one CTA (byte offsets from the CTA's shared window; accessed with explicit
 // ld.shared so the inner loops carry one 32-bit address register and no generic->shared conversions).
-constexpr uint32_t SM_G0 = 0;                       // float4[256]: x, y, A, B
-constexpr uint32_t SM_G1 = SM_G0 + 16 * TILE_SIZE;  // float4[256]: C, L, opacity, compact gid (bits)
-constexpr uint32_t SM_COL = SM_G1 + 16 * TILE_SIZE; // float4[256]: r, g, b, -
-constexpr uint32_t SM_BBOX = SM_COL + 16 * TILE_SIZE; // float4[256]: xmin, xmax, ymin, ymax of the alpha>=1/255 ellipse
-constexpr uint32_t SM_LIST = SM_BBOX + 16 * TILE_SIZE; // u16[8][256]: per warp, byte offsets (slot*16) of survivors
-constexpr uint32_t SM_BYTES = SM_LIST + 2 * TILE_SIZE * (TILE_SIZE / 32);
+constexpr uint32_t SM_SLOTS = TILE_SIZE + 1;          // slot 256 is a dummy splat that no pixel ever sees (list padding)
+constexpr uint32_t SM_G0 = 0;                         // float4[257]: x, y, A, B
+constexpr uint32_t SM_G1 = SM_G0 + 16 * SM_SLOTS;     // float4[257]: C, L, opacity, compact gid (bits)
+constexpr uint32_t SM_COL = SM_G1 + 16 * SM_SLOTS;    // float4[257]: r, g, b, -
+constexpr uint32_t SM_BBOX = SM_COL + 16 * SM_SLOTS;  // float4[256]: xmin, xmax, ymin, ymax of the alpha>=1/255 ellipse
+constexpr uint32_t SM_LIST = SM_BBOX + 16 * TILE_SIZE;  // u32[8][260]: per warp, shared-window addresses of the survivors' G0 entries
+constexpr uint32_t LIST_PAD = 4;                      // lists are padded with the dummy slot to a multiple of 4
+constexpr uint32_t LIST_STRIDE = 4 * (TILE_SIZE + LIST_PAD);
+constexpr uint32_t SM_BYTES = SM_LIST + LIST_STRIDE * (TILE_SIZE / 32);
 
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
@@ -78,16 +81,27 @@ __device__ __forceinline__ float4 lds128(uint32_t a) {
     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
     return v;
 }
-__device__ __forceinline__ uint32_t lds_u16(uint32_t a) {
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a) {
     uint32_t v;
-    asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a));
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ uint4 lds128u(uint32_t a) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
     return v;
 }
 __device__ __forceinline__ void sts128(uint32_t a, float4 v) {
     asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
-__device__ __forceinline__ void sts_u16(uint32_t a, uint32_t v) {
-    asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+__device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v) {
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+// The dummy slot: L = -inf, so q = -inf fails the visibility test for every pixel.
+__device__ __forceinline__ void init_dummy_slot(uint32_t sbase) {
+    sts128(sbase + SM_G0 + TILE_SIZE * 16, make_float4(0.f, 0.f, 0.f, 0.f));
+    sts128(sbase + SM_G1 + TILE_SIZE * 16, make_float4(0.f, __int_as_float(0xff800000), 0.f, 0.f));
+    sts128(sbase + SM_COL + TILE_SIZE * 16, make_float4(0.f, 0.f, 0.f, 0.f));
 }
 
 // Put one splat of the tile's list into shared memory in "log2 form" (see the kernel comment).
@@ -110,8 +124,9 @@ __device__ __forceinline__ void stage_splat(uint32_t sbase, uint32_t slot, const
     sts128(sbase + SM_BBOX + slot * 16, make_float4(x - ex, x + ex, y - ey, y + ey));
 }
 
-// Cull pass of one warp over the staged batch: one lane per splat against the warp's pixel block; the byte
-// offsets of the survivors are appended, in depth order, to the warp's list.  Returns the list length.
+// Cull pass of one warp over the staged batch: one lane per splat against the warp's pixel block; the
+// shared-window addresses of the survivors' G0 entries are appended, in depth order, to the warp's list, which
+// is then padded with the dummy slot to a multiple of LIST_PAD.  Returns the list length (without padding).
 // Only slots in [t_lo, t_max) take part.
 __device__ __forceinline__ uint32_t cull_to_list(uint32_t sbase, uint32_t list_addr, uint32_t lane, uint32_t t_lo,
                                                  uint32_t t_max, float rx0, float rx1, float ry0, float ry1) {
@@ -124,9 +139,10 @@ __device__ __forceinline__ uint32_t cull_to_list(uint32_t sbase, uint32_t list_a
             hit = bb.x <= rx1 && bb.y >= rx0 && bb.z <= ry1 && bb.w >= ry0;
         }
         const uint32_t mask = __ballot_sync(0xffffffffu, hit);
-        if (hit) sts_u16(list_addr + 2u * (n_list + __popc(mask & ((1u << lane) - 1u))), mine * 16u);
+        if (hit) sts_u32(list_addr + 4u * (n_list + __popc(mask & ((1u << lane) - 1u))), sbase + mine * 16u);
         n_list += __popc(mask);
     }
+    if (lane < LIST_PAD) sts_u32(list_addr + 4u * (n_list + lane), sbase + TILE_SIZE * 16u);
     __syncwarp();
     return n_list;
 }
@@ -139,7 +155,7 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
     __shared__ __align__(16) unsigned char smem[SM_BYTES];
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(smem);
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-    const uint32_t list_addr = sbase + SM_LIST + warp * (2u * TILE_SIZE);
+    const uint32_t list_addr = sbase + SM_LIST + warp * LIST_STRIDE;
     const uint32_t tile_id = blockIdx.x + blockIdx.y * cam.tiles_x;
     const uint32_t bx0 = blockIdx.x * TILE_WIDTH + (warp & 1u) * 8u, by0 = blockIdx.y * TILE_WIDTH + (warp >> 1) * 4u;
     const uint32_t px = bx0 + (lane & 7u), py = by0 + (lane >> 3);
@@ -168,7 +184,7 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
         for (uint32_t i0 = 0; i0 < n_list; i0 += 32) {
             const uint32_t i1 = min(i0 + 32u, n_list);
             for (uint32_t i = i0; i < i1; i++) {
-                const uint32_t a = sbase + lds_u16(list_addr + 2u * i);
+                const uint32_t a = lds_u32(list_addr + 4u * i);
                 const float4 g0 = lds128(a + SM_G0);
                 const float4 g1 = lds128(a + SM_G1);
                 const float dx = g0.x - pcx, dy = g0.y - pcy;
@@ -223,40 +239,95 @@ void launch_rasterize(const Cam& cam, const uint32_t* compact_gid_from_isect, co
 
 // ---------------------------------------------------------------------------------------------
 // Backward.  Per pixel, back to front (rasterize_backwards.wgsl:194-272), same warp-level culling as the
-// forward.  The nine per-splat gradient terms are summed over the warp with a butterfly that halves the
-// live values at each exchange (12 shuffles instead of 9*5), then added with one predicated
-// red.global.add.f32 -- the native replacement for the reference's CAS loops
-// (rasterize_backwards.wgsl:79-133).
-__device__ __forceinline__ float warp_reduce9(float v0, float v1, float v2, float v3, float v4, float v5, float v6,
-                                              float v7, float v8, uint32_t lane) {
-    const uint32_t F = 0xffffffffu;
-    const bool h16 = lane & 16u, h8 = lane & 8u, h4 = lane & 4u, h2 = lane & 2u;
-    float a0 = (h16 ? v4 : v0) + __shfl_xor_sync(F, h16 ? v0 : v4, 16);
-    float a1 = (h16 ? v5 : v1) + __shfl_xor_sync(F, h16 ? v1 : v5, 16);
-    float a2 = (h16 ? v6 : v2) + __shfl_xor_sync(F, h16 ? v2 : v6, 16);
-    float a3 = (h16 ? v7 : v3) + __shfl_xor_sync(F, h16 ? v3 : v7, 16);
-    float b0 = (h8 ? a2 : a0) + __shfl_xor_sync(F, h8 ? a0 : a2, 8);
-    float b1 = (h8 ? a3 : a1) + __shfl_xor_sync(F, h8 ? a1 : a3, 8);
-    float c = (h4 ? b1 : b0) + __shfl_xor_sync(F, h4 ? b0 : b1, 4);
-    float w = v8;
-    w += __shfl_xor_sync(F, w, 16);
-    w += __shfl_xor_sync(F, w, 8);
-    w += __shfl_xor_sync(F, w, 4);
-    float x = (h2 ? w : c) + __shfl_xor_sync(F, h2 ? c : w, 2);
-    x += __shfl_xor_sync(F, x, 1);
-    // lanes with (lane & 3) == 0 hold the total of value (lane >> 2); lanes with bit 1 set hold value 8
-    return x;
+// forward.  The reference sums each of the nine per-splat gradient terms over the subgroup for every
+// (subgroup, splat) step and adds them with a CAS loop (rasterize_backwards.wgsl:79-133,274-300).  A warp
+// butterfly per step makes this kernel issue-bound (ncu, profiles/r1a: ~107 of ~130 instructions per step
+// were reduction and gradient math on half-empty warps), so the work is split in two phases:
+//
+//  phase 1 (lane = pixel): walk the warp's survivor list in depth order; per (pixel, splat) pair keep only
+//      the two scalars that depend on the compositing order, va = vis * v_alpha and fac = alpha * T, in a
+//      per-warp shared-memory tile [32 splats][32 pixels]; splats with no active pixel take no row.
+//  phase 2 (lane = splat): each lane owns one row and accumulates, in registers and without any
+//      cross-lane traffic, the moments of va about its splat centre (1, dx, dy, dx^2, dx dy, dy^2) and
+//      fac * v_out.rgb over the 32 pixels; the nine gradient terms are linear in those sums
+//      (v_sigma = -opac * va).  Each lane then issues two red.global.add.v4.f32 and one scalar red for its
+//      own splat -- the native replacement for the reference's CAS loops.
+constexpr uint32_t BW_ROW = 32u * 8u + 16u;  // one row: 32 x (va, fac) + pad => conflict-free LDS.128 at lane stride
+constexpr uint32_t BW_GROUP = 4;             // survivors examined per phase-1 iteration (independent geometry => ILP)
+constexpr uint32_t BW_PAIR = SM_BYTES;       // per warp 32 rows
+constexpr uint32_t BW_PAIR_WARP = 32u * BW_ROW;
+constexpr uint32_t BW_PIX = BW_PAIR + (TILE_SIZE / 32u) * BW_PAIR_WARP;  // per warp float4[32]: v_out of its pixels
+constexpr uint32_t BW_CHUNK = BW_PIX + (TILE_SIZE / 32u) * 512u;         // per warp u32[32]: G0 address of each row's splat
+constexpr uint32_t BW_BYTES = BW_CHUNK + (TILE_SIZE / 32u) * 128u;
+
+__device__ __forceinline__ void sts64(uint32_t a, float x, float y) {
+    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(a), "f"(x), "f"(y) : "memory");
+}
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+    asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d)
+                 : "memory");
 }
 
-__global__ void __launch_bounds__(TILE_SIZE)
+// Phase 2 for the first k rows of the warp's pair tile.  (bx, by) = pixel-centre coordinates of the warp's
+// first pixel.
+__device__ __forceinline__ void flush_rows(uint32_t dummy_addr, uint32_t pair_addr, uint32_t pix_addr,
+                                           uint32_t chunk_addr, uint32_t lane, uint32_t k, float bx, float by,
+                                           float* __restrict__ v_projected) {
+    __syncwarp();
+    const bool valid = lane < k;
+    const uint32_t a = valid ? lds_u32(chunk_addr + 4u * lane) : dummy_addr;
+    const float4 g0 = lds128(a + SM_G0);  // x, y, A, B
+    const float4 g1 = lds128(a + SM_G1);  // C, L, opacity, compact gid
+    const uint32_t row = pair_addr + lane * BW_ROW;
+    float s0 = 0.f, sx = 0.f, sy = 0.f, sxx = 0.f, sxy = 0.f, syy = 0.f, r = 0.f, g = 0.f, b = 0.f;
+#pragma unroll
+    for (int py = 0; py < 4; py++) {
+        const float dy = g0.y - (by + (float)py);
+#pragma unroll
+        for (int kx = 0; kx < 8; kx += 2) {
+            const int p = py * 8 + kx;
+            const float4 e = lds128(row + p * 8);  // va, fac of pixels p and p+1
+            const float4 o0 = lds128(pix_addr + p * 16), o1 = lds128(pix_addr + p * 16 + 16);
+            {
+                const float dx = g0.x - (bx + (float)kx);
+                const float t1 = e.x * dx, t2 = e.x * dy;
+                s0 += e.x; sx += t1; sy += t2;
+                sxx = fmaf(t1, dx, sxx); sxy = fmaf(t1, dy, sxy); syy = fmaf(t2, dy, syy);
+                r = fmaf(e.y, o0.x, r); g = fmaf(e.y, o0.y, g); b = fmaf(e.y, o0.z, b);
+            }
+            {
+                const float dx = g0.x - (bx + (float)(kx + 1));
+                const float t1 = e.z * dx, t2 = e.z * dy;
+                s0 += e.z; sx += t1; sy += t2;
+                sxx = fmaf(t1, dx, sxx); sxy = fmaf(t1, dy, sxy); syy = fmaf(t2, dy, syy);
+                r = fmaf(e.w, o1.x, r); g = fmaf(e.w, o1.y, g); b = fmaf(e.w, o1.z, b);
+            }
+        }
+    }
+    if (valid) {
+        // v_sigma = -opac*va; conic = -ln2 * (2A, B, 2C) in log2 form
+        const float opac = g1.z, w = LN2 * opac;
+        float* dst = v_projected + (size_t)__float_as_uint(g1.w) * VP_STRIDE;
+        red_add_v4(dst, w * fmaf(2.0f * g0.z, sx, g0.w * sy), w * fmaf(g0.w, sx, 2.0f * g1.x * sy),
+                   -0.5f * opac * sxx, -opac * sxy);
+        red_add_v4(dst + 4, -0.5f * opac * syy, r, g, b);
+        atomicAdd(dst + 8, s0);
+    }
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(TILE_SIZE, 2)
 rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ compact_gid_from_isect,
                           const uint32_t* __restrict__ tile_bins, const float* __restrict__ projected,
                           const uint32_t* __restrict__ final_index, const float* __restrict__ out_img,
                           const float* __restrict__ v_out_img, float* __restrict__ v_projected) {
-    __shared__ __align__(16) unsigned char smem[SM_BYTES];
+    extern __shared__ __align__(16) unsigned char smem[];
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(smem);
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-    const uint32_t list_addr = sbase + SM_LIST + warp * (2u * TILE_SIZE);
+    const uint32_t list_addr = sbase + SM_LIST + warp * LIST_STRIDE;
+    const uint32_t pair_addr = sbase + BW_PAIR + warp * BW_PAIR_WARP;
+    const uint32_t pix_addr = sbase + BW_PIX + warp * 512u;
+    const uint32_t chunk_addr = sbase + BW_CHUNK + warp * 128u;
     const uint32_t tile_id = blockIdx.x;
     const uint32_t tile_x = tile_id % cam.tiles_x, tile_y = tile_id / cam.tiles_x;
     const uint32_t bx0 = tile_x * TILE_WIDTH + (warp & 1u) * 8u, by0 = tile_y * TILE_WIDTH + (warp >> 1) * 4u;
@@ -267,6 +338,7 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
 
     const uint2 range = __ldg(reinterpret_cast<const uint2*>(tile_bins) + tile_id);
     if (range.y <= range.x) return;
+    if (tid == 0) init_dummy_slot(sbase);
 
     float T_final = 1.0f;
     float4 v_out = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -277,14 +349,15 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
         final_isect = __ldg(final_index + pix_id);
         v_out = __ldg(reinterpret_cast<const float4*>(v_out_img) + pix_id);
     }
+    sts128(pix_addr + lane * 16u, v_out);
+    // Running state of the pixel (rasterize_backwards.wgsl:194-272 keeps T and the colour `buffer` behind the
+    // current splat): v_alpha = ra * (dot(c, v_rgb) * T_before - dot(buffer, v_rgb) + T_final * v_a), so only
+    // D = T_final * v_a - dot(buffer, v_rgb) is carried, not the three buffer channels.
     float T = T_final;
-    float br = 0.f, bg = 0.f, bb = 0.f;
+    float D = T_final * v_out.w;
     // Splats behind every pixel's last contributor are skipped warp-wide.
     const uint32_t warp_final = __reduce_max_sync(0xffffffffu, inside ? final_isect : 0u);
     const bool warp_any_inside = __any_sync(0xffffffffu, inside);
-    // after the butterfly, lane 4j holds gradient term j (j < 8) and lane 2 holds term 8
-    const bool red_lane = (lane & 3u) == 0u || lane == 2u;
-    const uint32_t red_term = (lane & 3u) == 0u ? (lane >> 2) : 8u;
 
     const uint32_t num_batches = (range.y - range.x + TILE_SIZE - 1) / TILE_SIZE;
     for (uint32_t b = 0; b < num_batches; b++) {
@@ -294,49 +367,52 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
         if (tid < remaining) stage_splat(sbase, tid, projected, __ldg(compact_gid_from_isect + batch_end - 1u - tid));
         __syncthreads();
         if (!warp_any_inside || batch_end - remaining > warp_final) continue;
-        // isect <= final  <=>  t >= batch_end-1-final; as byte offsets (slot*16) so the loop compares directly
+        // isect <= final  <=>  slot >= batch_end-1-final; compared as shared-window addresses of the G0 entries
         const uint32_t t_lo_warp = batch_end - 1u > warp_final ? batch_end - 1u - warp_final : 0u;
-        const uint32_t off_lo = !inside ? 0xffffffffu
-                                        : (batch_end - 1u > final_isect ? (batch_end - 1u - final_isect) * 16u : 0u);
+        const uint32_t a_lo = !inside ? 0xffffffffu
+                                      : sbase + (batch_end - 1u > final_isect ? (batch_end - 1u - final_isect) * 16u : 0u);
         const uint32_t n_list = cull_to_list(sbase, list_addr, lane, t_lo_warp, remaining, rx0, rx1, ry0, ry1);
-        for (uint32_t i = 0; i < n_list; i++) {
-            const uint32_t off = lds_u16(list_addr + 2u * i);
-            const uint32_t a = sbase + off;
-            const float4 g0 = lds128(a + SM_G0);
-            const float4 g1 = lds128(a + SM_G1);
-            const float dx = g0.x - pcx, dy = g0.y - pcy;
-            const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);
-            const float q = sp + g1.y;
-            // the same predicate, on the same instruction sequence, as the forward
-            const bool active = off >= off_lo && sp <= 0.0f && q >= LOG2_INV255;
-            if (!__any_sync(0xffffffffu, active)) continue;
-            float v_x = 0.f, v_y = 0.f, v_cxx = 0.f, v_cxy = 0.f, v_cyy = 0.f, v_r = 0.f, v_g = 0.f, v_b = 0.f,
-                  v_a = 0.f;
-            if (active) {
-                const float4 c = lds128(a + SM_COL);
-                const float vis = ex2_approx(sp);
-                const float av = g1.z * vis;
-                const float alpha = fminf(0.99f, av);  // 0.99 here, 0.999 forward (reference quirk)
-                const float ra = rcp_approx(1.0f - alpha);
-                T *= ra;
-                const float fac = alpha * T;
-                float v_alpha = (c.x * T - br * ra) * v_out.x + (c.y * T - bg * ra) * v_out.y +
-                                (c.z * T - bb * ra) * v_out.z;
-                v_alpha = fmaf(T_final * ra, v_out.w, v_alpha);
-                br = fmaf(c.x, fac, br); bg = fmaf(c.y, fac, bg); bb = fmaf(c.z, fac, bb);
-                const float v_sigma = -av * v_alpha;
-                const float vs2 = -LN2 * v_sigma;  // conic = -ln2 * (2A, B, 2C)
-                v_x = vs2 * fmaf(2.0f * g0.z, dx, g0.w * dy);
-                v_y = vs2 * fmaf(g0.w, dx, 2.0f * g1.x * dy);
-                const float hs = 0.5f * v_sigma;
-                v_cxx = hs * dx * dx;
-                v_cxy = v_sigma * dx * dy;
-                v_cyy = hs * dy * dy;
-                v_r = fac * v_out.x; v_g = fac * v_out.y; v_b = fac * v_out.z;
-                v_a = vis * v_alpha;
+        uint32_t k = 0;  // rows of the pair tile in use (warp-uniform); flushed before the batch buffer is reused
+        for (uint32_t i = 0;; i += BW_GROUP) {
+            const bool end = i >= n_list;
+            if (k > 32u - BW_GROUP || (end && k != 0u)) {
+                flush_rows(sbase + TILE_SIZE * 16u, pair_addr, pix_addr, chunk_addr, lane, k, rx0, ry0, v_projected);
+                k = 0;
             }
-            const float x = warp_reduce9(v_x, v_y, v_cxx, v_cxy, v_cyy, v_r, v_g, v_b, v_a, lane);
-            if (red_lane) atomicAdd(v_projected + (size_t)__float_as_uint(g1.w) * 9 + red_term, x);
+            if (end) break;
+            const uint4 a4 = lds128u(list_addr + 4u * i);
+            const uint32_t aa[BW_GROUP] = {a4.x, a4.y, a4.z, a4.w};
+            bool act[BW_GROUP];
+            float alpha[BW_GROUP], ra[BW_GROUP], visra[BW_GROUP];
+            // geometry of the four splats: independent of the running state, so the four chains overlap
+#pragma unroll
+            for (int j = 0; j < (int)BW_GROUP; j++) {
+                const float4 g0 = lds128(aa[j] + SM_G0);
+                const float4 g1 = lds128(aa[j] + SM_G1);
+                const float dx = g0.x - pcx, dy = g0.y - pcy;
+                const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);
+                const float q = sp + g1.y;
+                // the same predicate, on the same instruction sequence, as the forward
+                act[j] = aa[j] >= a_lo && sp <= 0.0f && q >= LOG2_INV255;
+                const float vis = act[j] ? ex2_approx(sp) : 0.0f;  // inactive: alpha = 0, ra = 1, everything below is a no-op
+                alpha[j] = fminf(0.99f, g1.z * vis);               // 0.99 here, 0.999 forward (reference quirk)
+                ra[j] = rcp_approx(1.0f - alpha[j]);
+                visra[j] = vis * ra[j];
+            }
+#pragma unroll
+            for (int j = 0; j < (int)BW_GROUP; j++) {
+                if (__any_sync(0xffffffffu, act[j])) {
+                    const float4 c = lds128(aa[j] + SM_COL);
+                    const float u = fmaf(c.z, v_out.z, fmaf(c.y, v_out.y, c.x * v_out.x));
+                    const float va = visra[j] * fmaf(u, T, D);  // vis * v_alpha
+                    T *= ra[j];
+                    const float fac = alpha[j] * T;
+                    D = fmaf(-fac, u, D);
+                    sts64(pair_addr + k * BW_ROW + lane * 8u, va, fac);
+                    sts_u32(chunk_addr + 4u * k, aa[j]);
+                    k++;
+                }
+            }
         }
     }
 }
@@ -346,9 +422,16 @@ void launch_rasterize_backward(const Cam& cam, const uint32_t* compact_gid_from_
                                const float* v_out_img, float* v_projected, cudaStream_t st) {
     const uint32_t tiles = cam.tiles_x * cam.tiles_y;
     if (tiles == 0) return;
+    static uint64_t configured_devices = 0;  // the opt-in to > 48 KB of shared memory is per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!(configured_devices >> dev & 1ull)) {
+        cudaFuncSetAttribute(rasterize_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BW_BYTES);
+        configured_devices |= 1ull << dev;
+    }
     g_launch_count++;
-    rasterize_backward_kernel<<<tiles, TILE_SIZE, 0, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
-                                                           final_index, out_img, v_out_img, v_projected);
+    rasterize_backward_kernel<<<tiles, TILE_SIZE, BW_BYTES, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
+                                                                 final_index, out_img, v_out_img, v_projected);
 }
 
 }  // namespace brush
