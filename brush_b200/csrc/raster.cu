@@ -253,12 +253,13 @@ void launch_rasterize(const Cam& cam, const uint32_t* compact_gid_from_isect, co
 //      (v_sigma = -opac * va).  Each lane then issues two red.global.add.v4.f32 and one scalar red for its
 //      own splat -- the native replacement for the reference's CAS loops.
 constexpr uint32_t BW_ROW = 32u * 8u + 16u;  // one row: 32 x (va, fac) + pad => conflict-free LDS.128 at lane stride
+constexpr uint32_t BW_ROWS = 16;             // rows per warp; phase 2 gives each row to two lanes (16 pixels each)
 constexpr uint32_t BW_GROUP = 4;             // survivors examined per phase-1 iteration (independent geometry => ILP)
-constexpr uint32_t BW_PAIR = SM_BYTES;       // per warp 32 rows
-constexpr uint32_t BW_PAIR_WARP = 32u * BW_ROW;
+constexpr uint32_t BW_PAIR = SM_BYTES;
+constexpr uint32_t BW_PAIR_WARP = BW_ROWS * BW_ROW;
 constexpr uint32_t BW_PIX = BW_PAIR + (TILE_SIZE / 32u) * BW_PAIR_WARP;  // per warp float4[32]: v_out of its pixels
-constexpr uint32_t BW_CHUNK = BW_PIX + (TILE_SIZE / 32u) * 512u;         // per warp u32[32]: G0 address of each row's splat
-constexpr uint32_t BW_BYTES = BW_CHUNK + (TILE_SIZE / 32u) * 128u;
+constexpr uint32_t BW_CHUNK = BW_PIX + (TILE_SIZE / 32u) * 512u;         // per warp u32[BW_ROWS]: G0 address of each row's splat
+constexpr uint32_t BW_BYTES = BW_CHUNK + (TILE_SIZE / 32u) * 4u * BW_ROWS;
 
 __device__ __forceinline__ void sts64(uint32_t a, float x, float y) {
     asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(a), "f"(x), "f"(y) : "memory");
@@ -268,26 +269,30 @@ __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, 
                  : "memory");
 }
 
-// Phase 2 for the first k rows of the warp's pair tile.  (bx, by) = pixel-centre coordinates of the warp's
-// first pixel.
+// Phase 2 for the first k (<= 16) rows of the warp's pair tile: lane l and lane l+16 share row l, the low lane
+// sums pixel rows 0-1 of the 8x4 block, the high lane rows 2-3; one xor-16 exchange completes the nine sums.
+// (bx, by) = pixel-centre coordinates of the warp's first pixel.
 __device__ __forceinline__ void flush_rows(uint32_t dummy_addr, uint32_t pair_addr, uint32_t pix_addr,
                                            uint32_t chunk_addr, uint32_t lane, uint32_t k, float bx, float by,
                                            float* __restrict__ v_projected) {
     __syncwarp();
-    const bool valid = lane < k;
-    const uint32_t a = valid ? lds_u32(chunk_addr + 4u * lane) : dummy_addr;
+    const uint32_t r_idx = lane & 15u, half = lane >> 4;
+    const bool valid = r_idx < k;
+    const uint32_t a = valid ? lds_u32(chunk_addr + 4u * r_idx) : dummy_addr;
     const float4 g0 = lds128(a + SM_G0);  // x, y, A, B
     const float4 g1 = lds128(a + SM_G1);  // C, L, opacity, compact gid
-    const uint32_t row = pair_addr + lane * BW_ROW;
+    const uint32_t row = pair_addr + r_idx * BW_ROW + half * 128u;
+    const uint32_t pix = pix_addr + half * 256u;
+    const float by_h = by + (float)(2u * half);
     float s0 = 0.f, sx = 0.f, sy = 0.f, sxx = 0.f, sxy = 0.f, syy = 0.f, r = 0.f, g = 0.f, b = 0.f;
 #pragma unroll
-    for (int py = 0; py < 4; py++) {
-        const float dy = g0.y - (by + (float)py);
+    for (int py = 0; py < 2; py++) {
+        const float dy = g0.y - (by_h + (float)py);
 #pragma unroll
         for (int kx = 0; kx < 8; kx += 2) {
             const int p = py * 8 + kx;
             const float4 e = lds128(row + p * 8);  // va, fac of pixels p and p+1
-            const float4 o0 = lds128(pix_addr + p * 16), o1 = lds128(pix_addr + p * 16 + 16);
+            const float4 o0 = lds128(pix + p * 16), o1 = lds128(pix + p * 16 + 16);
             {
                 const float dx = g0.x - (bx + (float)kx);
                 const float t1 = e.x * dx, t2 = e.x * dy;
@@ -304,19 +309,26 @@ __device__ __forceinline__ void flush_rows(uint32_t dummy_addr, uint32_t pair_ad
             }
         }
     }
+    const uint32_t F = 0xffffffffu;
+    s0 += __shfl_xor_sync(F, s0, 16); sx += __shfl_xor_sync(F, sx, 16); sy += __shfl_xor_sync(F, sy, 16);
+    sxx += __shfl_xor_sync(F, sxx, 16); sxy += __shfl_xor_sync(F, sxy, 16); syy += __shfl_xor_sync(F, syy, 16);
+    r += __shfl_xor_sync(F, r, 16); g += __shfl_xor_sync(F, g, 16); b += __shfl_xor_sync(F, b, 16);
     if (valid) {
         // v_sigma = -opac*va; conic = -ln2 * (2A, B, 2C) in log2 form
         const float opac = g1.z, w = LN2 * opac;
         float* dst = v_projected + (size_t)__float_as_uint(g1.w) * VP_STRIDE;
-        red_add_v4(dst, w * fmaf(2.0f * g0.z, sx, g0.w * sy), w * fmaf(g0.w, sx, 2.0f * g1.x * sy),
-                   -0.5f * opac * sxx, -opac * sxy);
-        red_add_v4(dst + 4, -0.5f * opac * syy, r, g, b);
-        atomicAdd(dst + 8, s0);
+        if (half == 0) {
+            red_add_v4(dst, w * fmaf(2.0f * g0.z, sx, g0.w * sy), w * fmaf(g0.w, sx, 2.0f * g1.x * sy),
+                       -0.5f * opac * sxx, -opac * sxy);
+        } else {
+            red_add_v4(dst + 4, -0.5f * opac * syy, r, g, b);
+            atomicAdd(dst + 8, s0);
+        }
     }
     __syncwarp();
 }
 
-__global__ void __launch_bounds__(TILE_SIZE, 2)
+__global__ void __launch_bounds__(TILE_SIZE, 3)
 rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ compact_gid_from_isect,
                           const uint32_t* __restrict__ tile_bins, const float* __restrict__ projected,
                           const uint32_t* __restrict__ final_index, const float* __restrict__ out_img,
@@ -327,7 +339,7 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
     const uint32_t list_addr = sbase + SM_LIST + warp * LIST_STRIDE;
     const uint32_t pair_addr = sbase + BW_PAIR + warp * BW_PAIR_WARP;
     const uint32_t pix_addr = sbase + BW_PIX + warp * 512u;
-    const uint32_t chunk_addr = sbase + BW_CHUNK + warp * 128u;
+    const uint32_t chunk_addr = sbase + BW_CHUNK + warp * (4u * BW_ROWS);
     const uint32_t tile_id = blockIdx.x;
     const uint32_t tile_x = tile_id % cam.tiles_x, tile_y = tile_id / cam.tiles_x;
     const uint32_t bx0 = tile_x * TILE_WIDTH + (warp & 1u) * 8u, by0 = tile_y * TILE_WIDTH + (warp >> 1) * 4u;
@@ -375,7 +387,7 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
         uint32_t k = 0;  // rows of the pair tile in use (warp-uniform); flushed before the batch buffer is reused
         for (uint32_t i = 0;; i += BW_GROUP) {
             const bool end = i >= n_list;
-            if (k > 32u - BW_GROUP || (end && k != 0u)) {
+            if (k > BW_ROWS - BW_GROUP || (end && k != 0u)) {
                 flush_rows(sbase + TILE_SIZE * 16u, pair_addr, pix_addr, chunk_addr, lane, k, rx0, ry0, v_projected);
                 k = 0;
             }
