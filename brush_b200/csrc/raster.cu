@@ -124,6 +124,35 @@ __device__ __forceinline__ void stage_splat(uint32_t sbase, uint32_t slot, const
     sts128(sbase + SM_BBOX + slot * 16, make_float4(x - ex, x + ex, y - ey, y + ey));
 }
 
+// Exact second stage of the cull: does the splat's alpha >= 1/255 region reach the (continuous) rectangle spanned
+// by the warp's pixel centres?  In log2 form the pair test is sp(d) >= log2(1/255) - L with sp a concave
+// quadratic in d = centre - pixel, so the question is whether max sp over the rectangle clears that bound: yes if
+// the centre is inside, else the maximum lies on one of the four edges, where sp is a 1-D parabola.  The bound
+// carries a slack well above the rounding error of sp, so this can only keep a splat the per-pixel test then
+// rejects, never drop one it would accept.
+__device__ __forceinline__ bool ellipse_reaches_block(uint32_t a, float rx0, float rx1, float ry0, float ry1) {
+    const float4 g0 = lds128(a + SM_G0);  // x, y, A, B
+    const float4 g1 = lds128(a + SM_G1);  // C, L, ...
+    const float A = g0.z, B = g0.w, C = g1.x;
+    const float dx0 = g0.x - rx1, dx1 = g0.x - rx0, dy0 = g0.y - ry1, dy1 = g0.y - ry0;  // d ranges over [d0, d1]
+    if (dx0 <= 0.0f && dx1 >= 0.0f && dy0 <= 0.0f && dy1 >= 0.0f) return true;
+    const float h1 = -B * rcp_approx(2.0f * C), h2 = -B * rcp_approx(2.0f * A);
+    float smax;
+    {
+        const float ya = fminf(fmaxf(h1 * dx0, dy0), dy1), yb = fminf(fmaxf(h1 * dx1, dy0), dy1);
+        const float xa = fminf(fmaxf(h2 * dy0, dx0), dx1), xb = fminf(fmaxf(h2 * dy1, dx0), dx1);
+        const float s0 = fmaf(C * ya, ya, fmaf(B, ya, A * dx0) * dx0);
+        const float s1 = fmaf(C * yb, yb, fmaf(B, yb, A * dx1) * dx1);
+        const float s2 = fmaf(C * dy0, dy0, fmaf(B, dy0, A * xa) * xa);
+        const float s3 = fmaf(C * dy1, dy1, fmaf(B, dy1, A * xb) * xb);
+        smax = fmaxf(fmaxf(s0, s1), fmaxf(s2, s3));
+    }
+    const float dxm = fmaxf(fabsf(dx0), fabsf(dx1)), dym = fmaxf(fabsf(dy0), fabsf(dy1));
+    const float mag = fabsf(A) * dxm * dxm + fabsf(C) * dym * dym + fabsf(B) * dxm * dym;
+    const float bound = (LOG2_INV255 - g1.y) - (0.01f + 1e-5f * mag);
+    return !(smax < bound);  // NaN (degenerate conic) keeps the splat
+}
+
 // Cull pass of one warp over the staged batch: one lane per splat against the warp's pixel block; the
 // shared-window addresses of the survivors' G0 entries are appended, in depth order, to the warp's list, which
 // is then padded with the dummy slot to a multiple of LIST_PAD.  Returns the list length (without padding).
@@ -137,6 +166,7 @@ __device__ __forceinline__ uint32_t cull_to_list(uint32_t sbase, uint32_t list_a
         if (mine >= t_lo && mine < t_max) {
             const float4 bb = lds128(sbase + SM_BBOX + mine * 16);
             hit = bb.x <= rx1 && bb.y >= rx0 && bb.z <= ry1 && bb.w >= ry0;
+            if (hit) hit = ellipse_reaches_block(sbase + mine * 16u, rx0, rx1, ry0, ry1);
         }
         const uint32_t mask = __ballot_sync(0xffffffffu, hit);
         if (hit) sts_u32(list_addr + 4u * (n_list + __popc(mask & ((1u << lane) - 1u))), sbase + mine * 16u);
@@ -170,6 +200,7 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
     float T = 1.0f;
     float pr = 0.f, pg = 0.f, pb = 0.f;
     uint32_t final_idx = 0;
+    if (tid == 0) init_dummy_slot(sbase);
 
     for (uint32_t b = 0; b < num_batches; b++) {
         // barrier before the batch buffer is overwritten + whole-tile early exit (the reference keeps
@@ -181,31 +212,43 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
         __syncthreads();
         if (__all_sync(0xffffffffu, done)) continue;
         const uint32_t n_list = cull_to_list(sbase, list_addr, lane, 0u, remaining, rx0, rx1, ry0, ry1);
-        for (uint32_t i0 = 0; i0 < n_list; i0 += 32) {
-            const uint32_t i1 = min(i0 + 32u, n_list);
-            for (uint32_t i = i0; i < i1; i++) {
-                const uint32_t a = lds_u32(list_addr + 4u * i);
-                const float4 g0 = lds128(a + SM_G0);
-                const float4 g1 = lds128(a + SM_G1);
+        // Four survivors per iteration: their geometry (sp, q, alpha) is independent of the compositing state, so
+        // the four chains overlap; the order-dependent part is then applied in depth order, predicated (no
+        // divergent branch).  The list is padded with the dummy slot, which no pixel sees.
+        uint32_t final_a = 0;
+        for (uint32_t i = 0; i < n_list; i += LIST_PAD) {
+            const uint4 a4 = lds128u(list_addr + 4u * i);
+            const uint32_t aa[4] = {a4.x, a4.y, a4.z, a4.w};
+            bool act[4];
+            float alpha[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const float4 g0 = lds128(aa[j] + SM_G0);
+                const float4 g1 = lds128(aa[j] + SM_G1);
                 const float dx = g0.x - pcx, dy = g0.y - pcy;
                 const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);  // -sigma * log2(e)
                 const float q = sp + g1.y;                                              // log2(opac * exp(-sigma))
-                if (!done && sp <= 0.0f && q >= LOG2_INV255) {
-                    const float alpha = fminf(0.999f, ex2_approx(q));
-                    const float next_T = T * (1.0f - alpha);
-                    if (next_T <= 1e-4f) {
-                        done = true;
-                    } else {
-                        const float fac = alpha * T;
-                        const float4 c = lds128(a + SM_COL);
-                        pr = fmaf(c.x, fac, pr); pg = fmaf(c.y, fac, pg); pb = fmaf(c.z, fac, pb);
-                        T = next_T;
-                        final_idx = batch_start + ((a - sbase) >> 4);
-                    }
+                act[j] = sp <= 0.0f && q >= LOG2_INV255;
+                alpha[j] = fminf(0.999f, ex2_approx(q));
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const bool live = act[j] && !done;
+                if (__any_sync(0xffffffffu, live)) {
+                    const float4 c = lds128(aa[j] + SM_COL);
+                    const float next_T = T * (1.0f - alpha[j]);
+                    const bool stop = live && next_T <= 1e-4f;  // rasterize.wgsl: stop BEFORE adding this splat
+                    const bool contrib = live && !stop;
+                    done = done || stop;
+                    const float fac = contrib ? alpha[j] * T : 0.0f;
+                    pr = fmaf(c.x, fac, pr); pg = fmaf(c.y, fac, pg); pb = fmaf(c.z, fac, pb);
+                    T = contrib ? next_T : T;
+                    final_a = contrib ? aa[j] : final_a;
                 }
             }
             if (__all_sync(0xffffffffu, done)) break;
         }
+        if (final_a) final_idx = batch_start + ((final_a - sbase) >> 4);
     }
     if (inside) {
         const size_t pix_id = (size_t)px + (size_t)py * cam.img_w;
