@@ -358,25 +358,20 @@ int brush_render_backward(brush_ctx* ctx, uint32_t N, uint32_t K, const float* m
     ENSURE(v_projected, (size_t)N * VP_STRIDE * 4 + 16);
     ctx->ev_used[BRUSH_STAGE_RASTERIZE_BWD] = ctx->ev_used[BRUSH_STAGE_GATHER_PROJECT_BWD] = false;
     if (N) {
-        // zero-init is a contract of the reference too (render.rs:505-507,539-540,547,573-575)
+        // The reference zero-fills nine accumulators and six outputs (render.rs:505-507,539-540,547,573-575).  Here
+        // only the rasterizer's accumulator is zeroed: the per-splat backward writes every row of every output,
+        // zeros included, in one coalesced pass.
         CU(cudaMemsetAsync(ctx->v_projected.p, 0, (size_t)N * VP_STRIDE * 4, st));
-        CU(cudaMemsetAsync(v_means, 0, (size_t)N * 3 * 4, st));
-        CU(cudaMemsetAsync(v_xy, 0, (size_t)N * 2 * 4, st));
-        CU(cudaMemsetAsync(v_log_scales, 0, (size_t)N * 3 * 4, st));
-        CU(cudaMemsetAsync(v_quats, 0, (size_t)N * 4 * 4, st));
-        CU(cudaMemsetAsync(v_sh_coeffs, 0, (size_t)N * K * 3 * 4, st));
-        CU(cudaMemsetAsync(v_raw_opacity, 0, (size_t)N * 4, st));
     }
     {   // render.rs:515-532
         StageTimer t(ctx, st, BRUSH_STAGE_RASTERIZE_BWD);
         launch_rasterize_backward(cam, (uint32_t*)aux->compact_gid_from_isect, (uint32_t*)aux->tile_bins,
-                                  aux->projected_splats, (uint32_t*)aux->final_index, out_img, v_out_img,
-                                  (float*)ctx->v_projected.p, st);
+                                  aux->projected_splats, (uint32_t*)aux->global_from_compact_gid,
+                                  (uint32_t*)aux->final_index, out_img, v_out_img, (float*)ctx->v_projected.p, st);
     }
     {   // render.rs:542-594
         StageTimer t(ctx, st, BRUSH_STAGE_GATHER_PROJECT_BWD);
         launch_gather_project_backward(cam, N, K, means, log_scales, quats, raw_opacity,
-                                       (uint32_t*)aux->global_from_compact_gid, aux->num_visible,
                                        (float*)ctx->v_projected.p, v_means, v_xy, v_log_scales, v_quats, v_sh_coeffs,
                                        v_raw_opacity, st);
     }

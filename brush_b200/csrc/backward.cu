@@ -1,8 +1,9 @@
-// Fused per-splat backward: gather_grads + project_backwards in one pass over the visible splats.
+// Fused per-splat backward: gather_grads + project_backwards in one coalesced pass over all splats.
 //   == crates/brush-render/src/shaders/gather_grads.wgsl:165-232       (SH VJP, opacity VJP, xy scatter)
 //   == crates/brush-render/src/shaders/project_backwards.wgsl:75-227   (conic/cov2d/J/W/R/S VJP chain)
 // The reference runs these as two kernels over three intermediate buffers; fusing them reads the
-// rasterizer's nine accumulated sums (v_projected[c][0..9), row stride VP_STRIDE) once and writes each dense gradient once.
+// rasterizer's nine accumulated sums (v_projected[g][0..9), rows by global splat id, stride VP_STRIDE) once and
+// writes every row of each dense gradient once, so the reference's zero-fill of the outputs disappears too.
 #include "internal.h"
 
 namespace brush {
@@ -40,20 +41,40 @@ template <int K>
 __global__ void __launch_bounds__(256)
 gather_project_backward_kernel(const __grid_constant__ Cam cam, const float* __restrict__ means,
                                const float* __restrict__ log_scales, const float* __restrict__ quats,
-                               const float* __restrict__ raw_opac, const uint32_t* __restrict__ global_from_compact,
-                               const int32_t* __restrict__ num_visible_dev, const float* __restrict__ v_projected,
+                               const float* __restrict__ raw_opac, const float* __restrict__ v_projected,
                                float* __restrict__ v_means, float* __restrict__ v_xy_out,
                                float* __restrict__ v_log_scales, float* __restrict__ v_quats,
                                float* __restrict__ v_coeffs, float* __restrict__ v_raw_opac) {
-    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= (uint32_t)*num_visible_dev) return;
-    const uint32_t g = global_from_compact[c];
-    const float4* vp = reinterpret_cast<const float4*>(v_projected + (size_t)c * VP_STRIDE);
+    // One thread per splat in GLOBAL id order: the rasterizer accumulated its nine sums into row g, so every
+    // read and write here is coalesced and every output row is written exactly once (dense gradients, zero
+    // for splats no pixel saw: render.rs:598-624), with no separate zero-fill pass.
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= cam.total_splats) return;
+    const float4* vp = reinterpret_cast<const float4*>(v_projected + (size_t)g * VP_STRIDE);
     const float4 vp0 = vp[0], vp1 = vp[1];
     const V2 v_xy = {vp0.x, vp0.y};
     const V3 v_conic = {vp0.z, vp0.w, vp1.x};
     const V3 v_rgb = {vp1.y, vp1.z, vp1.w};
     const float v_alpha = reinterpret_cast<const float*>(vp)[8];
+    float* out_sh = v_coeffs + (size_t)g * (3 * K);
+    // Every output is linear in the nine sums, so an all-zero row (culled splat, or no contributing pixel) gives
+    // exact zeros; skipping the chain also keeps 0 * inf out of the result for splats behind the camera.
+    if (vp0.x == 0.f && vp0.y == 0.f && vp0.z == 0.f && vp0.w == 0.f && vp1.x == 0.f && vp1.y == 0.f &&
+        vp1.z == 0.f && vp1.w == 0.f && v_alpha == 0.f) {
+        if ((3 * K) % 4 == 0) {
+#pragma unroll
+            for (int j = 0; j < (3 * K) / 4; j++) reinterpret_cast<float4*>(out_sh)[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 3 * K; j++) out_sh[j] = 0.f;
+        }
+        v_raw_opac[g] = 0.f;
+        reinterpret_cast<float2*>(v_xy_out)[g] = make_float2(0.f, 0.f);
+        v_means[3 * (size_t)g] = 0.f; v_means[3 * (size_t)g + 1] = 0.f; v_means[3 * (size_t)g + 2] = 0.f;
+        v_log_scales[3 * (size_t)g] = 0.f; v_log_scales[3 * (size_t)g + 1] = 0.f; v_log_scales[3 * (size_t)g + 2] = 0.f;
+        reinterpret_cast<float4*>(v_quats)[g] = make_float4(0.f, 0.f, 0.f, 0.f);
+        return;
+    }
 
     const V3 mean = {__ldg(means + 3 * (size_t)g), __ldg(means + 3 * (size_t)g + 1), __ldg(means + 3 * (size_t)g + 2)};
     const V3 scale = {__expf(__ldg(log_scales + 3 * (size_t)g)), __expf(__ldg(log_scales + 3 * (size_t)g + 1)),
@@ -68,7 +89,7 @@ gather_project_backward_kernel(const __grid_constant__ Cam cam, const float* __r
         V3 viewdir = d * inv;
         float b[K];
         sh_basis<K>(cam.sh_degree, viewdir, b);
-        float* out = v_coeffs + (size_t)g * (3 * K);
+        float* out = out_sh;
         if ((3 * K) % 4 == 0) {
             float o[3 * K];
 #pragma unroll
@@ -133,13 +154,12 @@ gather_project_backward_kernel(const __grid_constant__ Cam cam, const float* __r
 
 void launch_gather_project_backward(const Cam& cam, uint32_t N, uint32_t K, const float* means,
                                     const float* log_scales, const float* quats, const float* raw_opac,
-                                    const uint32_t* global_from_compact, const int32_t* num_visible_dev,
                                     const float* v_projected, float* v_means, float* v_xy, float* v_log_scales,
                                     float* v_quats, float* v_coeffs, float* v_raw_opac, cudaStream_t st) {
     if (N == 0) return;
     dim3 grid((N + 255) / 256), block(256);
     g_launch_count++;
-#define GB_ARGS cam, means, log_scales, quats, raw_opac, global_from_compact, num_visible_dev, v_projected, v_means, \
+#define GB_ARGS cam, means, log_scales, quats, raw_opac, v_projected, v_means, \
                 v_xy, v_log_scales, v_quats, v_coeffs, v_raw_opac
     switch (K) {
         case 1: gather_project_backward_kernel<1><<<grid, block, 0, st>>>(GB_ARGS); break;

@@ -70,13 +70,13 @@ void launch_rasterize(const Cam& cam, const uint32_t* compact_gid_from_isect, co
                       const float* projected, int raster_u32, void* out_img, uint32_t* final_index,
                       cudaStream_t st);
 void launch_rasterize_backward(const Cam& cam, const uint32_t* compact_gid_from_isect, const uint32_t* tile_bins,
-                               const float* projected, const uint32_t* final_index, const float* out_img,
-                               const float* v_out_img, float* v_projected /* [N,VP_STRIDE] zeroed */, cudaStream_t st);
+                               const float* projected, const uint32_t* global_from_compact,
+                               const uint32_t* final_index, const float* out_img, const float* v_out_img,
+                               float* v_projected /* [N,VP_STRIDE] by GLOBAL id, zeroed */, cudaStream_t st);
 
 // ---- backward.cu ----
 void launch_gather_project_backward(const Cam& cam, uint32_t N, uint32_t K, const float* means,
                                     const float* log_scales, const float* quats, const float* raw_opac,
-                                    const uint32_t* global_from_compact, const int32_t* num_visible_dev,
                                     const float* v_projected, float* v_means, float* v_xy, float* v_log_scales,
                                     float* v_quats, float* v_coeffs, float* v_raw_opac, cudaStream_t st);
 

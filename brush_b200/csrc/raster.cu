@@ -105,13 +105,14 @@ __device__ __forceinline__ void init_dummy_slot(uint32_t sbase) {
 }
 
 // Put one splat of the tile's list into shared memory in "log2 form" (see the kernel comment).
+// `tag` travels in G1.w: the backward uses it as the row of its gradient accumulator.
 __device__ __forceinline__ void stage_splat(uint32_t sbase, uint32_t slot, const float* __restrict__ projected,
-                                            uint32_t cg) {
+                                            uint32_t cg, uint32_t tag) {
     const float* p = projected + (size_t)cg * 9;
     const float x = __ldg(p), y = __ldg(p + 1), cxx = __ldg(p + 2), cxy = __ldg(p + 3), cyy = __ldg(p + 4);
     const float opac = __ldg(p + 8);
     sts128(sbase + SM_G0 + slot * 16, make_float4(x, y, -0.5f * LOG2E * cxx, -LOG2E * cxy));
-    sts128(sbase + SM_G1 + slot * 16, make_float4(-0.5f * LOG2E * cyy, __log2f(opac), opac, __uint_as_float(cg)));
+    sts128(sbase + SM_G1 + slot * 16, make_float4(-0.5f * LOG2E * cyy, __log2f(opac), opac, __uint_as_float(tag)));
     sts128(sbase + SM_COL + slot * 16, make_float4(__ldg(p + 5), __ldg(p + 6), __ldg(p + 7), 0.f));
     // sigma(d) <= t = ln(255 opac)  =>  |dx| <= sqrt(2 t cyy / det), |dy| <= sqrt(2 t cxx / det); slightly inflated
     // so that rounding can only keep a splat, never drop one.
@@ -208,7 +209,10 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
         if (__syncthreads_and(done)) break;
         const uint32_t batch_start = range.x + b * TILE_SIZE;
         const uint32_t remaining = min(TILE_SIZE, range.y - batch_start);
-        if (tid < remaining) stage_splat(sbase, tid, projected, __ldg(compact_gid_from_isect + batch_start + tid));
+        if (tid < remaining) {
+            const uint32_t cg = __ldg(compact_gid_from_isect + batch_start + tid);
+            stage_splat(sbase, tid, projected, cg, cg);
+        }
         __syncthreads();
         if (__all_sync(0xffffffffu, done)) continue;
         const uint32_t n_list = cull_to_list(sbase, list_addr, lane, 0u, remaining, rx0, rx1, ry0, ry1);
@@ -374,6 +378,7 @@ __device__ __forceinline__ void flush_rows(uint32_t dummy_addr, uint32_t pair_ad
 __global__ void __launch_bounds__(TILE_SIZE, 3)
 rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ compact_gid_from_isect,
                           const uint32_t* __restrict__ tile_bins, const float* __restrict__ projected,
+                          const uint32_t* __restrict__ global_from_compact,
                           const uint32_t* __restrict__ final_index, const float* __restrict__ out_img,
                           const float* __restrict__ v_out_img, float* __restrict__ v_projected) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -419,7 +424,10 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
         __syncthreads();
         const uint32_t batch_end = range.y - b * TILE_SIZE;  // slot t of this batch <-> isect batch_end-1-t
         const uint32_t remaining = min(TILE_SIZE, batch_end - range.x);
-        if (tid < remaining) stage_splat(sbase, tid, projected, __ldg(compact_gid_from_isect + batch_end - 1u - tid));
+        if (tid < remaining) {  // gradient rows are indexed by GLOBAL splat id, so the per-splat backward is coalesced
+            const uint32_t cg = __ldg(compact_gid_from_isect + batch_end - 1u - tid);
+            stage_splat(sbase, tid, projected, cg, __ldg(global_from_compact + cg));
+        }
         __syncthreads();
         if (!warp_any_inside || batch_end - remaining > warp_final) continue;
         // isect <= final  <=>  slot >= batch_end-1-final; compared as shared-window addresses of the G0 entries
@@ -473,7 +481,8 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
 }
 
 void launch_rasterize_backward(const Cam& cam, const uint32_t* compact_gid_from_isect, const uint32_t* tile_bins,
-                               const float* projected, const uint32_t* final_index, const float* out_img,
+                               const float* projected, const uint32_t* global_from_compact,
+                               const uint32_t* final_index, const float* out_img,
                                const float* v_out_img, float* v_projected, cudaStream_t st) {
     const uint32_t tiles = cam.tiles_x * cam.tiles_y;
     if (tiles == 0) return;
@@ -486,7 +495,7 @@ void launch_rasterize_backward(const Cam& cam, const uint32_t* compact_gid_from_
     }
     g_launch_count++;
     rasterize_backward_kernel<<<tiles, TILE_SIZE, BW_BYTES, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
-                                                                 final_index, out_img, v_out_img, v_projected);
+                                                                 global_from_compact, final_index, out_img, v_out_img, v_projected);
 }
 
 }  // namespace brush
