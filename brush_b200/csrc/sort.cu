@@ -16,6 +16,7 @@ constexpr int RS_THREADS = 256;
 constexpr int RS_WARPS = RS_THREADS / 32;
 constexpr int RS_RADIX = 256;
 constexpr int RS_MAX_PASSES = 8;
+constexpr int LB_WINDOW = 16;
 
 template <typename KeyT> struct SortCfg;
 template <> struct SortCfg<uint32_t> { static constexpr int ITEMS = 16; };
@@ -55,17 +56,28 @@ radix_hist_kernel(const KeyT* __restrict__ keys, const int32_t* __restrict__ n_d
     __syncthreads();
     const uint32_t lane = threadIdx.x & 31u;
     // warp-uniform loop bound so match_any always sees the whole warp
-    const uint32_t stride = gridDim.x * RS_THREADS;
-    for (uint32_t base = blockIdx.x * RS_THREADS; base < n; base += stride) {
-        const uint32_t i = base + threadIdx.x;
-        const bool valid = i < n;
-        const KeyT k = valid ? keys[i] : (KeyT)0;
-        for (uint32_t p = 0; p < plan.passes; p++) {
-            const uint32_t d = (uint32_t)(k >> plan.shift[p]) & plan.mask[p];
-            // warp-aggregated shared atomics: clustered keys (tile ids, depth exponents) would
-            // otherwise serialise 32-way on one bank.
-            const uint32_t peers = __match_any_sync(0xffffffffu, valid ? d : (RS_RADIX + lane));
-            if (valid && lane == (uint32_t)(31 - __clz(peers))) atomicAdd(&s_hist[p * RS_RADIX + d], __popc(peers));
+    // four independent key loads per thread per iteration (the loop is otherwise one L2/HBM round trip per key)
+    const uint32_t stride = gridDim.x * RS_THREADS * 4;
+    for (uint32_t base = blockIdx.x * RS_THREADS * 4; base < n; base += stride) {
+        KeyT k4[4];
+        bool valid4[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint32_t i = base + u * RS_THREADS + threadIdx.x;
+            valid4[u] = i < n;
+            k4[u] = valid4[u] ? keys[i] : (KeyT)0;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const bool valid = valid4[u];
+            const KeyT k = k4[u];
+            for (uint32_t p = 0; p < plan.passes; p++) {
+                const uint32_t d = (uint32_t)(k >> plan.shift[p]) & plan.mask[p];
+                // warp-aggregated shared atomics: clustered keys (tile ids, depth exponents) would
+                // otherwise serialise 32-way on one bank.
+                const uint32_t peers = __match_any_sync(0xffffffffu, valid ? d : (RS_RADIX + lane));
+                if (valid && lane == (uint32_t)(31 - __clz(peers))) atomicAdd(&s_hist[p * RS_RADIX + d], __popc(peers));
+            }
         }
     }
     __syncthreads();
@@ -162,23 +174,24 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ v
             vlb[me] = (2u << 30) | tile_count;
         } else {
             vlb[me] = (1u << 30) | tile_count;
-            // Walk back over the predecessors four at a time: the four status loads are independent, so a walk
-            // of d tiles costs about d/4 L2 round trips instead of d.
+            // Walk back over the predecessors LB_WINDOW at a time: the status loads of a window are independent,
+            // so a walk of d tiles costs about d/LB_WINDOW L2 round trips instead of d (when a whole pass fits in
+            // one wave of CTAs nothing is inclusive yet and every tile walks all the way back).
             int t = (int)tile - 1;
             bool found = false;
             while (!found) {
-                uint32_t w[4];
+                uint32_t w[LB_WINDOW];
 #pragma unroll
-                for (int u = 0; u < 4; u++) w[u] = t - u >= 0 ? vlb[(uint32_t)(t - u) * RS_RADIX + tid] : (2u << 30);
+                for (int u = 0; u < LB_WINDOW; u++) w[u] = t - u >= 0 ? vlb[(uint32_t)(t - u) * RS_RADIX + tid] : (2u << 30);
 #pragma unroll
-                for (int u = 0; u < 4; u++) {
+                for (int u = 0; u < LB_WINDOW; u++) {
                     if (found) break;
                     uint32_t sv = w[u];
                     while ((sv >> 30) == 0u) sv = vlb[(uint32_t)(t - u) * RS_RADIX + tid];
                     excl += sv & 0x3fffffffu;
                     found = (sv >> 30) == 2u;
                 }
-                t -= 4;
+                t -= LB_WINDOW;
             }
             vlb[me] = (2u << 30) | (excl + tile_count);
         }
@@ -249,8 +262,8 @@ static void radix_sort_impl(const KeyT* keys, const uint32_t* vals, const int32_
     cudaMemsetAsync(s.hist, 0, (size_t)plan.passes * RS_RADIX * 4, st);
     cudaMemsetAsync(s.lb, 0, (size_t)plan.passes * tiles * RS_RADIX * 4, st);
     cudaMemsetAsync(s.tickets, 0, RS_MAX_PASSES * 4, st);
-    uint32_t hist_blocks = (max_n + RS_THREADS - 1) / RS_THREADS;
-    if (hist_blocks > 148 * 2) hist_blocks = 148 * 2;  // every block ends with up to passes*256 global atomics
+    uint32_t hist_blocks = (max_n + RS_THREADS * 4 - 1) / (RS_THREADS * 4);
+    if (hist_blocks > 148 * 4) hist_blocks = 148 * 4;  // every block ends with up to passes*256 global atomics
     g_launch_count += 1 + plan.passes;
     radix_hist_kernel<KeyT><<<hist_blocks, RS_THREADS, 0, st>>>(keys, n_dev, max_n, plan, s.hist);
     const KeyT* src_k = keys;
