@@ -156,7 +156,15 @@ def run_ours(args):
     gt_dev = gt_host.to(dev)
     ctx = get_context(dev)
     trainer = SplatTrainer(N, TrainConfig(), dev, sh_coeffs_per_channel=K, process_group=pg,
-                           isect_capacity=args.capacity, optimize=not args.no_optim)
+                           isect_capacity=args.capacity, optimize=not args.no_optim, exchange=args.exchange)
+    splats = trainer.adopt(splats)  # peer exchange: parameters live in the peer-mapped replica
+    if world > 1 and trainer.exchange == "peer":
+        exchange_desc = ("gradient sum + Adam + parameter broadcast as ONE brush_dp_adam_step launch per rank over "
+                         f"NVLink peer memory ({'NVSwitch multimem.ld_reduce/st' if trainer.peer.grad_mc else 'peer loads/stores'})")
+    elif world > 1:
+        exchange_desc = "NCCL all-reduce of the flat dense gradient, replicated Adam"
+    else:
+        exchange_desc = "single GPU"
     loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
 
     def one_step(step_idx, host_inputs):
@@ -209,20 +217,20 @@ def run_ours(args):
     ctx.sync_check()
 
     # ---- per-stage device times (CUDA events around each stage, on the launching stream) ----
+    # Every rank runs these steps (the step holds a collective when world > 1); only rank 0's times are reported.
     stage_ms, counts = {}, None
+    ctx.set_timing(True)
+    acc = {}
+    reps = max(3, min(args.steps, 10))
+    for s in range(reps):
+        stats = one_step(1000 + s, False)
+        tm = ctx.stage_times_ms(torch.cuda.current_stream().cuda_stream)
+        for k_, v_ in tm.items():
+            acc[k_] = acc.get(k_, 0.0) + v_ / reps
+    ctx.set_timing(False)
+    stage_ms = acc
     if rank == 0:
-        ctx.set_timing(True)
-        acc = {}
-        reps = max(3, min(args.steps, 10))
-        for s in range(reps):
-            stats = one_step(1000 + s, False)
-            tm = ctx.stage_times_ms(torch.cuda.current_stream().cuda_stream)
-            for k_, v_ in tm.items():
-                acc[k_] = acc.get(k_, 0.0) + v_ / reps
-        ctx.set_timing(False)
-        stage_ms = acc
-        aux = stats.auxes[0]
-        counts = (aux.read_num_visible(), aux.read_num_intersections())
+        counts = (stats.auxes[0].read_num_visible(), stats.auxes[0].read_num_intersections())
     if world > 1:
         barrier()
 
@@ -238,24 +246,60 @@ def run_ours(args):
         stages.append({"stage": name, "ms": round(ms, 4), "alg_bytes": b,
                        "gbs": round(b / (ms * 1e-3) / 1e9, 1) if ms > 0 else None,
                        "frac_hbm": round(b / (ms * 1e-3) / 1e9 / peak, 4) if ms > 0 else None})
+    # ---- evaluated (pixel, splat) pairs of the two compositors, as the REFERENCE loops would count them
+    # (R_fwd, R_bwd), from the last step's aux tensors; outside every timed region ----
+    aux = stats.auxes[0]
+    fi = aux.final_index.to(torch.int64)
+    tb = aux.tile_bins.to(torch.int64)
+    ty = (torch.arange(H, device=dev) // 16)[:, None].expand(H, W)
+    tx = (torch.arange(W, device=dev) // 16)[None, :].expand(H, W)
+    start, end = tb[ty, tx, 0], tb[ty, tx, 1]
+    nonempty = end > start
+    r_bwd = int(torch.where(nonempty & (fi >= start), fi - start + 1, torch.zeros_like(fi)).sum().item())
+    opaque = stats.pred_images[0][..., 3] > 0.9998  # the pixel stopped early (T <= 1e-4): walked to final_index + 1
+    r_fwd = int(torch.where(nonempty, torch.where(opaque, torch.minimum(fi - start + 2, end - start), end - start),
+                            torch.zeros_like(fi)).sum().item())
+    fp32_peak = 148 * 128 * 2 * (clocks.get("sm_max_mhz") or 1965.0) * 1e6 / 1e12  # TFLOP/s, FMA = 2
+    flops = {"Rasterize": 26 * r_fwd, "RasterizeBackwards": 64 * r_bwd}  # SURVEY 8d per-pair figures
+    for s_ in stages:
+        if s_["stage"] in flops and s_["ms"] > 0:
+            s_["alg_flops"] = flops[s_["stage"]]
+            s_["tflops"] = round(flops[s_["stage"]] / (s_["ms"] * 1e-3) / 1e12, 2)
+            s_["frac_fp32"] = round(s_["tflops"] / fp32_peak, 4)
     dom = max(stages, key=lambda s_: s_["ms"])
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get(dom["stage"])
+    except OSError:
+        pass
+    if "tflops" in dom:
+        roofline = {"kernel": dom["stage"], "bound": "fp32", "achieved": dom["tflops"], "peak": round(fp32_peak, 1),
+                    "unit": "TFLOP/s", "frac": dom["frac_fp32"], "traffic": traffic,
+                    "peak_source": "148 SMs x 128 FP32 lanes x 2 x max SM clock (no tensor-core or HBM roofline applies: "
+                                   "the kernel is FP32-issue-bound, ncu in profiles/)",
+                    "pairs": r_bwd if dom["stage"] == "RasterizeBackwards" else r_fwd,
+                    "note": "achieved = 64 (bwd) / 26 (fwd) algorithmic flop per reference-evaluated (pixel, splat) "
+                            "pair / kernel time; pairs the kernel culls before evaluating them still count as work "
+                            "done. HBM view of the same kernel: "
+                            f"{dom['gbs']} GB/s of algorithmic bytes = {dom['frac_hbm']} of {peak} GB/s ({peak_src})"}
+    else:
+        roofline = {"kernel": dom["stage"], "bound": "hbm", "achieved": dom["gbs"], "peak": peak, "unit": "GB/s",
+                    "frac": dom["frac_hbm"], "traffic": traffic, "peak_source": peak_src}
     out = {
         "metric": METRIC, "value": round(world * 1000.0 / ms_step, 3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {N} random Gaussians, SH degree {sc.sh_degree}, {W}x{H}, one view per "
                                f"GPU per step, L1 loss, {'fused Adam' if not args.no_optim else 'no optimizer'}, "
-                               f"{'NCCL all-reduce of the flat dense gradient' if world > 1 else 'single GPU'}",
+                               f"{exchange_desc}",
                    "num_visible": V, "num_intersections": I, "views": N_VIEWS, "isect_capacity": args.capacity,
                    "l2": "inputs larger than L2 (236 MB of parameters + 244 MB of gradients per step vs 126 MB L2)"},
         "e2e": {"value": round(world * 1000.0 / ms_e2e_step, 3), "unit": UNIT, "ms_per_step": round(ms_e2e_step, 4),
                 "h2d_bytes_per_step": int(gt_host[0].numel() * 4 + 112), "d2h_bytes_per_step": 4},
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"kernel": dom["stage"], "bound": "hbm", "achieved": dom["gbs"], "peak": peak, "unit": "GB/s",
-                     "frac": dom["frac_hbm"], "traffic": None, "peak_source": peak_src,
-                     "note": "dominant kernel by time; it is FP32/MUFU/atomic-bound (SURVEY 8d), so the HBM fraction "
-                             "of its algorithmic bytes is a floor, not its ceiling; see stages[] and profiles/"},
+        "roofline": roofline,
         "stages": stages,
     }
     if not args.no_cpu_baseline and world == 1:
@@ -360,6 +404,8 @@ def main():
     ap.add_argument("--capacity", type=int, default=ISECT_CAPACITY)
     ap.add_argument("--no-optim", action="store_true", help="skip Adam (pure fwd+bwd, the reference bench shape)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exchange", choices=["peer", "nccl"], default="peer",
+                    help="multi-GPU gradient exchange: fused peer-memory kernel (default) or NCCL all-reduce")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

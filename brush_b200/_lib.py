@@ -37,6 +37,21 @@ class BrushAdamGroup(C.Structure):
                 ("sh_rest_lr_scale", C.c_float)]
 
 
+DP_MAX_WORLD = 8
+
+
+class BrushDpSegment(C.Structure):
+    _fields_ = [("src_offset", C.c_uint64), ("dst_offset", C.c_uint64), ("count", C.c_uint64), ("adam", C.c_int32),
+                ("lr", C.c_float), ("sh_coeffs_per_channel", C.c_uint32), ("sh_rest_lr_scale", C.c_float)]
+
+
+class BrushDpStep(C.Structure):
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("src", C.c_void_p * DP_MAX_WORLD),
+                ("dst", C.c_void_p * DP_MAX_WORLD), ("src_multicast", C.c_void_p), ("dst_multicast", C.c_void_p),
+                ("flags", C.c_void_p * DP_MAX_WORLD), ("m", C.c_void_p), ("v", C.c_void_p),
+                ("loss_offset", C.c_uint64), ("loss_out", C.c_void_p), ("epoch", C.c_uint32)]
+
+
 assert C.sizeof(BrushUniforms) == 112
 
 
@@ -75,6 +90,9 @@ _SIGS = {
     "brush_adam_step": (C.c_int, [C.c_void_p, C.POINTER(BrushAdamGroup), C.c_int, C.c_float, C.c_float, C.c_float,
                                   C.c_uint32, C.c_float, C.c_void_p]),
     "brush_launch_count": (C.c_uint64, []),
+    "brush_dp_adam_step": (C.c_int, [C.c_void_p, C.POINTER(BrushDpStep), C.POINTER(BrushDpSegment), C.c_int,
+                                     C.c_float, C.c_float, C.c_float, C.c_uint32, C.c_float, C.c_void_p]),
+    "brush_dp_owned_range": (None, [C.c_uint64, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "brush_quat_normalize": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]),
     "brush_quat_normalize_vjp": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]),
     "brush_xy_grad_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(BrushAux), C.c_uint32, C.c_uint32,

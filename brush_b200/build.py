@@ -27,6 +27,7 @@ UNITS = {
     "raster.cu": [],
     "backward.cu": [],
     "optim.cu": [],
+    "dp_adam.cu": [],
     "api.cu": [],
 }
 

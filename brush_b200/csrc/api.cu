@@ -543,5 +543,48 @@ int brush_adam_step(brush_ctx* ctx, const BrushAdamGroup* groups_host, int n_gro
     CU(cudaGetLastError());
     return BRUSH_OK;
 }
+
+void brush_dp_owned_range(uint64_t count, int world, int rank, uint64_t* begin, uint64_t* end) {
+    const uint64_t n4 = count / 4;
+    if (begin) *begin = 4 * (n4 * (uint64_t)rank / (uint64_t)(world > 0 ? world : 1));
+    if (end) *end = 4 * (n4 * (uint64_t)(rank + 1) / (uint64_t)(world > 0 ? world : 1));
+}
+
+int brush_dp_adam_step(brush_ctx* ctx, const BrushDpStep* sp, const BrushDpSegment* segs, int n_segs, float beta1,
+                       float beta2, float eps, uint32_t adam_step, float grad_scale, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (!sp || !segs || n_segs < 1 || n_segs > 8 || adam_step < 1 || sp->epoch < 1)
+        return fail(ctx, BRUSH_E_INVALID, "dp_adam: 1..8 segments, adam_step >= 1, epoch >= 1");
+    if (sp->world < 1 || sp->world > BRUSH_DP_MAX_WORLD || sp->rank < 0 || sp->rank >= sp->world)
+        return fail(ctx, BRUSH_E_INVALID, "dp_adam: world must be 1..8 and 0 <= rank < world");
+    CU(cudaSetDevice(ctx->device));
+    DpLaunch L{};
+    L.world = sp->world; L.rank = sp->rank; L.n_segs = n_segs;
+    for (int r = 0; r < sp->world; r++) {
+        if (!sp->src[r] || !sp->dst[r] || !sp->flags[r]) return fail(ctx, BRUSH_E_INVALID, "dp_adam: null peer buffer");
+        if (((uintptr_t)sp->src[r] | (uintptr_t)sp->dst[r]) & 15u)
+            return fail(ctx, BRUSH_E_INVALID, "dp_adam: peer buffers must be 16-byte aligned");
+        L.src[r] = sp->src[r]; L.dst[r] = sp->dst[r]; L.flags[r] = sp->flags[r];
+    }
+    L.src_mc = sp->src_multicast; L.dst_mc = sp->dst_multicast;
+    L.m = sp->m; L.v = sp->v;
+    L.loss_off = sp->loss_offset; L.loss_out = sp->loss_out;
+    L.arrive = (uint32_t*)ctx->sticky.p + 16;
+    L.epoch = sp->epoch;
+    for (int i = 0; i < n_segs; i++) {
+        const BrushDpSegment& g = segs[i];
+        if ((g.src_offset | g.dst_offset | g.count) & 3u)
+            return fail(ctx, BRUSH_E_INVALID, "dp_adam: segment offsets and counts must be multiples of 4 floats");
+        if (g.adam && (!sp->m || !sp->v || (((uintptr_t)sp->m | (uintptr_t)sp->v) & 15u)))
+            return fail(ctx, BRUSH_E_INVALID, "dp_adam: Adam segments need 16-byte aligned m and v");
+        L.seg[i] = DpSeg{g.src_offset, g.dst_offset, g.count, g.adam, g.lr, g.sh_coeffs_per_channel, g.sh_rest_lr_scale};
+    }
+    L.beta1 = beta1; L.beta2 = beta2; L.eps = eps; L.grad_scale = grad_scale;
+    L.inv_bc1 = (float)(1.0 / (1.0 - std::pow((double)beta1, (double)adam_step)));
+    L.inv_bc2 = (float)(1.0 / (1.0 - std::pow((double)beta2, (double)adam_step)));
+    launch_dp_adam(L, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
 #pragma GCC visibility pop
 }  // extern "C"

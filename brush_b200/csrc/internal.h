@@ -107,4 +107,32 @@ void launch_xy_grad_stats(const float* v_xy, const uint32_t* gfc, const int32_t*
                           float half_w, float half_h, int accumulate, float* grad_norm, float* visible,
                           cudaStream_t st);
 
+
+// ---- dp_adam.cu: view-parallel optimizer step over NVLink peer memory ----
+constexpr int DP_MAX_WORLD = BRUSH_DP_MAX_WORLD;
+struct DpSeg {
+    uint64_t src_off, dst_off, count;  // floats; multiples of 4
+    int adam;                          // 1: Adam on the summed gradient; 0: plain sum copied to dst
+    float lr;
+    uint32_t sh_k;
+    float sh_rest_scale;
+};
+struct DpLaunch {
+    int world, rank, n_segs;
+    const float* src[DP_MAX_WORLD];
+    float* dst[DP_MAX_WORLD];
+    const float* src_mc;
+    float* dst_mc;
+    uint32_t* flags[DP_MAX_WORLD];
+    float* m;
+    float* v;
+    uint64_t loss_off;
+    float* loss_out;
+    uint32_t* arrive;
+    uint32_t epoch;
+    float beta1, beta2, eps, inv_bc1, inv_bc2, grad_scale;
+    DpSeg seg[8];
+};
+void launch_dp_adam(const DpLaunch& L, cudaStream_t st);
+
 }  // namespace brush

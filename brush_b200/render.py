@@ -316,6 +316,22 @@ class Splats:
                                      requires_grad=True)
 
     @classmethod
+    def from_views(cls, means, sh_coeffs, rotation, raw_opacity, log_scales) -> "Splats":
+        """Wraps existing storage WITHOUT copying (the peer exchange keeps the parameters in a peer-mapped flat
+        buffer that brush_dp_adam_step updates in place)."""
+        self = cls.__new__(cls)
+
+        def p(t):
+            assert t.dtype == torch.float32 and t.is_contiguous()
+            return t.detach().requires_grad_(True)
+
+        self.means, self.sh_coeffs, self.rotation = p(means), p(sh_coeffs), p(rotation)
+        self.raw_opacity, self.log_scales = p(raw_opacity), p(log_scales)
+        self.xys_dummy = torch.zeros((self.means.shape[0], 2), dtype=torch.float32, device=self.means.device,
+                                     requires_grad=True)
+        return self
+
+    @classmethod
     def from_safetensors(cls, tensors: dict, device) -> "Splats":  # gaussian_splats.rs:208-223
         def t(name):
             return torch.as_tensor(np.asarray(tensors[name]), dtype=torch.float32, device=device)

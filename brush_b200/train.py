@@ -19,7 +19,7 @@ from typing import List, Optional
 import torch
 
 from . import _lib
-from .parallel import FlatGradLayout, allreduce_flat, global_grad_scale
+from .parallel import FlatGradLayout, FlatParamLayout, PeerBuffers, allreduce_flat, global_grad_scale
 from .render import Camera, RenderAux, Splats, _stream_ptr, get_context, make_uniforms, render_backward, render_forward
 
 
@@ -66,7 +66,8 @@ class SplatTrainer:
 
     # flat buffer layout: means 3N | xy 2N | log_scales 3N | quats 4N | sh 3KN | opac N | grad-norm N | visible N
     def __init__(self, num_points: int, config: TrainConfig, device, sh_coeffs_per_channel: int = 1,
-                 process_group=None, isect_capacity: Optional[int] = None, optimize: bool = True):
+                 process_group=None, isect_capacity: Optional[int] = None, optimize: bool = True,
+                 exchange: str = "nccl"):
         if config.ssim_weight != 0.0:
             raise NotImplementedError("SSIM loss is not built yet (SURVEY.md 8f-1); use ssim_weight=0")
         self.config = config
@@ -75,15 +76,28 @@ class SplatTrainer:
         self.pg = process_group
         self.isect_capacity = isect_capacity
         self.optimize = optimize
+        if exchange not in ("nccl", "peer"):
+            raise ValueError("exchange must be 'nccl' or 'peer'")
+        # "peer": gradient sum + Adam + parameter broadcast as one launch over NVLink peer memory (parallel.py)
+        self.exchange = exchange if (process_group is not None and process_group.size() > 1) else "nccl"
+        self.peer: Optional[PeerBuffers] = None
+        self.epoch = 0
         self._alloc(num_points, sh_coeffs_per_channel)
 
     def _alloc(self, n: int, k: int):
         f = dict(dtype=torch.float32, device=self.device)
         self.n, self.k = n, k
         self.layout = FlatGradLayout(n, k)
-        self.flat_grad = self.layout.alloc(self.device)
+        self.param_layout = FlatParamLayout(n, k)
+        if self.exchange == "peer":
+            self.peer = PeerBuffers(self.layout, self.param_layout, self.pg, self.device)
+            self.flat_grad = self.peer.grad
+            self.peer_m = torch.zeros(self.param_layout.total, **f)
+            self.peer_v = torch.zeros(self.param_layout.total, **f)
+        else:
+            self.flat_grad = self.layout.alloc(self.device)
         (self.g_means, self.g_xy, self.g_scales, self.g_quats, self.g_sh, self.g_opac, self.stat_grad_norm,
-         self.stat_visible) = self.layout.views(self.flat_grad)
+         self.stat_visible, self.g_loss) = self.layout.views(self.flat_grad)
         self.tmp = None  # second gradient set, only for batches of more than one view per rank
         self.grad_2d_accum = torch.zeros(n, **f)   # train.rs:195-196
         self.xy_grad_counts = torch.zeros(n, **f)
@@ -94,6 +108,19 @@ class SplatTrainer:
         self.v_out = None
         self.gt_dev = None
         self.render_bufs: List = []
+
+    def adopt(self, splats: Splats) -> Splats:
+        """Peer mode: moves the parameters into this rank's peer-mapped replica and returns Splats whose tensors
+        are views of it (brush_dp_adam_step updates every rank's replica in place).  A no-op otherwise."""
+        if self.peer is None:
+            return splats
+        pm, po, psh, pr, ps, _, _ = self.param_layout.views(self.peer.param)
+        for dst, src in ((pm, splats.means), (po, splats.raw_opacity), (psh, splats.sh_coeffs), (pr, splats.rotation),
+                         (ps, splats.log_scales)):
+            dst.copy_(src.detach())
+        torch.cuda.synchronize(self.device)
+        torch.distributed.barrier(self.pg)
+        return Splats.from_views(pm, psh, pr, po, ps)
 
     def _adam_state(self, name, p):
         if name not in self.state or self.state[name][0].shape != p.shape:
@@ -152,23 +179,63 @@ class SplatTrainer:
                         a.add_(b)
                 preds.append(pred)
                 auxes.append(aux)
-            if self.pg is not None and world > 1:
-                allreduce_flat(self.flat_grad, self.pg)  # ONE NCCL all-reduce over NVLink
-                allreduce_flat(self.loss_total, self.pg)
             grad_scale = global_grad_scale(B, world)
-            # VJP of the rotation normalisation (Burn autodiff in the reference), linear so it commutes with the sum
+            # VJP of the rotation normalisation (Burn autodiff in the reference); linear, so it commutes with the sum
             ctx.check(L.brush_quat_normalize_vjp(ctx.handle, p_rot.data_ptr(), self.n, self.g_quats.data_ptr(), st))
-            if self.iter > cfg.warmup_steps:  # train.rs:286-316
-                self.grad_2d_accum.add_(self.stat_grad_norm, alpha=grad_scale)
-                self.xy_grad_counts.copy_(torch.maximum(self.xy_grad_counts, (self.stat_visible > 0).float()))
             lr_mean = cfg.lr_mean * batch.scene_extent
             self.iter += 1
-            if self.optimize:
-                self._adam(ctx, splats, lr_mean, grad_scale, st)
-        loss = self.loss_total * grad_scale if (B * world) > 1 else self.loss_total
+            if self.peer is not None:
+                if splats.means.data_ptr() != self.peer.param.data_ptr() + 4 * self.param_layout.offset("means"):
+                    raise ValueError("peer exchange: pass the Splats returned by SplatTrainer.adopt()")
+                self.g_loss[:1].copy_(self.loss_total)
+                stat_norm, stat_vis = self._peer_step(ctx, lr_mean, grad_scale, st)
+                loss = self.loss_buf  # grad_scale * sum over ranks, written by the exchange kernel
+            else:
+                if self.pg is not None and world > 1:
+                    allreduce_flat(self.flat_grad, self.pg)  # ONE NCCL all-reduce over NVLink
+                    allreduce_flat(self.loss_total, self.pg)
+                stat_norm, stat_vis = self.stat_grad_norm, self.stat_visible
+                if self.optimize:
+                    self._adam(ctx, splats, lr_mean, grad_scale, st)
+                loss = self.loss_total * grad_scale if (B * world) > 1 else self.loss_total
+            if self.iter - 1 > cfg.warmup_steps:  # train.rs:286-316
+                self.grad_2d_accum.add_(stat_norm, alpha=grad_scale)
+                self.xy_grad_counts.copy_(torch.maximum(self.xy_grad_counts, (stat_vis > 0).float()))
         stats = TrainStepStats(preds, auxes, loss, lr_mean, cfg.lr_rotation, cfg.lr_scale, cfg.lr_coeffs_dc,
                                cfg.lr_opac)
         return splats, stats
+
+    def _peer_step(self, ctx, lr_mean: float, grad_scale: float, st):
+        """One brush_dp_adam_step launch: sum of the ranks' gradients on the owned slice -> Adam (train.rs:318-359)
+        -> new parameters into every replica; the refine statistics ride along as plain-sum segments."""
+        cfg, pl, gl, peer = self.config, self.param_layout, self.layout, self.peer
+        lrs = {"means": lr_mean, "opacity": cfg.lr_opac, "sh": cfg.lr_coeffs_dc, "rotation": cfg.lr_rotation,
+               "log_scales": cfg.lr_scale}
+        names = list(pl.NAMES)
+        segs = (_lib.BrushDpSegment * len(names))()
+        for i, name in enumerate(names):
+            segs[i].src_offset = gl.offset(pl.GRAD_OF[name])
+            segs[i].dst_offset = pl.offset(name)
+            segs[i].count = pl.padded_size(name)
+            segs[i].adam = int(name in lrs and self.optimize)
+            segs[i].lr = lrs.get(name, 0.0)
+            segs[i].sh_coeffs_per_channel = self.k if name == "sh" else 0
+            segs[i].sh_rest_lr_scale = 1.0 / cfg.lr_coeffs_sh_scale
+        if not self.optimize:  # gradients only: leave the parameters alone, still reduce the statistics
+            segs = (_lib.BrushDpSegment * 2)(segs[names.index("grad_norm")], segs[names.index("visible")])
+        self.epoch += 1
+        sp = _lib.BrushDpStep()
+        sp.world, sp.rank = peer.world, peer.rank
+        for r in range(peer.world):
+            sp.src[r], sp.dst[r], sp.flags[r] = peer.grad_ptrs[r], peer.param_ptrs[r], peer.flag_ptrs[r]
+        sp.src_multicast, sp.dst_multicast = peer.grad_mc or None, peer.param_mc or None
+        sp.m, sp.v = self.peer_m.data_ptr(), self.peer_v.data_ptr()
+        sp.loss_offset, sp.loss_out = gl.offset("loss"), self.loss_buf.data_ptr()
+        sp.epoch = self.epoch
+        ctx.check(_lib.lib().brush_dp_adam_step(ctx.handle, C.byref(sp), segs, len(segs), cfg.adam_beta1,
+                                                cfg.adam_beta2, cfg.adam_eps, self.iter, grad_scale, st))
+        views = pl.views(peer.param)
+        return views[5], views[6]
 
     def _adam(self, ctx, splats: Splats, lr_mean: float, grad_scale: float, st):
         cfg = self.config

@@ -174,6 +174,45 @@ int brush_quat_normalize_vjp(brush_ctx* ctx, const float* quats, uint32_t n, flo
 int brush_xy_grad_stats(brush_ctx* ctx, const float* v_xy, const BrushAux* aux, uint32_t n, uint32_t width,
                         uint32_t height, int accumulate, float* grad_norm, float* visible, void* stream);
 
+/* ---- view-parallel optimizer step over NVLink peer memory (no reference counterpart: the
+ * reference asserts a batch of one view on one device, crates/brush-train/src/train.rs:216-219) ----
+ * One launch per rank replaces "all-reduce the dense gradients, then brush_adam_step on every rank": rank r owns
+ * the r-th 1/world of every segment, sums that slice of all ranks' `src` buffers through peer loads (or one
+ * multimem.ld_reduce when multicast pointers are given), applies the Adam update of brush_adam_step to it (moments
+ * m, v are touched only on the owned slice) or just the sum (adam = 0: refine statistics), and stores the result
+ * into every rank's `dst` buffer.  All buffers named here except m, v, loss_out must be peer-mapped on every rank
+ * (cudaIpc / CUDA VMM / torch symmetric memory); src[i], dst[i], flags[i] are rank i's buffers as mapped in THIS
+ * process.  flags[i]: uint32[2 * BRUSH_DP_MAX_WORLD], zeroed once at allocation.  epoch: the same strictly
+ * increasing value (>= 1) on every rank for every call.  Every rank must make the matching call. */
+#define BRUSH_DP_MAX_WORLD 8
+typedef struct BrushDpSegment {
+    uint64_t src_offset;   /* floats, multiple of 4 */
+    uint64_t dst_offset;   /* floats, multiple of 4 */
+    uint64_t count;        /* floats, multiple of 4 */
+    int32_t adam;
+    float lr;
+    uint32_t sh_coeffs_per_channel;
+    float sh_rest_lr_scale;
+} BrushDpSegment;
+typedef struct BrushDpStep {
+    int32_t world, rank;
+    const float* src[BRUSH_DP_MAX_WORLD];
+    float* dst[BRUSH_DP_MAX_WORLD];
+    const float* src_multicast;   /* NVSwitch multicast mapping of src (sum = one multimem.ld_reduce), or NULL */
+    float* dst_multicast;         /* NVSwitch multicast mapping of dst (broadcast = one multimem.st), or NULL */
+    uint32_t* flags[BRUSH_DP_MAX_WORLD];
+    float* m;                     /* local Adam moments, indexed like dst */
+    float* v;
+    uint64_t loss_offset;         /* float index inside src of the rank's loss term */
+    float* loss_out;              /* local f32[1] = grad_scale * sum of the ranks' loss terms, or NULL */
+    uint32_t epoch;
+} BrushDpStep;
+int brush_dp_adam_step(brush_ctx* ctx, const BrushDpStep* step_host, const BrushDpSegment* segments_host,
+                       int n_segments, float beta1, float beta2, float eps, uint32_t adam_step, float grad_scale,
+                       void* stream);
+/* The slice [begin, end) of a segment of `count` floats that `rank` owns (host helper, no GPU needed). */
+void brush_dp_owned_range(uint64_t count, int world, int rank, uint64_t* begin, uint64_t* end);
+
 /* Number of kernels this library has launched in this process (all contexts). */
 uint64_t brush_launch_count(void);
 

@@ -23,7 +23,8 @@ def _worker(rank, world, port, out):
 
     n, k = 37, 16
     lay = FlatGradLayout(n, k)
-    assert lay.total == (13 + 3 * k + 2) * n
+    # every segment starts on a 16-byte boundary (the peer exchange moves float4s); payload = (13+3k+2)*n + loss
+    assert all(o % 4 == 0 for o in lay.offsets) and sum(lay.sizes) == (13 + 3 * k + 2) * n + 4
     flat = lay.alloc("cpu")
     views = lay.views(flat)
     # each rank writes its own per-view gradients through the VIEWS (as brush_render_backward does via pointers)
@@ -39,6 +40,22 @@ def _worker(rank, world, port, out):
     gathered = [None] * world
     dist.all_gather_object(gathered, mine)
     ok &= sorted(sum(gathered, [])) == list(range(16))
+    # peer-exchange ownership: emulate "reduce my slice, then hand it to everyone" with gloo point-to-point
+    # collectives and check it equals the all-reduce -- the host-side contract of brush_dp_adam_step
+    from brush_b200.parallel import owned_range
+
+    torch.manual_seed(100 + rank)
+    seg = torch.randn(4 * 25 + 3)
+    full = seg.clone()
+    dist.all_reduce(full)
+    gathered_seg = [torch.empty_like(seg) for _ in range(world)]
+    dist.all_gather(gathered_seg, seg)
+    rebuilt = torch.zeros_like(seg)
+    for r in range(world):
+        b, e = owned_range(seg.numel(), world, r)
+        rebuilt[b:e] = sum(g[b:e] for g in gathered_seg)  # what rank r would compute and store into every replica
+    covered = owned_range(seg.numel(), world, world - 1)[1]
+    ok &= covered == seg.numel() // 4 * 4 and bool(torch.allclose(rebuilt[:covered], full[:covered]))
     out[rank] = ok
     dist.destroy_process_group()
 
@@ -58,4 +75,26 @@ def test_single_rank_is_noop():
     lay = FlatGradLayout(5, 1)
     flat = lay.alloc("cpu") + 3.0
     allreduce_flat(flat, None)
-    assert torch.all(flat == 3.0) and lay.bytes_per_allreduce() == 4 * 18 * 5
+    assert torch.all(flat == 3.0) and lay.bytes_per_allreduce() == 4 * lay.total
+
+
+def test_owned_ranges_partition_and_match_c_helper():
+    import ctypes as C
+
+    from brush_b200 import _lib
+    from brush_b200.parallel import FlatGradLayout, FlatParamLayout, owned_range
+
+    L = _lib.lib()  # dlopen only; no GPU call
+    for count in (0, 4, 12, 100, 3_000_000, 48_000_000, 1_000_003 * 4):
+        for world in (1, 2, 3, 8):
+            prev = 0
+            for rank in range(world):
+                b, e = owned_range(count, world, rank)
+                cb, ce = C.c_uint64(), C.c_uint64()
+                L.brush_dp_owned_range(count, world, rank, C.byref(cb), C.byref(ce))
+                assert (b, e) == (cb.value, ce.value) and b == prev and b % 4 == 0 and e % 4 == 0
+                prev = e
+            assert prev == count // 4 * 4
+    g, p = FlatGradLayout(1001, 16), FlatParamLayout(1001, 16)
+    for name, gname in p.GRAD_OF.items():  # every exchanged segment has the same padded length on both sides
+        assert p.padded_size(name) == g.padded_size(gname) and p.offset(name) % 4 == 0 and g.offset(gname) % 4 == 0
