@@ -5,8 +5,10 @@
     python bench.py --impl reference [--steps K --warmup W]    the reference's CPU path (oracle port), host cores
 
 One "step" = one complete training iteration of brush_b200.train.SplatTrainer.step on one view per GPU:
-rotation normalise -> render forward -> L1 loss + d loss/d image -> render backward -> refine statistics
--> (N > 1: one NCCL all-reduce of the flat dense gradient) -> normalisation VJP -> fused Adam.
+rotation normalise -> render forward -> image loss (0.8 L1 - 0.2 SSIM, the reference default) + d loss/d image
+-> render backward -> refine statistics
+-> normalisation VJP -> fused Adam (N > 1: gradient sum + Adam + parameter broadcast as one peer-memory kernel,
+or --exchange nccl: all-reduce of the flat dense gradient, then replicated Adam).
 Workload = BASELINE.json configs[3]: 1M random Gaussians, SH degree 3, 1920x1080 (synthetic, seeded;
 generator in brush_b200/scene.py).  `value` times steps whose ground-truth view is already in HBM; `e2e`
 times the same steps with the view's image coming from pinned host memory (H2D inside the timed region)
@@ -291,7 +293,7 @@ def run_ours(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {N} random Gaussians, SH degree {sc.sh_degree}, {W}x{H}, one view per "
-                               f"GPU per step, L1 loss, {'fused Adam' if not args.no_optim else 'no optimizer'}, "
+                               f"GPU per step, loss 0.8 L1 - 0.2 SSIM (reference default), {'fused Adam' if not args.no_optim else 'no optimizer'}, "
                                f"{exchange_desc}",
                    "num_visible": V, "num_intersections": I, "views": N_VIEWS, "isect_capacity": args.capacity,
                    "l2": "inputs larger than L2 (236 MB of parameters + 244 MB of gradients per step vs 126 MB L2)"},

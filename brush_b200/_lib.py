@@ -87,6 +87,8 @@ _SIGS = {
     "brush_prefix_sum_u32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]),
     "brush_l1_loss_backward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
                                          C.c_void_p, C.c_void_p, C.c_void_p]),
+    "brush_image_loss_backward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
+                                            C.c_float, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "brush_adam_step": (C.c_int, [C.c_void_p, C.POINTER(BrushAdamGroup), C.c_int, C.c_float, C.c_float, C.c_float,
                                   C.c_uint32, C.c_float, C.c_void_p]),
     "brush_launch_count": (C.c_uint64, []),

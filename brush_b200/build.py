@@ -28,6 +28,7 @@ UNITS = {
     "backward.cu": [],
     "optim.cu": [],
     "dp_adam.cu": [],
+    "ssim.cu": [],
     "api.cu": [],
 }
 

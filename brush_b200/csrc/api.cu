@@ -23,7 +23,7 @@ struct brush_ctx {
     int timing = 0;
     // scratch, grown on demand (growth synchronises; steady state never allocates)
     Buf control, presort_gid, depth_bits, depth_sorted, num_tiles_hit, keys_tmp, vals_tmp, hist, lb, tickets,
-        tile_ids_unsorted, cg_unsorted, tile_ids_sorted, v_projected, sticky;
+        tile_ids_unsorted, cg_unsorted, tile_ids_sorted, v_projected, sticky, loss_scratch;
     // host-staged path
     Buf h_means, h_lscales, h_quats, h_sh, h_opac, h_img, h_aux[9];
     cudaEvent_t ev[BRUSH_STAGE_COUNT + 1][2];
@@ -136,7 +136,7 @@ void brush_ctx_destroy(brush_ctx* ctx) {
     cudaSetDevice(ctx->device);
     Buf* bufs[] = {&ctx->control, &ctx->presort_gid, &ctx->depth_bits, &ctx->depth_sorted, &ctx->num_tiles_hit,
                    &ctx->keys_tmp, &ctx->vals_tmp, &ctx->hist, &ctx->lb, &ctx->tickets, &ctx->tile_ids_unsorted,
-                   &ctx->cg_unsorted, &ctx->tile_ids_sorted, &ctx->v_projected, &ctx->sticky, &ctx->h_means, &ctx->h_lscales,
+                   &ctx->cg_unsorted, &ctx->tile_ids_sorted, &ctx->v_projected, &ctx->sticky, &ctx->loss_scratch, &ctx->h_means, &ctx->h_lscales,
                    &ctx->h_quats, &ctx->h_sh, &ctx->h_opac, &ctx->h_img};
     for (Buf* b : bufs)
         if (b->p) cudaFree(b->p);
@@ -519,6 +519,26 @@ int brush_l1_loss_backward(brush_ctx* ctx, const float* pred, const float* gt, u
     cudaStream_t st = (cudaStream_t)stream;
     CU(cudaMemsetAsync(loss_out, 0, 4, st));
     launch_l1_loss_backward(pred, gt, height * width, gt_channels, v_out_img, loss_out, st);
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
+
+int brush_image_loss_backward(brush_ctx* ctx, const float* pred, const float* gt, uint32_t height, uint32_t width,
+                              uint32_t gt_channels, float ssim_weight, uint32_t ssim_window, float* v_out_img,
+                              float* loss_out, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (!pred || !gt || !v_out_img || !loss_out) return fail(ctx, BRUSH_E_INVALID, "null argument");
+    if (gt_channels != 3 && gt_channels != 4) return fail(ctx, BRUSH_E_INVALID, "gt_channels must be 3 or 4");
+    if (!(ssim_weight >= 0.f && ssim_weight <= 1.f)) return fail(ctx, BRUSH_E_INVALID, "ssim_weight must be in [0, 1]");
+    if (ssim_weight > 0.f && ssim_window != 11)
+        return fail(ctx, BRUSH_E_INVALID, "ssim_window must be 11 (TrainConfig::ssim_window_size default)");
+    if (height == 0 || width == 0) return fail(ctx, BRUSH_E_INVALID, "empty image");
+    CU(cudaSetDevice(ctx->device));
+    const size_t plane = (size_t)(height + 2) * (width + 2);
+    ENSURE(loss_scratch, 64 + 9 * plane * 4);
+    float* sums = (float*)ctx->loss_scratch.p;
+    launch_image_loss_backward(pred, gt, height, width, gt_channels, ssim_weight, sums + 16, sums, v_out_img,
+                               loss_out, (cudaStream_t)stream);
     CU(cudaGetLastError());
     return BRUSH_OK;
 }

@@ -6,8 +6,8 @@
 
 Scope: the graded path is render fwd+bwd; loss, Adam, the rotation normalisation and the refine
 statistics are small fused CUDA kernels in libbrush_b200.so so that a benchmarked step is a complete training
-step with no PyTorch arithmetic in it.  SSIM (ssim_weight) and refine_splats are not built yet: ssim_weight
-must be 0 and refinement is a no-op.
+step with no PyTorch arithmetic in it.  The image loss is the reference's (1-w) L1 - w SSIM (ssim.rs) with its
+default window; refine_splats is not built yet (refinement is a no-op).
 Multi-GPU: batch views are sharded over ranks; the dense per-Gaussian gradients (+ the two refine
 statistics) are summed with ONE NCCL all-reduce over a flat buffer before the (replicated) Adam step."""
 from __future__ import annotations
@@ -25,13 +25,16 @@ from .render import Camera, RenderAux, Splats, _stream_ptr, get_context, make_un
 
 @dataclass
 class TrainConfig:  # train.rs:19-87 defaults
-    lr_mean: float = 1.6e-4
+    lr_mean: float = 1.6e-4            # ExponentialLrSchedulerConfig::new(lr_max, decay): initial lr ...
+    lr_mean_decay: float = 1.0         # ... and per-step gamma (load_data.rs:51-67: 1e-2^(1/total_steps))
     lr_coeffs_dc: float = 0.004
     lr_coeffs_sh_scale: float = 20.0
     lr_opac: float = 0.05
     lr_scale: float = 0.01
     lr_rotation: float = 0.002
-    ssim_weight: float = 0.0  # reference default 0.2; SSIM is a "next" row
+    ssim_weight: float = 0.2           # train.rs:56-57
+    ssim_window_size: int = 11         # train.rs:59-60 (the kernel implements the default window only)
+    scale_mean_lr_by_extent: bool = True
     warmup_steps: int = 500
     refine_every: int = 100
     max_refine_step: int = 15000
@@ -68,8 +71,8 @@ class SplatTrainer:
     def __init__(self, num_points: int, config: TrainConfig, device, sh_coeffs_per_channel: int = 1,
                  process_group=None, isect_capacity: Optional[int] = None, optimize: bool = True,
                  exchange: str = "nccl"):
-        if config.ssim_weight != 0.0:
-            raise NotImplementedError("SSIM loss is not built yet (SURVEY.md 8f-1); use ssim_weight=0")
+        if config.ssim_weight > 0.0 and config.ssim_window_size != 11:
+            raise ValueError("ssim_window_size must be 11 (the only window the loss kernel implements)")
         self.config = config
         self.device = torch.device(device)
         self.iter = 0
@@ -157,8 +160,10 @@ class SplatTrainer:
                                            isect_capacity=self.isect_capacity, ctx=ctx, reuse=reuse)
                 if reuse is None:
                     self.render_bufs.append((pred, aux))
-                ctx.check(L.brush_l1_loss_backward(ctx.handle, pred.data_ptr(), gt.data_ptr(), H, W, Cc,
-                                                   self.v_out.data_ptr(), self.loss_buf.data_ptr(), st))
+                # loss = (1-w) L1 - w SSIM and d loss / d pred in two launches (train.rs:249-268, ssim.rs)
+                ctx.check(L.brush_image_loss_backward(ctx.handle, pred.data_ptr(), gt.data_ptr(), H, W, Cc,
+                                                      cfg.ssim_weight, cfg.ssim_window_size, self.v_out.data_ptr(),
+                                                      self.loss_buf.data_ptr(), st))
                 if i == 0:
                     self.loss_total.copy_(self.loss_buf)
                     dst = outs
@@ -182,7 +187,10 @@ class SplatTrainer:
             grad_scale = global_grad_scale(B, world)
             # VJP of the rotation normalisation (Burn autodiff in the reference); linear, so it commutes with the sum
             ctx.check(L.brush_quat_normalize_vjp(ctx.handle, p_rot.data_ptr(), self.n, self.g_quats.data_ptr(), st))
-            lr_mean = cfg.lr_mean * batch.scene_extent
+            # ExponentialLrScheduler (Burn 0.16): step k (1-based) returns initial_lr * gamma^(k-1); train.rs:276-278
+            lr_mean = cfg.lr_mean * cfg.lr_mean_decay ** self.iter
+            if cfg.scale_mean_lr_by_extent:
+                lr_mean *= batch.scene_extent
             self.iter += 1
             if self.peer is not None:
                 if splats.means.data_ptr() != self.peer.param.data_ptr() + 4 * self.param_layout.offset("means"):

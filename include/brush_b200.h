@@ -146,6 +146,15 @@ int brush_render_forward_host(brush_ctx* ctx, const BrushUniforms* uniforms_host
 int brush_l1_loss_backward(brush_ctx* ctx, const float* pred, const float* gt, uint32_t height, uint32_t width,
                            uint32_t gt_channels, float* v_out_img, float* loss_out, void* stream);
 
+/* == the full image loss of SplatTrainer::step and its gradient, crates/brush-train/src/train.rs:249-268 with
+ * crates/brush-train/src/ssim.rs:7-112:  loss = (1 - w) * mean|pred_compare - gt| - w * ssim(pred_rgb, gt_rgb),
+ * SSIM with the reference's 11-tap sigma-1.5 window, zero padding 6 (maps are (H+2) x (W+2)), variances clamped
+ * at 0.  ssim_window must be 11 (the reference default, TrainConfig::ssim_window_size); ssim_weight = 0 gives
+ * brush_l1_loss_backward.  Writes v_out_img f32[H,W,4] and loss_out f32[1]. */
+int brush_image_loss_backward(brush_ctx* ctx, const float* pred, const float* gt, uint32_t height, uint32_t width,
+                              uint32_t gt_channels, float ssim_weight, uint32_t ssim_window, float* v_out_img,
+                              float* loss_out, void* stream);
+
 /* == the five optim.step calls of SplatTrainer::step, crates/brush-train/src/train.rs:318-359, as ONE launch.
  * Burn Adam: m = b1 m + (1-b1) g; v = b2 v + (1-b2) g^2; p -= lr * (m/(1-b1^t)) / (sqrt(v/(1-b2^t)) + eps).
  * sh_coeffs_per_channel > 1 marks the SH group [N,K,3]: coefficients k > 0 use lr * sh_rest_lr_scale
