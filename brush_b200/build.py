@@ -65,7 +65,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     def compile_one(item):
         unit, extra = item
         obj = os.path.join(OBJDIR, unit.replace(".cu", ".o"))
-        cmd = [nvcc, *ARCH, *COMMON, *extra, "-c", os.path.join(CSRC, unit), "-o", obj]
+        cmd = [nvcc, *ARCH, *COMMON, *extra, *os.environ.get("BRUSH_NVCC_EXTRA", "").split(), "-c",
+               os.path.join(CSRC, unit), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         r = subprocess.run(cmd, capture_output=True, text=True)

@@ -18,6 +18,27 @@ constexpr int RS_RADIX = 256;
 constexpr int RS_MAX_PASSES = 8;
 constexpr int LB_WINDOW = 16;
 
+// Lanes holding the same 8-bit digit, by eight ballots: fixed latency, unlike match.any whose cost grows with the
+// number of distinct values in the warp (random digits: ~28 distinct of 32 -- measured 22 us per 1M-key pass with
+// match.any).  Lanes with valid == false match nothing.
+__device__ __forceinline__ uint32_t match_digit(uint32_t d, bool valid) {
+    uint32_t peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+    for (int b = 0; b < 8; b++) {
+        const bool bit = (d >> b) & 1u;
+        const uint32_t bal = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? bal : ~bal;
+    }
+    return peers;
+}
+
+#ifdef BRUSH_SORT_PROF  // debug build only (scratch/): phase clocks of one tile
+__device__ unsigned long long g_sort_prof[16];
+#define PROF_MARK(i) do { if (tid == 0 && tile == gridDim.x / 8) g_sort_prof[i] = clock64(); } while (0)
+#else
+#define PROF_MARK(i) do { } while (0)
+#endif
+
 template <typename KeyT> struct SortCfg;
 template <> struct SortCfg<uint32_t> { static constexpr int ITEMS = 16; };
 template <> struct SortCfg<uint64_t> { static constexpr int ITEMS = 8; };
@@ -75,7 +96,7 @@ radix_hist_kernel(const KeyT* __restrict__ keys, const int32_t* __restrict__ n_d
                 const uint32_t d = (uint32_t)(k >> plan.shift[p]) & plan.mask[p];
                 // warp-aggregated shared atomics: clustered keys (tile ids, depth exponents) would
                 // otherwise serialise 32-way on one bank.
-                const uint32_t peers = __match_any_sync(0xffffffffu, valid ? d : (RS_RADIX + lane));
+                const uint32_t peers = match_digit(d, valid);
                 if (valid && lane == (uint32_t)(31 - __clz(peers))) atomicAdd(&s_hist[p * RS_RADIX + d], __popc(peers));
             }
         }
@@ -112,6 +133,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ v
     if (tile_start >= n) return;
     const uint32_t count = (uint32_t)min((uint64_t)TILE, (uint64_t)n - tile_start);
 
+    PROF_MARK(0);
     // global exclusive digit base = exclusive scan of this pass's histogram (thread d <-> digit d)
     uint32_t bin_base;
     {
@@ -139,12 +161,13 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ v
         uint32_t idx = chunk + i * 32 + lane;
         key[i] = idx < count ? keys_in[tile_start + idx] : (KeyT)0;
     }
+    PROF_MARK(1);
     // stable per-warp multisplit: match_any groups equal digits, the group leader bumps the warp counter
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         const bool valid = chunk + i * 32 + lane < count;
         const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
-        const uint32_t peers = __match_any_sync(0xffffffffu, valid ? d : (RS_RADIX + lane));
+        const uint32_t peers = match_digit(d, valid) | (1u << lane);  // an invalid lane is its own (unused) group
         const uint32_t leader = 31 - __clz(peers);
         uint32_t pre = 0;
         if (valid && lane == leader) {
@@ -157,6 +180,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ v
     }
     __syncthreads();
 
+    PROF_MARK(2);
     // thread d: exclusive scan of digit d's count over the warps -> tile count of digit d
     uint32_t tile_count = 0;
 #pragma unroll
@@ -165,6 +189,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ v
         s_whist[w][tid] = tile_count;
         tile_count += t;
     }
+    PROF_MARK(3);
     // decoupled look-back per digit: status word = flag[31:30] | count[29:0]
     {
         volatile uint32_t* vlb = lb;
@@ -197,6 +222,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ v
         }
         s_goff[tid] = bin_base + excl;
     }
+    PROF_MARK(4);
     // exclusive scan of tile_count over digits -> position of each digit's run inside the tile
     {
         uint32_t incl = tile_count;
@@ -215,6 +241,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ v
     }
     __syncthreads();
 
+    PROF_MARK(5);
     // scatter into shared memory in sorted order, then stream out digit runs (coalesced)
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
@@ -227,6 +254,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ v
         }
     }
     __syncthreads();
+    PROF_MARK(6);
     for (uint32_t j = tid; j < count; j += RS_THREADS) {
         const KeyT k = s_keys[j];
         const uint32_t d = (uint32_t)(k >> shift) & mask;
@@ -234,6 +262,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ v
         keys_out[dst] = k;
         vals_out[dst] = s_vals[j];
     }
+    PROF_MARK(7);
 }
 
 template <typename KeyT>
@@ -280,6 +309,12 @@ static void radix_sort_impl(const KeyT* keys, const uint32_t* vals, const int32_
         src_v = dst_v;
     }
 }
+
+#ifdef BRUSH_SORT_PROF
+extern "C" __attribute__((visibility("default"))) void brush_debug_sort_prof(unsigned long long* out) {
+    cudaMemcpyFromSymbol(out, g_sort_prof, sizeof(unsigned long long) * 16);
+}
+#endif
 
 void launch_radix_sort_u32(const uint32_t* keys, const uint32_t* vals, const int32_t* n_dev, uint32_t max_n,
                            uint32_t bits, uint32_t* keys_out, uint32_t* vals_out, const SortScratch& s,
