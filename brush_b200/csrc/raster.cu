@@ -46,18 +46,20 @@ void launch_tile_bins(const uint32_t* sorted_tile_ids, const uint64_t* sorted_ke
 //  * at staging time each splat is put in "log2 form": q(d) = L + A dx^2 + B dx dy + C dy^2 with
 //    L = log2(opac), (A,B,C) = -log2(e) * (cxx/2, cxy, cyy/2), so alpha = 2^q, and the visibility test
 //    "sigma >= 0 && alpha >= 1/255" becomes "q - L <= 0 && q >= log2(1/255)" -- no exp for rejected pairs;
-//  * each splat also gets the pixel-space bounding box of its alpha >= 1/255 ellipse; every warp tests 32
-//    splats at a time against its 8x4 block (one lane per splat), ballots, and only walks the survivors
-//    (about half of the tile's list at 1M splats / 1080p), in depth order;
+//  * the staging thread also decides, once per splat, which of the tile's eight 8x4 pixel blocks (= warps) the
+//    splat's alpha >= 1/255 ellipse can reach (bounding box, then an exact ellipse-vs-rectangle test) and stores
+//    the 8-bit mask; every warp turns its bit into a depth-ordered survivor list by ballot and only walks that
+//    (about 40% of the tile's list at 1M splats / 1080p);
+//  * survivors are processed four at a time: their geometry is independent of the compositing state, so the four
+//    dependency chains overlap; the order-dependent update is predicated, not branched;
 //  * whole-warp and whole-tile early exit once every pixel's transmittance is spent.
 // Shared-memory layout of one CTA (byte offsets from the CTA's shared window; accessed with explicit
 // ld.shared so the inner loops carry one 32-bit address register and no generic->shared conversions).
 constexpr uint32_t SM_SLOTS = TILE_SIZE + 1;          // slot 256 is a dummy splat that no pixel ever sees (list padding)
 constexpr uint32_t SM_G0 = 0;                         // float4[257]: x, y, A, B
 constexpr uint32_t SM_G1 = SM_G0 + 16 * SM_SLOTS;     // float4[257]: C, L, opacity, compact gid (bits)
-constexpr uint32_t SM_COL = SM_G1 + 16 * SM_SLOTS;    // float4[257]: r, g, b, -
-constexpr uint32_t SM_BBOX = SM_COL + 16 * SM_SLOTS;  // float4[256]: xmin, xmax, ymin, ymax of the alpha>=1/255 ellipse
-constexpr uint32_t SM_LIST = SM_BBOX + 16 * TILE_SIZE;  // u32[8][260]: per warp, shared-window addresses of the survivors' G0 entries
+constexpr uint32_t SM_COL = SM_G1 + 16 * SM_SLOTS;    // float4[257]: r, g, b, mask of the 8x4 blocks the splat reaches
+constexpr uint32_t SM_LIST = SM_COL + 16 * SM_SLOTS;  // u32[8][260]: per warp, shared-window addresses of the survivors' G0 entries
 constexpr uint32_t LIST_PAD = 4;                      // lists are padded with the dummy slot to a multiple of 4
 constexpr uint32_t LIST_STRIDE = 4 * (TILE_SIZE + LIST_PAD);
 constexpr uint32_t SM_BYTES = SM_LIST + LIST_STRIDE * (TILE_SIZE / 32);
@@ -104,71 +106,79 @@ __device__ __forceinline__ void init_dummy_slot(uint32_t sbase) {
     sts128(sbase + SM_COL + TILE_SIZE * 16, make_float4(0.f, 0.f, 0.f, 0.f));
 }
 
-// Put one splat of the tile's list into shared memory in "log2 form" (see the kernel comment).
+// Does the splat's alpha >= 1/255 region reach the (continuous) rectangle [rx0, rx1] x [ry0, ry1] of pixel centres?
+// In log2 form the pair test is sp(d) >= log2(1/255) - L with sp a concave quadratic in d = centre - pixel, so the
+// question is whether max sp over the rectangle clears that bound: yes if the centre is inside, else the maximum
+// lies on one of the four edges, where sp is a 1-D parabola.  The bound carries a slack well above the rounding
+// error of sp, so this can only keep a splat the per-pixel test then rejects, never drop one it would accept.
+struct CullForm {
+    float x, y, A, B, C, h1, h2, L;
+};
+__device__ __forceinline__ bool ellipse_reaches_block(const CullForm& f, float rx0, float rx1, float ry0, float ry1) {
+    const float dx0 = f.x - rx1, dx1 = f.x - rx0, dy0 = f.y - ry1, dy1 = f.y - ry0;  // d ranges over [d0, d1]
+    if (dx0 <= 0.0f && dx1 >= 0.0f && dy0 <= 0.0f && dy1 >= 0.0f) return true;
+    const float ya = fminf(fmaxf(f.h1 * dx0, dy0), dy1), yb = fminf(fmaxf(f.h1 * dx1, dy0), dy1);
+    const float xa = fminf(fmaxf(f.h2 * dy0, dx0), dx1), xb = fminf(fmaxf(f.h2 * dy1, dx0), dx1);
+    const float s0 = fmaf(f.C * ya, ya, fmaf(f.B, ya, f.A * dx0) * dx0);
+    const float s1 = fmaf(f.C * yb, yb, fmaf(f.B, yb, f.A * dx1) * dx1);
+    const float s2 = fmaf(f.C * dy0, dy0, fmaf(f.B, dy0, f.A * xa) * xa);
+    const float s3 = fmaf(f.C * dy1, dy1, fmaf(f.B, dy1, f.A * xb) * xb);
+    const float smax = fmaxf(fmaxf(s0, s1), fmaxf(s2, s3));
+    const float dxm = fmaxf(fabsf(dx0), fabsf(dx1)), dym = fmaxf(fabsf(dy0), fabsf(dy1));
+    const float mag = fabsf(f.A) * dxm * dxm + fabsf(f.C) * dym * dym + fabsf(f.B) * dxm * dym;
+    const float bound = (LOG2_INV255 - f.L) - (0.01f + 1e-5f * mag);
+    return !(smax < bound);  // NaN (degenerate conic) keeps the splat
+}
+
+// Put one splat of the tile's list into shared memory in "log2 form" (see the kernel comment), together with the
+// 8-bit mask of the tile's 8x4 pixel blocks (= warps) its alpha >= 1/255 region can reach: the cull is done ONCE
+// per splat by the staging thread, and every warp's list pass is then a bit test.
 // `tag` travels in G1.w: the backward uses it as the row of its gradient accumulator.
+// (tile_px, tile_py) = pixel coordinates of the tile's first pixel.
 __device__ __forceinline__ void stage_splat(uint32_t sbase, uint32_t slot, const float* __restrict__ projected,
-                                            uint32_t cg, uint32_t tag) {
+                                            uint32_t cg, uint32_t tag, float tile_px, float tile_py) {
     const float* p = projected + (size_t)cg * 9;
     const float x = __ldg(p), y = __ldg(p + 1), cxx = __ldg(p + 2), cxy = __ldg(p + 3), cyy = __ldg(p + 4);
     const float opac = __ldg(p + 8);
-    sts128(sbase + SM_G0 + slot * 16, make_float4(x, y, -0.5f * LOG2E * cxx, -LOG2E * cxy));
-    sts128(sbase + SM_G1 + slot * 16, make_float4(-0.5f * LOG2E * cyy, __log2f(opac), opac, __uint_as_float(tag)));
-    sts128(sbase + SM_COL + slot * 16, make_float4(__ldg(p + 5), __ldg(p + 6), __ldg(p + 7), 0.f));
-    // sigma(d) <= t = ln(255 opac)  =>  |dx| <= sqrt(2 t cyy / det), |dy| <= sqrt(2 t cxx / det); slightly inflated
-    // so that rounding can only keep a splat, never drop one.
+    CullForm f;
+    f.x = x; f.y = y;
+    f.A = -0.5f * LOG2E * cxx; f.B = -LOG2E * cxy; f.C = -0.5f * LOG2E * cyy;
+    f.L = __log2f(opac);
+    f.h1 = -f.B * rcp_approx(2.0f * f.C); f.h2 = -f.B * rcp_approx(2.0f * f.A);
+    sts128(sbase + SM_G0 + slot * 16, make_float4(x, y, f.A, f.B));
+    sts128(sbase + SM_G1 + slot * 16, make_float4(f.C, f.L, opac, __uint_as_float(tag)));
+    // first stage: bounding box of the region.  sigma(d) <= t = ln(255 opac)  =>  |dx| <= sqrt(2 t cyy / det),
+    // |dy| <= sqrt(2 t cxx / det); slightly inflated so that rounding can only keep a splat, never drop one.
     const float t = __logf(255.0f * opac) + 1e-3f;
     const float det = cxx * cyy - cxy * cxy;
     const float k = 2.0f * t * rcp_approx(det);
     float ex = sqrtf(k * cyy) * 1.001f + 1e-2f;
     float ey = sqrtf(k * cxx) * 1.001f + 1e-2f;
     if (!(det > 0.0f) || !(ex < 1e30f) || !(ey < 1e30f)) ex = ey = 1e30f;  // degenerate: never cull
-    sts128(sbase + SM_BBOX + slot * 16, make_float4(x - ex, x + ex, y - ey, y + ey));
-}
-
-// Exact second stage of the cull: does the splat's alpha >= 1/255 region reach the (continuous) rectangle spanned
-// by the warp's pixel centres?  In log2 form the pair test is sp(d) >= log2(1/255) - L with sp a concave
-// quadratic in d = centre - pixel, so the question is whether max sp over the rectangle clears that bound: yes if
-// the centre is inside, else the maximum lies on one of the four edges, where sp is a 1-D parabola.  The bound
-// carries a slack well above the rounding error of sp, so this can only keep a splat the per-pixel test then
-// rejects, never drop one it would accept.
-__device__ __forceinline__ bool ellipse_reaches_block(uint32_t a, float rx0, float rx1, float ry0, float ry1) {
-    const float4 g0 = lds128(a + SM_G0);  // x, y, A, B
-    const float4 g1 = lds128(a + SM_G1);  // C, L, ...
-    const float A = g0.z, B = g0.w, C = g1.x;
-    const float dx0 = g0.x - rx1, dx1 = g0.x - rx0, dy0 = g0.y - ry1, dy1 = g0.y - ry0;  // d ranges over [d0, d1]
-    if (dx0 <= 0.0f && dx1 >= 0.0f && dy0 <= 0.0f && dy1 >= 0.0f) return true;
-    const float h1 = -B * rcp_approx(2.0f * C), h2 = -B * rcp_approx(2.0f * A);
-    float smax;
-    {
-        const float ya = fminf(fmaxf(h1 * dx0, dy0), dy1), yb = fminf(fmaxf(h1 * dx1, dy0), dy1);
-        const float xa = fminf(fmaxf(h2 * dy0, dx0), dx1), xb = fminf(fmaxf(h2 * dy1, dx0), dx1);
-        const float s0 = fmaf(C * ya, ya, fmaf(B, ya, A * dx0) * dx0);
-        const float s1 = fmaf(C * yb, yb, fmaf(B, yb, A * dx1) * dx1);
-        const float s2 = fmaf(C * dy0, dy0, fmaf(B, dy0, A * xa) * xa);
-        const float s3 = fmaf(C * dy1, dy1, fmaf(B, dy1, A * xb) * xb);
-        smax = fmaxf(fmaxf(s0, s1), fmaxf(s2, s3));
+    const float bx0 = x - ex, bx1 = x + ex, by0 = y - ey, by1 = y + ey;
+    uint32_t mask = 0;
+#pragma unroll
+    for (uint32_t b = 0; b < TILE_SIZE / 32u; b++) {  // block b = warp b: 8 wide, 4 tall
+        const float rx0 = tile_px + (float)((b & 1u) * 8u) + 0.5f, ry0 = tile_py + (float)((b >> 1) * 4u) + 0.5f;
+        const float rx1 = rx0 + 7.0f, ry1 = ry0 + 3.0f;
+        bool hit = bx0 <= rx1 && bx1 >= rx0 && by0 <= ry1 && by1 >= ry0;
+        if (hit) hit = ellipse_reaches_block(f, rx0, rx1, ry0, ry1);
+        mask |= (hit ? 1u : 0u) << b;
     }
-    const float dxm = fmaxf(fabsf(dx0), fabsf(dx1)), dym = fmaxf(fabsf(dy0), fabsf(dy1));
-    const float mag = fabsf(A) * dxm * dxm + fabsf(C) * dym * dym + fabsf(B) * dxm * dym;
-    const float bound = (LOG2_INV255 - g1.y) - (0.01f + 1e-5f * mag);
-    return !(smax < bound);  // NaN (degenerate conic) keeps the splat
+    sts128(sbase + SM_COL + slot * 16, make_float4(__ldg(p + 5), __ldg(p + 6), __ldg(p + 7), __uint_as_float(mask)));
 }
 
-// Cull pass of one warp over the staged batch: one lane per splat against the warp's pixel block; the
-// shared-window addresses of the survivors' G0 entries are appended, in depth order, to the warp's list, which
-// is then padded with the dummy slot to a multiple of LIST_PAD.  Returns the list length (without padding).
+// List pass of one warp over the staged batch: one lane per splat tests its block's bit; the shared-window
+// addresses of the survivors' G0 entries are appended, in depth order, to the warp's list, which is then padded
+// with the dummy slot to a multiple of LIST_PAD.  Returns the list length (without padding).
 // Only slots in [t_lo, t_max) take part.
-__device__ __forceinline__ uint32_t cull_to_list(uint32_t sbase, uint32_t list_addr, uint32_t lane, uint32_t t_lo,
-                                                 uint32_t t_max, float rx0, float rx1, float ry0, float ry1) {
+__device__ __forceinline__ uint32_t cull_to_list(uint32_t sbase, uint32_t list_addr, uint32_t lane, uint32_t warp,
+                                                 uint32_t t_lo, uint32_t t_max) {
     uint32_t n_list = 0;
     for (uint32_t c0 = t_lo & ~31u; c0 < t_max; c0 += 32) {
         const uint32_t mine = c0 + lane;
         bool hit = false;
-        if (mine >= t_lo && mine < t_max) {
-            const float4 bb = lds128(sbase + SM_BBOX + mine * 16);
-            hit = bb.x <= rx1 && bb.y >= rx0 && bb.z <= ry1 && bb.w >= ry0;
-            if (hit) hit = ellipse_reaches_block(sbase + mine * 16u, rx0, rx1, ry0, ry1);
-        }
+        if (mine >= t_lo && mine < t_max) hit = (lds_u32(sbase + SM_COL + mine * 16u + 12u) >> warp) & 1u;
         const uint32_t mask = __ballot_sync(0xffffffffu, hit);
         if (hit) sts_u32(list_addr + 4u * (n_list + __popc(mask & ((1u << lane) - 1u))), sbase + mine * 16u);
         n_list += __popc(mask);
@@ -192,8 +202,6 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
     const uint32_t px = bx0 + (lane & 7u), py = by0 + (lane >> 3);
     const bool inside = px < cam.img_w && py < cam.img_h;
     const float pcx = (float)px + 0.5f, pcy = (float)py + 0.5f;
-    // the warp's block in pixel-centre coordinates
-    const float rx0 = (float)bx0 + 0.5f, rx1 = (float)bx0 + 7.5f, ry0 = (float)by0 + 0.5f, ry1 = (float)by0 + 3.5f;
     bool done = !inside;
 
     const uint2 range = __ldg(reinterpret_cast<const uint2*>(tile_bins) + tile_id);
@@ -211,11 +219,11 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
         const uint32_t remaining = min(TILE_SIZE, range.y - batch_start);
         if (tid < remaining) {
             const uint32_t cg = __ldg(compact_gid_from_isect + batch_start + tid);
-            stage_splat(sbase, tid, projected, cg, cg);
+            stage_splat(sbase, tid, projected, cg, cg, (float)(blockIdx.x * TILE_WIDTH), (float)(blockIdx.y * TILE_WIDTH));
         }
         __syncthreads();
         if (__all_sync(0xffffffffu, done)) continue;
-        const uint32_t n_list = cull_to_list(sbase, list_addr, lane, 0u, remaining, rx0, rx1, ry0, ry1);
+        const uint32_t n_list = cull_to_list(sbase, list_addr, lane, warp, 0u, remaining);
         // Four survivors per iteration: their geometry (sp, q, alpha) is independent of the compositing state, so
         // the four chains overlap; the order-dependent part is then applied in depth order, predicated (no
         // divergent branch).  The list is padded with the dummy slot, which no pixel sees.
@@ -394,7 +402,7 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
     const uint32_t px = bx0 + (lane & 7u), py = by0 + (lane >> 3);
     const bool inside = px < cam.img_w && py < cam.img_h;
     const float pcx = (float)px + 0.5f, pcy = (float)py + 0.5f;
-    const float rx0 = (float)bx0 + 0.5f, rx1 = (float)bx0 + 7.5f, ry0 = (float)by0 + 0.5f, ry1 = (float)by0 + 3.5f;
+    const float rx0 = (float)bx0 + 0.5f, ry0 = (float)by0 + 0.5f;  // pixel centre of the warp's first pixel
 
     const uint2 range = __ldg(reinterpret_cast<const uint2*>(tile_bins) + tile_id);
     if (range.y <= range.x) return;
@@ -426,7 +434,8 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
         const uint32_t remaining = min(TILE_SIZE, batch_end - range.x);
         if (tid < remaining) {  // gradient rows are indexed by GLOBAL splat id, so the per-splat backward is coalesced
             const uint32_t cg = __ldg(compact_gid_from_isect + batch_end - 1u - tid);
-            stage_splat(sbase, tid, projected, cg, __ldg(global_from_compact + cg));
+            stage_splat(sbase, tid, projected, cg, __ldg(global_from_compact + cg), (float)(tile_x * TILE_WIDTH),
+                        (float)(tile_y * TILE_WIDTH));
         }
         __syncthreads();
         if (!warp_any_inside || batch_end - remaining > warp_final) continue;
@@ -434,7 +443,7 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
         const uint32_t t_lo_warp = batch_end - 1u > warp_final ? batch_end - 1u - warp_final : 0u;
         const uint32_t a_lo = !inside ? 0xffffffffu
                                       : sbase + (batch_end - 1u > final_isect ? (batch_end - 1u - final_isect) * 16u : 0u);
-        const uint32_t n_list = cull_to_list(sbase, list_addr, lane, t_lo_warp, remaining, rx0, rx1, ry0, ry1);
+        const uint32_t n_list = cull_to_list(sbase, list_addr, lane, warp, t_lo_warp, remaining);
         uint32_t k = 0;  // rows of the pair tile in use (warp-uniform); flushed before the batch buffer is reused
         for (uint32_t i = 0;; i += BW_GROUP) {
             const bool end = i >= n_list;
