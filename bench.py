@@ -157,7 +157,8 @@ def run_ours(args):
     gt_host = torch.from_numpy(rng.uniform(0, 1, (N_VIEWS, H, W, 3)).astype(np.float32)).pin_memory()
     gt_dev = gt_host.to(dev)
     ctx = get_context(dev)
-    trainer = SplatTrainer(N, TrainConfig(), dev, sh_coeffs_per_channel=K, process_group=pg,
+    # reference defaults, except that refinement is off: the benchmark times a fixed number of splats
+    trainer = SplatTrainer(N, TrainConfig(max_refine_step=0), dev, sh_coeffs_per_channel=K, process_group=pg,
                            isect_capacity=args.capacity, optimize=not args.no_optim, exchange=args.exchange)
     splats = trainer.adopt(splats)  # peer exchange: parameters live in the peer-mapped replica
     if world > 1 and trainer.exchange == "peer":

@@ -339,8 +339,8 @@ int brush_render_backward(brush_ctx* ctx, uint32_t N, uint32_t K, const float* m
                           void* stream) {
     if (!ctx) return BRUSH_E_INVALID;
     if (!valid_k(K)) return fail(ctx, BRUSH_E_INVALID, "Invalid nr. of sh bases " + std::to_string(K));
-    if (!aux || !out_img || !v_out_img || !v_means || !v_xy || !v_log_scales || !v_quats || !v_sh_coeffs ||
-        !v_raw_opacity)
+    if (!aux || !out_img || !v_out_img ||
+        (N > 0 && (!v_means || !v_xy || !v_log_scales || !v_quats || !v_sh_coeffs || !v_raw_opacity)))
         return fail(ctx, BRUSH_E_INVALID, "null argument");
     cudaStream_t st = (cudaStream_t)stream;
     CU(cudaSetDevice(ctx->device));

@@ -13,6 +13,7 @@ statistics) are summed with ONE NCCL all-reduce over a flat buffer before the (r
 from __future__ import annotations
 
 import ctypes as C
+import math
 from dataclasses import dataclass
 from typing import List, Optional
 
@@ -35,9 +36,16 @@ class TrainConfig:  # train.rs:19-87 defaults
     ssim_weight: float = 0.2           # train.rs:56-57
     ssim_window_size: int = 11         # train.rs:59-60 (the kernel implements the default window only)
     scale_mean_lr_by_extent: bool = True
-    warmup_steps: int = 500
+    warmup_steps: int = 500            # train.rs:22-31
     refine_every: int = 100
     max_refine_step: int = 15000
+    reset_alpha_value: float = 0.004   # train.rs:33-54
+    cull_alpha_thresh: float = 0.005
+    cull_scale_thresh: float = 5.0
+    reset_alpha_every_refine: int = 30
+    densify_grad_thresh: float = 0.0002
+    densify_size_thresh: float = 0.005
+    seed: int = 42
     adam_beta1: float = 0.9
     adam_beta2: float = 0.999
     adam_eps: float = 1e-15  # train.rs:184
@@ -48,6 +56,28 @@ class SceneBatch:  # train.rs:89-94
     gt_images: torch.Tensor          # [B,H,W,C] f32, C = 3 or 4; on the device, or in pinned host memory
     gt_views: List[Camera]
     scene_extent: float = 1.0
+
+
+@dataclass
+class RefineStats:  # train.rs:112-118
+    num_split: int
+    num_cloned: int
+    num_transparent_pruned: int
+    num_scale_pruned: int
+
+
+def quaternion_vec_multiply(q: torch.Tensor, v: torch.Tensor) -> torch.Tensor:
+    """train.rs:140-177: rotates v[n,3] by the (w, x, y, z) quaternions q[n,4], term for term."""
+    qw, qx, qy, qz = q[:, 0:1], q[:, 1:2], q[:, 2:3], q[:, 3:4]
+    vx, vy, vz = v[:, 0:1], v[:, 1:2], v[:, 2:3]
+    t1 = qw * vx + qy * vz - qz * vy
+    t2 = qw * vy - qx * vz + qz * vx
+    t3 = qw * vz + qx * vy - qy * vx
+    t4 = qx * vx + qy * vy + qz * vz
+    rx = vx + (qw * t1 + qx * t4 - qy * t3 + qz * t2) * 2.0
+    ry = vy + (qw * t2 - qx * t3 + qy * t4 + qz * t1) * 2.0
+    rz = vz + (qw * t3 + qx * t2 - qy * t1 + qz * t4) * 2.0
+    return torch.cat([rx, ry, rz], 1)
 
 
 @dataclass
@@ -191,6 +221,11 @@ class SplatTrainer:
             lr_mean = cfg.lr_mean * cfg.lr_mean_decay ** self.iter
             if cfg.scale_mean_lr_by_extent:
                 lr_mean *= batch.scene_extent
+            # train.rs:361-365 (iter = the value before this step's increment)
+            do_refine = (self.iter < cfg.max_refine_step and self.iter >= cfg.warmup_steps
+                         and self.iter % cfg.refine_every == 1 and self.optimize)
+            pre_step = [p.detach().clone() for p in (splats.means, splats.sh_coeffs, splats.rotation,
+                                                     splats.raw_opacity, splats.log_scales)] if do_refine else None
             self.iter += 1
             if self.peer is not None:
                 if splats.means.data_ptr() != self.peer.param.data_ptr() + 4 * self.param_layout.offset("means"):
@@ -208,10 +243,68 @@ class SplatTrainer:
                 loss = self.loss_total * grad_scale if (B * world) > 1 else self.loss_total
             if self.iter - 1 > cfg.warmup_steps:  # train.rs:286-316
                 self.grad_2d_accum.add_(stat_norm, alpha=grad_scale)
-                self.xy_grad_counts.copy_(torch.maximum(self.xy_grad_counts, (stat_vis > 0).float()))
+                self.xy_grad_counts.add_(stat_vis)  # select_assign == scatter-ADD in Burn 0.16: a visibility count
+            refine = None
+            if do_refine:
+                loss = loss.clone()
+                splats, refine = self.refine_splats(pre_step, splats)
         stats = TrainStepStats(preds, auxes, loss, lr_mean, cfg.lr_rotation, cfg.lr_scale, cfg.lr_coeffs_dc,
-                               cfg.lr_opac)
+                               cfg.lr_opac, refine)
         return splats, stats
+
+    def refine_splats(self, pre_step, post: Splats, samples: Optional[torch.Tensor] = None):
+        """train.rs:395-553: clone small / split large high-gradient splats, prune transparent and huge ones, reset
+        opacities every `reset_alpha_every_refine` refines, reset the statistics and the optimizer state.
+        `pre_step` = (means, sh, rotation, raw_opacity, log_scales) BEFORE this step's optimizer update.
+        As in the reference, the edits it makes to the SPLIT splats themselves (smaller scale, offset mean) are
+        applied to clones that are then dropped (train.rs:401-402,481-507 vs :519): only the appended copies
+        carry them.  Every rank takes the same decisions: the statistics are the reduced ones and the split
+        offsets come from a generator seeded with (config.seed, iter).  `samples` [num_split, 3] overrides the
+        N(0, 0.5) draws (tests)."""
+        cfg = self.config
+        pre_means, pre_sh, pre_rot, pre_opac, pre_scales = pre_step
+        p_means, p_sh, p_rot = post.means.detach(), post.sh_coeffs.detach(), post.rotation.detach()
+        p_opac, p_scales = post.raw_opacity.detach(), post.log_scales.detach()
+        grads = self.grad_2d_accum / self.xy_grad_counts.clamp_min(1.0)
+        big_grad = grads >= cfg.densify_grad_thresh
+        small = torch.exp(p_scales).amax(dim=1) < cfg.densify_size_thresh
+        clone_inds = torch.nonzero(small & big_grad).squeeze(1)
+        split_inds = torch.nonzero(~small & big_grad).squeeze(1)
+        n_clone, n_split = int(clone_inds.numel()), int(split_inds.numel())
+        app = [[], [], [], [], []]  # means, rotation, sh, opacity, log_scales
+        if n_clone:
+            for dst, src in zip(app, (pre_means, pre_rot, pre_sh, pre_opac, pre_scales)):
+                dst.append(src[clone_inds])
+        if n_split:
+            cur_rot, cur_scale = p_rot[split_inds], torch.exp(p_scales[split_inds])
+            if samples is None:
+                gen = torch.Generator(device=self.device)
+                gen.manual_seed((cfg.seed << 20) + self.iter)
+                samples = torch.randn((n_split, 3), device=self.device, generator=gen) * 0.5
+            offset = quaternion_vec_multiply(cur_rot, samples * cur_scale)
+            app[0].append(pre_means[split_inds] + offset)
+            app[1].append(cur_rot)
+            app[2].append(p_sh[split_inds])
+            app[3].append(p_opac[split_inds])
+            app[4].append(torch.log(cur_scale / 1.6))
+        new = [p_means, p_rot, p_sh, p_opac, p_scales]
+        if n_clone or n_split:
+            new = [torch.cat([base] + extra, 0) for base, extra in zip(new, app)]
+        start = new[0].shape[0]
+        keep = ~(torch.sigmoid(new[3]) < cfg.cull_alpha_thresh)          # prune_points, train.rs:530-531
+        new = [t[keep] for t in new]
+        alpha_pruned = start - new[0].shape[0]
+        keep = ~(torch.exp(new[4]).amax(dim=1) > cfg.cull_scale_thresh)  # train.rs:536-541
+        new = [t[keep] for t in new]
+        scale_pruned = start - new[0].shape[0]                           # cumulative, as train.rs:543
+        refine_step = (self.iter - 1) // cfg.refine_every                # self.iter was already incremented
+        if refine_step % cfg.reset_alpha_every_refine == 0:              # train.rs:545-548
+            new[3] = torch.full_like(new[3], math.log(cfg.reset_alpha_value / (1.0 - cfg.reset_alpha_value)))
+        it = self.iter
+        self._alloc(new[0].shape[0], self.k)  # reset_stats + a fresh optimizer (train.rs:550-554)
+        self.iter = it
+        out = self.adopt(Splats(new[0], new[2], new[1], new[3], new[4]))
+        return out, RefineStats(n_split, n_clone, alpha_pruned, scale_pruned)
 
     def _peer_step(self, ctx, lr_mean: float, grad_scale: float, st):
         """One brush_dp_adam_step launch: sum of the ranks' gradients on the owned slice -> Adam (train.rs:318-359)

@@ -24,7 +24,7 @@ def timeit(fn, reps=30):
     t = torch.tensor([e0.elapsed_time(e1) / reps], device=dev); dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t)
 for mode, force_p2p in (("peer", "mm/mm"), ("peer", "mm/p2p"), ("peer", "p2p/mm"), ("peer", "p2p/p2p"), ("nccl", False)):
-    tr = SplatTrainer(N, TrainConfig(), dev, sh_coeffs_per_channel=K, process_group=dist.group.WORLD, exchange=mode)
+    tr = SplatTrainer(N, TrainConfig(max_refine_step=0), dev, sh_coeffs_per_channel=K, process_group=dist.group.WORLD, exchange=mode)
     sp = tr.adopt(mk())
     tr.flat_grad.normal_(0, 1e-3)
     if mode == "peer":

@@ -95,7 +95,7 @@ def _train_worker(rank, world, port, out):
     rng = np.random.default_rng(9)
     gts = torch.as_tensor(rng.uniform(0, 1, (4, h, w, 3)).astype(np.float32), device=dev)
     cams = [Camera(*ring_camera_params(w, h, j, 300)) for j in range(4)]
-    cfg = TrainConfig(warmup_steps=0)
+    cfg = TrainConfig(warmup_steps=0, max_refine_step=0)
     results = {}
     for mode in ("nccl", "peer"):
         splats = Splats(t(sc.means), t(sc.sh_coeffs), t(sc.quats), t(sc.raw_opacity), t(sc.log_scales))

@@ -103,7 +103,7 @@ def test_trainer_step_reduces_loss_and_counts_visible():
     rng = np.random.default_rng(0)
     start = Splats(t(sc.means), t(sc.sh_coeffs + rng.normal(0, 0.3, sc.sh_coeffs.shape).astype(np.float32)),
                    t(sc.quats), t(sc.raw_opacity), t(sc.log_scales))
-    cfg = TrainConfig(warmup_steps=0)
+    cfg = TrainConfig(warmup_steps=0, max_refine_step=0)  # statistics from step 1 on, no refinement
     tr = SplatTrainer(n, cfg, DEV, sh_coeffs_per_channel=4)
     losses = []
     for i in range(30):
@@ -161,3 +161,67 @@ def test_image_loss_ssim_forward_and_gradient(channels, h, w):
     with pytest.raises(_lib.BrushError):
         ctx.check(L.brush_image_loss_backward(ctx.handle, p_d.data_ptr(), g_d.data_ptr(), h, w, channels, 0.2, 7,
                                               v_out.data_ptr(), loss.data_ptr(), st))
+
+
+def test_refine_splats_matches_oracle():
+    """SplatTrainer.refine_splats vs the numpy restatement of train.rs:395-553 on the same statistics and draws."""
+    from brush_b200 import Splats, scene
+    from brush_b200.train import SplatTrainer, TrainConfig
+    from oracle import refine_oracle as ro
+
+    n = 5000
+    sc = scene.make_scene(n, 128, 128, 1, 21)
+    rng = np.random.default_rng(2)
+    t = lambda a: torch.as_tensor(np.ascontiguousarray(a, dtype=np.float32), device=DEV)
+    pre = dict(means=sc.means, sh=sc.sh_coeffs, rotation=sc.quats, raw_opacity=sc.raw_opacity,
+               log_scales=np.log(np.exp(sc.log_scales) * rng.choice([0.05, 1.0, 400.0], (n, 1), p=[0.45, 0.5, 0.05]))
+               .astype(np.float32))
+    post = {k: (v + rng.normal(0, 1e-3, v.shape)).astype(np.float32) for k, v in pre.items()}
+    post["raw_opacity"][rng.uniform(size=n) < 0.1] = -8.0  # some transparent ones to prune
+    accum = rng.uniform(0, 6e-4, n).astype(np.float32) * 3
+    counts = rng.integers(0, 4, n).astype(np.float32)
+    for iter_before, reset_every in ((101, 30), (3001, 30)):
+        cfg = TrainConfig(warmup_steps=0)
+        tr = SplatTrainer(n, cfg, DEV, sh_coeffs_per_channel=4)
+        tr.grad_2d_accum.copy_(t(accum))
+        tr.xy_grad_counts.copy_(t(counts))
+        tr.iter = iter_before + 1
+        n_split = int(((accum / np.maximum(counts, 1) >= np.float32(cfg.densify_grad_thresh)) &
+                       ~(np.exp(post["log_scales"]).max(1) < np.float32(cfg.densify_size_thresh))).sum())
+        samples = (rng.normal(0, 0.5, (n_split, 3))).astype(np.float32)
+        order = ("means", "sh", "rotation", "raw_opacity", "log_scales")
+        out, stats = tr.refine_splats([t(pre[k]) for k in order],
+                                      Splats(*[t(post[k]) for k in order]), samples=t(samples))
+        ref, ref_stats = ro.refine(pre, post, accum, counts, samples, iter_before, cfg)
+        assert (stats.num_split, stats.num_cloned, stats.num_transparent_pruned, stats.num_scale_pruned) == ref_stats
+        assert stats.num_split > 0 and stats.num_cloned > 0 and stats.num_transparent_pruned > 0
+        assert stats.num_scale_pruned > stats.num_transparent_pruned
+        got = dict(means=out.means, sh=out.sh_coeffs, rotation=out.rotation, raw_opacity=out.raw_opacity,
+                   log_scales=out.log_scales)
+        for k in order:
+            assert got[k].shape == ref[k].shape, k
+            assert np.allclose(got[k].detach().cpu().numpy(), ref[k], rtol=1e-5, atol=1e-6), k
+        assert tr.n == out.means.shape[0] and float(tr.grad_2d_accum.abs().sum()) == 0.0 and tr.state == {}
+
+
+def test_training_loop_survives_refinement():
+    """A short run with refinement every 5 steps: the splat count changes, buffers are re-made, training goes on."""
+    from brush_b200 import Camera, Splats, scene
+    from brush_b200.scene import bench_camera_params
+    from brush_b200.train import SceneBatch, SplatTrainer, TrainConfig
+
+    w, h, n = 128, 96, 2000
+    sc = scene.make_scene(n, w, h, 0, 5)
+    t = lambda a: torch.as_tensor(a, device=DEV)
+    cam = Camera(*bench_camera_params(w, h))
+    splats = Splats(t(sc.means), t(sc.sh_coeffs), t(sc.quats), t(sc.raw_opacity), t(sc.log_scales))
+    gt = torch.rand((1, h, w, 3), device=DEV)
+    cfg = TrainConfig(warmup_steps=0, refine_every=5, densify_grad_thresh=1e-7, reset_alpha_value=0.05)
+    tr = SplatTrainer(n, cfg, DEV, sh_coeffs_per_channel=1)
+    counts, refines = [], 0
+    for i in range(14):
+        splats, stats = tr.step(SceneBatch(gt, [cam], 1.0), splats)
+        counts.append(splats.num_splats())
+        refines += stats.refine is not None
+        assert np.isfinite(float(stats.loss))
+    assert refines == 3 and counts[-1] != n and tr.n == counts[-1]  # iters 1, 6, 11
