@@ -225,3 +225,41 @@ def test_training_loop_survives_refinement():
         refines += stats.refine is not None
         assert np.isfinite(float(stats.loss))
     assert refines == 3 and counts[-1] != n and tr.n == counts[-1]  # iters 1, 6, 11
+
+
+def test_eval_stats_and_loader_driven_training():
+    """SceneLoader -> SplatTrainer.step on pinned host batches, then eval_stats: PSNR / SSIM against the oracle."""
+    from brush_b200 import Camera, Splats, scene
+    from brush_b200.feed import Scene, SceneLoader, SceneView, eval_stats
+    from brush_b200.scene import ring_camera_params
+    from brush_b200.train import SplatTrainer, TrainConfig
+    from oracle import ssim_oracle as so
+
+    w, h, n = 96, 64, 1500
+    sc = scene.make_scene(n, w, h, 0, 9)
+    t = lambda a: torch.as_tensor(a, device=DEV)
+    target = Splats(t(sc.means), t(sc.sh_coeffs), t(sc.quats), t(sc.raw_opacity), t(sc.log_scales))
+    views = []
+    for j in range(3):
+        cam = Camera(*ring_camera_params(w, h, j, 200))
+        with torch.no_grad():
+            img, _ = target.render(cam, (w, h), False)
+        u8 = (img[..., :3].clamp(0, 1) * 255).round().to(torch.uint8).cpu().numpy()
+        views.append(SceneView(f"view{j}", cam, u8))
+    data = Scene(views)
+    loader = SceneLoader(data, 1, seed=3)
+    splats = Splats(t(sc.means), t(sc.sh_coeffs * 0.5), t(sc.quats), t(sc.raw_opacity), t(sc.log_scales))
+    tr = SplatTrainer(n, TrainConfig(max_refine_step=0), DEV, sh_coeffs_per_channel=1)
+    before = eval_stats(splats, data, None, np.random.default_rng(0), DEV)
+    for _ in range(40):
+        splats, _ = tr.step(loader.next_batch(), splats)
+    loader.close()
+    after = eval_stats(splats, data, 2, np.random.default_rng(0), DEV)
+    assert len(before) == 3 and len(after) == 2
+    assert np.mean([e.psnr for e in after]) > np.mean([e.psnr for e in before]) + 1.0
+    e = after[0]
+    gt = e.view.image.astype(np.float32) / np.float32(255)
+    rgb = e.rendered.cpu().numpy()
+    mse = float(np.mean((rgb.astype(np.float64) - gt) ** 2))
+    assert abs(e.psnr - 10 * np.log10(1 / mse)) < 1e-3
+    assert abs(e.ssim - so.ssim(rgb, gt)) < 5e-6
