@@ -2,14 +2,16 @@
 
     TrainConfig        == train.rs:19-87 (the fields the step uses)
     SceneBatch         == train.rs:89-94
-    SplatTrainer.step  == train.rs:211-393 (render -> L1 loss -> backward -> xy-grad stats -> Adam)
+    SplatTrainer.step  == train.rs:211-393 (render -> image loss -> backward -> xy-grad stats -> Adam -> refine)
+    refine_splats      == train.rs:395-553
 
-Scope: the graded path is render fwd+bwd; loss, Adam, the rotation normalisation and the refine
-statistics are small fused CUDA kernels in libbrush_b200.so so that a benchmarked step is a complete training
-step with no PyTorch arithmetic in it.  The image loss is the reference's (1-w) L1 - w SSIM (ssim.rs) with its
-default window; refine_splats is not built yet (refinement is a no-op).
+Scope: the graded path is render fwd+bwd; loss (L1 + SSIM), Adam, the rotation normalisation and
+the refine statistics are CUDA kernels in libbrush_b200.so, so a benchmarked step is a complete training step with
+no PyTorch arithmetic in it.  refine_splats runs once per `refine_every` steps and is host-orchestrated tensor
+selection / concatenation, like the reference's (Burn ops + argwhere readbacks).
 Multi-GPU: batch views are sharded over ranks; the dense per-Gaussian gradients (+ the two refine
-statistics) are summed with ONE NCCL all-reduce over a flat buffer before the (replicated) Adam step."""
+statistics) are exchanged either by ONE brush_dp_adam_step launch per rank over NVLink peer memory (exchange =
+"peer": sum + Adam + parameter broadcast fused) or by ONE NCCL all-reduce followed by the replicated Adam."""
 from __future__ import annotations
 
 import ctypes as C
@@ -56,6 +58,8 @@ class SceneBatch:  # train.rs:89-94
     gt_images: torch.Tensor          # [B,H,W,C] f32, C = 3 or 4; on the device, or in pinned host memory
     gt_views: List[Camera]
     scene_extent: float = 1.0
+    ready: Optional[object] = None     # CUDA event: the images' host->device copy (SplatTrainer.prefetch)
+    slot: Optional[int] = None         # staging slot the images live in
 
 
 @dataclass
@@ -115,6 +119,7 @@ class SplatTrainer:
         self.exchange = exchange if (process_group is not None and process_group.size() > 1) else "nccl"
         self.peer: Optional[PeerBuffers] = None
         self.epoch = 0
+        self._copy_stream = None
         self._alloc(num_points, sh_coeffs_per_channel)
 
     def _alloc(self, n: int, k: int):
@@ -141,6 +146,29 @@ class SplatTrainer:
         self.v_out = None
         self.gt_dev = None
         self.render_bufs: List = []
+
+    def prefetch(self, batch: SceneBatch) -> SceneBatch:
+        """Starts the host->device copy of a (pinned) batch on a side stream and returns the batch with device
+        images; step() waits for the copy on its own stream.  Two staging slots alternate, so the copy of step
+        t+1 runs under the kernels of step t -- what the reference's SceneLoader prefetch does for its uploads
+        (crates/brush-dataset/src/scene_loader.rs:16-19)."""
+        if batch.gt_images.is_cuda:
+            return batch
+        dev = self.device
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(dev)
+            self._slots, self._slot_free, self._next_slot = [None, None], [None, None], 0
+        k = self._next_slot
+        self._next_slot ^= 1
+        if self._slots[k] is None or self._slots[k].shape != batch.gt_images.shape:
+            self._slots[k] = torch.empty(batch.gt_images.shape, dtype=torch.float32, device=dev)
+        with torch.cuda.stream(self._copy_stream):
+            if self._slot_free[k] is not None:
+                self._copy_stream.wait_event(self._slot_free[k])  # the step that last read this slot is done
+            self._slots[k].copy_(batch.gt_images, non_blocking=True)
+            ready = torch.cuda.Event()
+            ready.record(self._copy_stream)
+        return SceneBatch(self._slots[k], batch.gt_views, batch.scene_extent, ready, k)
 
     def adopt(self, splats: Splats) -> Splats:
         """Peer mode: moves the parameters into this rank's peer-mapped replica and returns Splats whose tensors
@@ -176,6 +204,8 @@ class SplatTrainer:
         outs = (self.g_means, self.g_xy, self.g_scales, self.g_quats, self.g_sh, self.g_opac)
         preds, auxes = [], []
         with torch.cuda.device(dev):
+            if batch.ready is not None:
+                torch.cuda.current_stream(dev).wait_event(batch.ready)
             ctx.check(L.brush_quat_normalize(ctx.handle, p_rot.data_ptr(), self.n, self.norm_rot.data_ptr(), st))
             for i, cam in enumerate(batch.gt_views):  # train.rs:229-237 (batch looped)
                 gt = batch.gt_images[i]
@@ -244,6 +274,9 @@ class SplatTrainer:
             if self.iter - 1 > cfg.warmup_steps:  # train.rs:286-316
                 self.grad_2d_accum.add_(stat_norm, alpha=grad_scale)
                 self.xy_grad_counts.add_(stat_vis)  # select_assign == scatter-ADD in Burn 0.16: a visibility count
+            if batch.slot is not None:
+                self._slot_free[batch.slot] = torch.cuda.Event()
+                self._slot_free[batch.slot].record(torch.cuda.current_stream(dev))
             refine = None
             if do_refine:
                 loss = loss.clone()
