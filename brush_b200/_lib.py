@@ -37,6 +37,14 @@ class BrushAdamGroup(C.Structure):
                 ("sh_rest_lr_scale", C.c_float)]
 
 
+class BrushTrainState(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in (
+        "means", "log_scales", "rotation", "sh_coeffs", "raw_opacity", "m_means", "v_means", "m_log_scales",
+        "v_log_scales", "m_rotation", "v_rotation", "m_sh_coeffs", "v_sh_coeffs", "m_raw_opacity",
+        "v_raw_opacity")] + [(n, C.c_float) for n in (
+            "lr_mean", "lr_scale", "lr_rotation", "lr_coeffs_dc", "lr_opac", "sh_rest_lr_scale")]
+
+
 DP_MAX_WORLD = 8
 
 
@@ -80,6 +88,9 @@ _SIGS = {
                              [C.c_void_p] * 5 + [C.c_int, C.c_void_p, C.POINTER(BrushAux), C.c_void_p]),
     "brush_render_backward": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32] + [C.c_void_p] * 6 +
                               [C.POINTER(BrushAux)] + [C.c_void_p] * 6 + [C.c_void_p]),
+    "brush_render_backward_adam": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(BrushTrainState),
+                                             C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(BrushAux), C.c_void_p,
+                                             C.c_float, C.c_float, C.c_float, C.c_uint32, C.c_float, C.c_void_p]),
     "brush_radix_argsort_u32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32,
                                           C.c_void_p, C.c_void_p, C.c_void_p]),
     "brush_radix_argsort_u64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32,

@@ -379,6 +379,61 @@ int brush_render_backward(brush_ctx* ctx, uint32_t N, uint32_t K, const float* m
     return BRUSH_OK;
 }
 
+int brush_render_backward_adam(brush_ctx* ctx, uint32_t N, uint32_t K, const BrushTrainState* state,
+                               const float* quats, const float* out_img, const float* v_out_img,
+                               const BrushAux* aux, float* v_xy, float beta1, float beta2, float eps,
+                               uint32_t step, float grad_scale, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (!valid_k(K)) return fail(ctx, BRUSH_E_INVALID, "Invalid nr. of sh bases " + std::to_string(K));
+    if (!aux || !out_img || !v_out_img || !state || step < 1) return fail(ctx, BRUSH_E_INVALID, "null argument");
+    const BrushTrainState& s = *state;
+    if (N > 0 && (!quats || !v_xy || !s.means || !s.log_scales || !s.rotation || !s.sh_coeffs || !s.raw_opacity ||
+                  !s.m_means || !s.v_means || !s.m_log_scales || !s.v_log_scales || !s.m_rotation || !s.v_rotation ||
+                  !s.m_sh_coeffs || !s.v_sh_coeffs || !s.m_raw_opacity || !s.v_raw_opacity))
+        return fail(ctx, BRUSH_E_INVALID, "null argument");
+    if (((uintptr_t)s.rotation | (uintptr_t)s.m_rotation | (uintptr_t)s.v_rotation | (uintptr_t)s.sh_coeffs |
+         (uintptr_t)s.m_sh_coeffs | (uintptr_t)s.v_sh_coeffs | (uintptr_t)quats) & 15u)
+        return fail(ctx, BRUSH_E_INVALID, "rotation / sh_coeffs buffers must be 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(ctx->device));
+    BrushUniforms u;
+    bool cached = false;
+    for (auto& e : ctx->uni_cache)
+        if (e.first == aux->uniforms_buffer) { u = e.second; cached = true; }
+    if (!cached) {
+        CU(cudaMemcpyAsync(&u, aux->uniforms_buffer, sizeof(u), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+    }
+    if (u.total_splats != N || u.sh_degree != degree_of(K))
+        return fail(ctx, BRUSH_E_INVALID, "aux.uniforms_buffer does not match N / K");
+    const Cam cam = make_cam(u);
+    ENSURE(v_projected, (size_t)N * VP_STRIDE * 4 + 16);
+    ctx->ev_used[BRUSH_STAGE_RASTERIZE_BWD] = ctx->ev_used[BRUSH_STAGE_GATHER_PROJECT_BWD] = false;
+    if (N) CU(cudaMemsetAsync(ctx->v_projected.p, 0, (size_t)N * VP_STRIDE * 4, st));
+    {
+        StageTimer t(ctx, st, BRUSH_STAGE_RASTERIZE_BWD);
+        launch_rasterize_backward(cam, (uint32_t*)aux->compact_gid_from_isect, (uint32_t*)aux->tile_bins,
+                                  aux->projected_splats, (uint32_t*)aux->global_from_compact_gid,
+                                  (uint32_t*)aux->final_index, out_img, v_out_img, (float*)ctx->v_projected.p, st);
+    }
+    FusedAdamLaunch A{};
+    A.means = s.means; A.log_scales = s.log_scales; A.rotation = s.rotation; A.sh = s.sh_coeffs; A.raw_opac = s.raw_opacity;
+    A.m_means = s.m_means; A.v_means = s.v_means; A.m_scales = s.m_log_scales; A.v_scales = s.v_log_scales;
+    A.m_rot = s.m_rotation; A.v_rot = s.v_rotation; A.m_sh = s.m_sh_coeffs; A.v_sh = s.v_sh_coeffs;
+    A.m_opac = s.m_raw_opacity; A.v_opac = s.v_raw_opacity;
+    A.lr_mean = s.lr_mean; A.lr_scale = s.lr_scale; A.lr_rot = s.lr_rotation; A.lr_sh_dc = s.lr_coeffs_dc;
+    A.lr_sh_rest = s.lr_coeffs_dc * s.sh_rest_lr_scale; A.lr_opac = s.lr_opac;
+    A.beta1 = beta1; A.beta2 = beta2; A.eps = eps; A.grad_scale = grad_scale;
+    A.inv_bc1 = (float)(1.0 / (1.0 - std::pow((double)beta1, (double)step)));
+    A.inv_bc2 = (float)(1.0 / (1.0 - std::pow((double)beta2, (double)step)));
+    {   // gather_grads + project_backwards + normalisation VJP + Adam in one pass
+        StageTimer t(ctx, st, BRUSH_STAGE_GATHER_PROJECT_BWD);
+        launch_backward_adam(cam, N, K, quats, (float*)ctx->v_projected.p, A, v_xy, st);
+    }
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
+
 int brush_radix_argsort_u32(brush_ctx* ctx, const uint32_t* keys, const uint32_t* values, const int32_t* n_dev,
                             uint32_t max_n, uint32_t bits, uint32_t* keys_out, uint32_t* values_out, void* stream) {
     if (!ctx) return BRUSH_E_INVALID;

@@ -37,6 +37,52 @@ BD V3 cov2d_to_conic_vjp(V3 conic, V3 v_conic) {  // project_backwards.wgsl:59-7
     return {-S.c[0].x, -(S.c[1].x + S.c[0].y), -S.c[1].y};
 }
 
+// project_backwards.wgsl:83-226: VJP of (mean, scale = exp(log_scale), quat) -> (xy, conic) for one splat.
+BD void project_backward_chain(const Cam& cam, V3 mean, V3 scale, V4 quat, V2 v_xy, V3 v_conic, V3& v_mean_out,
+                               V3& v_log_scale_out, V4& v_quat_out) {
+    const M3& W = cam.W;
+    const V3 p_view = mul(W, mean) + cam.t;
+    V3 v_mean = mul(transpose(W), project_pix_vjp(cam, p_view, v_xy));
+    const V3 cov2d = calc_cov2d(cam, p_view, scale, quat);
+    const V3 conic = cov_to_conic(cov2d);
+    const V3 v_cov2d = cov2d_to_conic_vjp(conic, v_conic);
+    const float rz = 1.0f / p_view.z;
+    const float rz2 = rz * rz;
+    const M3 J = {{{cam.fx * rz, 0.f, 0.f}, {0.f, cam.fy * rz, 0.f},
+                   {-cam.fx * p_view.x * rz2, -cam.fy * p_view.y * rz2, 0.f}}};  // no frustum clamp here (quirk)
+    const M3 R = quat_to_rotmat(quat);
+    const M3 S = {{{scale.x, 0.f, 0.f}, {0.f, scale.y, 0.f}, {0.f, 0.f, scale.z}}};
+    const M3 M = mul(R, S);
+    const M3 V = mul(M, transpose(M));
+    const M3 v_cov = {{{v_cov2d.x, 0.5f * v_cov2d.y, 0.f}, {0.5f * v_cov2d.y, v_cov2d.z, 0.f}, {0.f, 0.f, 0.f}}};
+    const M3 T = mul(J, W);
+    const M3 v_V = mul(mul(transpose(T), v_cov), T);
+    const M3 v_T = add(mul(mul(v_cov, T), transpose(V)), mul(mul(transpose(v_cov), T), V));
+    const float v_cov3d0 = v_V.c[0].x;
+    const float v_cov3d1 = v_V.c[0].y + v_V.c[1].x;
+    const float v_cov3d2 = v_V.c[0].z + v_V.c[2].x;
+    const float v_cov3d3 = v_V.c[1].y;
+    const float v_cov3d4 = v_V.c[1].z + v_V.c[2].y;
+    const float v_cov3d5 = v_V.c[2].z;
+    const M3 v_J = mul(v_T, transpose(W));
+    const float rz3 = rz2 * rz;
+    const V3 v_t = {-cam.fx * rz2 * v_J.c[2].x, -cam.fy * rz2 * v_J.c[2].y,
+                    -cam.fx * rz2 * v_J.c[0].x + 2.0f * cam.fx * p_view.x * rz3 * v_J.c[2].x -
+                        cam.fy * rz2 * v_J.c[1].y + 2.0f * cam.fy * p_view.y * rz3 * v_J.c[2].y};
+    v_mean = v_mean + V3{dot3(v_t, W.c[0]), dot3(v_t, W.c[1]), dot3(v_t, W.c[2])};
+    const M3 v_V_symm = {{{v_cov3d0, 0.5f * v_cov3d1, 0.5f * v_cov3d2},
+                          {0.5f * v_cov3d1, v_cov3d3, 0.5f * v_cov3d4},
+                          {0.5f * v_cov3d2, 0.5f * v_cov3d4, v_cov3d5}}};
+    const M3 v_M = mul(scale_all(v_V_symm, 2.0f), M);
+    const V3 v_scale = {dot3(R.c[0], v_M.c[0]), dot3(R.c[1], v_M.c[1]), dot3(R.c[2], v_M.c[2])};
+    const M3 v_R = mul(v_M, S);
+    const V4 v_quat = quat_to_rotmat_vjp(quat, v_R);
+
+    v_mean_out = v_mean;
+    v_log_scale_out = {v_scale.x * scale.x, v_scale.y * scale.y, v_scale.z * scale.z};
+    v_quat_out = v_quat;
+}
+
 template <int K>
 __global__ void __launch_bounds__(256)
 gather_project_backward_kernel(const __grid_constant__ Cam cam, const float* __restrict__ means,
@@ -106,49 +152,14 @@ gather_project_backward_kernel(const __grid_constant__ Cam cam, const float* __r
         reinterpret_cast<float2*>(v_xy_out)[g] = make_float2(v_xy.x, v_xy.y);
     }
 
-    // ---- project_backwards.wgsl:83-226 ----
-    const M3& W = cam.W;
-    const V3 p_view = mul(W, mean) + cam.t;
-    V3 v_mean = mul(transpose(W), project_pix_vjp(cam, p_view, v_xy));
-    const V3 cov2d = calc_cov2d(cam, p_view, scale, quat);
-    const V3 conic = cov_to_conic(cov2d);
-    const V3 v_cov2d = cov2d_to_conic_vjp(conic, v_conic);
-    const float rz = 1.0f / p_view.z;
-    const float rz2 = rz * rz;
-    const M3 J = {{{cam.fx * rz, 0.f, 0.f}, {0.f, cam.fy * rz, 0.f},
-                   {-cam.fx * p_view.x * rz2, -cam.fy * p_view.y * rz2, 0.f}}};  // no frustum clamp here (quirk)
-    const M3 R = quat_to_rotmat(quat);
-    const M3 S = {{{scale.x, 0.f, 0.f}, {0.f, scale.y, 0.f}, {0.f, 0.f, scale.z}}};
-    const M3 M = mul(R, S);
-    const M3 V = mul(M, transpose(M));
-    const M3 v_cov = {{{v_cov2d.x, 0.5f * v_cov2d.y, 0.f}, {0.5f * v_cov2d.y, v_cov2d.z, 0.f}, {0.f, 0.f, 0.f}}};
-    const M3 T = mul(J, W);
-    const M3 v_V = mul(mul(transpose(T), v_cov), T);
-    const M3 v_T = add(mul(mul(v_cov, T), transpose(V)), mul(mul(transpose(v_cov), T), V));
-    const float v_cov3d0 = v_V.c[0].x;
-    const float v_cov3d1 = v_V.c[0].y + v_V.c[1].x;
-    const float v_cov3d2 = v_V.c[0].z + v_V.c[2].x;
-    const float v_cov3d3 = v_V.c[1].y;
-    const float v_cov3d4 = v_V.c[1].z + v_V.c[2].y;
-    const float v_cov3d5 = v_V.c[2].z;
-    const M3 v_J = mul(v_T, transpose(W));
-    const float rz3 = rz2 * rz;
-    const V3 v_t = {-cam.fx * rz2 * v_J.c[2].x, -cam.fy * rz2 * v_J.c[2].y,
-                    -cam.fx * rz2 * v_J.c[0].x + 2.0f * cam.fx * p_view.x * rz3 * v_J.c[2].x -
-                        cam.fy * rz2 * v_J.c[1].y + 2.0f * cam.fy * p_view.y * rz3 * v_J.c[2].y};
-    v_mean = v_mean + V3{dot3(v_t, W.c[0]), dot3(v_t, W.c[1]), dot3(v_t, W.c[2])};
-    const M3 v_V_symm = {{{v_cov3d0, 0.5f * v_cov3d1, 0.5f * v_cov3d2},
-                          {0.5f * v_cov3d1, v_cov3d3, 0.5f * v_cov3d4},
-                          {0.5f * v_cov3d2, 0.5f * v_cov3d4, v_cov3d5}}};
-    const M3 v_M = mul(scale_all(v_V_symm, 2.0f), M);
-    const V3 v_scale = {dot3(R.c[0], v_M.c[0]), dot3(R.c[1], v_M.c[1]), dot3(R.c[2], v_M.c[2])};
-    const M3 v_R = mul(v_M, S);
-    const V4 v_quat = quat_to_rotmat_vjp(quat, v_R);
+    V3 v_mean, v_log_scale;
+    V4 v_quat;
+    project_backward_chain(cam, mean, scale, quat, v_xy, v_conic, v_mean, v_log_scale, v_quat);
 
     v_means[3 * (size_t)g] = v_mean.x; v_means[3 * (size_t)g + 1] = v_mean.y; v_means[3 * (size_t)g + 2] = v_mean.z;
-    v_log_scales[3 * (size_t)g] = v_scale.x * scale.x;
-    v_log_scales[3 * (size_t)g + 1] = v_scale.y * scale.y;
-    v_log_scales[3 * (size_t)g + 2] = v_scale.z * scale.z;
+    v_log_scales[3 * (size_t)g] = v_log_scale.x;
+    v_log_scales[3 * (size_t)g + 1] = v_log_scale.y;
+    v_log_scales[3 * (size_t)g + 2] = v_log_scale.z;
     reinterpret_cast<float4*>(v_quats)[g] = make_float4(v_quat.x, v_quat.y, v_quat.z, v_quat.w);
 }
 
@@ -169,6 +180,163 @@ void launch_gather_project_backward(const Cam& cam, uint32_t N, uint32_t K, cons
         case 25: gather_project_backward_kernel<25><<<grid, block, 0, st>>>(GB_ARGS); break;
     }
 #undef GB_ARGS
+}
+
+// ---------------------------------------------------------------------------------------------
+// Single-device fast path: the per-splat backward, the VJP of the rotation normalisation and the Adam update of
+// all five parameter groups in ONE pass, so the dense gradients (244 B per splat at SH degree 3) are never written
+// to or re-read from HBM.  == gather_grads + project_backwards (above) -> autodiff of
+// gaussian_splats.rs:174-175 -> the five optim.step calls of train.rs:318-359, same formulas and operation order
+// as gather_project_backward_kernel + quat_normalize_vjp_kernel + adam_kernel.
+//   phase 1 (thread = splat): nine sums -> v_mean, v_log_scale, v_quat (+ normalisation VJP), v_opac; Adam on
+//       those 11 parameters; SH basis and v_rgb of the splat go to shared memory; v_xy is written out for the
+//       refine statistics.
+//   phase 2 (block-cooperative): the block's 256 SH rows are contiguous, so parameter and moments stream through
+//       as coalesced float4s; element e of row s has gradient basis[s][e / 3] * v_rgb[s][e % 3].
+BD void adam_update(float& p, float g, float& m, float& v, float lr, const FusedAdamLaunch& A) {
+    p = adam_update_value(p, g, m, v, lr, A.beta1, A.beta2, A.eps, A.inv_bc1, A.inv_bc2, A.grad_scale);
+}
+
+#ifndef BA_MINB
+#define BA_MINB 2
+#endif
+template <int K>
+__global__ void __launch_bounds__(256, BA_MINB)
+backward_adam_kernel(const __grid_constant__ Cam cam, const float* __restrict__ norm_quats,
+                     const float* __restrict__ v_projected, const __grid_constant__ FusedAdamLaunch A,
+                     float* __restrict__ v_xy_out) {
+    constexpr int ROW = K + 3;
+    __shared__ float s_sh[256][ROW + 1];  // basis[K], v_rgb[3]
+    const uint32_t N = cam.total_splats;
+    const uint32_t g = blockIdx.x * 256u + threadIdx.x;
+    if (g < N) {
+        const float4* vp = reinterpret_cast<const float4*>(v_projected + (size_t)g * VP_STRIDE);
+        const float4 vp0 = vp[0], vp1 = vp[1];
+        const float v_alpha = reinterpret_cast<const float*>(vp)[8];
+        const bool zero = vp0.x == 0.f && vp0.y == 0.f && vp0.z == 0.f && vp0.w == 0.f && vp1.x == 0.f &&
+                          vp1.y == 0.f && vp1.z == 0.f && vp1.w == 0.f && v_alpha == 0.f;
+        float mean[3] = {A.means[3 * (size_t)g], A.means[3 * (size_t)g + 1], A.means[3 * (size_t)g + 2]};
+        float ls[3] = {A.log_scales[3 * (size_t)g], A.log_scales[3 * (size_t)g + 1], A.log_scales[3 * (size_t)g + 2]};
+        float4 q_raw = reinterpret_cast<const float4*>(A.rotation)[g];
+        float opac = A.raw_opac[g];
+        V3 v_mean = {0.f, 0.f, 0.f}, v_ls = {0.f, 0.f, 0.f};
+        V4 v_q = {0.f, 0.f, 0.f, 0.f};
+        float v_opac = 0.f;
+        float b[K];
+#pragma unroll
+        for (int k = 0; k < K; k++) b[k] = 0.f;
+        if (!zero) {  // all outputs are linear in the nine sums: an all-zero row gives exact zeros
+            const V3 mean_v = {mean[0], mean[1], mean[2]};
+            const V3 scale = {__expf(ls[0]), __expf(ls[1]), __expf(ls[2])};
+            const float4 q4 = __ldg(reinterpret_cast<const float4*>(norm_quats) + g);
+            project_backward_chain(cam, mean_v, scale, V4{q4.x, q4.y, q4.z, q4.w}, V2{vp0.x, vp0.y},
+                                   V3{vp0.z, vp0.w, vp1.x}, v_mean, v_ls, v_q);
+            // VJP of q / |q| (quat_normalize_vjp_kernel)
+            const float inv = 1.0f / sqrtf(q_raw.x * q_raw.x + q_raw.y * q_raw.y + q_raw.z * q_raw.z + q_raw.w * q_raw.w);
+            const float hx = q_raw.x * inv, hy = q_raw.y * inv, hz = q_raw.z * inv, hw = q_raw.w * inv;
+            const float d = hx * v_q.x + hy * v_q.y + hz * v_q.z + hw * v_q.w;
+            v_q = {(v_q.x - hx * d) * inv, (v_q.y - hy * d) * inv, (v_q.z - hz * d) * inv, (v_q.w - hw * d) * inv};
+            const float sgm = 1.0f / (1.0f + __expf(-opac));
+            v_opac = v_alpha * (sgm * (1.0f - sgm));
+            const V3 dv = mean_v - cam.t;
+            sh_basis<K>(cam.sh_degree, dv * rsqrtf(dot3(dv, dv)), b);
+        }
+        reinterpret_cast<float2*>(v_xy_out)[g] = make_float2(vp0.x, vp0.y);
+#pragma unroll
+        for (int k = 0; k < K; k++) s_sh[threadIdx.x][k] = b[k];
+        s_sh[threadIdx.x][K] = vp1.y; s_sh[threadIdx.x][K + 1] = vp1.z; s_sh[threadIdx.x][K + 2] = vp1.w;
+        // Adam on the 11 per-splat parameters (order of train.rs:320-356: means, opacity, [sh], rotation, scale)
+        const float gm[3] = {v_mean.x, v_mean.y, v_mean.z}, gs[3] = {v_ls.x, v_ls.y, v_ls.z};
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            const size_t e = 3 * (size_t)g + c;
+            float m = A.m_means[e], v = A.v_means[e];
+            adam_update(mean[c], gm[c], m, v, A.lr_mean, A);
+            A.means[e] = mean[c]; A.m_means[e] = m; A.v_means[e] = v;
+            m = A.m_scales[e]; v = A.v_scales[e];
+            adam_update(ls[c], gs[c], m, v, A.lr_scale, A);
+            A.log_scales[e] = ls[c]; A.m_scales[e] = m; A.v_scales[e] = v;
+        }
+        {
+            float m = A.m_opac[g], v = A.v_opac[g];
+            adam_update(opac, v_opac, m, v, A.lr_opac, A);
+            A.raw_opac[g] = opac; A.m_opac[g] = m; A.v_opac[g] = v;
+            float4 m4 = reinterpret_cast<float4*>(A.m_rot)[g], v4 = reinterpret_cast<float4*>(A.v_rot)[g];
+            adam_update(q_raw.x, v_q.x, m4.x, v4.x, A.lr_rot, A);
+            adam_update(q_raw.y, v_q.y, m4.y, v4.y, A.lr_rot, A);
+            adam_update(q_raw.z, v_q.z, m4.z, v4.z, A.lr_rot, A);
+            adam_update(q_raw.w, v_q.w, m4.w, v4.w, A.lr_rot, A);
+            reinterpret_cast<float4*>(A.rotation)[g] = q_raw;
+            reinterpret_cast<float4*>(A.m_rot)[g] = m4;
+            reinterpret_cast<float4*>(A.v_rot)[g] = v4;
+        }
+    }
+    __syncthreads();
+    // phase 2: the block's SH rows, [256][3K] floats, contiguous and 16-byte aligned (256 * 3K is a multiple of 4)
+    const size_t total = (size_t)N * (3 * K);
+    const size_t base = (size_t)blockIdx.x * 256u * (3 * K);
+    constexpr int F4 = 256 * 3 * K / 4;
+    constexpr int U = 4;  // float4 triples in flight per thread: the pass is pure streaming, latency-bound otherwise
+    for (int i0 = threadIdx.x; i0 < F4; i0 += 256 * U) {
+        float4 p[U], m[U], v[U];
+        bool full[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int i = i0 + 256 * u;
+            const size_t e0 = base + 4 * (size_t)i;
+            full[u] = i < F4 && e0 + 3 < total;
+            if (full[u]) {
+                p[u] = *reinterpret_cast<const float4*>(A.sh + e0);
+                m[u] = *reinterpret_cast<const float4*>(A.m_sh + e0);
+                v[u] = *reinterpret_cast<const float4*>(A.v_sh + e0);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int i = i0 + 256 * u;
+            const size_t e0 = base + 4 * (size_t)i;
+            if (i >= F4 || e0 >= total) continue;
+            float gsh[4], lr[4];
+            int srow = (4 * i) / (3 * K), r = 4 * i - srow * (3 * K), kk = r / 3, ch = r - 3 * kk;
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                gsh[c] = s_sh[srow][kk] * s_sh[srow][K + ch];
+                lr[c] = r >= 3 ? A.lr_sh_rest : A.lr_sh_dc;
+                r++;
+                if (++ch == 3) { ch = 0; kk++; }
+                if (r == 3 * K) { r = 0; kk = 0; srow++; }
+            }
+            if (full[u]) {
+                adam_update(p[u].x, gsh[0], m[u].x, v[u].x, lr[0], A);
+                adam_update(p[u].y, gsh[1], m[u].y, v[u].y, lr[1], A);
+                adam_update(p[u].z, gsh[2], m[u].z, v[u].z, lr[2], A);
+                adam_update(p[u].w, gsh[3], m[u].w, v[u].w, lr[3], A);
+                *reinterpret_cast<float4*>(A.sh + e0) = p[u];
+                *reinterpret_cast<float4*>(A.m_sh + e0) = m[u];
+                *reinterpret_cast<float4*>(A.v_sh + e0) = v[u];
+            } else {  // the last, partial float4 of the whole array
+                for (int c = 0; c < 4 && e0 + c < total; c++) {
+                    float ps = A.sh[e0 + c], ms = A.m_sh[e0 + c], vs = A.v_sh[e0 + c];
+                    adam_update(ps, gsh[c], ms, vs, lr[c], A);
+                    A.sh[e0 + c] = ps; A.m_sh[e0 + c] = ms; A.v_sh[e0 + c] = vs;
+                }
+            }
+        }
+    }
+}
+
+void launch_backward_adam(const Cam& cam, uint32_t N, uint32_t K, const float* norm_quats, const float* v_projected,
+                          const FusedAdamLaunch& A, float* v_xy, cudaStream_t st) {
+    if (N == 0) return;
+    dim3 grid((N + 255) / 256), block(256);
+    g_launch_count++;
+    switch (K) {
+        case 1: backward_adam_kernel<1><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy); break;
+        case 4: backward_adam_kernel<4><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy); break;
+        case 9: backward_adam_kernel<9><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy); break;
+        case 16: backward_adam_kernel<16><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy); break;
+        case 25: backward_adam_kernel<25><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy); break;
+    }
 }
 
 }  // namespace brush

@@ -55,10 +55,7 @@ __device__ __forceinline__ void wait_flags(const uint32_t* my_flags, int which, 
 }
 
 __device__ __forceinline__ float adam_elem(float p, float g, float& m, float& v, float lr, const DpLaunch& L) {
-    g *= L.grad_scale;
-    m = L.beta1 * m + (1.0f - L.beta1) * g;
-    v = L.beta2 * v + (1.0f - L.beta2) * g * g;
-    return p - lr * ((m * L.inv_bc1) / (sqrtf(v * L.inv_bc2) + L.eps));
+    return adam_update_value(p, g, m, v, lr, L.beta1, L.beta2, L.eps, L.inv_bc1, L.inv_bc2, L.grad_scale);
 }
 
 template <bool MM_LD, bool MM_ST>

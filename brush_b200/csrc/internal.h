@@ -80,6 +80,35 @@ void launch_gather_project_backward(const Cam& cam, uint32_t N, uint32_t K, cons
                                     const float* v_projected, float* v_means, float* v_xy, float* v_log_scales,
                                     float* v_quats, float* v_coeffs, float* v_raw_opac, cudaStream_t st);
 
+#ifdef __CUDACC__
+// The one Adam update every optimizer kernel uses (adam_kernel, dp_adam_kernel, backward_adam_kernel), so the three
+// step paths give the same bits on the same gradients.  == AdamState::step of Burn 0.16 as brush-train calls it
+// (train.rs:318-359): bias-corrected moments, p -= lr * m_hat / (sqrt(v_hat) + eps).  div.approx / sqrt.approx
+// (<= 2 ulp / 1 ulp): the IEEE sequences take their slow path whenever v is tiny -- every splat a view does not
+// see -- and WGSL's own `/` and `sqrt` are not correctly rounded either (2.5 ulp).
+__device__ __forceinline__ float adam_update_value(float p, float g, float& m, float& v, float lr, float beta1,
+                                                   float beta2, float eps, float inv_bc1, float inv_bc2,
+                                                   float grad_scale) {
+    // explicit roundings: the compiler may not contract these differently in different kernels
+    g = __fmul_rn(g, grad_scale);
+    m = __fmaf_rn(beta1, m, __fmul_rn(1.0f - beta1, g));
+    v = __fmaf_rn(beta2, v, __fmul_rn(__fmul_rn(1.0f - beta2, g), g));
+    float root;
+    asm("sqrt.approx.f32 %0, %1;" : "=f"(root) : "f"(__fmul_rn(v, inv_bc2)));
+    return __fmaf_rn(-lr, __fdividef(__fmul_rn(m, inv_bc1), __fadd_rn(root, eps)), p);
+}
+#endif
+
+// Fused single-device backward tail (backward.cu): parameters are updated in place.
+struct FusedAdamLaunch {
+    float *means, *log_scales, *rotation, *sh, *raw_opac;
+    float *m_means, *v_means, *m_scales, *v_scales, *m_rot, *v_rot, *m_sh, *v_sh, *m_opac, *v_opac;
+    float lr_mean, lr_scale, lr_rot, lr_sh_dc, lr_sh_rest, lr_opac;
+    float beta1, beta2, eps, inv_bc1, inv_bc2, grad_scale;
+};
+void launch_backward_adam(const Cam& cam, uint32_t N, uint32_t K, const float* norm_quats, const float* v_projected,
+                          const FusedAdamLaunch& A, float* v_xy, cudaStream_t st);
+
 // ---- optim.cu ----
 extern std::atomic<uint64_t> g_launch_count;  // kernels launched by this library (bench.py's gpu_launches)
 struct AdamSeg {

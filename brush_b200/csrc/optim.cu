@@ -61,10 +61,7 @@ void launch_l1_loss_backward(const float* pred, const float* gt, uint32_t P, uin
 // use lr * sh_rest_scale (the reference's 1/lr_coeffs_sh_scale lerp, train.rs:334-348; Adam's update is linear
 // in lr so the lerp is exactly a smaller lr).
 __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, float lr, const AdamLaunch& L) {
-    g *= L.grad_scale;
-    m = L.beta1 * m + (1.0f - L.beta1) * g;
-    v = L.beta2 * v + (1.0f - L.beta2) * g * g;
-    p -= lr * ((m * L.inv_bc1) / (sqrtf(v * L.inv_bc2) + L.eps));
+    p = adam_update_value(p, g, m, v, lr, L.beta1, L.beta2, L.eps, L.inv_bc1, L.inv_bc2, L.grad_scale);
 }
 
 __global__ void __launch_bounds__(256)

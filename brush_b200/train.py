@@ -104,7 +104,7 @@ class SplatTrainer:
     # flat buffer layout: means 3N | xy 2N | log_scales 3N | quats 4N | sh 3KN | opac N | grad-norm N | visible N
     def __init__(self, num_points: int, config: TrainConfig, device, sh_coeffs_per_channel: int = 1,
                  process_group=None, isect_capacity: Optional[int] = None, optimize: bool = True,
-                 exchange: str = "nccl"):
+                 exchange: str = "nccl", fused_tail: bool = True):
         if config.ssim_weight > 0.0 and config.ssim_window_size != 11:
             raise ValueError("ssim_window_size must be 11 (the only window the loss kernel implements)")
         self.config = config
@@ -113,6 +113,7 @@ class SplatTrainer:
         self.pg = process_group
         self.isect_capacity = isect_capacity
         self.optimize = optimize
+        self.fused_tail = fused_tail  # single device, one view per step: backward tail + Adam in one kernel
         if exchange not in ("nccl", "peer"):
             raise ValueError("exchange must be 'nccl' or 'peer'")
         # "peer": gradient sum + Adam + parameter broadcast as one launch over NVLink peer memory (parallel.py)
@@ -203,7 +204,13 @@ class SplatTrainer:
         p_sh, p_opac, p_rot = splats.sh_coeffs.detach(), splats.raw_opacity.detach(), splats.rotation.detach()
         outs = (self.g_means, self.g_xy, self.g_scales, self.g_quats, self.g_sh, self.g_opac)
         preds, auxes = [], []
+        fused = self.fused_tail and self.optimize and world == 1 and B == 1 and self.peer is None
+        # train.rs:361-365 (iter = the value before this step's increment)
+        do_refine = (self.iter < cfg.max_refine_step and self.iter >= cfg.warmup_steps
+                     and self.iter % cfg.refine_every == 1 and self.optimize)
         with torch.cuda.device(dev):
+            pre_step = [p.detach().clone() for p in (splats.means, splats.sh_coeffs, splats.rotation,
+                                                     splats.raw_opacity, splats.log_scales)] if do_refine else None
             if batch.ready is not None:
                 torch.cuda.current_stream(dev).wait_event(batch.ready)
             ctx.check(L.brush_quat_normalize(ctx.handle, p_rot.data_ptr(), self.n, self.norm_rot.data_ptr(), st))
@@ -232,8 +239,14 @@ class SplatTrainer:
                     if self.tmp is None:
                         self.tmp = tuple(torch.empty_like(v) for v in outs)
                     dst = self.tmp
-                render_backward(aux, p_means, p_scales, self.norm_rot, p_sh.shape, p_opac, pred, self.v_out, ctx=ctx,
-                                out=dst)
+                if fused:
+                    # single device, one view: per-splat backward + normalisation VJP + Adam in one kernel; the
+                    # dense gradients are never materialised (only v_xy, for the refine statistics)
+                    lr_mean = self._lr_mean(batch)
+                    self._backward_adam(ctx, splats, aux, pred, lr_mean, st)
+                else:
+                    render_backward(aux, p_means, p_scales, self.norm_rot, p_sh.shape, p_opac, pred, self.v_out,
+                                    ctx=ctx, out=dst)
                 # refine statistics are per view, BEFORE the reduction (the norm is nonlinear; train.rs:300-314)
                 caux = aux._c()
                 ctx.check(L.brush_xy_grad_stats(ctx.handle, dst[1].data_ptr(), C.byref(caux), self.n, W, H,
@@ -245,17 +258,11 @@ class SplatTrainer:
                 preds.append(pred)
                 auxes.append(aux)
             grad_scale = global_grad_scale(B, world)
-            # VJP of the rotation normalisation (Burn autodiff in the reference); linear, so it commutes with the sum
-            ctx.check(L.brush_quat_normalize_vjp(ctx.handle, p_rot.data_ptr(), self.n, self.g_quats.data_ptr(), st))
-            # ExponentialLrScheduler (Burn 0.16): step k (1-based) returns initial_lr * gamma^(k-1); train.rs:276-278
-            lr_mean = cfg.lr_mean * cfg.lr_mean_decay ** self.iter
-            if cfg.scale_mean_lr_by_extent:
-                lr_mean *= batch.scene_extent
-            # train.rs:361-365 (iter = the value before this step's increment)
-            do_refine = (self.iter < cfg.max_refine_step and self.iter >= cfg.warmup_steps
-                         and self.iter % cfg.refine_every == 1 and self.optimize)
-            pre_step = [p.detach().clone() for p in (splats.means, splats.sh_coeffs, splats.rotation,
-                                                     splats.raw_opacity, splats.log_scales)] if do_refine else None
+            lr_mean = self._lr_mean(batch)
+            if not fused:
+                # VJP of the rotation normalisation (Burn autodiff in the reference); linear: commutes with the sum
+                ctx.check(L.brush_quat_normalize_vjp(ctx.handle, p_rot.data_ptr(), self.n, self.g_quats.data_ptr(),
+                                                     st))
             self.iter += 1
             if self.peer is not None:
                 if splats.means.data_ptr() != self.peer.param.data_ptr() + 4 * self.param_layout.offset("means"):
@@ -268,7 +275,7 @@ class SplatTrainer:
                     allreduce_flat(self.flat_grad, self.pg)  # ONE NCCL all-reduce over NVLink
                     allreduce_flat(self.loss_total, self.pg)
                 stat_norm, stat_vis = self.stat_grad_norm, self.stat_visible
-                if self.optimize:
+                if self.optimize and not fused:
                     self._adam(ctx, splats, lr_mean, grad_scale, st)
                 loss = self.loss_total * grad_scale if (B * world) > 1 else self.loss_total
             if self.iter - 1 > cfg.warmup_steps:  # train.rs:286-316
@@ -370,6 +377,31 @@ class SplatTrainer:
                                                 cfg.adam_beta2, cfg.adam_eps, self.iter, grad_scale, st))
         views = pl.views(peer.param)
         return views[5], views[6]
+
+    def _lr_mean(self, batch: SceneBatch) -> float:
+        """ExponentialLrScheduler (Burn 0.16): step k (1-based) returns initial_lr * gamma^(k-1); train.rs:276-278."""
+        cfg = self.config
+        lr_mean = cfg.lr_mean * cfg.lr_mean_decay ** self.iter
+        if cfg.scale_mean_lr_by_extent:
+            lr_mean *= batch.scene_extent
+        return lr_mean
+
+    def _backward_adam(self, ctx, splats: Splats, aux, pred, lr_mean: float, st):
+        cfg = self.config
+        S = _lib.BrushTrainState()
+        for field, name, p in (("means", "means", splats.means), ("raw_opacity", "opac", splats.raw_opacity),
+                               ("sh_coeffs", "sh", splats.sh_coeffs), ("rotation", "rot", splats.rotation),
+                               ("log_scales", "scale", splats.log_scales)):
+            m, v = self._adam_state(name, p)
+            setattr(S, field, p.data_ptr())
+            setattr(S, "m_" + field, m.data_ptr())
+            setattr(S, "v_" + field, v.data_ptr())
+        S.lr_mean, S.lr_scale, S.lr_rotation = lr_mean, cfg.lr_scale, cfg.lr_rotation
+        S.lr_coeffs_dc, S.lr_opac, S.sh_rest_lr_scale = cfg.lr_coeffs_dc, cfg.lr_opac, 1.0 / cfg.lr_coeffs_sh_scale
+        caux = aux._c()
+        ctx.check(_lib.lib().brush_render_backward_adam(
+            ctx.handle, self.n, self.k, C.byref(S), self.norm_rot.data_ptr(), pred.data_ptr(), self.v_out.data_ptr(),
+            C.byref(caux), self.g_xy.data_ptr(), cfg.adam_beta1, cfg.adam_beta2, cfg.adam_eps, self.iter + 1, 1.0, st))
 
     def _adam(self, ctx, splats: Splats, lr_mean: float, grad_scale: float, st):
         cfg = self.config

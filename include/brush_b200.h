@@ -172,6 +172,26 @@ typedef struct BrushAdamGroup {
 int brush_adam_step(brush_ctx* ctx, const BrushAdamGroup* groups_host, int n_groups, float beta1, float beta2,
                     float eps, uint32_t step, float grad_scale, void* stream);
 
+/* == rasterize_backwards + gather_grads/project_backwards (render.rs:494-594), the autodiff VJP of the rotation
+ * normalisation (gaussian_splats.rs:174-175) and the five optimizer steps of train.rs:318-359, for the
+ * single-device step with one view per batch: same rasterizer launch as brush_render_backward, then ONE kernel
+ * computes each splat's gradients in registers and applies brush_adam_step's update in place, so the dense
+ * gradients never touch HBM.  `rotation` is the raw (un-normalised) parameter, `quats` the normalised copy the
+ * forward rendered with; v_xy [N,2] is still written (refine statistics).  All pointers are device pointers;
+ * parameters and moments are updated in place.  Results equal brush_render_backward -> brush_quat_normalize_vjp
+ * -> brush_adam_step on the same inputs. */
+typedef struct BrushTrainState {
+    float *means, *log_scales, *rotation, *sh_coeffs, *raw_opacity;          /* parameters */
+    float *m_means, *v_means, *m_log_scales, *v_log_scales, *m_rotation, *v_rotation;
+    float *m_sh_coeffs, *v_sh_coeffs, *m_raw_opacity, *v_raw_opacity;        /* Adam moments, zero at start */
+    float lr_mean, lr_scale, lr_rotation, lr_coeffs_dc, lr_opac;
+    float sh_rest_lr_scale;                                                    /* 1 / lr_coeffs_sh_scale */
+} BrushTrainState;
+int brush_render_backward_adam(brush_ctx* ctx, uint32_t N, uint32_t K, const BrushTrainState* state,
+                               const float* quats, const float* out_img, const float* v_out_img,
+                               const BrushAux* aux, float* v_xy, float beta1, float beta2, float eps,
+                               uint32_t step, float grad_scale, void* stream);
+
 /* == the rotation normalisation Splats::render applies before the operator and its VJP (Burn elementwise ops +
  * autodiff in the reference, crates/brush-render/src/gaussian_splats.rs:174-175).  quats f32[n,4]. */
 int brush_quat_normalize(brush_ctx* ctx, const float* quats, uint32_t n, float* out, void* stream);

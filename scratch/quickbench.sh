@@ -1,9 +1,9 @@
 #!/bin/bash
 # usage: scratch/quickbench.sh TAG  -> runs gpu tests + bench, prints stage table
 TAG=${1:-x}
-python -m pytest tests -m gpu -x -q 2>&1 | tail -3 > gpurun_out/pytest_$TAG.log
+python -m pytest tests -m gpu -x -q 2>&1 | tail -40 > gpurun_out/pytest_$TAG.log
 python bench.py --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/bench_$TAG.log 2>&1
-cat gpurun_out/pytest_$TAG.log
+tail -15 gpurun_out/pytest_$TAG.log
 python -c "
 import json
 d=json.loads(open('gpurun_out/bench_$TAG.log').read().strip().splitlines()[-1])

@@ -121,6 +121,49 @@ def test_trainer_step_reduces_loss_and_counts_visible():
     assert float(tr.grad_2d_accum.sum()) > 0
 
 
+@pytest.mark.parametrize("k,n", [(1, 777), (4, 3000), (16, 2049)])
+def test_fused_backward_adam_matches_separate_kernels(k, n):
+    """brush_render_backward_adam (one pass: per-splat backward + normalisation VJP + Adam) against the three
+    separate entry points on the same inputs, for several steps.  Both paths evaluate the same expressions in the
+    same order."""
+    from brush_b200 import Camera, Splats, scene
+    from brush_b200.scene import bench_camera_params
+    from brush_b200.train import SceneBatch, SplatTrainer, TrainConfig
+
+    w, h = 160, 120
+    deg = {1: 0, 4: 1, 16: 3}[k]
+    sc = scene.make_scene(n, w, h, deg, 5)
+    t = lambda a: torch.as_tensor(a, device=DEV)
+    pos, rot, fx, fy = bench_camera_params(w, h)
+    cam = Camera(pos, rot, fx, fy)
+    gt = torch.rand((1, h, w, 3), device=DEV)
+    rng = np.random.default_rng(3)
+    raw_rot = (sc.quats * rng.uniform(0.5, 2.0, (n, 1))).astype(np.float32)  # un-normalised, as during training
+    cfg = TrainConfig(warmup_steps=0, max_refine_step=0)
+    results = []
+    for fused in (True, False):
+        sp = Splats(t(sc.means), t(sc.sh_coeffs), t(raw_rot), t(sc.raw_opacity), t(sc.log_scales))
+        tr = SplatTrainer(n, cfg, DEV, sh_coeffs_per_channel=k, fused_tail=fused)
+        for i in range(5):
+            sp, stats = tr.step(SceneBatch(gt, [cam], 1.3), sp)
+        results.append(([sp.means, sp.sh_coeffs, sp.rotation, sp.raw_opacity, sp.log_scales],
+                        [tr.state[x] for x in ("means", "sh", "rot", "opac", "scale")],
+                        tr.grad_2d_accum.clone(), tr.xy_grad_counts.clone(), float(stats.loss)))
+    (pa, sa, ga, ca, la), (pb, sb, gb, cb, lb) = results
+    # the rasterizer's gradient atomics land in a different order every run, so two runs of the SAME path differ
+    # in the last bits too; after five steps: updates within 2e-3 of the largest update, moments within 1e-4
+    assert abs(la - lb) <= 1e-5
+    assert torch.equal(ca, cb) and float((ga - gb).abs().max()) <= 1e-4 * float(gb.abs().max())
+    for name, a, b, o in zip(("means", "sh", "rotation", "opacity", "scales"), pa, pb,
+                             (sc.means, sc.sh_coeffs, raw_rot, sc.raw_opacity, sc.log_scales)):
+        delta = float((b - t(o)).abs().max())
+        assert delta > 1e-5, name  # the optimizer really stepped
+        assert float((a - b).abs().max()) <= 2e-3 * delta, name
+    for (ma, va), (mb, vb) in zip(sa, sb):
+        assert float((ma - mb).abs().max()) <= 1e-4 * float(mb.abs().max())
+        assert float((va - vb).abs().max()) <= 1e-4 * float(vb.abs().max())
+
+
 @pytest.mark.parametrize("channels,h,w", [(3, 37, 53), (4, 64, 48), (3, 16, 16)])
 def test_image_loss_ssim_forward_and_gradient(channels, h, w):
     """brush_image_loss_backward vs the numpy oracle (loss value) and torch autograd of the same definition
