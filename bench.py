@@ -7,8 +7,10 @@
 One "step" = one complete training iteration of brush_b200.train.SplatTrainer.step on one view per GPU:
 rotation normalise -> render forward -> image loss (0.8 L1 - 0.2 SSIM, the reference default) + d loss/d image
 -> render backward -> refine statistics
--> normalisation VJP -> fused Adam (N > 1: gradient sum + Adam + parameter broadcast as one peer-memory kernel,
-or --exchange nccl: all-reduce of the flat dense gradient, then replicated Adam).
+-> per-splat backward + normalisation VJP + Adam in one kernel.  N > 1 (--exchange views, default): each rank
+publishes its view's 48-byte per-splat rows in NVLink peer memory and every rank redoes the per-splat backward of
+every view and updates its own replica; --exchange peer: dense gradient sum + Adam + parameter broadcast as one
+peer-memory kernel; --exchange nccl: all-reduce of the flat dense gradient, then replicated Adam.
 Workload = BASELINE.json configs[3]: 1M random Gaussians, SH degree 3, 1920x1080 (synthetic, seeded;
 generator in brush_b200/scene.py).  `value` times steps whose ground-truth view is already in HBM; `e2e`
 times the same steps with the view's image coming from pinned host memory (H2D inside the timed region)
@@ -159,9 +161,14 @@ def run_ours(args):
     ctx = get_context(dev)
     # reference defaults, except that refinement is off: the benchmark times a fixed number of splats
     trainer = SplatTrainer(N, TrainConfig(max_refine_step=0), dev, sh_coeffs_per_channel=K, process_group=pg,
-                           isect_capacity=args.capacity, optimize=not args.no_optim, exchange=args.exchange)
+                           isect_capacity=args.capacity, optimize=not args.no_optim,
+                           exchange=args.exchange if world > 1 else "nccl")
     splats = trainer.adopt(splats)  # peer exchange: parameters live in the peer-mapped replica
-    if world > 1 and trainer.exchange == "peer":
+    if world > 1 and trainer.exchange == "views":
+        exchange_desc = ("no gradient exchange: every rank publishes its view's nine per-splat sums (48 B rows) in NVLink "
+                         "peer memory, then redoes the per-splat backward of all views + Adam on its own replica in ONE "
+                         "kernel (brush_views_adam_step)")
+    elif world > 1 and trainer.exchange == "peer":
         exchange_desc = ("gradient sum + Adam + parameter broadcast as ONE brush_dp_adam_step launch per rank over "
                          f"NVLink peer memory ({'NVSwitch multimem.ld_reduce/st' if trainer.peer.grad_mc else 'peer loads/stores'})")
     elif world > 1:
@@ -428,8 +435,9 @@ def main():
     ap.add_argument("--capacity", type=int, default=ISECT_CAPACITY)
     ap.add_argument("--no-optim", action="store_true", help="skip Adam (pure fwd+bwd, the reference bench shape)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--exchange", choices=["peer", "nccl"], default="peer",
-                    help="multi-GPU gradient exchange: fused peer-memory kernel (default) or NCCL all-reduce")
+    ap.add_argument("--exchange", choices=["views", "peer", "nccl"], default="views",
+                    help="multi-GPU step: per-view rows in peer memory + replicated fused tail (default), dense "
+                         "gradient sum fused with Adam over peer memory, or NCCL all-reduce")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

@@ -48,6 +48,11 @@ class BrushTrainState(C.Structure):
 DP_MAX_WORLD = 8
 
 
+class BrushViewExchange(C.Structure):
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("rows", C.c_void_p * DP_MAX_WORLD),
+                ("flags", C.c_void_p * DP_MAX_WORLD), ("epoch", C.c_uint32)]
+
+
 class BrushDpSegment(C.Structure):
     _fields_ = [("src_offset", C.c_uint64), ("dst_offset", C.c_uint64), ("count", C.c_uint64), ("adam", C.c_int32),
                 ("lr", C.c_float), ("sh_coeffs_per_channel", C.c_uint32), ("sh_rest_lr_scale", C.c_float)]
@@ -91,6 +96,12 @@ _SIGS = {
     "brush_render_backward_adam": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(BrushTrainState),
                                              C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(BrushAux), C.c_void_p,
                                              C.c_float, C.c_float, C.c_float, C.c_uint32, C.c_float, C.c_void_p]),
+    "brush_render_backward_rows": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,
+                                             C.POINTER(BrushAux), C.c_void_p, C.POINTER(BrushViewExchange),
+                                             C.c_void_p]),
+    "brush_views_adam_step": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(BrushTrainState), C.c_void_p,
+                                        C.POINTER(BrushViewExchange), C.c_void_p, C.c_void_p, C.c_void_p,
+                                        C.c_float, C.c_float, C.c_float, C.c_uint32, C.c_float, C.c_void_p]),
     "brush_radix_argsort_u32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32,
                                           C.c_void_p, C.c_void_p, C.c_void_p]),
     "brush_radix_argsort_u64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32,

@@ -379,6 +379,100 @@ int brush_render_backward(brush_ctx* ctx, uint32_t N, uint32_t K, const float* m
     return BRUSH_OK;
 }
 
+static bool train_state_ok(const BrushTrainState& s) {
+    return s.means && s.log_scales && s.rotation && s.sh_coeffs && s.raw_opacity && s.m_means && s.v_means &&
+           s.m_log_scales && s.v_log_scales && s.m_rotation && s.v_rotation && s.m_sh_coeffs && s.v_sh_coeffs &&
+           s.m_raw_opacity && s.v_raw_opacity &&
+           !(((uintptr_t)s.rotation | (uintptr_t)s.m_rotation | (uintptr_t)s.v_rotation | (uintptr_t)s.sh_coeffs |
+              (uintptr_t)s.m_sh_coeffs | (uintptr_t)s.v_sh_coeffs) & 15u);
+}
+static FusedAdamLaunch fused_adam_launch(const BrushTrainState& s, float beta1, float beta2, float eps, uint32_t step,
+                                         float grad_scale) {
+    FusedAdamLaunch A{};
+    A.means = s.means; A.log_scales = s.log_scales; A.rotation = s.rotation; A.sh = s.sh_coeffs; A.raw_opac = s.raw_opacity;
+    A.m_means = s.m_means; A.v_means = s.v_means; A.m_scales = s.m_log_scales; A.v_scales = s.v_log_scales;
+    A.m_rot = s.m_rotation; A.v_rot = s.v_rotation; A.m_sh = s.m_sh_coeffs; A.v_sh = s.v_sh_coeffs;
+    A.m_opac = s.m_raw_opacity; A.v_opac = s.v_raw_opacity;
+    A.lr_mean = s.lr_mean; A.lr_scale = s.lr_scale; A.lr_rot = s.lr_rotation; A.lr_sh_dc = s.lr_coeffs_dc;
+    A.lr_sh_rest = s.lr_coeffs_dc * s.sh_rest_lr_scale; A.lr_opac = s.lr_opac;
+    A.beta1 = beta1; A.beta2 = beta2; A.eps = eps; A.grad_scale = grad_scale;
+    A.inv_bc1 = (float)(1.0 / (1.0 - std::pow((double)beta1, (double)step)));
+    A.inv_bc2 = (float)(1.0 / (1.0 - std::pow((double)beta2, (double)step)));
+    return A;
+}
+
+static int views_launch(brush_ctx* ctx, const BrushViewExchange* x, ViewsLaunch* X) {
+    if (!x || x->world < 1 || x->world > BRUSH_DP_MAX_WORLD || x->rank < 0 || x->rank >= x->world || x->epoch < 1)
+        return fail(ctx, BRUSH_E_INVALID, "view exchange: world 1..8, 0 <= rank < world, epoch >= 1");
+    *X = ViewsLaunch{};
+    X->world = x->world; X->rank = x->rank; X->epoch = x->epoch;
+    for (int r = 0; r < x->world; r++) {
+        if (!x->rows[r] || !x->flags[r]) return fail(ctx, BRUSH_E_INVALID, "view exchange: null peer buffer");
+        if ((uintptr_t)x->rows[r] & 15u) return fail(ctx, BRUSH_E_INVALID, "view exchange: rows must be 16-byte aligned");
+        X->rows[r] = x->rows[r]; X->flags[r] = x->flags[r];
+    }
+    return BRUSH_OK;
+}
+
+int brush_render_backward_rows(brush_ctx* ctx, uint32_t N, uint32_t K, const float* out_img, const float* v_out_img,
+                               const BrushAux* aux, const float* loss_term, const BrushViewExchange* x,
+                               void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (!valid_k(K)) return fail(ctx, BRUSH_E_INVALID, "Invalid nr. of sh bases " + std::to_string(K));
+    if (!aux || !out_img || !v_out_img || N == 0) return fail(ctx, BRUSH_E_INVALID, "null argument or N == 0");
+    ViewsLaunch X;
+    int r = views_launch(ctx, x, &X);
+    if (r != BRUSH_OK) return r;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(ctx->device));
+    BrushUniforms u;
+    bool cached = false;
+    for (auto& e : ctx->uni_cache)
+        if (e.first == aux->uniforms_buffer) { u = e.second; cached = true; }
+    if (!cached) {
+        CU(cudaMemcpyAsync(&u, aux->uniforms_buffer, sizeof(u), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+    }
+    if (u.total_splats != N || u.sh_degree != degree_of(K))
+        return fail(ctx, BRUSH_E_INVALID, "aux.uniforms_buffer does not match N / K");
+    const Cam cam = make_cam(u);
+    float* rows = x->rows[x->rank];
+    ctx->ev_used[BRUSH_STAGE_RASTERIZE_BWD] = ctx->ev_used[BRUSH_STAGE_GATHER_PROJECT_BWD] = false;
+    CU(cudaMemsetAsync(rows, 0, (size_t)N * VP_STRIDE * 4, st));
+    {
+        StageTimer t(ctx, st, BRUSH_STAGE_RASTERIZE_BWD);
+        launch_rasterize_backward(cam, (uint32_t*)aux->compact_gid_from_isect, (uint32_t*)aux->tile_bins,
+                                  aux->projected_splats, (uint32_t*)aux->global_from_compact_gid,
+                                  (uint32_t*)aux->final_index, out_img, v_out_img, rows, st);
+    }
+    launch_publish_view(rows, N, (const uint32_t*)aux->global_from_compact_gid, aux->uniforms_buffer, loss_term, X, st);
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
+
+int brush_views_adam_step(brush_ctx* ctx, uint32_t N, uint32_t K, const BrushTrainState* state, const float* quats,
+                          const BrushViewExchange* x, float* grad_norm_accum, float* visible_accum, float* loss_out,
+                          float beta1, float beta2, float eps, uint32_t step, float grad_scale, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (!valid_k(K)) return fail(ctx, BRUSH_E_INVALID, "Invalid nr. of sh bases " + std::to_string(K));
+    if (!state || !quats || N == 0 || step < 1 || ((uintptr_t)quats & 15u) || !train_state_ok(*state) ||
+        (!grad_norm_accum) != (!visible_accum))
+        return fail(ctx, BRUSH_E_INVALID, "null / misaligned argument or N == 0");
+    ViewsLaunch X;
+    int r = views_launch(ctx, x, &X);
+    if (r != BRUSH_OK) return r;
+    X.loss_out = loss_out; X.grad_norm_accum = grad_norm_accum; X.visible_accum = visible_accum;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(ctx->device));
+    const FusedAdamLaunch A = fused_adam_launch(*state, beta1, beta2, eps, step, grad_scale);
+    {
+        StageTimer t(ctx, st, BRUSH_STAGE_GATHER_PROJECT_BWD);
+        if (launch_views_adam(X, N, K, quats, A, st) != 0) return fail(ctx, BRUSH_E_CUDA, "views_adam launch failed");
+    }
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
+
 int brush_render_backward_adam(brush_ctx* ctx, uint32_t N, uint32_t K, const BrushTrainState* state,
                                const float* quats, const float* out_img, const float* v_out_img,
                                const BrushAux* aux, float* v_xy, float beta1, float beta2, float eps,
@@ -416,16 +510,7 @@ int brush_render_backward_adam(brush_ctx* ctx, uint32_t N, uint32_t K, const Bru
                                   aux->projected_splats, (uint32_t*)aux->global_from_compact_gid,
                                   (uint32_t*)aux->final_index, out_img, v_out_img, (float*)ctx->v_projected.p, st);
     }
-    FusedAdamLaunch A{};
-    A.means = s.means; A.log_scales = s.log_scales; A.rotation = s.rotation; A.sh = s.sh_coeffs; A.raw_opac = s.raw_opacity;
-    A.m_means = s.m_means; A.v_means = s.v_means; A.m_scales = s.m_log_scales; A.v_scales = s.v_log_scales;
-    A.m_rot = s.m_rotation; A.v_rot = s.v_rotation; A.m_sh = s.m_sh_coeffs; A.v_sh = s.v_sh_coeffs;
-    A.m_opac = s.m_raw_opacity; A.v_opac = s.v_raw_opacity;
-    A.lr_mean = s.lr_mean; A.lr_scale = s.lr_scale; A.lr_rot = s.lr_rotation; A.lr_sh_dc = s.lr_coeffs_dc;
-    A.lr_sh_rest = s.lr_coeffs_dc * s.sh_rest_lr_scale; A.lr_opac = s.lr_opac;
-    A.beta1 = beta1; A.beta2 = beta2; A.eps = eps; A.grad_scale = grad_scale;
-    A.inv_bc1 = (float)(1.0 / (1.0 - std::pow((double)beta1, (double)step)));
-    A.inv_bc2 = (float)(1.0 / (1.0 - std::pow((double)beta2, (double)step)));
+    const FusedAdamLaunch A = fused_adam_launch(s, beta1, beta2, eps, step, grad_scale);
     {   // gather_grads + project_backwards + normalisation VJP + Adam in one pass
         StageTimer t(ctx, st, BRUSH_STAGE_GATHER_PROJECT_BWD);
         launch_backward_adam(cam, N, K, quats, (float*)ctx->v_projected.p, A, v_xy, st);

@@ -5,6 +5,7 @@
 // rasterizer's nine accumulated sums (v_projected[g][0..9), rows by global splat id, stride VP_STRIDE) once and
 // writes every row of each dense gradient once, so the reference's zero-fill of the outputs disappears too.
 #include "internal.h"
+#include "peer.cuh"
 
 namespace brush {
 
@@ -197,6 +198,98 @@ BD void adam_update(float& p, float g, float& m, float& v, float lr, const Fused
     p = adam_update_value(p, g, m, v, lr, A.beta1, A.beta2, A.eps, A.inv_bc1, A.inv_bc2, A.grad_scale);
 }
 
+// The block's 256 SH rows, [256][3K] floats, are contiguous and 16-byte aligned (256 * 3K is a multiple of 4):
+// parameter and moments stream through as coalesced float4s; grad(srow, k, channel) supplies the gradient of
+// coefficient k / channel of the block's srow-th splat.
+template <int K, typename GradFn>
+BD void sh_rows_adam(const FusedAdamLaunch& A, uint32_t N, GradFn grad) {
+    const size_t total = (size_t)N * (3 * K);
+    const size_t base = (size_t)blockIdx.x * 256u * (3 * K);
+    constexpr int F4 = 256 * 3 * K / 4;
+    constexpr int U = 4;  // float4 triples in flight per thread: the pass is pure streaming, latency-bound otherwise
+    for (int i0 = threadIdx.x; i0 < F4; i0 += 256 * U) {
+        float4 p[U], m[U], v[U];
+        bool full[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int i = i0 + 256 * u;
+            const size_t e0 = base + 4 * (size_t)i;
+            full[u] = i < F4 && e0 + 3 < total;
+            if (full[u]) {
+                p[u] = *reinterpret_cast<const float4*>(A.sh + e0);
+                m[u] = *reinterpret_cast<const float4*>(A.m_sh + e0);
+                v[u] = *reinterpret_cast<const float4*>(A.v_sh + e0);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int i = i0 + 256 * u;
+            const size_t e0 = base + 4 * (size_t)i;
+            if (i >= F4 || e0 >= total) continue;
+            float gsh[4], lr[4];
+            int srow = (4 * i) / (3 * K), r = 4 * i - srow * (3 * K), kk = r / 3, ch = r - 3 * kk;
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                gsh[c] = grad(srow, kk, ch);
+                lr[c] = r >= 3 ? A.lr_sh_rest : A.lr_sh_dc;
+                r++;
+                if (++ch == 3) { ch = 0; kk++; }
+                if (r == 3 * K) { r = 0; kk = 0; srow++; }
+            }
+            if (full[u]) {
+                adam_update(p[u].x, gsh[0], m[u].x, v[u].x, lr[0], A);
+                adam_update(p[u].y, gsh[1], m[u].y, v[u].y, lr[1], A);
+                adam_update(p[u].z, gsh[2], m[u].z, v[u].z, lr[2], A);
+                adam_update(p[u].w, gsh[3], m[u].w, v[u].w, lr[3], A);
+                *reinterpret_cast<float4*>(A.sh + e0) = p[u];
+                *reinterpret_cast<float4*>(A.m_sh + e0) = m[u];
+                *reinterpret_cast<float4*>(A.v_sh + e0) = v[u];
+            } else {  // the last, partial float4 of the whole array
+                for (int c = 0; c < 4 && e0 + c < total; c++) {
+                    float ps = A.sh[e0 + c], ms = A.m_sh[e0 + c], vs = A.v_sh[e0 + c];
+                    adam_update(ps, gsh[c], ms, vs, lr[c], A);
+                    A.sh[e0 + c] = ps; A.m_sh[e0 + c] = ms; A.v_sh[e0 + c] = vs;
+                }
+            }
+        }
+    }
+}
+
+// Adam on the 11 per-splat parameters of splat g (order of train.rs:320-356: means, opacity, [sh], rotation, scale)
+BD void small_params_adam(const FusedAdamLaunch& A, uint32_t g, float* mean, float* ls, float4 q_raw, float opac,
+                          V3 v_mean, V3 v_ls, V4 v_q, float v_opac) {
+    const float gm[3] = {v_mean.x, v_mean.y, v_mean.z}, gs[3] = {v_ls.x, v_ls.y, v_ls.z};
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        const size_t e = 3 * (size_t)g + c;
+        float m = A.m_means[e], v = A.v_means[e];
+        adam_update(mean[c], gm[c], m, v, A.lr_mean, A);
+        A.means[e] = mean[c]; A.m_means[e] = m; A.v_means[e] = v;
+        m = A.m_scales[e]; v = A.v_scales[e];
+        adam_update(ls[c], gs[c], m, v, A.lr_scale, A);
+        A.log_scales[e] = ls[c]; A.m_scales[e] = m; A.v_scales[e] = v;
+    }
+    float m = A.m_opac[g], v = A.v_opac[g];
+    adam_update(opac, v_opac, m, v, A.lr_opac, A);
+    A.raw_opac[g] = opac; A.m_opac[g] = m; A.v_opac[g] = v;
+    float4 m4 = reinterpret_cast<float4*>(A.m_rot)[g], v4 = reinterpret_cast<float4*>(A.v_rot)[g];
+    adam_update(q_raw.x, v_q.x, m4.x, v4.x, A.lr_rot, A);
+    adam_update(q_raw.y, v_q.y, m4.y, v4.y, A.lr_rot, A);
+    adam_update(q_raw.z, v_q.z, m4.z, v4.z, A.lr_rot, A);
+    adam_update(q_raw.w, v_q.w, m4.w, v4.w, A.lr_rot, A);
+    reinterpret_cast<float4*>(A.rotation)[g] = q_raw;
+    reinterpret_cast<float4*>(A.m_rot)[g] = m4;
+    reinterpret_cast<float4*>(A.v_rot)[g] = v4;
+}
+
+// VJP of q / |q| (== quat_normalize_vjp_kernel)
+BD V4 quat_normalize_vjp(float4 q_raw, V4 v_q) {
+    const float inv = 1.0f / sqrtf(q_raw.x * q_raw.x + q_raw.y * q_raw.y + q_raw.z * q_raw.z + q_raw.w * q_raw.w);
+    const float hx = q_raw.x * inv, hy = q_raw.y * inv, hz = q_raw.z * inv, hw = q_raw.w * inv;
+    const float d = hx * v_q.x + hy * v_q.y + hz * v_q.z + hw * v_q.w;
+    return {(v_q.x - hx * d) * inv, (v_q.y - hy * d) * inv, (v_q.z - hz * d) * inv, (v_q.w - hw * d) * inv};
+}
+
 #ifndef BA_MINB
 #define BA_MINB 2
 #endif
@@ -231,11 +324,7 @@ backward_adam_kernel(const __grid_constant__ Cam cam, const float* __restrict__ 
             const float4 q4 = __ldg(reinterpret_cast<const float4*>(norm_quats) + g);
             project_backward_chain(cam, mean_v, scale, V4{q4.x, q4.y, q4.z, q4.w}, V2{vp0.x, vp0.y},
                                    V3{vp0.z, vp0.w, vp1.x}, v_mean, v_ls, v_q);
-            // VJP of q / |q| (quat_normalize_vjp_kernel)
-            const float inv = 1.0f / sqrtf(q_raw.x * q_raw.x + q_raw.y * q_raw.y + q_raw.z * q_raw.z + q_raw.w * q_raw.w);
-            const float hx = q_raw.x * inv, hy = q_raw.y * inv, hz = q_raw.z * inv, hw = q_raw.w * inv;
-            const float d = hx * v_q.x + hy * v_q.y + hz * v_q.z + hw * v_q.w;
-            v_q = {(v_q.x - hx * d) * inv, (v_q.y - hy * d) * inv, (v_q.z - hz * d) * inv, (v_q.w - hw * d) * inv};
+            v_q = quat_normalize_vjp(q_raw, v_q);
             const float sgm = 1.0f / (1.0f + __expf(-opac));
             v_opac = v_alpha * (sgm * (1.0f - sgm));
             const V3 dv = mean_v - cam.t;
@@ -245,84 +334,10 @@ backward_adam_kernel(const __grid_constant__ Cam cam, const float* __restrict__ 
 #pragma unroll
         for (int k = 0; k < K; k++) s_sh[threadIdx.x][k] = b[k];
         s_sh[threadIdx.x][K] = vp1.y; s_sh[threadIdx.x][K + 1] = vp1.z; s_sh[threadIdx.x][K + 2] = vp1.w;
-        // Adam on the 11 per-splat parameters (order of train.rs:320-356: means, opacity, [sh], rotation, scale)
-        const float gm[3] = {v_mean.x, v_mean.y, v_mean.z}, gs[3] = {v_ls.x, v_ls.y, v_ls.z};
-#pragma unroll
-        for (int c = 0; c < 3; c++) {
-            const size_t e = 3 * (size_t)g + c;
-            float m = A.m_means[e], v = A.v_means[e];
-            adam_update(mean[c], gm[c], m, v, A.lr_mean, A);
-            A.means[e] = mean[c]; A.m_means[e] = m; A.v_means[e] = v;
-            m = A.m_scales[e]; v = A.v_scales[e];
-            adam_update(ls[c], gs[c], m, v, A.lr_scale, A);
-            A.log_scales[e] = ls[c]; A.m_scales[e] = m; A.v_scales[e] = v;
-        }
-        {
-            float m = A.m_opac[g], v = A.v_opac[g];
-            adam_update(opac, v_opac, m, v, A.lr_opac, A);
-            A.raw_opac[g] = opac; A.m_opac[g] = m; A.v_opac[g] = v;
-            float4 m4 = reinterpret_cast<float4*>(A.m_rot)[g], v4 = reinterpret_cast<float4*>(A.v_rot)[g];
-            adam_update(q_raw.x, v_q.x, m4.x, v4.x, A.lr_rot, A);
-            adam_update(q_raw.y, v_q.y, m4.y, v4.y, A.lr_rot, A);
-            adam_update(q_raw.z, v_q.z, m4.z, v4.z, A.lr_rot, A);
-            adam_update(q_raw.w, v_q.w, m4.w, v4.w, A.lr_rot, A);
-            reinterpret_cast<float4*>(A.rotation)[g] = q_raw;
-            reinterpret_cast<float4*>(A.m_rot)[g] = m4;
-            reinterpret_cast<float4*>(A.v_rot)[g] = v4;
-        }
+        small_params_adam(A, g, mean, ls, q_raw, opac, v_mean, v_ls, v_q, v_opac);
     }
     __syncthreads();
-    // phase 2: the block's SH rows, [256][3K] floats, contiguous and 16-byte aligned (256 * 3K is a multiple of 4)
-    const size_t total = (size_t)N * (3 * K);
-    const size_t base = (size_t)blockIdx.x * 256u * (3 * K);
-    constexpr int F4 = 256 * 3 * K / 4;
-    constexpr int U = 4;  // float4 triples in flight per thread: the pass is pure streaming, latency-bound otherwise
-    for (int i0 = threadIdx.x; i0 < F4; i0 += 256 * U) {
-        float4 p[U], m[U], v[U];
-        bool full[U];
-#pragma unroll
-        for (int u = 0; u < U; u++) {
-            const int i = i0 + 256 * u;
-            const size_t e0 = base + 4 * (size_t)i;
-            full[u] = i < F4 && e0 + 3 < total;
-            if (full[u]) {
-                p[u] = *reinterpret_cast<const float4*>(A.sh + e0);
-                m[u] = *reinterpret_cast<const float4*>(A.m_sh + e0);
-                v[u] = *reinterpret_cast<const float4*>(A.v_sh + e0);
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < U; u++) {
-            const int i = i0 + 256 * u;
-            const size_t e0 = base + 4 * (size_t)i;
-            if (i >= F4 || e0 >= total) continue;
-            float gsh[4], lr[4];
-            int srow = (4 * i) / (3 * K), r = 4 * i - srow * (3 * K), kk = r / 3, ch = r - 3 * kk;
-#pragma unroll
-            for (int c = 0; c < 4; c++) {
-                gsh[c] = s_sh[srow][kk] * s_sh[srow][K + ch];
-                lr[c] = r >= 3 ? A.lr_sh_rest : A.lr_sh_dc;
-                r++;
-                if (++ch == 3) { ch = 0; kk++; }
-                if (r == 3 * K) { r = 0; kk = 0; srow++; }
-            }
-            if (full[u]) {
-                adam_update(p[u].x, gsh[0], m[u].x, v[u].x, lr[0], A);
-                adam_update(p[u].y, gsh[1], m[u].y, v[u].y, lr[1], A);
-                adam_update(p[u].z, gsh[2], m[u].z, v[u].z, lr[2], A);
-                adam_update(p[u].w, gsh[3], m[u].w, v[u].w, lr[3], A);
-                *reinterpret_cast<float4*>(A.sh + e0) = p[u];
-                *reinterpret_cast<float4*>(A.m_sh + e0) = m[u];
-                *reinterpret_cast<float4*>(A.v_sh + e0) = v[u];
-            } else {  // the last, partial float4 of the whole array
-                for (int c = 0; c < 4 && e0 + c < total; c++) {
-                    float ps = A.sh[e0 + c], ms = A.m_sh[e0 + c], vs = A.v_sh[e0 + c];
-                    adam_update(ps, gsh[c], ms, vs, lr[c], A);
-                    A.sh[e0 + c] = ps; A.m_sh[e0 + c] = ms; A.v_sh[e0 + c] = vs;
-                }
-            }
-        }
-    }
+    sh_rows_adam<K>(A, N, [&](int srow, int kk, int ch) { return s_sh[srow][kk] * s_sh[srow][K + ch]; });
 }
 
 void launch_backward_adam(const Cam& cam, uint32_t N, uint32_t K, const float* norm_quats, const float* v_projected,
@@ -337,6 +352,183 @@ void launch_backward_adam(const Cam& cam, uint32_t N, uint32_t K, const float* n
         case 16: backward_adam_kernel<16><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy); break;
         case 25: backward_adam_kernel<25><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy); break;
     }
+}
+
+// ---------------------------------------------------------------------------------------------
+// View-parallel step without exchanging dense gradients.  The per-splat backward is nonlinear in the
+// camera but cheap, and its input -- the nine sums rasterize_backwards leaves per splat -- is 5x smaller than its
+// output.  So every rank reads every view's rows (48 B per splat and view, over NVLink for the peers' views),
+// redoes project_backwards + the SH VJP per view in registers, sums in a fixed view order, and applies Adam to
+// its own full replica: replicas stay bit-identical without any parameter broadcast, and the only cross-GPU
+// traffic of a training step is 48 * N * (world - 1) bytes per rank.
+//   publish_view_kernel: marks the view's visible splats in word 9 of their rows, copies the view's uniforms and
+//       loss term behind the rows;  arrive_kernel: release-stores this step's epoch into every rank's flag block.
+//   views_adam_kernel: acquire-waits for all ranks' epochs, then per block of 256 splats: for each view, the
+//       block's 12 KB of rows is fetched coalesced (next view in flight while this one is processed), staged in
+//       shared memory, and each thread runs the chain for its splat; SH gradients accumulate in shared memory;
+//       Adam as in backward_adam_kernel.  Row buffers alternate between two halves by step parity, so no second
+//       barrier is needed: a rank can overwrite a half only after every peer has arrived at the step in between.
+__global__ void __launch_bounds__(256)
+publish_view_kernel(float* __restrict__ rows, uint32_t N, const uint32_t* __restrict__ global_from_compact,
+                    const uint32_t* __restrict__ uniforms, const float* __restrict__ loss) {
+    const uint32_t i = blockIdx.x * 256u + threadIdx.x;
+    const uint32_t nv = uniforms[25];  // num_visible, written by the forward (RenderUniforms word 25)
+    if (i < nv && i < N) rows[(size_t)global_from_compact[i] * VP_STRIDE + 9] = 1.0f;
+    float* trailer = rows + (size_t)N * VP_STRIDE;
+    if (i < 28) reinterpret_cast<uint32_t*>(trailer)[i] = uniforms[i];
+    if (i == 28) trailer[28] = loss ? *loss : 0.0f;
+}
+
+struct ArriveLaunch { uint32_t* flags[DP_MAX_WORLD]; int world, rank; uint32_t epoch; };
+__global__ void arrive_kernel(const __grid_constant__ ArriveLaunch L) {
+    if (threadIdx.x < (uint32_t)L.world) {
+        __threadfence_system();
+        st_release_sys(L.flags[threadIdx.x] + L.rank, L.epoch);
+    }
+}
+
+void launch_publish_view(float* rows, uint32_t N, const uint32_t* global_from_compact, const void* uniforms_dev,
+                         const float* loss_dev, const ViewsLaunch& X, cudaStream_t st) {
+    const uint32_t threads = N > 32 ? N : 32;
+    g_launch_count += 2;
+    publish_view_kernel<<<(threads + 255) / 256, 256, 0, st>>>(rows, N, global_from_compact,
+                                                               (const uint32_t*)uniforms_dev, loss_dev);
+    ArriveLaunch L{};
+    for (int r = 0; r < X.world; r++) L.flags[r] = X.flags[r];
+    L.world = X.world; L.rank = X.rank; L.epoch = X.epoch;
+    arrive_kernel<<<1, 32, 0, st>>>(L);
+}
+
+template <int K>
+__global__ void __launch_bounds__(256, 2)
+views_adam_kernel(const __grid_constant__ ViewsLaunch X, uint32_t N, const float* __restrict__ norm_quats,
+                  const __grid_constant__ FusedAdamLaunch A) {
+    constexpr int S = (3 * K) | 1;  // odd row stride: thread-per-row accumulation is bank-conflict free
+    extern __shared__ float4 views_smem[];
+    float* s_g = reinterpret_cast<float*>(views_smem);            // [256][S] SH gradients, summed over views
+    float4* s_rows = reinterpret_cast<float4*>(s_g + 256 * S);    // [256 * 3] one view's rows of this block
+    __shared__ Cam s_cam[DP_MAX_WORLD];
+    const int world = X.world, tid = threadIdx.x;
+
+    if (tid < world) {  // every rank has published this step's rows
+        const uint32_t* f = X.flags[X.rank] + tid;
+        while ((int32_t)(ld_acquire_sys(f) - X.epoch) < 0) {}
+    }
+    __syncthreads();
+    if (tid < world) {
+        BrushUniforms u;
+        const float* trailer = X.rows[tid] + (size_t)N * VP_STRIDE;
+        float4* dst = reinterpret_cast<float4*>(&u);
+#pragma unroll
+        for (int j = 0; j < 7; j++) dst[j] = ld_peer_v4(trailer + 4 * j);
+        s_cam[tid] = make_cam(u);
+    }
+    if (blockIdx.x == 0 && tid == 0 && X.loss_out) {
+        float l = 0.f;
+        for (int w = 0; w < world; w++) l += ld_peer_v4(X.rows[w] + (size_t)N * VP_STRIDE + 28).x;
+        *X.loss_out = l * A.grad_scale;
+    }
+
+    const uint32_t first = blockIdx.x * 256u, g = first + tid;
+    const int nf4 = 3 * (int)min(256u, N - first);
+    float4 pre[3];
+    auto fetch = [&](int w) {
+        const float* src = X.rows[w] + (size_t)first * VP_STRIDE;
+#pragma unroll
+        for (int j = 0; j < 3; j++)
+            if (tid + 256 * j < nf4) pre[j] = ld_peer_v4(src + 4 * (tid + 256 * j));
+    };
+    fetch(0);
+
+    float mean[3] = {0.f, 0.f, 0.f}, ls[3] = {0.f, 0.f, 0.f}, opac = 0.f;
+    float4 q_raw = make_float4(0.f, 0.f, 0.f, 1.f), q4 = q_raw;
+    if (g < N) {
+#pragma unroll
+        for (int c = 0; c < 3; c++) { mean[c] = A.means[3 * (size_t)g + c]; ls[c] = A.log_scales[3 * (size_t)g + c]; }
+        q_raw = reinterpret_cast<const float4*>(A.rotation)[g];
+        q4 = __ldg(reinterpret_cast<const float4*>(norm_quats) + g);
+        opac = A.raw_opac[g];
+    }
+    const V3 mean_v = {mean[0], mean[1], mean[2]};
+    const V3 scale = {__expf(ls[0]), __expf(ls[1]), __expf(ls[2])};
+#pragma unroll 4
+    for (int e = 0; e < 3 * K; e++) s_g[tid * S + e] = 0.f;
+    V3 v_mean = {0.f, 0.f, 0.f}, v_ls = {0.f, 0.f, 0.f};
+    V4 v_q = {0.f, 0.f, 0.f, 0.f};
+    float v_alpha_sum = 0.f, norm_sum = 0.f, vis_sum = 0.f;
+
+    for (int w = 0; w < world; w++) {
+        __syncthreads();  // the previous view's rows are consumed (first pass: s_cam is complete)
+#pragma unroll
+        for (int j = 0; j < 3; j++)
+            if (tid + 256 * j < nf4) s_rows[tid + 256 * j] = pre[j];
+        __syncthreads();
+        if (w + 1 < world) fetch(w + 1);
+        if (g < N) {
+            const float4 r0 = s_rows[3 * tid], r1 = s_rows[3 * tid + 1], r2 = s_rows[3 * tid + 2];
+            const Cam& cam = s_cam[w];
+            vis_sum += r2.y;
+            const bool zero = r0.x == 0.f && r0.y == 0.f && r0.z == 0.f && r0.w == 0.f && r1.x == 0.f &&
+                              r1.y == 0.f && r1.z == 0.f && r1.w == 0.f && r2.x == 0.f;
+            if (!zero) {
+                V3 vm, vl;
+                V4 vq;
+                project_backward_chain(cam, mean_v, scale, V4{q4.x, q4.y, q4.z, q4.w}, V2{r0.x, r0.y},
+                                       V3{r0.z, r0.w, r1.x}, vm, vl, vq);
+                v_mean = v_mean + vm;
+                v_ls = v_ls + vl;
+                v_q = {v_q.x + vq.x, v_q.y + vq.y, v_q.z + vq.z, v_q.w + vq.w};
+                v_alpha_sum += r2.x;
+                const float gx = r0.x * (0.5f * (float)cam.img_w), gy = r0.y * (0.5f * (float)cam.img_h);
+                norm_sum += sqrtf(gx * gx + gy * gy);
+                float b[K];
+                const V3 dv = mean_v - cam.t;
+                sh_basis<K>(cam.sh_degree, dv * rsqrtf(dot3(dv, dv)), b);
+#pragma unroll
+                for (int k = 0; k < K; k++) {
+                    s_g[tid * S + 3 * k] += b[k] * r1.y;
+                    s_g[tid * S + 3 * k + 1] += b[k] * r1.z;
+                    s_g[tid * S + 3 * k + 2] += b[k] * r1.w;
+                }
+            }
+        }
+    }
+    if (g < N) {
+        v_q = quat_normalize_vjp(q_raw, v_q);
+        const float sgm = 1.0f / (1.0f + __expf(-opac));
+        const float v_opac = v_alpha_sum * (sgm * (1.0f - sgm));
+        small_params_adam(A, g, mean, ls, q_raw, opac, v_mean, v_ls, v_q, v_opac);
+        if (X.grad_norm_accum) {  // refine statistics, train.rs:284-316, summed over the step's views
+            X.grad_norm_accum[g] += norm_sum * A.grad_scale;
+            X.visible_accum[g] += vis_sum;
+        }
+    }
+    __syncthreads();
+    sh_rows_adam<K>(A, N, [&](int srow, int kk, int ch) { return s_g[srow * S + 3 * kk + ch]; });
+}
+
+template <int K>
+static int launch_views_adam_k(const ViewsLaunch& X, uint32_t N, const float* norm_quats, const FusedAdamLaunch& A,
+                               cudaStream_t st) {
+    const size_t smem = (size_t)256 * ((3 * K) | 1) * 4 + 256 * 3 * 16;
+    cudaError_t e = cudaFuncSetAttribute(views_adam_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    views_adam_kernel<K><<<(N + 255) / 256, 256, smem, st>>>(X, N, norm_quats, A);
+    return 0;
+}
+
+int launch_views_adam(const ViewsLaunch& X, uint32_t N, uint32_t K, const float* norm_quats, const FusedAdamLaunch& A,
+                      cudaStream_t st) {
+    if (N == 0) return 0;
+    g_launch_count++;
+    switch (K) {
+        case 1: return launch_views_adam_k<1>(X, N, norm_quats, A, st);
+        case 4: return launch_views_adam_k<4>(X, N, norm_quats, A, st);
+        case 9: return launch_views_adam_k<9>(X, N, norm_quats, A, st);
+        case 16: return launch_views_adam_k<16>(X, N, norm_quats, A, st);
+        case 25: return launch_views_adam_k<25>(X, N, norm_quats, A, st);
+    }
+    return -1;
 }
 
 }  // namespace brush

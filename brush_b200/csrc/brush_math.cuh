@@ -128,7 +128,7 @@ struct Cam {
     uint32_t sh_degree, total_splats;
 };
 
-__host__ inline Cam make_cam(const BrushUniforms& u) {
+__host__ __device__ inline Cam make_cam(const BrushUniforms& u) {
     Cam c;
     const float* m = u.viewmat;
     c.W = {{{m[0], m[1], m[2]}, {m[4], m[5], m[6]}, {m[8], m[9], m[10]}}};

@@ -15,35 +15,9 @@
 // complete" before the first peer load, and "I have finished reading your gradients and writing your parameters"
 // before the kernel retires.
 #include "internal.h"
+#include "peer.cuh"
 
 namespace brush {
-
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-    uint32_t v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ float4 ld_peer_v4(const float* p) {  // peer gradients are read exactly once
-    float4 v;
-    asm volatile("ld.global.relaxed.sys.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
-    return v;
-}
-__device__ __forceinline__ void st_peer_v4(float* p, float4 v) {
-    asm volatile("st.global.relaxed.sys.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
-}
-__device__ __forceinline__ float4 multimem_ld_reduce_v4(const float* mc) {
-    float4 v;
-    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
-                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
-    return v;
-}
-__device__ __forceinline__ void multimem_st_v4(float* mc, float4 v) {
-    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
-                 : "memory");
-}
 
 // Wait until every rank has published `epoch` in slot [which][rank'] of THIS rank's flag block.
 __device__ __forceinline__ void wait_flags(const uint32_t* my_flags, int which, int world, uint32_t epoch) {

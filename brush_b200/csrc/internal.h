@@ -109,6 +109,26 @@ struct FusedAdamLaunch {
 void launch_backward_adam(const Cam& cam, uint32_t N, uint32_t K, const float* norm_quats, const float* v_projected,
                           const FusedAdamLaunch& A, float* v_xy, cudaStream_t st);
 
+// View-parallel step without a gradient exchange (backward.cu): every rank publishes the nine per-splat sums of ITS
+// view (48 B per splat instead of 252 B of dense gradients), then redoes the per-splat backward for every view and
+// applies the same Adam update to its full replica.  rows: f32[N * VP_STRIDE + VIEW_TRAILER]; a row's word 9 is the
+// view's visibility flag; the trailer holds the view's RenderUniforms (28 words) and its loss term (word 28).
+constexpr int DP_MAX_WORLD = BRUSH_DP_MAX_WORLD;
+constexpr int VIEW_TRAILER = 32;
+struct ViewsLaunch {
+    int world, rank;
+    const float* rows[DP_MAX_WORLD];
+    uint32_t* flags[DP_MAX_WORLD];
+    uint32_t epoch;
+    float* loss_out;
+    float* grad_norm_accum;
+    float* visible_accum;
+};
+void launch_publish_view(float* rows, uint32_t N, const uint32_t* global_from_compact, const void* uniforms_dev,
+                         const float* loss_dev, const ViewsLaunch& X, cudaStream_t st);
+int launch_views_adam(const ViewsLaunch& X, uint32_t N, uint32_t K, const float* norm_quats, const FusedAdamLaunch& A,
+                      cudaStream_t st);
+
 // ---- optim.cu ----
 extern std::atomic<uint64_t> g_launch_count;  // kernels launched by this library (bench.py's gpu_launches)
 struct AdamSeg {
@@ -142,7 +162,6 @@ void launch_xy_grad_stats(const float* v_xy, const uint32_t* gfc, const int32_t*
 
 
 // ---- dp_adam.cu: view-parallel optimizer step over NVLink peer memory ----
-constexpr int DP_MAX_WORLD = BRUSH_DP_MAX_WORLD;
 struct DpSeg {
     uint64_t src_off, dst_off, count;  // floats; multiples of 4
     int adam;                          // 1: Adam on the summed gradient; 0: plain sum copied to dst

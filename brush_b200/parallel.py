@@ -3,7 +3,11 @@
 prescribes: every rank holds a full replica of the Gaussians, renders different camera views, and the dense
 per-Gaussian gradients are summed before the Adam step.
 
-Two exchange modes:
+Three exchange modes:
+  * "views": nothing dense is exchanged.  Each rank publishes the nine per-splat sums rasterize_backwards leaves for
+             its view (48-byte rows) in peer-mapped memory; every rank redoes the cheap per-splat backward for every
+             view and applies Adam to its own full replica (csrc/backward.cu views_adam_kernel).  Cross-GPU traffic
+             48*N*(world-1) bytes per rank and step instead of ~2*244*N, one flag barrier.
   * "nccl":  ONE all-reduce over a flat f32 buffer, then the replicated brush_adam_step (the baseline);
   * "peer":  ONE brush_dp_adam_step launch per rank over NVLink peer memory: rank r sums its 1/world slice of
              every rank's gradient buffer, applies Adam there (moments sharded), and stores the new parameters into
@@ -140,3 +144,51 @@ class PeerBuffers:
         self.param_mc = int(hp.multicast_ptr) if mc_ok else 0
         torch.cuda.synchronize(device)
         torch.distributed.barrier(group)  # every rank's zero-fill has landed before anyone's first exchange
+
+
+VP_STRIDE = 12      # floats per row (csrc/internal.h)
+VIEW_TRAILER = 32   # floats behind the rows: the view's RenderUniforms + loss term
+
+
+class ViewBuffers:
+    """The peer-mapped buffers of the "views" exchange mode: two row blocks (alternating by step parity, which is
+    what lets one flag barrier per step suffice) and one flag block per rank.  group=None: plain device memory,
+    world 1."""
+
+    def __init__(self, n: int, group, device):
+        from . import _lib
+
+        self.n = n
+        self.block = n * VP_STRIDE + VIEW_TRAILER  # floats; 16-byte multiple
+        self.world = group.size() if group is not None else 1
+        self.rank = group.rank() if group is not None else 0
+        if self.world > _lib.DP_MAX_WORLD:
+            raise ValueError("views exchange supports at most 8 ranks (one NVSwitch domain)")
+        if self.world > 1:
+            import torch.distributed._symmetric_memory as symm
+
+            self.rows = symm.empty(2 * self.block, dtype=torch.float32, device=device)
+            self.flags = symm.empty(64, dtype=torch.int32, device=device)
+            self.rows.zero_()
+            self.flags.zero_()
+            hr, hf = symm.rendezvous(self.rows, group.group_name), symm.rendezvous(self.flags, group.group_name)
+            self._handles = (hr, hf)
+            self.row_ptrs = [int(p) for p in hr.buffer_ptrs]
+            self.flag_ptrs = [int(p) for p in hf.buffer_ptrs]
+            torch.cuda.synchronize(device)
+            torch.distributed.barrier(group)
+        else:
+            self.rows = torch.zeros(2 * self.block, dtype=torch.float32, device=device)
+            self.flags = torch.zeros(64, dtype=torch.int32, device=device)
+            self.row_ptrs, self.flag_ptrs = [self.rows.data_ptr()], [self.flags.data_ptr()]
+
+    def exchange(self, epoch: int):
+        """The BrushViewExchange of step `epoch` (>= 1, the same on every rank)."""
+        from . import _lib
+
+        x = _lib.BrushViewExchange()
+        x.world, x.rank, x.epoch = self.world, self.rank, epoch
+        off = 4 * self.block * (epoch & 1)
+        for r in range(self.world):
+            x.rows[r], x.flags[r] = self.row_ptrs[r] + off, self.flag_ptrs[r]
+        return x

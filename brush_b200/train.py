@@ -22,7 +22,7 @@ from typing import List, Optional
 import torch
 
 from . import _lib
-from .parallel import FlatGradLayout, FlatParamLayout, PeerBuffers, allreduce_flat, global_grad_scale
+from .parallel import ViewBuffers, FlatGradLayout, FlatParamLayout, PeerBuffers, allreduce_flat, global_grad_scale
 from .render import Camera, RenderAux, Splats, _stream_ptr, get_context, make_uniforms, render_backward, render_forward
 
 
@@ -114,11 +114,15 @@ class SplatTrainer:
         self.isect_capacity = isect_capacity
         self.optimize = optimize
         self.fused_tail = fused_tail  # single device, one view per step: backward tail + Adam in one kernel
-        if exchange not in ("nccl", "peer"):
-            raise ValueError("exchange must be 'nccl' or 'peer'")
+        if exchange not in ("nccl", "peer", "views"):
+            raise ValueError("exchange must be 'nccl', 'peer' or 'views'")
         # "peer": gradient sum + Adam + parameter broadcast as one launch over NVLink peer memory (parallel.py)
-        self.exchange = exchange if (process_group is not None and process_group.size() > 1) else "nccl"
+        # "views": no gradient exchange at all: 48-byte per-splat rows are published, every rank redoes the
+        #          per-splat backward of every view and updates its own replica (one view per rank per step)
+        multi = process_group is not None and process_group.size() > 1
+        self.exchange = exchange if (multi or exchange == "views") else "nccl"
         self.peer: Optional[PeerBuffers] = None
+        self.views: Optional[ViewBuffers] = None
         self.epoch = 0
         self._copy_stream = None
         self._alloc(num_points, sh_coeffs_per_channel)
@@ -135,6 +139,8 @@ class SplatTrainer:
             self.peer_v = torch.zeros(self.param_layout.total, **f)
         else:
             self.flat_grad = self.layout.alloc(self.device)
+        if self.exchange == "views":
+            self.views = ViewBuffers(n, self.pg, self.device)
         (self.g_means, self.g_xy, self.g_scales, self.g_quats, self.g_sh, self.g_opac, self.stat_grad_norm,
          self.stat_visible, self.g_loss) = self.layout.views(self.flat_grad)
         self.tmp = None  # second gradient set, only for batches of more than one view per rank
@@ -204,7 +210,8 @@ class SplatTrainer:
         p_sh, p_opac, p_rot = splats.sh_coeffs.detach(), splats.raw_opacity.detach(), splats.rotation.detach()
         outs = (self.g_means, self.g_xy, self.g_scales, self.g_quats, self.g_sh, self.g_opac)
         preds, auxes = [], []
-        fused = self.fused_tail and self.optimize and world == 1 and B == 1 and self.peer is None
+        views = self.views is not None and self.optimize and B == 1
+        fused = self.fused_tail and self.optimize and world == 1 and B == 1 and self.peer is None and not views
         # train.rs:361-365 (iter = the value before this step's increment)
         do_refine = (self.iter < cfg.max_refine_step and self.iter >= cfg.warmup_steps
                      and self.iter % cfg.refine_every == 1 and self.optimize)
@@ -239,6 +246,17 @@ class SplatTrainer:
                     if self.tmp is None:
                         self.tmp = tuple(torch.empty_like(v) for v in outs)
                     dst = self.tmp
+                if views:
+                    # publish this view's per-splat rows; the dense gradients are never formed (see _views_step)
+                    self.epoch += 1
+                    vx = self.views.exchange(self.epoch)
+                    caux = aux._c()
+                    ctx.check(L.brush_render_backward_rows(ctx.handle, self.n, self.k, pred.data_ptr(),
+                                                           self.v_out.data_ptr(), C.byref(caux),
+                                                           self.loss_buf.data_ptr(), C.byref(vx), st))
+                    preds.append(pred)
+                    auxes.append(aux)
+                    break
                 if fused:
                     # single device, one view: per-splat backward + normalisation VJP + Adam in one kernel; the
                     # dense gradients are never materialised (only v_xy, for the refine statistics)
@@ -259,12 +277,16 @@ class SplatTrainer:
                 auxes.append(aux)
             grad_scale = global_grad_scale(B, world)
             lr_mean = self._lr_mean(batch)
-            if not fused:
+            if not fused and not views:
                 # VJP of the rotation normalisation (Burn autodiff in the reference); linear: commutes with the sum
                 ctx.check(L.brush_quat_normalize_vjp(ctx.handle, p_rot.data_ptr(), self.n, self.g_quats.data_ptr(),
                                                      st))
             self.iter += 1
-            if self.peer is not None:
+            if views:
+                with_stats = self.iter - 1 > cfg.warmup_steps  # train.rs:286-316
+                self._views_step(ctx, splats, vx, lr_mean, grad_scale, with_stats, st)
+                loss = self.loss_total
+            elif self.peer is not None:
                 if splats.means.data_ptr() != self.peer.param.data_ptr() + 4 * self.param_layout.offset("means"):
                     raise ValueError("peer exchange: pass the Splats returned by SplatTrainer.adopt()")
                 self.g_loss[:1].copy_(self.loss_total)
@@ -278,7 +300,7 @@ class SplatTrainer:
                 if self.optimize and not fused:
                     self._adam(ctx, splats, lr_mean, grad_scale, st)
                 loss = self.loss_total * grad_scale if (B * world) > 1 else self.loss_total
-            if self.iter - 1 > cfg.warmup_steps:  # train.rs:286-316
+            if self.iter - 1 > cfg.warmup_steps and not views:  # train.rs:286-316
                 self.grad_2d_accum.add_(stat_norm, alpha=grad_scale)
                 self.xy_grad_counts.add_(stat_vis)  # select_assign == scatter-ADD in Burn 0.16: a visibility count
             if batch.slot is not None:
@@ -386,7 +408,7 @@ class SplatTrainer:
             lr_mean *= batch.scene_extent
         return lr_mean
 
-    def _backward_adam(self, ctx, splats: Splats, aux, pred, lr_mean: float, st):
+    def _train_state(self, splats: Splats, lr_mean: float):
         cfg = self.config
         S = _lib.BrushTrainState()
         for field, name, p in (("means", "means", splats.means), ("raw_opacity", "opac", splats.raw_opacity),
@@ -398,6 +420,20 @@ class SplatTrainer:
             setattr(S, "v_" + field, v.data_ptr())
         S.lr_mean, S.lr_scale, S.lr_rotation = lr_mean, cfg.lr_scale, cfg.lr_rotation
         S.lr_coeffs_dc, S.lr_opac, S.sh_rest_lr_scale = cfg.lr_coeffs_dc, cfg.lr_opac, 1.0 / cfg.lr_coeffs_sh_scale
+        return S
+
+    def _views_step(self, ctx, splats: Splats, vx, lr_mean: float, grad_scale: float, with_stats: bool, st):
+        """brush_views_adam_step: per-splat backward of every rank's view + Adam on this rank's replica."""
+        cfg = self.config
+        S = self._train_state(splats, lr_mean)
+        accum = (self.grad_2d_accum.data_ptr(), self.xy_grad_counts.data_ptr()) if with_stats else (None, None)
+        ctx.check(_lib.lib().brush_views_adam_step(
+            ctx.handle, self.n, self.k, C.byref(S), self.norm_rot.data_ptr(), C.byref(vx), accum[0], accum[1],
+            self.loss_total.data_ptr(), cfg.adam_beta1, cfg.adam_beta2, cfg.adam_eps, self.iter, grad_scale, st))
+
+    def _backward_adam(self, ctx, splats: Splats, aux, pred, lr_mean: float, st):
+        cfg = self.config
+        S = self._train_state(splats, lr_mean)
         caux = aux._c()
         ctx.check(_lib.lib().brush_render_backward_adam(
             ctx.handle, self.n, self.k, C.byref(S), self.norm_rot.data_ptr(), pred.data_ptr(), self.v_out.data_ptr(),

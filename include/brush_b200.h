@@ -192,6 +192,35 @@ int brush_render_backward_adam(brush_ctx* ctx, uint32_t N, uint32_t K, const Bru
                                const BrushAux* aux, float* v_xy, float beta1, float beta2, float eps,
                                uint32_t step, float grad_scale, void* stream);
 
+#define BRUSH_DP_MAX_WORLD 8
+/* ---- view-parallel step without a gradient exchange (no reference counterpart) ----
+ * Every rank renders its own view and publishes only what rasterize_backwards leaves per splat: the nine sums of
+ * render.rs:505-507 (48-byte rows) -- 5x less than the dense gradients.  Then every rank runs
+ * gather_grads/project_backwards for EVERY view on those rows (peer loads over NVLink), sums the gradients in view
+ * order, and applies the Adam update of brush_render_backward_adam to its own full replica.  Replicas stay
+ * bit-identical with no parameter broadcast.
+ *   rows[i]:  rank i's row block for THIS step as mapped in this process: f32[N*12 + 32], peer-mapped on every
+ *             rank; callers alternate between two blocks by step parity (that is what makes one barrier enough).
+ *   flags[i]: rank i's flag block, u32[8], zeroed once at allocation, peer-mapped.
+ *   epoch:    the same strictly increasing value (>= 1) on every rank for every step.
+ * brush_render_backward_rows = rasterize_backwards into rows[rank] + the view's visibility flags, uniforms and
+ * loss term (device f32, may be NULL), then signals every rank.  brush_views_adam_step waits for all ranks'
+ * signals and does the rest; grad_norm_accum / visible_accum (f32[N], both or neither) receive the refine
+ * statistics of train.rs:284-316 summed over the step's views (+= norm * grad_scale, += visible count);
+ * loss_out (device f32, may be NULL) = grad_scale * sum of the ranks' loss terms. */
+typedef struct BrushViewExchange {
+    int32_t world, rank;
+    float* rows[BRUSH_DP_MAX_WORLD];
+    uint32_t* flags[BRUSH_DP_MAX_WORLD];
+    uint32_t epoch;
+} BrushViewExchange;
+int brush_render_backward_rows(brush_ctx* ctx, uint32_t N, uint32_t K, const float* out_img, const float* v_out_img,
+                               const BrushAux* aux, const float* loss_term, const BrushViewExchange* x,
+                               void* stream);
+int brush_views_adam_step(brush_ctx* ctx, uint32_t N, uint32_t K, const BrushTrainState* state, const float* quats,
+                          const BrushViewExchange* x, float* grad_norm_accum, float* visible_accum, float* loss_out,
+                          float beta1, float beta2, float eps, uint32_t step, float grad_scale, void* stream);
+
 /* == the rotation normalisation Splats::render applies before the operator and its VJP (Burn elementwise ops +
  * autodiff in the reference, crates/brush-render/src/gaussian_splats.rs:174-175).  quats f32[n,4]. */
 int brush_quat_normalize(brush_ctx* ctx, const float* quats, uint32_t n, float* out, void* stream);
@@ -213,7 +242,6 @@ int brush_xy_grad_stats(brush_ctx* ctx, const float* v_xy, const BrushAux* aux, 
  * (cudaIpc / CUDA VMM / torch symmetric memory); src[i], dst[i], flags[i] are rank i's buffers as mapped in THIS
  * process.  flags[i]: uint32[2 * BRUSH_DP_MAX_WORLD], zeroed once at allocation.  epoch: the same strictly
  * increasing value (>= 1) on every rank for every call.  Every rank must make the matching call. */
-#define BRUSH_DP_MAX_WORLD 8
 typedef struct BrushDpSegment {
     uint64_t src_offset;   /* floats, multiple of 4 */
     uint64_t dst_offset;   /* floats, multiple of 4 */

@@ -97,14 +97,14 @@ def _train_worker(rank, world, port, out):
     cams = [Camera(*ring_camera_params(w, h, j, 300)) for j in range(4)]
     cfg = TrainConfig(warmup_steps=0, max_refine_step=0)
     results = {}
-    for mode in ("nccl", "peer"):
+    for mode in ("nccl", "peer", "views"):
         splats = Splats(t(sc.means), t(sc.sh_coeffs), t(sc.quats), t(sc.raw_opacity), t(sc.log_scales))
         tr = SplatTrainer(n, cfg, dev, sh_coeffs_per_channel=16, process_group=dist.group.WORLD, exchange=mode)
         splats = tr.adopt(splats)
         losses = []
         for step in range(4):
             v = (step * world + rank) % 4
-            _, stats = tr.step(SceneBatch(gts[v:v + 1], [cams[v]], 1.0), splats)
+            splats, stats = tr.step(SceneBatch(gts[v:v + 1], [cams[v]], 1.0), splats)
             losses.append(float(stats.loss))
         torch.cuda.synchronize()
         results[mode] = ([p.detach().cpu().numpy().copy() for p in (splats.means, splats.raw_opacity, splats.sh_coeffs,
@@ -133,3 +133,13 @@ def test_peer_exchange_matches_nccl_world2():
         assert close.all() if name != "rotation" else close.mean() > 0.999, name
     assert np.allclose(r0["peer"][1], r0["nccl"][1], rtol=1e-5)
     assert np.allclose(r0["peer"][2], r0["nccl"][2], rtol=1e-4, atol=1e-9) and np.array_equal(r0["peer"][3], r0["nccl"][3])
+    # "views": every rank recomputes every view's per-splat backward from the same published rows in the same
+    # order, so the replicas are bit-identical without any parameter broadcast, and equal to the all-reduce path
+    for a, b in zip(r0["views"][0], r1["views"][0]):
+        assert np.array_equal(a, b)
+    for name, a, b in zip(("means", "opacity", "sh", "rotation", "log_scales"), r0["views"][0], r0["nccl"][0]):
+        close = np.isclose(a, b, rtol=2e-5, atol=2e-6)
+        assert close.all() if name != "rotation" else close.mean() > 0.999, name
+    assert np.allclose(r0["views"][1], r0["nccl"][1], rtol=1e-5) and np.allclose(r0["views"][1], r1["views"][1])
+    assert np.allclose(r0["views"][2], r0["nccl"][2], rtol=1e-4, atol=1e-9)
+    assert np.array_equal(r0["views"][3], r0["nccl"][3]) and np.array_equal(r0["views"][2], r1["views"][2])

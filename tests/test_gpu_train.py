@@ -164,6 +164,138 @@ def test_fused_backward_adam_matches_separate_kernels(k, n):
         assert float((va - vb).abs().max()) <= 1e-4 * float(vb.abs().max())
 
 
+def test_views_step_world1_equals_fused_step():
+    """exchange="views" with one rank must reproduce the fused single-device step: same rows, same chain, same
+    Adam; the statistics are accumulated inside the kernel instead of by two elementwise launches."""
+    from brush_b200 import Camera, Splats, scene
+    from brush_b200.scene import bench_camera_params
+    from brush_b200.train import SceneBatch, SplatTrainer, TrainConfig
+
+    w, h, n, k = 160, 120, 2500, 16
+    sc = scene.make_scene(n, w, h, 3, 9)
+    t = lambda a: torch.as_tensor(a, device=DEV)
+    pos, rot, fx, fy = bench_camera_params(w, h)
+    cam = Camera(pos, rot, fx, fy)
+    gt = torch.rand((1, h, w, 3), device=DEV)
+    cfg = TrainConfig(warmup_steps=0, max_refine_step=0)
+    res = []
+    for mode in ("views", "nccl"):
+        sp = Splats(t(sc.means), t(sc.sh_coeffs), t(sc.quats * 1.7), t(sc.raw_opacity), t(sc.log_scales))
+        tr = SplatTrainer(n, cfg, DEV, sh_coeffs_per_channel=k, exchange=mode)
+        for i in range(4):
+            sp, stats = tr.step(SceneBatch(gt, [cam], 1.0), sp)
+        res.append(([sp.means, sp.sh_coeffs, sp.rotation, sp.raw_opacity, sp.log_scales], tr.grad_2d_accum.clone(),
+                    tr.xy_grad_counts.clone(), float(stats.loss)))
+    (pa, ga, ca, la), (pb, gb, cb, lb) = res
+    assert abs(la - lb) <= 1e-5 and torch.equal(ca, cb) and float(ca.sum()) > 0
+    assert float((ga - gb).abs().max()) <= 1e-4 * float(gb.abs().max())
+    for name, a, b, o in zip(("means", "sh", "rotation", "opacity", "scales"), pa, pb,
+                             (sc.means, sc.sh_coeffs, sc.quats * 1.7, sc.raw_opacity, sc.log_scales)):
+        delta = float((b - t(o)).abs().max())
+        assert delta > 1e-5 and float((a - b).abs().max()) <= 2e-3 * delta, name
+
+
+@pytest.mark.parametrize("k", [1, 16])
+def test_views_step_two_views_on_one_device(k):
+    """The multi-view kernel with world = 2 emulated on one GPU: "rank 0" and "rank 1" publish the rows of two
+    different cameras into two local blocks that share one flag block, then the step runs as rank 0.  Reference:
+    the separate entry points -- brush_render_backward per view, gradients summed, normalisation VJP,
+    brush_adam_step with grad_scale 1/2 -- and brush_xy_grad_stats for the statistics."""
+    import ctypes as C
+
+    from brush_b200 import Camera, _lib, get_context, scene
+    from brush_b200.render import make_uniforms, render_backward, render_forward
+    from brush_b200.scene import bench_camera_params
+
+    L = _lib.lib()
+    ctx = get_context(DEV)
+    w, h, n = 176, 128, 3001
+    sc = scene.make_scene(n, w, h, {1: 0, 16: 3}[k], 21)
+    t = lambda a: torch.as_tensor(a, device=DEV)
+    pos, rot, fx, fy = bench_camera_params(w, h)
+    cams = [Camera(pos, rot, fx, fy), Camera(pos + np.array([0.4, -0.2, 0.1], np.float32), rot, fx * 1.1, fy * 1.1)]
+    raw_rot = t(sc.quats * 0.6)
+    norm_rot = torch.empty_like(raw_rot)
+    ctx.check(L.brush_quat_normalize(ctx.handle, raw_rot.data_ptr(), n, norm_rot.data_ptr(), None))
+    params = {"means": t(sc.means), "log_scales": t(sc.log_scales), "rotation": raw_rot, "sh_coeffs": t(sc.sh_coeffs),
+              "raw_opacity": t(sc.raw_opacity)}
+    lrs = dict(lr_mean=1e-3, lr_scale=5e-3, lr_rotation=2e-3, lr_coeffs_dc=3e-3, lr_opac=2e-2, sh_rest_lr_scale=0.05)
+    torch.manual_seed(0)
+    v_out = [torch.randn((h, w, 4), device=DEV) * 0.01 for _ in cams]
+    block = n * 12 + 32
+    rows = torch.zeros(2 * block, device=DEV)
+    flags = torch.zeros(64, dtype=torch.int32, device=DEV)
+    ref_g, ref_norm, ref_vis, keep = None, torch.zeros(n, device=DEV), torch.zeros(n, device=DEV), []
+    for r, cam in enumerate(cams):
+        u = make_uniforms(cam.world_to_local(), cam.focal((w, h)), (w, h), cam.center((w, h)))
+        pred, aux = render_forward(u, params["means"], params["log_scales"], norm_rot, params["sh_coeffs"],
+                                   params["raw_opacity"], False, ctx=ctx)
+        keep.append((pred, aux))
+        x = _lib.BrushViewExchange()
+        x.world, x.rank, x.epoch = 2, r, 1
+        for i in range(2):
+            x.rows[i], x.flags[i] = rows.data_ptr() + 4 * block * i, flags.data_ptr()
+        loss_term = torch.full((1,), 0.25 * (r + 1), device=DEV)
+        caux = aux._c()
+        ctx.check(L.brush_render_backward_rows(ctx.handle, n, k, pred.data_ptr(), v_out[r].data_ptr(), C.byref(caux),
+                                               loss_term.data_ptr(), C.byref(x), None))
+        g = render_backward(aux, params["means"], params["log_scales"], norm_rot, params["sh_coeffs"].shape,
+                            params["raw_opacity"], pred, v_out[r], ctx=ctx)
+        gn, gv = torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)
+        ctx.check(L.brush_xy_grad_stats(ctx.handle, g[1].data_ptr(), C.byref(caux), n, w, h, 0, gn.data_ptr(),
+                                        gv.data_ptr(), None))
+        ref_norm += 0.5 * gn
+        ref_vis += gv
+        ref_g = [a.clone() for a in g] if ref_g is None else [a + b for a, b in zip(ref_g, g)]
+    v_means, _, v_scales, v_quats, v_sh, v_opac = ref_g
+    ctx.check(L.brush_quat_normalize_vjp(ctx.handle, raw_rot.data_ptr(), n, v_quats.data_ptr(), None))
+    # reference: brush_adam_step on clones
+    ref_p = {kk: v.clone() for kk, v in params.items()}
+    groups = (_lib.BrushAdamGroup * 5)()
+    spec = [("means", v_means, lrs["lr_mean"], 0), ("raw_opacity", v_opac, lrs["lr_opac"], 0),
+            ("sh_coeffs", v_sh, lrs["lr_coeffs_dc"], k), ("rotation", v_quats, lrs["lr_rotation"], 0),
+            ("log_scales", v_scales, lrs["lr_scale"], 0)]
+    ref_state = {}
+    for i, (name, g, lr, shk) in enumerate(spec):
+        ref_state[name] = (torch.zeros_like(ref_p[name]), torch.zeros_like(ref_p[name]))
+        groups[i].param, groups[i].grad = ref_p[name].data_ptr(), g.data_ptr()
+        groups[i].m, groups[i].v = ref_state[name][0].data_ptr(), ref_state[name][1].data_ptr()
+        groups[i].count, groups[i].lr = ref_p[name].numel(), lr
+        groups[i].sh_coeffs_per_channel, groups[i].sh_rest_lr_scale = shk, lrs["sh_rest_lr_scale"]
+    ctx.check(L.brush_adam_step(ctx.handle, groups, 5, 0.9, 0.999, 1e-15, 1, 0.5, None))
+    # the step under test, as rank 0
+    S = _lib.BrushTrainState()
+    state = {}
+    for name, p in params.items():
+        state[name] = (torch.zeros_like(p), torch.zeros_like(p))
+        setattr(S, name, p.data_ptr())
+        setattr(S, "m_" + name, state[name][0].data_ptr())
+        setattr(S, "v_" + name, state[name][1].data_ptr())
+    for kk, v in lrs.items():
+        setattr(S, kk, v)
+    x = _lib.BrushViewExchange()
+    x.world, x.rank, x.epoch = 2, 0, 1
+    for i in range(2):
+        x.rows[i], x.flags[i] = rows.data_ptr() + 4 * block * i, flags.data_ptr()
+    acc_norm, acc_vis, loss = torch.zeros(n, device=DEV), torch.zeros(n, device=DEV), torch.zeros(1, device=DEV)
+    ctx.check(L.brush_views_adam_step(ctx.handle, n, k, C.byref(S), norm_rot.data_ptr(), C.byref(x),
+                                      acc_norm.data_ptr(), acc_vis.data_ptr(), loss.data_ptr(), 0.9, 0.999, 1e-15, 1,
+                                      0.5, None))
+    torch.cuda.synchronize()
+    assert abs(float(loss) - 0.375) < 1e-6
+    assert torch.equal(acc_vis, ref_vis) and float(acc_vis.max()) == 2.0
+    assert float((acc_norm - ref_norm).abs().max()) <= 1e-5 * float(ref_norm.abs().max())
+    # first-step Adam moves every touched parameter by ~lr (sign-like), so compare the moments: they carry the
+    # summed gradients themselves (m = 0.1 * g / 2).  Atomics-order noise only: 1e-4 of the largest entry.
+    for name in params:
+        m, v = state[name]
+        rm, rv = ref_state[name]
+        assert float(rm.abs().max()) > 0
+        assert float((m - rm).abs().max()) <= 1e-4 * float(rm.abs().max()), name
+        assert float((v - rv).abs().max()) <= 2e-4 * float(rv.abs().max()), name
+        assert float((params[name] - ref_p[name]).abs().max()) <= 0.05 * max(lrs.values()), name
+
+
 @pytest.mark.parametrize("channels,h,w", [(3, 37, 53), (4, 64, 48), (3, 16, 16)])
 def test_image_loss_ssim_forward_and_gradient(channels, h, w):
     """brush_image_loss_backward vs the numpy oracle (loss value) and torch autograd of the same definition
