@@ -364,8 +364,8 @@ void launch_backward_adam(const Cam& cam, uint32_t N, uint32_t K, const float* n
 //   publish_view_kernel: marks the view's visible splats in word 9 of their rows, copies the view's uniforms and
 //       loss term behind the rows;  arrive_kernel: release-stores this step's epoch into every rank's flag block.
 //   views_adam_kernel: acquire-waits for all ranks' epochs, then per block of 256 splats: for each view, the
-//       block's 12 KB of rows is fetched coalesced (next view in flight while this one is processed), staged in
-//       shared memory, and each thread runs the chain for its splat; SH gradients accumulate in shared memory;
+//       block's 12 KB of rows is fetched coalesced with cp.async into a ring in shared memory (two views in flight
+//       while one is processed), and each thread runs the chain for its splat; SH gradients accumulate in shared memory;
 //       Adam as in backward_adam_kernel.  Row buffers alternate between two halves by step parity, so no second
 //       barrier is needed: a rank can overwrite a half only after every peer has arrived at the step in between.
 __global__ void __launch_bounds__(256)
@@ -399,6 +399,7 @@ void launch_publish_view(float* rows, uint32_t N, const uint32_t* global_from_co
     arrive_kernel<<<1, 32, 0, st>>>(L);
 }
 
+constexpr int VIEW_STAGES = 3;
 template <int K>
 __global__ void __launch_bounds__(256, 2)
 views_adam_kernel(const __grid_constant__ ViewsLaunch X, uint32_t N, const float* __restrict__ norm_quats,
@@ -406,7 +407,7 @@ views_adam_kernel(const __grid_constant__ ViewsLaunch X, uint32_t N, const float
     constexpr int S = (3 * K) | 1;  // odd row stride: thread-per-row accumulation is bank-conflict free
     extern __shared__ float4 views_smem[];
     float* s_g = reinterpret_cast<float*>(views_smem);            // [256][S] SH gradients, summed over views
-    float4* s_rows = reinterpret_cast<float4*>(s_g + 256 * S);    // [256 * 3] one view's rows of this block
+    float4* s_rows = reinterpret_cast<float4*>(s_g + 256 * S);    // [VIEW_STAGES][256 * 3] rows of this block, per view
     __shared__ Cam s_cam[DP_MAX_WORLD];
     const int world = X.world, tid = threadIdx.x;
 
@@ -431,14 +432,21 @@ views_adam_kernel(const __grid_constant__ ViewsLaunch X, uint32_t N, const float
 
     const uint32_t first = blockIdx.x * 256u, g = first + tid;
     const int nf4 = 3 * (int)min(256u, N - first);
-    float4 pre[3];
+    // VIEW_STAGES - 1 views' rows in flight per block, global -> shared without passing through registers
     auto fetch = [&](int w) {
-        const float* src = X.rows[w] + (size_t)first * VP_STRIDE;
+        if (w < world) {
+            const float* src = X.rows[w] + (size_t)first * VP_STRIDE;
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(s_rows + (w % VIEW_STAGES) * 768);
 #pragma unroll
-        for (int j = 0; j < 3; j++)
-            if (tid + 256 * j < nf4) pre[j] = ld_peer_v4(src + 4 * (tid + 256 * j));
+            for (int j = 0; j < 3; j++)
+                if (tid + 256 * j < nf4)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * (tid + 256 * j)),
+                                 "l"(src + 4 * (tid + 256 * j)) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
     };
-    fetch(0);
+#pragma unroll
+    for (int w = 0; w < VIEW_STAGES - 1; w++) fetch(w);
 
     float mean[3] = {0.f, 0.f, 0.f}, ls[3] = {0.f, 0.f, 0.f}, opac = 0.f;
     float4 q_raw = make_float4(0.f, 0.f, 0.f, 1.f), q4 = q_raw;
@@ -458,14 +466,12 @@ views_adam_kernel(const __grid_constant__ ViewsLaunch X, uint32_t N, const float
     float v_alpha_sum = 0.f, norm_sum = 0.f, vis_sum = 0.f;
 
     for (int w = 0; w < world; w++) {
-        __syncthreads();  // the previous view's rows are consumed (first pass: s_cam is complete)
-#pragma unroll
-        for (int j = 0; j < 3; j++)
-            if (tid + 256 * j < nf4) s_rows[tid + 256 * j] = pre[j];
-        __syncthreads();
-        if (w + 1 < world) fetch(w + 1);
+        asm volatile("cp.async.wait_group %0;" ::"n"(VIEW_STAGES - 2) : "memory");
+        __syncthreads();  // view w has landed for every thread; view w - 1 is consumed (first pass: s_cam is complete)
+        fetch(w + VIEW_STAGES - 1);  // into the slot view w - 1 occupied
         if (g < N) {
-            const float4 r0 = s_rows[3 * tid], r1 = s_rows[3 * tid + 1], r2 = s_rows[3 * tid + 2];
+            const float4* row = s_rows + (w % VIEW_STAGES) * 768 + 3 * tid;
+            const float4 r0 = row[0], r1 = row[1], r2 = row[2];
             const Cam& cam = s_cam[w];
             vis_sum += r2.y;
             const bool zero = r0.x == 0.f && r0.y == 0.f && r0.z == 0.f && r0.w == 0.f && r1.x == 0.f &&
@@ -510,7 +516,7 @@ views_adam_kernel(const __grid_constant__ ViewsLaunch X, uint32_t N, const float
 template <int K>
 static int launch_views_adam_k(const ViewsLaunch& X, uint32_t N, const float* norm_quats, const FusedAdamLaunch& A,
                                cudaStream_t st) {
-    const size_t smem = (size_t)256 * ((3 * K) | 1) * 4 + 256 * 3 * 16;
+    const size_t smem = (size_t)256 * ((3 * K) | 1) * 4 + (size_t)VIEW_STAGES * 256 * 3 * 16;
     cudaError_t e = cudaFuncSetAttribute(views_adam_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     views_adam_kernel<K><<<(N + 255) / 256, 256, smem, st>>>(X, N, norm_quats, A);

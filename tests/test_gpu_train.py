@@ -287,13 +287,17 @@ def test_views_step_two_views_on_one_device(k):
     assert float((acc_norm - ref_norm).abs().max()) <= 1e-5 * float(ref_norm.abs().max())
     # first-step Adam moves every touched parameter by ~lr (sign-like), so compare the moments: they carry the
     # summed gradients themselves (m = 0.1 * g / 2).  Atomics-order noise only: 1e-4 of the largest entry.
+    group_lr = {"means": lrs["lr_mean"], "log_scales": lrs["lr_scale"], "rotation": lrs["lr_rotation"],
+                "sh_coeffs": lrs["lr_coeffs_dc"], "raw_opacity": lrs["lr_opac"]}
     for name in params:
         m, v = state[name]
         rm, rv = ref_state[name]
         assert float(rm.abs().max()) > 0
         assert float((m - rm).abs().max()) <= 1e-4 * float(rm.abs().max()), name
         assert float((v - rv).abs().max()) <= 2e-4 * float(rv.abs().max()), name
-        assert float((params[name] - ref_p[name]).abs().max()) <= 0.05 * max(lrs.values()), name
+        # a gradient within noise of zero may step the other way (first-step Adam is sign-like): at most 2 lr apart
+        diff = (params[name] - ref_p[name]).abs()
+        assert float(diff.max()) <= 2.01 * group_lr[name] and float((diff <= 1e-6).float().mean()) > 0.999, name
 
 
 @pytest.mark.parametrize("channels,h,w", [(3, 37, 53), (4, 64, 48), (3, 16, 16)])
