@@ -156,18 +156,20 @@ def run_ours(args):
     splats = Splats(t(sc.means), t(sc.sh_coeffs), t(sc.quats), t(sc.raw_opacity), t(sc.log_scales))
     cams = view_cameras(W, H)
     ctx = get_context(dev)
-    # Ground truth = the scene's own render of each view + pixel noise (sigma 0.1): the loss gradient is dense and
-    # non-zero but has no consistent direction, so the workload (visible splats, intersections, pairs) stays what
-    # BASELINE.json names for the whole run.  (Uniform-noise targets drive every opacity down: the per-step cost
-    # falls by a third within 300 steps, faster with more views per step.)
+    # Targets = the scene's own render of each view; training starts from perturbed colours and opacities.  The
+    # loss gradient is dense and non-zero, but its only consistent direction is back towards the scene, so the
+    # workload (visible splats, intersections, pairs) stays what BASELINE.json names for the whole run.  (Noise
+    # targets drive every opacity down: the per-step cost falls by a third within 300 steps, and faster with
+    # more views per step, which would flatter the multi-GPU numbers.)
     gen = torch.Generator(device=dev)
     gen.manual_seed(4242)
     gt_dev = torch.empty((N_VIEWS, H, W, 3), dtype=torch.float32, device=dev)
     with torch.no_grad():
         for v, cam in enumerate(cams):
             img, _ = splats.render(cam, (W, H), False)
-            noise = torch.randn((H, W, 3), device=dev, generator=gen) * 0.1
-            gt_dev[v] = (img[..., :3] + noise).clamp_(0.0, 1.0)
+            gt_dev[v] = img[..., :3].clamp_(0.0, 1.0)
+        splats.sh_coeffs.add_(torch.randn(splats.sh_coeffs.shape, device=dev, generator=gen) * 0.1)
+        splats.raw_opacity.add_(torch.randn(splats.raw_opacity.shape, device=dev, generator=gen) * 0.3)
     gt_host = gt_dev.cpu().pin_memory()
     # measured on 8xB200 (profiles/): publishing 48-byte rows and replicating the tail wins up to 4 ranks (its
     # inbound NVLink traffic grows with world - 1), the sharded sum + Adam + multicast broadcast wins at 8
@@ -252,6 +254,13 @@ def run_ours(args):
     for s in range(args.warmup):
         one_step(s, False)
     ctx.sync_check()  # raises if the intersection capacity was too small
+    if args.profile_step:  # ncu --profile-from-start off: exactly one steady-state step is captured
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        one_step(args.warmup, False)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        return
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -339,7 +348,7 @@ def run_ours(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {N} random Gaussians, SH degree {sc.sh_degree}, {W}x{H}, one view per "
-                               f"GPU per step ({N_VIEWS} views; targets = the scene's own render + N(0, 0.1) noise), loss 0.8 L1 - 0.2 SSIM "
+                               f"GPU per step ({N_VIEWS} views; targets = the scene's own renders, start = colours and opacities perturbed), loss 0.8 L1 - 0.2 SSIM "
                                f"(reference default), {'fused Adam' if not args.no_optim else 'no optimizer'}, "
                                f"{exchange_desc}",
                    "num_visible": V, "num_intersections": I, "views": N_VIEWS, "isect_capacity": args.capacity,
@@ -453,6 +462,9 @@ def main():
     ap.add_argument("--capacity", type=int, default=ISECT_CAPACITY)
     ap.add_argument("--no-optim", action="store_true", help="skip Adam (pure fwd+bwd, the reference bench shape)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile-step", action="store_true",
+                    help="run the warm-up, then ONE step between cudaProfilerStart/Stop and exit (for ncu "
+                         "--profile-from-start off); prints no bench line")
     ap.add_argument("--exchange", choices=["auto", "views", "peer", "nccl"], default="auto",
                     help="multi-GPU step: per-view rows in peer memory + replicated fused tail (default), dense "
                          "gradient sum fused with Adam over peer memory, or NCCL all-reduce")
