@@ -212,13 +212,19 @@ def run_ours(args):
         """The user-facing loop: every step's view comes from pinned host memory (copy started one step ahead on
         a side stream, as a prefetching feed does) and every step's loss is read back to the host; the host waits
         for the loss of step t only after it has launched step t+1, so the device never idles on the host."""
-        nxt = trainer.prefetch(make_batch(first_idx, True))
+        dbg = os.environ.get("BRUSH_E2E_DEBUG", "")
+        host_in = "nohost" not in dbg
+        nxt = trainer.prefetch(make_batch(first_idx, host_in))
         for s in range(n_steps):
             _, stats = trainer.step(nxt, splats)
+            if "noloss" in dbg:
+                if s + 1 < n_steps:
+                    nxt = trainer.prefetch(make_batch(first_idx + s + 1, host_in))
+                continue
             loss_slots[s & 1].copy_(stats.loss, non_blocking=True)
             loss_events[s & 1].record()
             if s + 1 < n_steps:
-                nxt = trainer.prefetch(make_batch(first_idx + s + 1, True))
+                nxt = trainer.prefetch(make_batch(first_idx + s + 1, host_in))
             if s >= 1:
                 loss_events[(s - 1) & 1].synchronize()
                 loss_host.copy_(loss_slots[(s - 1) & 1])

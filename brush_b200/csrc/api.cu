@@ -269,12 +269,12 @@ int brush_render_forward(brush_ctx* ctx, const BrushUniforms* uniforms_host, uin
             ctx->uni_cache.emplace_back(aux->uniforms_buffer, u);
         }
     }
-    CU(cudaMemsetAsync(ctl, 0, cl.total, st));
+    CU(zero_async(ctl, cl.total, st));
     g_launch_count++;
     write_uniforms_kernel<<<1, 32, 0, st>>>(u, aux->uniforms_buffer);
-    CU(cudaMemsetAsync(aux->num_visible, 0, 4, st));
-    CU(cudaMemsetAsync(aux->num_intersections, 0, 4, st));
-    if (N) CU(cudaMemsetAsync(gfc, 0, (size_t)N * 4, st));  // int_zeros, render.rs:124
+    CU(zero_async(aux->num_visible, 4, st));
+    CU(zero_async(aux->num_intersections, 4, st));
+    if (N) CU(zero_async(gfc, (size_t)N * 4, st));  // int_zeros, render.rs:124
 
     {   // render.rs:127-142
         StageTimer t(ctx, st, BRUSH_STAGE_PROJECT_SPLATS);
@@ -361,7 +361,7 @@ int brush_render_backward(brush_ctx* ctx, uint32_t N, uint32_t K, const float* m
         // The reference zero-fills nine accumulators and six outputs (render.rs:505-507,539-540,547,573-575).  Here
         // only the rasterizer's accumulator is zeroed: the per-splat backward writes every row of every output,
         // zeros included, in one coalesced pass.
-        CU(cudaMemsetAsync(ctx->v_projected.p, 0, (size_t)N * VP_STRIDE * 4, st));
+        CU(zero_async(ctx->v_projected.p, (size_t)N * VP_STRIDE * 4, st));
     }
     {   // render.rs:515-532
         StageTimer t(ctx, st, BRUSH_STAGE_RASTERIZE_BWD);
@@ -438,7 +438,7 @@ int brush_render_backward_rows(brush_ctx* ctx, uint32_t N, uint32_t K, const flo
     const Cam cam = make_cam(u);
     float* rows = x->rows[x->rank];
     ctx->ev_used[BRUSH_STAGE_RASTERIZE_BWD] = ctx->ev_used[BRUSH_STAGE_GATHER_PROJECT_BWD] = false;
-    CU(cudaMemsetAsync(rows, 0, (size_t)N * VP_STRIDE * 4, st));
+    CU(zero_async(rows, (size_t)N * VP_STRIDE * 4, st));
     {
         StageTimer t(ctx, st, BRUSH_STAGE_RASTERIZE_BWD);
         launch_rasterize_backward(cam, (uint32_t*)aux->compact_gid_from_isect, (uint32_t*)aux->tile_bins,
@@ -503,7 +503,7 @@ int brush_render_backward_adam(brush_ctx* ctx, uint32_t N, uint32_t K, const Bru
     const Cam cam = make_cam(u);
     ENSURE(v_projected, (size_t)N * VP_STRIDE * 4 + 16);
     ctx->ev_used[BRUSH_STAGE_RASTERIZE_BWD] = ctx->ev_used[BRUSH_STAGE_GATHER_PROJECT_BWD] = false;
-    if (N) CU(cudaMemsetAsync(ctx->v_projected.p, 0, (size_t)N * VP_STRIDE * 4, st));
+    if (N) CU(zero_async(ctx->v_projected.p, (size_t)N * VP_STRIDE * 4, st));
     {
         StageTimer t(ctx, st, BRUSH_STAGE_RASTERIZE_BWD);
         launch_rasterize_backward(cam, (uint32_t*)aux->compact_gid_from_isect, (uint32_t*)aux->tile_bins,
@@ -559,7 +559,7 @@ int brush_prefix_sum_u32(brush_ctx* ctx, const uint32_t* in, uint32_t n, uint32_
     cudaStream_t st = (cudaStream_t)stream;
     size_t bytes = 64 + scan_status_words(n) * 8;
     ENSURE(control, bytes);
-    CU(cudaMemsetAsync(ctx->control.p, 0, bytes, st));
+    CU(zero_async(ctx->control.p, bytes, st));
     launch_inclusive_scan(in, n, out, (uint64_t*)((char*)ctx->control.p + 64), (uint32_t*)ctx->control.p, nullptr,
                           ~0ull, nullptr, st);
     CU(cudaGetLastError());
@@ -657,7 +657,7 @@ int brush_l1_loss_backward(brush_ctx* ctx, const float* pred, const float* gt, u
     if (gt_channels != 3 && gt_channels != 4) return fail(ctx, BRUSH_E_INVALID, "gt_channels must be 3 or 4");
     CU(cudaSetDevice(ctx->device));
     cudaStream_t st = (cudaStream_t)stream;
-    CU(cudaMemsetAsync(loss_out, 0, 4, st));
+    CU(zero_async(loss_out, 4, st));
     launch_l1_loss_backward(pred, gt, height * width, gt_channels, v_out_img, loss_out, st);
     CU(cudaGetLastError());
     return BRUSH_OK;

@@ -130,6 +130,10 @@ int launch_views_adam(const ViewsLaunch& X, uint32_t N, uint32_t K, const float*
                       cudaStream_t st);
 
 // ---- optim.cu ----
+// Zero-fill by a kernel on `st` (16-byte granular when aligned).  Used instead of cudaMemsetAsync everywhere in the
+// step: driver memsets and small copies may be routed through a copy engine, where they queue behind a concurrent
+// host->device upload of the next training view on another stream and stall the compute stream.
+cudaError_t zero_async(void* p, size_t bytes, cudaStream_t st);
 extern std::atomic<uint64_t> g_launch_count;  // kernels launched by this library (bench.py's gpu_launches)
 struct AdamSeg {
     float* param;

@@ -180,4 +180,27 @@ void launch_xy_grad_stats(const float* v_xy, const uint32_t* gfc, const int32_t*
     visible_flags_kernel<<<(n + 255) / 256, 256, 0, st>>>(gfc, num_visible_dev, visible);
 }
 
+__global__ void __launch_bounds__(256)
+zero_fill_kernel(uint4* __restrict__ p16, size_t n16, unsigned char* __restrict__ tail, uint32_t ntail) {
+    const size_t stride = (size_t)gridDim.x * 256u;
+    for (size_t i = (size_t)blockIdx.x * 256u + threadIdx.x; i < n16; i += stride) p16[i] = make_uint4(0u, 0u, 0u, 0u);
+    if (blockIdx.x == 0 && threadIdx.x < ntail) tail[threadIdx.x] = 0;
+}
+cudaError_t zero_async(void* p, size_t bytes, cudaStream_t st) {
+    if (!bytes) return cudaSuccess;
+    unsigned char* b = (unsigned char*)p;
+    if (((uintptr_t)b & 15u) || bytes < 16) {  // unaligned or tiny: byte-wise through the tail path when it fits
+        if (bytes <= 256) {
+            zero_fill_kernel<<<1, 256, 0, st>>>(nullptr, 0, b, (uint32_t)bytes);
+            return cudaGetLastError();
+        }
+        return cudaMemsetAsync(p, 0, bytes, st);
+    }
+    const size_t n16 = bytes / 16;
+    size_t blocks = (n16 + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    zero_fill_kernel<<<(uint32_t)blocks, 256, 0, st>>>((uint4*)b, n16, b + n16 * 16, (uint32_t)(bytes - n16 * 16));
+    return cudaGetLastError();
+}
+
 }  // namespace brush

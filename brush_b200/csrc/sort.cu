@@ -288,9 +288,9 @@ static void radix_sort_impl(const KeyT* keys, const uint32_t* vals, const int32_
         return;
     }
     const uint32_t tiles = (uint32_t)sort_tiles(max_n, sizeof(KeyT));
-    cudaMemsetAsync(s.hist, 0, (size_t)plan.passes * RS_RADIX * 4, st);
-    cudaMemsetAsync(s.lb, 0, (size_t)plan.passes * tiles * RS_RADIX * 4, st);
-    cudaMemsetAsync(s.tickets, 0, RS_MAX_PASSES * 4, st);
+    zero_async(s.hist, (size_t)plan.passes * RS_RADIX * 4, st);
+    zero_async(s.lb, (size_t)plan.passes * tiles * RS_RADIX * 4, st);
+    zero_async(s.tickets, RS_MAX_PASSES * 4, st);
     uint32_t hist_blocks = (max_n + RS_THREADS * 4 - 1) / (RS_THREADS * 4);
     if (hist_blocks > 148 * 4) hist_blocks = 148 * 4;  // every block ends with up to passes*256 global atomics
     g_launch_count += 1 + plan.passes;

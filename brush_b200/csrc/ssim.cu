@@ -268,7 +268,7 @@ void launch_image_loss_backward(const float* pred, const float* gt, uint32_t H, 
                                 float ssim_weight, float* maps, float* sums, float* v_out, float* loss_out,
                                 cudaStream_t st) {
     static const SsimWin win = make_window();
-    cudaMemsetAsync(sums, 0, 32, st);
+    zero_async(sums, 32, st);
     if (ssim_weight > 0.f) {
         dim3 grid((W + 2 + SS_TX - 1) / SS_TX, (H + 2 + SS_TY - 1) / SS_TY);
         g_launch_count++;

@@ -237,9 +237,8 @@ class SplatTrainer:
                 # loss = (1-w) L1 - w SSIM and d loss / d pred in two launches (train.rs:249-268, ssim.rs)
                 ctx.check(L.brush_image_loss_backward(ctx.handle, pred.data_ptr(), gt.data_ptr(), H, W, Cc,
                                                       cfg.ssim_weight, cfg.ssim_window_size, self.v_out.data_ptr(),
-                                                      self.loss_buf.data_ptr(), st))
+                                                      (self.loss_total if i == 0 else self.loss_buf).data_ptr(), st))
                 if i == 0:
-                    self.loss_total.copy_(self.loss_buf)
                     dst = outs
                 else:
                     self.loss_total.add_(self.loss_buf)
@@ -253,7 +252,7 @@ class SplatTrainer:
                     caux = aux._c()
                     ctx.check(L.brush_render_backward_rows(ctx.handle, self.n, self.k, pred.data_ptr(),
                                                            self.v_out.data_ptr(), C.byref(caux),
-                                                           self.loss_buf.data_ptr(), C.byref(vx), st))
+                                                           self.loss_total.data_ptr(), C.byref(vx), st))
                     preds.append(pred)
                     auxes.append(aux)
                     break
@@ -285,7 +284,7 @@ class SplatTrainer:
             if views:
                 with_stats = self.iter - 1 > cfg.warmup_steps  # train.rs:286-316
                 self._views_step(ctx, splats, vx, lr_mean, grad_scale, with_stats, st)
-                loss = self.loss_total
+                loss = self.loss_buf  # grad_scale * sum over ranks, written by the step kernel
             elif self.peer is not None:
                 if splats.means.data_ptr() != self.peer.param.data_ptr() + 4 * self.param_layout.offset("means"):
                     raise ValueError("peer exchange: pass the Splats returned by SplatTrainer.adopt()")
@@ -429,7 +428,7 @@ class SplatTrainer:
         accum = (self.grad_2d_accum.data_ptr(), self.xy_grad_counts.data_ptr()) if with_stats else (None, None)
         ctx.check(_lib.lib().brush_views_adam_step(
             ctx.handle, self.n, self.k, C.byref(S), self.norm_rot.data_ptr(), C.byref(vx), accum[0], accum[1],
-            self.loss_total.data_ptr(), cfg.adam_beta1, cfg.adam_beta2, cfg.adam_eps, self.iter, grad_scale, st))
+            self.loss_buf.data_ptr(), cfg.adam_beta1, cfg.adam_beta2, cfg.adam_eps, self.iter, grad_scale, st))
 
     def _backward_adam(self, ctx, splats: Splats, aux, pred, lr_mean: float, st):
         cfg = self.config
