@@ -117,6 +117,7 @@ _SIGS = {
     "brush_dp_adam_step": (C.c_int, [C.c_void_p, C.POINTER(BrushDpStep), C.POINTER(BrushDpSegment), C.c_int,
                                      C.c_float, C.c_float, C.c_float, C.c_uint32, C.c_float, C.c_void_p]),
     "brush_dp_owned_range": (None, [C.c_uint64, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "brush_image_u8_to_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
     "brush_quat_normalize": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]),
     "brush_quat_normalize_vjp": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]),
     "brush_xy_grad_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(BrushAux), C.c_uint32, C.c_uint32,

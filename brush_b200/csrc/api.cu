@@ -623,6 +623,15 @@ int brush_render_forward_host(brush_ctx* ctx, const BrushUniforms* uniforms_host
 
 uint64_t brush_launch_count(void) { return g_launch_count.load(); }
 
+int brush_image_u8_to_f32(brush_ctx* ctx, const uint8_t* src, uint64_t n, float* dst, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (n && (!src || !dst)) return fail(ctx, BRUSH_E_INVALID, "null argument");
+    if (((uintptr_t)src & 3u) || ((uintptr_t)dst & 15u)) return fail(ctx, BRUSH_E_INVALID, "image buffers must be aligned");
+    CU(cudaSetDevice(ctx->device));
+    launch_image_u8_to_f32(src, (size_t)n, dst, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
 int brush_quat_normalize(brush_ctx* ctx, const float* quats, uint32_t n, float* out, void* stream) {
     if (!ctx) return BRUSH_E_INVALID;
     if (n && (!quats || !out)) return fail(ctx, BRUSH_E_INVALID, "null argument");

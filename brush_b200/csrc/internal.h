@@ -158,6 +158,7 @@ void launch_adam(const AdamLaunch& L, cudaStream_t st);
 void launch_image_loss_backward(const float* pred, const float* gt, uint32_t H, uint32_t W, uint32_t C,
                                 float ssim_weight, float* maps, float* sums, float* v_out, float* loss_out,
                                 cudaStream_t st);
+void launch_image_u8_to_f32(const unsigned char* src, size_t n, float* dst, cudaStream_t st);
 void launch_quat_normalize(const float* q, uint32_t n, float* out, cudaStream_t st);
 void launch_quat_normalize_vjp(const float* q, uint32_t n, float* v_inout, cudaStream_t st);
 void launch_xy_grad_stats(const float* v_xy, const uint32_t* gfc, const int32_t* num_visible_dev, uint32_t n,

@@ -160,6 +160,29 @@ visible_flags_kernel(const uint32_t* __restrict__ global_from_compact, const int
     visible[global_from_compact[c]] += 1.0f;  // compact ids are unique: no race
 }
 
+// == image_to_tensor's u8 -> f32 / 255 (crates/brush-dataset/src/lib.rs), done after the upload instead of before
+// it: the host keeps (and PCIe carries) one byte per channel.  Four channels' worth per thread.
+__global__ void __launch_bounds__(256)
+image_u8_to_f32_kernel(const uchar4* __restrict__ src, size_t n4, float4* __restrict__ dst,
+                       const unsigned char* __restrict__ src1, float* __restrict__ dst1, uint32_t ntail) {
+    const size_t stride = (size_t)gridDim.x * 256u;
+    for (size_t i = (size_t)blockIdx.x * 256u + threadIdx.x; i < n4; i += stride) {
+        const uchar4 v = src[i];
+        dst[i] = make_float4((float)v.x / 255.0f, (float)v.y / 255.0f, (float)v.z / 255.0f, (float)v.w / 255.0f);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < ntail) dst1[threadIdx.x] = (float)src1[threadIdx.x] / 255.0f;
+}
+void launch_image_u8_to_f32(const unsigned char* src, size_t n, float* dst, cudaStream_t st) {
+    if (!n) return;
+    const size_t n4 = n / 4;
+    size_t blocks = (n4 + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks == 0) blocks = 1;
+    g_launch_count++;
+    image_u8_to_f32_kernel<<<(uint32_t)blocks, 256, 0, st>>>((const uchar4*)src, n4, (float4*)dst, src + 4 * n4,
+                                                             dst + 4 * n4, (uint32_t)(n - 4 * n4));
+}
+
 void launch_quat_normalize(const float* q, uint32_t n, float* out, cudaStream_t st) {
     if (!n) return;
     g_launch_count++;

@@ -165,17 +165,31 @@ class SplatTrainer:
         if self._copy_stream is None:
             self._copy_stream = torch.cuda.Stream(dev)
             self._slots, self._slot_free, self._next_slot = [None, None], [None, None], 0
+            self._slots_u8 = [None, None]
         k = self._next_slot
         self._next_slot ^= 1
         if self._slots[k] is None or self._slots[k].shape != batch.gt_images.shape:
             self._slots[k] = torch.empty(batch.gt_images.shape, dtype=torch.float32, device=dev)
+        quantized = batch.gt_images.dtype == torch.uint8  # bytes cross PCIe, /255 happens on the device
+        if quantized and (self._slots_u8[k] is None or self._slots_u8[k].shape != batch.gt_images.shape):
+            self._slots_u8[k] = torch.empty(batch.gt_images.shape, dtype=torch.uint8, device=dev)
         with torch.cuda.stream(self._copy_stream):
             if self._slot_free[k] is not None:
                 self._copy_stream.wait_event(self._slot_free[k])  # the step that last read this slot is done
-            self._slots[k].copy_(batch.gt_images, non_blocking=True)
+            if quantized:
+                self._slots_u8[k].copy_(batch.gt_images, non_blocking=True)
+                self._dequantize(self._slots_u8[k], self._slots[k], self._copy_stream.cuda_stream)
+            else:
+                self._slots[k].copy_(batch.gt_images, non_blocking=True)
             ready = torch.cuda.Event()
             ready.record(self._copy_stream)
         return SceneBatch(self._slots[k], batch.gt_views, batch.scene_extent, ready, k)
+
+    def _dequantize(self, src_u8: torch.Tensor, dst_f32: torch.Tensor, stream_ptr: int) -> None:
+        """u8 -> f32 / 255 on the device (== image_to_tensor of brush-dataset, after the upload)."""
+        ctx = get_context(self.device)
+        ctx.check(_lib.lib().brush_image_u8_to_f32(ctx.handle, src_u8.data_ptr(), src_u8.numel(), dst_f32.data_ptr(),
+                                                   C.c_void_p(stream_ptr)))
 
     def adopt(self, splats: Splats) -> Splats:
         """Peer mode: moves the parameters into this rank's peer-mapped replica and returns Splats whose tensors
@@ -223,10 +237,15 @@ class SplatTrainer:
             ctx.check(L.brush_quat_normalize(ctx.handle, p_rot.data_ptr(), self.n, self.norm_rot.data_ptr(), st))
             for i, cam in enumerate(batch.gt_views):  # train.rs:229-237 (batch looped)
                 gt = batch.gt_images[i]
-                if not gt.is_cuda:  # the view feed hands over pinned host images: H2D on the compute stream
+                if not gt.is_cuda or gt.dtype == torch.uint8:
+                    # the view feed hands over pinned host images and / or bytes: H2D and /255 on the compute stream
                     if self.gt_dev is None or self.gt_dev.shape != gt.shape:
                         self.gt_dev = torch.empty(gt.shape, dtype=torch.float32, device=dev)
-                    self.gt_dev.copy_(gt, non_blocking=True)
+                    if gt.dtype == torch.uint8:
+                        gt_u8 = gt if gt.is_cuda else gt.to(dev, non_blocking=True)
+                        self._dequantize(gt_u8, self.gt_dev, _stream_ptr(dev))
+                    else:
+                        self.gt_dev.copy_(gt, non_blocking=True)
                     gt = self.gt_dev
                 u = make_uniforms(cam.world_to_local(), cam.focal((W, H)), (W, H), cam.center((W, H)))
                 reuse = self.render_bufs[i] if i < len(self.render_bufs) else None

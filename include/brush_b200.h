@@ -221,6 +221,11 @@ int brush_views_adam_step(brush_ctx* ctx, uint32_t N, uint32_t K, const BrushTra
                           const BrushViewExchange* x, float* grad_norm_accum, float* visible_accum, float* loss_out,
                           float beta1, float beta2, float eps, uint32_t step, float grad_scale, void* stream);
 
+/* == image_to_tensor (crates/brush-dataset/src/lib.rs:11-24: u8 pixels -> f32 / 255) applied on the device after the
+ * upload, so the host keeps one byte per channel and the per-step upload is 4x smaller.  n = number of channel
+ * values (H*W*C); src 4-byte aligned, dst 16-byte aligned. */
+int brush_image_u8_to_f32(brush_ctx* ctx, const uint8_t* src, uint64_t n, float* dst, void* stream);
+
 /* == the rotation normalisation Splats::render applies before the operator and its VJP (Burn elementwise ops +
  * autodiff in the reference, crates/brush-render/src/gaussian_splats.rs:174-175).  quats f32[n,4]. */
 int brush_quat_normalize(brush_ctx* ctx, const float* quats, uint32_t n, float* out, void* stream);

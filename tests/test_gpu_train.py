@@ -164,6 +164,42 @@ def test_fused_backward_adam_matches_separate_kernels(k, n):
         assert float((va - vb).abs().max()) <= 1e-4 * float(vb.abs().max())
 
 
+def test_u8_targets_upload_and_dequantize():
+    """8-bit target images: uploaded as bytes (prefetch on the side stream or inline) and divided by 255 on the
+    device by brush_image_u8_to_f32 == image_to_tensor before the upload: the same pixels bit for bit, the same loss."""
+    from brush_b200 import Camera, Splats, scene
+    from brush_b200.scene import bench_camera_params
+    from brush_b200.train import SceneBatch, SplatTrainer, TrainConfig
+
+    w, h, n = 150, 90, 1500  # 150*90*3 is not a multiple of 4: exercises the tail
+    sc = scene.make_scene(n, w, h, 1, 3)
+    t = lambda a: torch.as_tensor(a, device=DEV)
+    cam = Camera(*bench_camera_params(w, h))
+    rng = np.random.default_rng(5)
+    gt_u8 = torch.as_tensor(rng.integers(0, 256, (1, h, w, 3), dtype=np.uint8))
+    gt_f32 = (gt_u8.to(torch.float32) / 255.0).to(DEV)
+    cfg = TrainConfig(max_refine_step=0)
+    losses = []
+    for kind in ("f32", "u8_host_prefetch", "u8_host_inline", "u8_device"):
+        sp = Splats(t(sc.means), t(sc.sh_coeffs), t(sc.quats), t(sc.raw_opacity), t(sc.log_scales))
+        tr = SplatTrainer(n, cfg, DEV, sh_coeffs_per_channel=4, optimize=False)
+        if kind == "f32":
+            batch = SceneBatch(gt_f32, [cam], 1.0)
+        elif kind == "u8_host_prefetch":
+            batch = tr.prefetch(SceneBatch(gt_u8.pin_memory(), [cam], 1.0))
+        elif kind == "u8_host_inline":
+            batch = SceneBatch(gt_u8.pin_memory(), [cam], 1.0)
+        else:
+            batch = SceneBatch(gt_u8.to(DEV), [cam], 1.0)
+        _, stats = tr.step(batch, sp)
+        losses.append(float(stats.loss))
+    # the loss is a sum of atomics: equal up to their order
+    assert max(losses) - min(losses) <= 1e-6 * abs(losses[0]), losses
+    out = torch.empty_like(gt_f32)
+    tr._dequantize(gt_u8.to(DEV), out, torch.cuda.current_stream().cuda_stream)
+    assert torch.equal(out, gt_f32)
+
+
 def test_views_step_world1_equals_fused_step():
     """exchange="views" with one rank must reproduce the fused single-device step: same rows, same chain, same
     Adam; the statistics are accumulated inside the kernel instead of by two elementwise launches."""
