@@ -128,7 +128,8 @@ class SceneLoader:
 
     PREFETCH = 5
 
-    def __init__(self, scene: Scene, batch_size: int, seed: int, rank: int = 0, world: int = 1, pin: bool = True):
+    def __init__(self, scene: Scene, batch_size: int, seed: int, rank: int = 0, world: int = 1, pin: bool = True,
+                 quantized: bool = False):
         if not scene.views:
             raise ValueError("SceneLoader needs at least one view")
         self.scene, self.batch_size = scene, batch_size
@@ -136,6 +137,9 @@ class SceneLoader:
         self._rng = np.random.default_rng(seed)
         self._rank, self._world = rank, world
         self._pin = pin and torch.cuda.is_available()
+        # quantized: batches keep the 8-bit pixels; SplatTrainer uploads the bytes and applies image_to_tensor's
+        # /255 on the device (a quarter of the PCIe traffic per step)
+        self._quantized = quantized
         self._q: "queue.Queue[SceneBatch]" = queue.Queue(maxsize=self.PREFETCH)
         self._stop = threading.Event()
         self._thread = threading.Thread(target=self._produce, daemon=True)
@@ -145,7 +149,10 @@ class SceneLoader:
         idx = self._rng.integers(0, len(self.scene.views), self.batch_size * self._world)
         mine = idx[self._rank * self.batch_size:(self._rank + 1) * self.batch_size]
         views = [self.scene.views[i] for i in mine]
-        imgs = torch.stack([image_to_tensor(v.image) for v in views], 0)
+        if self._quantized and all(np.asarray(v.image).dtype == np.uint8 for v in views):
+            imgs = torch.stack([torch.from_numpy(np.ascontiguousarray(v.image)) for v in views], 0)
+        else:
+            imgs = torch.stack([image_to_tensor(v.image) for v in views], 0)
         if self._pin:
             imgs = imgs.pin_memory()
         return SceneBatch(imgs, [v.camera for v in views], self._extent)

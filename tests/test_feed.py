@@ -73,3 +73,25 @@ def test_scene_loader_prefetch_seed_and_rank_slices():
     finally:
         for l in (a, b, r0, r1):
             l.close()
+
+
+def test_scene_loader_quantized_batches_keep_bytes():
+    """quantized=True hands the 8-bit pixels through unchanged (the trainer divides by 255 after the upload)."""
+    import numpy as np
+    import torch
+
+    from brush_b200 import Camera
+    from brush_b200.feed import Scene, SceneLoader, SceneView, image_to_tensor
+
+    rng = np.random.default_rng(0)
+    views = [SceneView(f"v{i}", Camera((0.0, 0.0, -float(i + 1)), (0.0, 0.0, 0.0, 1.0), 0.8, 0.6),
+                       rng.integers(0, 256, (6, 8, 3), dtype=np.uint8)) for i in range(3)]
+    loader = SceneLoader(Scene(views), 1, seed=1, pin=False, quantized=True)
+    try:
+        b = loader.next_batch()
+    finally:
+        loader.close()
+    assert b.gt_images.dtype == torch.uint8 and tuple(b.gt_images.shape) == (1, 6, 8, 3)
+    match = [v for v in views if np.array_equal(v.image, b.gt_images[0].numpy())]
+    assert len(match) == 1
+    assert torch.equal(image_to_tensor(match[0].image), b.gt_images[0].to(torch.float32) / 255.0)
