@@ -95,6 +95,7 @@ _SIGS = {
                               [C.POINTER(BrushAux)] + [C.c_void_p] * 6 + [C.c_void_p]),
     "brush_render_backward_adam": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(BrushTrainState),
                                              C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(BrushAux), C.c_void_p,
+                                             C.c_void_p, C.c_void_p,
                                              C.c_float, C.c_float, C.c_float, C.c_uint32, C.c_float, C.c_void_p]),
     "brush_render_backward_rows": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,
                                              C.POINTER(BrushAux), C.c_void_p, C.POINTER(BrushViewExchange),

@@ -23,7 +23,8 @@ struct brush_ctx {
     int timing = 0;
     // scratch, grown on demand (growth synchronises; steady state never allocates)
     Buf control, presort_gid, depth_bits, depth_sorted, num_tiles_hit, keys_tmp, vals_tmp, hist, lb, tickets,
-        tile_ids_unsorted, cg_unsorted, tile_ids_sorted, v_projected, sticky, loss_scratch;
+        tile_ids_unsorted, cg_unsorted, tile_ids_sorted, v_projected, sticky, loss_scratch, visible_mask;
+    const void* visible_owner = nullptr;  // aux.uniforms_buffer of the forward whose visibility visible_mask holds
     // host-staged path
     Buf h_means, h_lscales, h_quats, h_sh, h_opac, h_img, h_aux[9];
     cudaEvent_t ev[BRUSH_STAGE_COUNT + 1][2];
@@ -241,6 +242,7 @@ int brush_render_forward(brush_ctx* ctx, const BrushUniforms* uniforms_host, uin
     ENSURE(depth_bits, (size_t)N * 4);
     ENSURE(depth_sorted, (size_t)N * 4);
     ENSURE(num_tiles_hit, (size_t)N * 4);
+    ENSURE(visible_mask, (size_t)N + 16);
     ENSURE(tile_ids_unsorted, (size_t)cap * (fused ? 8 : 4));
     ENSURE(cg_unsorted, (size_t)cap * 4);
     if (fused || !aux->tile_id_from_isect) ENSURE(tile_ids_sorted, (size_t)cap * (fused ? 8 : 4));
@@ -280,7 +282,8 @@ int brush_render_forward(brush_ctx* ctx, const BrushUniforms* uniforms_host, uin
         StageTimer t(ctx, st, BRUSH_STAGE_PROJECT_SPLATS);
         launch_project_forward(cam, N, means, log_scales, quats, (uint32_t*)ctx->presort_gid.p,
                                (uint32_t*)ctx->depth_bits.p, lb_project, &control->ticket[0], aux->uniforms_buffer,
-                               aux->num_visible, st);
+                               aux->num_visible, (uint8_t*)ctx->visible_mask.p, st);
+        ctx->visible_owner = aux->uniforms_buffer;
     }
     {   // render.rs:151-156
         StageTimer t(ctx, st, BRUSH_STAGE_DEPTH_SORT);
@@ -379,6 +382,19 @@ int brush_render_backward(brush_ctx* ctx, uint32_t N, uint32_t K, const float* m
     return BRUSH_OK;
 }
 
+// Per-gid visibility of the forward that produced `aux`: project_forward leaves it in the ctx; if another forward
+// has run on this ctx since, it is rebuilt from the aux's compact list.
+static int visible_mask_for(brush_ctx* ctx, const BrushAux* aux, uint32_t N, cudaStream_t st, const uint8_t** out) {
+    ENSURE(visible_mask, (size_t)N + 16);
+    if (ctx->visible_owner != aux->uniforms_buffer) {
+        launch_visible_mask_from_list((const uint32_t*)aux->global_from_compact_gid, aux->num_visible, N,
+                                      (uint8_t*)ctx->visible_mask.p, st);
+        ctx->visible_owner = aux->uniforms_buffer;
+    }
+    *out = (const uint8_t*)ctx->visible_mask.p;
+    return BRUSH_OK;
+}
+
 static bool train_state_ok(const BrushTrainState& s) {
     return s.means && s.log_scales && s.rotation && s.sh_coeffs && s.raw_opacity && s.m_means && s.v_means &&
            s.m_log_scales && s.v_log_scales && s.m_rotation && s.v_rotation && s.m_sh_coeffs && s.v_sh_coeffs &&
@@ -445,7 +461,10 @@ int brush_render_backward_rows(brush_ctx* ctx, uint32_t N, uint32_t K, const flo
                                   aux->projected_splats, (uint32_t*)aux->global_from_compact_gid,
                                   (uint32_t*)aux->final_index, out_img, v_out_img, rows, st);
     }
-    launch_publish_view(rows, N, (const uint32_t*)aux->global_from_compact_gid, aux->uniforms_buffer, loss_term, X, st);
+    const uint8_t* mask = nullptr;
+    r = visible_mask_for(ctx, aux, N, st, &mask);
+    if (r != BRUSH_OK) return r;
+    launch_publish_view(rows, N, mask, aux->uniforms_buffer, loss_term, X, st);
     CU(cudaGetLastError());
     return BRUSH_OK;
 }
@@ -475,13 +494,14 @@ int brush_views_adam_step(brush_ctx* ctx, uint32_t N, uint32_t K, const BrushTra
 
 int brush_render_backward_adam(brush_ctx* ctx, uint32_t N, uint32_t K, const BrushTrainState* state,
                                const float* quats, const float* out_img, const float* v_out_img,
-                               const BrushAux* aux, float* v_xy, float beta1, float beta2, float eps,
-                               uint32_t step, float grad_scale, void* stream) {
+                               const BrushAux* aux, float* v_xy, float* grad_norm_accum, float* visible_accum,
+                               float beta1, float beta2, float eps, uint32_t step, float grad_scale, void* stream) {
     if (!ctx) return BRUSH_E_INVALID;
     if (!valid_k(K)) return fail(ctx, BRUSH_E_INVALID, "Invalid nr. of sh bases " + std::to_string(K));
     if (!aux || !out_img || !v_out_img || !state || step < 1) return fail(ctx, BRUSH_E_INVALID, "null argument");
     const BrushTrainState& s = *state;
-    if (N > 0 && (!quats || !v_xy || !s.means || !s.log_scales || !s.rotation || !s.sh_coeffs || !s.raw_opacity ||
+    if ((!grad_norm_accum) != (!visible_accum)) return fail(ctx, BRUSH_E_INVALID, "statistics: both accumulators or neither");
+    if (N > 0 && (!quats || !s.means || !s.log_scales || !s.rotation || !s.sh_coeffs || !s.raw_opacity ||
                   !s.m_means || !s.v_means || !s.m_log_scales || !s.v_log_scales || !s.m_rotation || !s.v_rotation ||
                   !s.m_sh_coeffs || !s.v_sh_coeffs || !s.m_raw_opacity || !s.v_raw_opacity))
         return fail(ctx, BRUSH_E_INVALID, "null argument");
@@ -513,7 +533,13 @@ int brush_render_backward_adam(brush_ctx* ctx, uint32_t N, uint32_t K, const Bru
     const FusedAdamLaunch A = fused_adam_launch(s, beta1, beta2, eps, step, grad_scale);
     {   // gather_grads + project_backwards + normalisation VJP + Adam in one pass
         StageTimer t(ctx, st, BRUSH_STAGE_GATHER_PROJECT_BWD);
-        launch_backward_adam(cam, N, K, quats, (float*)ctx->v_projected.p, A, v_xy, st);
+        const uint8_t* mask = nullptr;
+        if (grad_norm_accum) {
+            int r = visible_mask_for(ctx, aux, N, st, &mask);
+            if (r != BRUSH_OK) return r;
+        }
+        launch_backward_adam(cam, N, K, quats, (float*)ctx->v_projected.p, A, v_xy, mask, grad_norm_accum,
+                             visible_accum, st);
     }
     CU(cudaGetLastError());
     return BRUSH_OK;

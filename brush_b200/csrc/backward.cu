@@ -297,7 +297,8 @@ template <int K>
 __global__ void __launch_bounds__(256, BA_MINB)
 backward_adam_kernel(const __grid_constant__ Cam cam, const float* __restrict__ norm_quats,
                      const float* __restrict__ v_projected, const __grid_constant__ FusedAdamLaunch A,
-                     float* __restrict__ v_xy_out) {
+                     float* __restrict__ v_xy_out, const uint8_t* __restrict__ visible_mask,
+                     float* __restrict__ grad_norm_accum, float* __restrict__ visible_accum) {
     constexpr int ROW = K + 3;
     __shared__ float s_sh[256][ROW + 1];  // basis[K], v_rgb[3]
     const uint32_t N = cam.total_splats;
@@ -330,7 +331,12 @@ backward_adam_kernel(const __grid_constant__ Cam cam, const float* __restrict__ 
             const V3 dv = mean_v - cam.t;
             sh_basis<K>(cam.sh_degree, dv * rsqrtf(dot3(dv, dv)), b);
         }
-        reinterpret_cast<float2*>(v_xy_out)[g] = make_float2(vp0.x, vp0.y);
+        if (v_xy_out) reinterpret_cast<float2*>(v_xy_out)[g] = make_float2(vp0.x, vp0.y);
+        if (grad_norm_accum) {  // refine statistics (== xy_grad_stats_kernel + visible_flags_kernel + two adds)
+            const float gx = vp0.x * (0.5f * (float)cam.img_w), gy = vp0.y * (0.5f * (float)cam.img_h);
+            grad_norm_accum[g] += sqrtf(gx * gx + gy * gy) * A.grad_scale;
+            visible_accum[g] += (float)visible_mask[g];
+        }
 #pragma unroll
         for (int k = 0; k < K; k++) s_sh[threadIdx.x][k] = b[k];
         s_sh[threadIdx.x][K] = vp1.y; s_sh[threadIdx.x][K + 1] = vp1.z; s_sh[threadIdx.x][K + 2] = vp1.w;
@@ -341,16 +347,22 @@ backward_adam_kernel(const __grid_constant__ Cam cam, const float* __restrict__ 
 }
 
 void launch_backward_adam(const Cam& cam, uint32_t N, uint32_t K, const float* norm_quats, const float* v_projected,
-                          const FusedAdamLaunch& A, float* v_xy, cudaStream_t st) {
+                          const FusedAdamLaunch& A, float* v_xy, const uint8_t* visible_mask, float* grad_norm_accum,
+                          float* visible_accum, cudaStream_t st) {
     if (N == 0) return;
     dim3 grid((N + 255) / 256), block(256);
     g_launch_count++;
     switch (K) {
-        case 1: backward_adam_kernel<1><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy); break;
-        case 4: backward_adam_kernel<4><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy); break;
-        case 9: backward_adam_kernel<9><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy); break;
-        case 16: backward_adam_kernel<16><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy); break;
-        case 25: backward_adam_kernel<25><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy); break;
+        case 1: backward_adam_kernel<1><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy, visible_mask,
+                                                                 grad_norm_accum, visible_accum); break;
+        case 4: backward_adam_kernel<4><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy, visible_mask,
+                                                                 grad_norm_accum, visible_accum); break;
+        case 9: backward_adam_kernel<9><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy, visible_mask,
+                                                                 grad_norm_accum, visible_accum); break;
+        case 16: backward_adam_kernel<16><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy, visible_mask,
+                                                                 grad_norm_accum, visible_accum); break;
+        case 25: backward_adam_kernel<25><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy, visible_mask,
+                                                                 grad_norm_accum, visible_accum); break;
     }
 }
 
@@ -369,14 +381,29 @@ void launch_backward_adam(const Cam& cam, uint32_t N, uint32_t K, const float* n
 //       Adam as in backward_adam_kernel.  Row buffers alternate between two halves by step parity, so no second
 //       barrier is needed: a rank can overwrite a half only after every peer has arrived at the step in between.
 __global__ void __launch_bounds__(256)
-publish_view_kernel(float* __restrict__ rows, uint32_t N, const uint32_t* __restrict__ global_from_compact,
+publish_view_kernel(float* __restrict__ rows, uint32_t N, const uint8_t* __restrict__ visible_mask,
                     const uint32_t* __restrict__ uniforms, const float* __restrict__ loss) {
     const uint32_t i = blockIdx.x * 256u + threadIdx.x;
-    const uint32_t nv = uniforms[25];  // num_visible, written by the forward (RenderUniforms word 25)
-    if (i < nv && i < N) rows[(size_t)global_from_compact[i] * VP_STRIDE + 9] = 1.0f;
+    if (i < N) rows[(size_t)i * VP_STRIDE + 9] = (float)visible_mask[i];  // the rows are still in L2
     float* trailer = rows + (size_t)N * VP_STRIDE;
     if (i < 28) reinterpret_cast<uint32_t*>(trailer)[i] = uniforms[i];
     if (i == 28) trailer[28] = loss ? *loss : 0.0f;
+}
+
+// Fallback when the mask of the forward that produced `aux` is no longer held by the ctx: rebuild it from the
+// compact list (zero-filled first).
+__global__ void __launch_bounds__(256)
+visible_mask_from_list_kernel(const uint32_t* __restrict__ global_from_compact,
+                              const int32_t* __restrict__ num_visible_dev, uint8_t* __restrict__ visible_mask) {
+    const uint32_t c = blockIdx.x * 256u + threadIdx.x;
+    if (c < (uint32_t)*num_visible_dev) visible_mask[global_from_compact[c]] = 1;
+}
+void launch_visible_mask_from_list(const uint32_t* global_from_compact, const int32_t* num_visible_dev, uint32_t N,
+                                   uint8_t* visible_mask, cudaStream_t st) {
+    if (!N) return;
+    zero_async(visible_mask, N, st);
+    g_launch_count++;
+    visible_mask_from_list_kernel<<<(N + 255) / 256, 256, 0, st>>>(global_from_compact, num_visible_dev, visible_mask);
 }
 
 struct ArriveLaunch { uint32_t* flags[DP_MAX_WORLD]; int world, rank; uint32_t epoch; };
@@ -387,11 +414,11 @@ __global__ void arrive_kernel(const __grid_constant__ ArriveLaunch L) {
     }
 }
 
-void launch_publish_view(float* rows, uint32_t N, const uint32_t* global_from_compact, const void* uniforms_dev,
+void launch_publish_view(float* rows, uint32_t N, const uint8_t* visible_mask, const void* uniforms_dev,
                          const float* loss_dev, const ViewsLaunch& X, cudaStream_t st) {
     const uint32_t threads = N > 32 ? N : 32;
     g_launch_count += 2;
-    publish_view_kernel<<<(threads + 255) / 256, 256, 0, st>>>(rows, N, global_from_compact,
+    publish_view_kernel<<<(threads + 255) / 256, 256, 0, st>>>(rows, N, visible_mask,
                                                                (const uint32_t*)uniforms_dev, loss_dev);
     ArriveLaunch L{};
     for (int r = 0; r < X.world; r++) L.flags[r] = X.flags[r];

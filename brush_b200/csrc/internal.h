@@ -29,7 +29,7 @@ struct Control {
 void launch_project_forward(const Cam& cam, uint32_t N, const float* means, const float* log_scales,
                             const float* quats, uint32_t* presort_gid, uint32_t* depth_bits,
                             uint64_t* lb_status, uint32_t* ticket, int32_t* uniforms_dev, int32_t* num_visible_out,
-                            cudaStream_t st);
+                            uint8_t* visible_mask, cudaStream_t st);
 void launch_project_visible(const Cam& cam, uint32_t N, uint32_t K, const float* means, const float* log_scales,
                             const float* quats, const float* coeffs, const float* raw_opac,
                             const uint32_t* global_from_compact, const int32_t* num_visible_dev, float* projected,
@@ -106,8 +106,13 @@ struct FusedAdamLaunch {
     float lr_mean, lr_scale, lr_rot, lr_sh_dc, lr_sh_rest, lr_opac;
     float beta1, beta2, eps, inv_bc1, inv_bc2, grad_scale;
 };
+// visible_mask: u8[N] written by project_forward; grad_norm_accum / visible_accum (both or neither): the refine
+// statistics of train.rs:284-316 are accumulated in the same pass.  v_xy may be null.
 void launch_backward_adam(const Cam& cam, uint32_t N, uint32_t K, const float* norm_quats, const float* v_projected,
-                          const FusedAdamLaunch& A, float* v_xy, cudaStream_t st);
+                          const FusedAdamLaunch& A, float* v_xy, const uint8_t* visible_mask, float* grad_norm_accum,
+                          float* visible_accum, cudaStream_t st);
+void launch_visible_mask_from_list(const uint32_t* global_from_compact, const int32_t* num_visible_dev, uint32_t N,
+                                   uint8_t* visible_mask, cudaStream_t st);
 
 // View-parallel step without a gradient exchange (backward.cu): every rank publishes the nine per-splat sums of ITS
 // view (48 B per splat instead of 252 B of dense gradients), then redoes the per-splat backward for every view and
@@ -124,7 +129,7 @@ struct ViewsLaunch {
     float* grad_norm_accum;
     float* visible_accum;
 };
-void launch_publish_view(float* rows, uint32_t N, const uint32_t* global_from_compact, const void* uniforms_dev,
+void launch_publish_view(float* rows, uint32_t N, const uint8_t* visible_mask, const void* uniforms_dev,
                          const float* loss_dev, const ViewsLaunch& X, cudaStream_t st);
 int launch_views_adam(const ViewsLaunch& X, uint32_t N, uint32_t K, const float* norm_quats, const FusedAdamLaunch& A,
                       cudaStream_t st);

@@ -31,7 +31,8 @@ __global__ void __launch_bounds__(PF_THREADS)
 project_forward_kernel(const __grid_constant__ Cam cam, const float* __restrict__ means,
                        const float* __restrict__ log_scales, const float* __restrict__ quats,
                        uint32_t* __restrict__ presort_gid, uint32_t* __restrict__ depth_bits, uint64_t* lb_status,
-                       uint32_t* ticket, int32_t* uniforms_dev, int32_t* num_visible_out) {
+                       uint32_t* ticket, int32_t* uniforms_dev, int32_t* num_visible_out,
+                       uint8_t* __restrict__ visible_mask) {
     __shared__ __align__(16) float s_mean[PF_THREADS * 3];
     __shared__ __align__(16) float s_lscale[PF_THREADS * 3];
     __shared__ uint32_t s_warp_tot[PF_THREADS / 32];
@@ -67,6 +68,7 @@ project_forward_kernel(const __grid_constant__ Cam cam, const float* __restrict_
             }
         }
     }
+    if (g < N) visible_mask[g] = visible ? 1 : 0;  // per-gid visibility for the refine statistics (train.rs:300-314)
     // Deterministic compaction: ballot -> warp offsets -> block scan -> chained look-back across tiles.
     const uint32_t ballot = __ballot_sync(0xffffffffu, visible);
     const uint32_t in_warp = __popc(ballot & ((1u << lane) - 1u));
@@ -101,12 +103,14 @@ project_forward_kernel(const __grid_constant__ Cam cam, const float* __restrict_
 
 void launch_project_forward(const Cam& cam, uint32_t N, const float* means, const float* log_scales,
                             const float* quats, uint32_t* presort_gid, uint32_t* depth_bits, uint64_t* lb_status,
-                            uint32_t* ticket, int32_t* uniforms_dev, int32_t* num_visible_out, cudaStream_t st) {
+                            uint32_t* ticket, int32_t* uniforms_dev, int32_t* num_visible_out, uint8_t* visible_mask,
+                            cudaStream_t st) {
     if (N == 0) return;
     uint32_t tiles = (N + PF_THREADS - 1) / PF_THREADS;
     g_launch_count++;
     project_forward_kernel<<<tiles, PF_THREADS, 0, st>>>(cam, means, log_scales, quats, presort_gid, depth_bits,
-                                                         lb_status, ticket, uniforms_dev, num_visible_out);
+                                                         lb_status, ticket, uniforms_dev, num_visible_out,
+                                                         visible_mask);
 }
 
 // ---------------------------------------------------------------------------------------------

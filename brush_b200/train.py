@@ -276,10 +276,13 @@ class SplatTrainer:
                     auxes.append(aux)
                     break
                 if fused:
-                    # single device, one view: per-splat backward + normalisation VJP + Adam in one kernel; the
-                    # dense gradients are never materialised (only v_xy, for the refine statistics)
+                    # single device, one view: per-splat backward + normalisation VJP + Adam + refine statistics in
+                    # one kernel; the dense gradients are never materialised
                     lr_mean = self._lr_mean(batch)
-                    self._backward_adam(ctx, splats, aux, pred, lr_mean, st)
+                    self._backward_adam(ctx, splats, aux, pred, lr_mean, self.iter > cfg.warmup_steps, st)
+                    preds.append(pred)
+                    auxes.append(aux)
+                    break
                 else:
                     render_backward(aux, p_means, p_scales, self.norm_rot, p_sh.shape, p_opac, pred, self.v_out,
                                     ctx=ctx, out=dst)
@@ -318,7 +321,7 @@ class SplatTrainer:
                 if self.optimize and not fused:
                     self._adam(ctx, splats, lr_mean, grad_scale, st)
                 loss = self.loss_total * grad_scale if (B * world) > 1 else self.loss_total
-            if self.iter - 1 > cfg.warmup_steps and not views:  # train.rs:286-316
+            if self.iter - 1 > cfg.warmup_steps and not views and not fused:  # train.rs:286-316
                 self.grad_2d_accum.add_(stat_norm, alpha=grad_scale)
                 self.xy_grad_counts.add_(stat_vis)  # select_assign == scatter-ADD in Burn 0.16: a visibility count
             if batch.slot is not None:
@@ -449,13 +452,15 @@ class SplatTrainer:
             ctx.handle, self.n, self.k, C.byref(S), self.norm_rot.data_ptr(), C.byref(vx), accum[0], accum[1],
             self.loss_buf.data_ptr(), cfg.adam_beta1, cfg.adam_beta2, cfg.adam_eps, self.iter, grad_scale, st))
 
-    def _backward_adam(self, ctx, splats: Splats, aux, pred, lr_mean: float, st):
+    def _backward_adam(self, ctx, splats: Splats, aux, pred, lr_mean: float, with_stats: bool, st):
         cfg = self.config
         S = self._train_state(splats, lr_mean)
         caux = aux._c()
+        accum = (self.grad_2d_accum.data_ptr(), self.xy_grad_counts.data_ptr()) if with_stats else (None, None)
         ctx.check(_lib.lib().brush_render_backward_adam(
             ctx.handle, self.n, self.k, C.byref(S), self.norm_rot.data_ptr(), pred.data_ptr(), self.v_out.data_ptr(),
-            C.byref(caux), self.g_xy.data_ptr(), cfg.adam_beta1, cfg.adam_beta2, cfg.adam_eps, self.iter + 1, 1.0, st))
+            C.byref(caux), None, accum[0], accum[1], cfg.adam_beta1, cfg.adam_beta2, cfg.adam_eps, self.iter + 1, 1.0,
+            st))
 
     def _adam(self, ctx, splats: Splats, lr_mean: float, grad_scale: float, st):
         cfg = self.config

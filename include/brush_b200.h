@@ -177,7 +177,9 @@ int brush_adam_step(brush_ctx* ctx, const BrushAdamGroup* groups_host, int n_gro
  * single-device step with one view per batch: same rasterizer launch as brush_render_backward, then ONE kernel
  * computes each splat's gradients in registers and applies brush_adam_step's update in place, so the dense
  * gradients never touch HBM.  `rotation` is the raw (un-normalised) parameter, `quats` the normalised copy the
- * forward rendered with; v_xy [N,2] is still written (refine statistics).  All pointers are device pointers;
+ * forward rendered with; v_xy [N,2] (may be NULL) receives the xy gradient; grad_norm_accum / visible_accum (f32[N],
+ * both or neither) receive the refine statistics of train.rs:284-316 in the same pass (+= |v_xy * (w/2, h/2)| *
+ * grad_scale, += 1 for visible splats).  All pointers are device pointers;
  * parameters and moments are updated in place.  Results equal brush_render_backward -> brush_quat_normalize_vjp
  * -> brush_adam_step on the same inputs. */
 typedef struct BrushTrainState {
@@ -189,8 +191,8 @@ typedef struct BrushTrainState {
 } BrushTrainState;
 int brush_render_backward_adam(brush_ctx* ctx, uint32_t N, uint32_t K, const BrushTrainState* state,
                                const float* quats, const float* out_img, const float* v_out_img,
-                               const BrushAux* aux, float* v_xy, float beta1, float beta2, float eps,
-                               uint32_t step, float grad_scale, void* stream);
+                               const BrushAux* aux, float* v_xy, float* grad_norm_accum, float* visible_accum,
+                               float beta1, float beta2, float eps, uint32_t step, float grad_scale, void* stream);
 
 #define BRUSH_DP_MAX_WORLD 8
 /* ---- view-parallel step without a gradient exchange (no reference counterpart) ----
