@@ -23,7 +23,7 @@ struct brush_ctx {
     int timing = 0;
     // scratch, grown on demand (growth synchronises; steady state never allocates)
     Buf control, presort_gid, depth_bits, depth_sorted, num_tiles_hit, keys_tmp, vals_tmp, hist, lb, tickets,
-        tile_ids_unsorted, cg_unsorted, tile_ids_sorted, v_projected, sticky, loss_scratch, visible_mask;
+        tile_ids_unsorted, cg_unsorted, tile_ids_sorted, v_projected, sticky, loss_scratch, visible_mask, tile_masks, tile_boxes;
     const void* visible_owner = nullptr;  // aux.uniforms_buffer of the forward whose visibility visible_mask holds
     // host-staged path
     Buf h_means, h_lscales, h_quats, h_sh, h_opac, h_img, h_aux[9];
@@ -243,6 +243,8 @@ int brush_render_forward(brush_ctx* ctx, const BrushUniforms* uniforms_host, uin
     ENSURE(depth_sorted, (size_t)N * 4);
     ENSURE(num_tiles_hit, (size_t)N * 4);
     ENSURE(visible_mask, (size_t)N + 16);
+    ENSURE(tile_masks, (size_t)N * 8);
+    ENSURE(tile_boxes, (size_t)N * 4);
     ENSURE(tile_ids_unsorted, (size_t)cap * (fused ? 8 : 4));
     ENSURE(cg_unsorted, (size_t)cap * 4);
     if (fused || !aux->tile_id_from_isect) ENSURE(tile_ids_sorted, (size_t)cap * (fused ? 8 : 4));
@@ -293,7 +295,8 @@ int brush_render_forward(brush_ctx* ctx, const BrushUniforms* uniforms_host, uin
     {   // render.rs:168-184
         StageTimer t(ctx, st, BRUSH_STAGE_PROJECT_VISIBLE);
         launch_project_visible(cam, N, K, means, log_scales, quats, sh_coeffs, raw_opacity, gfc, aux->num_visible,
-                               aux->projected_splats, (uint32_t*)ctx->num_tiles_hit.p, st);
+                               aux->projected_splats, (uint32_t*)ctx->num_tiles_hit.p, (uint64_t*)ctx->tile_masks.p,
+                               (uint32_t*)ctx->tile_boxes.p, st);
     }
     {   // render.rs:186-192
         StageTimer t(ctx, st, BRUSH_STAGE_PREFIX_SUM);
@@ -307,7 +310,8 @@ int brush_render_forward(brush_ctx* ctx, const BrushUniforms* uniforms_host, uin
         StageTimer t(ctx, st, BRUSH_STAGE_MAP_INTERSECTS);
         launch_map_intersects(cam, N, aux->projected_splats, (uint32_t*)aux->cum_tiles_hit, aux->num_visible, cap,
                               fused ? nullptr : tid_unsorted, (uint32_t*)ctx->cg_unsorted.p,
-                              (uint32_t*)ctx->depth_sorted.p, fused ? (uint64_t*)tid_unsorted : nullptr, sticky, st);
+                              (uint32_t*)ctx->depth_sorted.p, fused ? (uint64_t*)tid_unsorted : nullptr, sticky,
+                              (const uint64_t*)ctx->tile_masks.p, (const uint32_t*)ctx->tile_boxes.p, st);
     }
     {   // render.rs:227-237
         StageTimer t(ctx, st, BRUSH_STAGE_TILE_SORT);

@@ -33,11 +33,12 @@ void launch_project_forward(const Cam& cam, uint32_t N, const float* means, cons
 void launch_project_visible(const Cam& cam, uint32_t N, uint32_t K, const float* means, const float* log_scales,
                             const float* quats, const float* coeffs, const float* raw_opac,
                             const uint32_t* global_from_compact, const int32_t* num_visible_dev, float* projected,
-                            uint32_t* num_tiles_hit, cudaStream_t st);
+                            uint32_t* num_tiles_hit, uint64_t* tile_masks, uint32_t* tile_boxes, cudaStream_t st);
 void launch_map_intersects(const Cam& cam, uint32_t N, const float* projected, const uint32_t* cum_tiles_hit,
                            const int32_t* num_visible_dev, uint64_t capacity, uint32_t* tile_id_from_isect,
                            uint32_t* compact_gid_from_isect, const uint32_t* depth_sorted_bits,
-                           uint64_t* key64_from_isect, uint32_t* status_word, cudaStream_t st);
+                           uint64_t* key64_from_isect, uint32_t* status_word, const uint64_t* tile_masks,
+                           const uint32_t* tile_boxes, cudaStream_t st);
 
 // ---- scan.cu ----
 // Inclusive scan of in[0..n) -> out. If total_out != nullptr, also writes the grand total (min(total,cap)) there

@@ -141,57 +141,127 @@ __device__ __forceinline__ V3 eval_sh_color(uint32_t degree, V3 viewdir, const f
     return col;
 }
 
+// Tile hits of 32 splats, found by the whole warp.  A thread-per-splat walk over its own bounding box leaves most
+// lanes idle (boxes differ from 1 to hundreds of tiles; measured 13 of 32 lanes active), so the (splat, tile)
+// candidates of the warp's 32 splats are flattened: lane i of each pass tests candidate base + i, whichever splat
+// it belongs to (found by binary search over the warp's running box sizes), with the reference's exact test
+// (can_be_visible, helpers.wgsl:264-279).  Each owner lane collects the ballot bits of its own candidates: their
+// count is num_tiles_hit, and for boxes of up to 64 tiles the bits themselves are kept as a row-major hit mask,
+// which map_intersects expands without repeating the test.
+constexpr uint32_t BOX_BIG = 0x80000000u;  // tile_boxes flag: box > 64 tiles (or coordinates > 1023): no mask
+struct TileHits { uint32_t count; uint32_t box; uint64_t mask; };
+
+BD TileHits warp_tile_hits(const VisTest& vt, const TileBox& b, bool valid, uint32_t lane) {
+    const uint32_t FULL = 0xffffffffu;
+    const uint32_t w = valid && vt.any ? b.maxx - b.minx : 0u, h = valid && vt.any ? b.maxy - b.miny : 0u;
+    const uint32_t n = w * h;
+    uint32_t incl = n;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(FULL, incl, o);
+        if (lane >= (uint32_t)o) incl += t;
+    }
+    const uint32_t excl = incl - n, total = __shfl_sync(FULL, incl, 31);
+    const uint32_t origin = b.minx | (b.miny << 16);
+    TileHits out{0u, 0u, 0ull};
+    for (uint32_t base = 0; base < total; base += 32) {
+        const uint32_t k = base + lane;
+        uint32_t owner = 0;  // number of lanes whose boxes end at or before candidate k
+#pragma unroll
+        for (int step = 16; step >= 1; step >>= 1) {
+            const uint32_t v = __shfl_sync(FULL, incl, (owner + step - 1) & 31u);
+            if (v <= k) owner += step;
+        }
+        owner &= 31u;
+        const uint32_t o_excl = __shfl_sync(FULL, excl, owner), o_w = __shfl_sync(FULL, w, owner);
+        const uint32_t o_origin = __shfl_sync(FULL, origin, owner);
+        VisTest ot;
+        ot.any = true;
+        ot.conic_scaled.c[0].x = __shfl_sync(FULL, vt.conic_scaled.c[0].x, owner);
+        ot.conic_scaled.c[0].y = __shfl_sync(FULL, vt.conic_scaled.c[0].y, owner);
+        ot.conic_scaled.c[1].y = __shfl_sync(FULL, vt.conic_scaled.c[1].y, owner);
+        ot.conic_scaled.c[1].x = ot.conic_scaled.c[0].y;
+        ot.xy.x = __shfl_sync(FULL, vt.xy.x, owner);
+        ot.xy.y = __shfl_sync(FULL, vt.xy.y, owner);
+        bool pass = false;
+        if (k < total) {
+            const uint32_t j = k - o_excl;
+            // j / o_w for small integers: (j + 0.5) / w is never within rounding distance of an integer
+            const uint32_t row = (uint32_t)__float2uint_rz(__fdividef((float)j + 0.5f, (float)o_w));
+            const uint32_t col = j - row * o_w;
+            pass = can_be_visible(ot, (o_origin & 0xffffu) + col, (o_origin >> 16) + row);
+        }
+        const uint32_t ballot = __ballot_sync(FULL, pass);
+        if (n) {  // this lane's own candidates inside the pass
+            const int s0 = max((int)excl - (int)base, 0), e0 = min((int)incl - (int)base, 32);
+            if (e0 > s0) {
+                const uint32_t len = (uint32_t)(e0 - s0);
+                const uint32_t seg = (ballot >> s0) & (len == 32u ? 0xffffffffu : ((1u << len) - 1u));
+                out.count += __popc(seg);
+                const uint32_t pos = base + (uint32_t)s0 - excl;
+                if (pos < 64u) out.mask |= (uint64_t)seg << pos;
+            }
+        }
+    }
+    const bool big = n > 64u || b.minx > 1023u || b.miny > 1023u || w > 1023u;
+    out.box = big ? BOX_BIG : (b.minx | (b.miny << 10) | (w << 20));
+    return out;
+}
+
 template <int K>
 __global__ void __launch_bounds__(256)
 project_visible_kernel(const __grid_constant__ Cam cam, const float* __restrict__ means,
                        const float* __restrict__ log_scales, const float* __restrict__ quats,
                        const float* __restrict__ coeffs, const float* __restrict__ raw_opac,
                        const uint32_t* __restrict__ global_from_compact, const int32_t* __restrict__ num_visible_dev,
-                       float* __restrict__ projected, uint32_t* __restrict__ num_tiles_hit) {
+                       float* __restrict__ projected, uint32_t* __restrict__ num_tiles_hit,
+                       uint64_t* __restrict__ tile_masks, uint32_t* __restrict__ tile_boxes) {
     const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= cam.total_splats) return;
     const uint32_t V = (uint32_t)*num_visible_dev;
-    if (c >= V) {
-        num_tiles_hit[c] = 0u;  // the scan runs over all N (render.rs:164-165,187)
-        return;
+    const bool valid = c < V;  // V <= total_splats
+    if (c < cam.total_splats && !valid) num_tiles_hit[c] = 0u;  // the scan runs over all N (render.rs:164-165,187)
+    if (__all_sync(0xffffffffu, !valid)) return;
+    VisTest vt{};
+    TileBox b{0u, 0u, 0u, 0u};
+    if (valid) {
+        const uint32_t g = global_from_compact[c];
+        V3 mean = {__ldg(means + 3 * (size_t)g), __ldg(means + 3 * (size_t)g + 1), __ldg(means + 3 * (size_t)g + 2)};
+        V3 ls = {__ldg(log_scales + 3 * (size_t)g), __ldg(log_scales + 3 * (size_t)g + 1),
+                 __ldg(log_scales + 3 * (size_t)g + 2)};
+        float4 q4 = __ldg(reinterpret_cast<const float4*>(quats) + g);
+        V3 scale = exp3(ls);
+        float opac = sigmoid_det(__ldg(raw_opac + g));
+        V3 p_view = mul(cam.W, mean) + cam.t;
+        V3 cov2d = calc_cov2d(cam, p_view, scale, V4{q4.x, q4.y, q4.z, q4.w});
+        V3 conic = cov_to_conic(cov2d);
+        V2 xy = project_pix(cam, p_view);
+        V3 viewdir = normalize3(mean - cam.t);  // project_visible.wgsl:232-233
+        V3 color = eval_sh_color<K>(cam.sh_degree, viewdir, coeffs, g);
+        color = {color.x + 0.5f, color.y + 0.5f, color.z + 0.5f};
+        uint32_t radius = radius_from_conic(conic);
+        b = get_tile_bbox(xy, radius, cam.tiles_x, cam.tiles_y);
+        vt = make_vis_test(xy, conic, opac);
+        float* p = projected + (size_t)c * 9;
+        p[0] = xy.x; p[1] = xy.y; p[2] = conic.x; p[3] = conic.y; p[4] = conic.z;
+        p[5] = color.x; p[6] = color.y; p[7] = color.z; p[8] = opac;
     }
-    const uint32_t g = global_from_compact[c];
-    V3 mean = {__ldg(means + 3 * (size_t)g), __ldg(means + 3 * (size_t)g + 1), __ldg(means + 3 * (size_t)g + 2)};
-    V3 ls = {__ldg(log_scales + 3 * (size_t)g), __ldg(log_scales + 3 * (size_t)g + 1),
-             __ldg(log_scales + 3 * (size_t)g + 2)};
-    float4 q4 = __ldg(reinterpret_cast<const float4*>(quats) + g);
-    V3 scale = exp3(ls);
-    float opac = sigmoid_det(__ldg(raw_opac + g));
-    V3 p_view = mul(cam.W, mean) + cam.t;
-    V3 cov2d = calc_cov2d(cam, p_view, scale, V4{q4.x, q4.y, q4.z, q4.w});
-    V3 conic = cov_to_conic(cov2d);
-    V2 xy = project_pix(cam, p_view);
-    V3 viewdir = normalize3(mean - cam.t);  // project_visible.wgsl:232-233
-    V3 color = eval_sh_color<K>(cam.sh_degree, viewdir, coeffs, g);
-    color = {color.x + 0.5f, color.y + 0.5f, color.z + 0.5f};
-
-    uint32_t radius = radius_from_conic(conic);
-    TileBox b = get_tile_bbox(xy, radius, cam.tiles_x, cam.tiles_y);
-    VisTest vt = make_vis_test(xy, conic, opac);
-    uint32_t area = 0;
-    for (uint32_t ty = b.miny; ty < b.maxy; ty++)
-        for (uint32_t tx = b.minx; tx < b.maxx; tx++) area += can_be_visible(vt, tx, ty) ? 1u : 0u;
-
-    float* p = projected + (size_t)c * 9;
-    p[0] = xy.x; p[1] = xy.y; p[2] = conic.x; p[3] = conic.y; p[4] = conic.z;
-    p[5] = color.x; p[6] = color.y; p[7] = color.z; p[8] = opac;
-    num_tiles_hit[c] = area;
+    const TileHits hits = warp_tile_hits(vt, b, valid, threadIdx.x & 31u);
+    if (valid) {
+        num_tiles_hit[c] = hits.count;
+        tile_masks[c] = hits.mask;
+        tile_boxes[c] = hits.box;
+    }
 }
 
 void launch_project_visible(const Cam& cam, uint32_t N, uint32_t K, const float* means, const float* log_scales,
                             const float* quats, const float* coeffs, const float* raw_opac,
                             const uint32_t* global_from_compact, const int32_t* num_visible_dev, float* projected,
-                            uint32_t* num_tiles_hit, cudaStream_t st) {
+                            uint32_t* num_tiles_hit, uint64_t* tile_masks, uint32_t* tile_boxes, cudaStream_t st) {
     if (N == 0) return;
     dim3 grid((N + 255) / 256), block(256);
     g_launch_count++;
 #define PV_ARGS cam, means, log_scales, quats, coeffs, raw_opac, global_from_compact, num_visible_dev, projected, \
-                num_tiles_hit
+                num_tiles_hit, tile_masks, tile_boxes
     switch (K) {
         case 1: project_visible_kernel<1><<<grid, block, 0, st>>>(PV_ARGS); break;
         case 4: project_visible_kernel<4><<<grid, block, 0, st>>>(PV_ARGS); break;
@@ -208,10 +278,35 @@ map_intersects_kernel(const __grid_constant__ Cam cam, const float* __restrict__
                       const uint32_t* __restrict__ cum_tiles_hit, const int32_t* __restrict__ num_visible_dev,
                       uint64_t capacity, uint32_t* __restrict__ tile_id_from_isect,
                       uint32_t* __restrict__ compact_gid_from_isect, const uint32_t* __restrict__ depth_sorted_bits,
-                      uint64_t* __restrict__ key64_from_isect) {
+                      uint64_t* __restrict__ key64_from_isect, const uint64_t* __restrict__ tile_masks,
+                      const uint32_t* __restrict__ tile_boxes) {
     const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t V = (uint32_t)*num_visible_dev;
     if (c >= V) return;
+    uint64_t isect = c > 0 ? cum_tiles_hit[c - 1] : 0u;
+    const uint64_t depth_lo = key64_from_isect ? (uint64_t)depth_sorted_bits[c] : 0ull;
+    auto emit = [&](uint32_t tx, uint32_t ty) {
+        if (isect < capacity) {
+            const uint32_t tile_id = tx + ty * cam.tiles_x;
+            if (key64_from_isect) key64_from_isect[isect] = ((uint64_t)tile_id << 32) | depth_lo;
+            else tile_id_from_isect[isect] = tile_id;
+            compact_gid_from_isect[isect] = c;
+            isect++;
+        }
+    };
+    const uint32_t box = tile_boxes[c];
+    if (!(box & BOX_BIG)) {  // expand project_visible's hit mask: row-major order, as the reference's loop
+        uint64_t m = tile_masks[c];
+        const uint32_t minx = box & 1023u, miny = (box >> 10) & 1023u, w = box >> 20;
+        const float fw = (float)w;
+        while (m) {
+            const uint32_t j = (uint32_t)__ffsll((long long)m) - 1u;
+            m &= m - 1ull;
+            const uint32_t row = (uint32_t)__float2uint_rz(__fdividef((float)j + 0.5f, fw));
+            emit(minx + j - row * w, miny + row);
+        }
+        return;
+    }
     const float* p = projected + (size_t)c * 9;
     V2 xy = {p[0], p[1]};
     V3 conic = {p[2], p[3], p[4]};
@@ -219,28 +314,22 @@ map_intersects_kernel(const __grid_constant__ Cam cam, const float* __restrict__
     uint32_t radius = radius_from_conic(conic);
     TileBox b = get_tile_bbox(xy, radius, cam.tiles_x, cam.tiles_y);
     VisTest vt = make_vis_test(xy, conic, opac);
-    uint64_t isect = c > 0 ? cum_tiles_hit[c - 1] : 0u;
-    const uint64_t depth_lo = key64_from_isect ? (uint64_t)depth_sorted_bits[c] : 0ull;
     for (uint32_t ty = b.miny; ty < b.maxy; ty++)
         for (uint32_t tx = b.minx; tx < b.maxx; tx++)
-            if (can_be_visible(vt, tx, ty) && isect < capacity) {
-                uint32_t tile_id = tx + ty * cam.tiles_x;
-                if (key64_from_isect) key64_from_isect[isect] = ((uint64_t)tile_id << 32) | depth_lo;
-                else tile_id_from_isect[isect] = tile_id;
-                compact_gid_from_isect[isect] = c;
-                isect++;
-            }
+            if (can_be_visible(vt, tx, ty)) emit(tx, ty);
 }
 
 void launch_map_intersects(const Cam& cam, uint32_t N, const float* projected, const uint32_t* cum_tiles_hit,
                            const int32_t* num_visible_dev, uint64_t capacity, uint32_t* tile_id_from_isect,
                            uint32_t* compact_gid_from_isect, const uint32_t* depth_sorted_bits,
-                           uint64_t* key64_from_isect, uint32_t* /*status_word*/, cudaStream_t st) {
+                           uint64_t* key64_from_isect, uint32_t* /*status_word*/, const uint64_t* tile_masks,
+                           const uint32_t* tile_boxes, cudaStream_t st) {
     if (N == 0) return;
     g_launch_count++;
     map_intersects_kernel<<<(N + 255) / 256, 256, 0, st>>>(cam, projected, cum_tiles_hit, num_visible_dev, capacity,
                                                            tile_id_from_isect, compact_gid_from_isect,
-                                                           depth_sorted_bits, key64_from_isect);
+                                                           depth_sorted_bits, key64_from_isect, tile_masks,
+                                                           tile_boxes);
 }
 
 }  // namespace brush
