@@ -202,6 +202,7 @@ static int sort_scratch(brush_ctx* ctx, uint32_t max_n, int key_bytes, uint32_t 
     s->hist = (uint32_t*)ctx->hist.p;
     s->lb = (uint32_t*)ctx->lb.p;
     s->tickets = (uint32_t*)ctx->tickets.p;
+    s->pre_zeroed = false;
     return BRUSH_OK;
 }
 
@@ -249,11 +250,32 @@ int brush_render_forward(brush_ctx* ctx, const BrushUniforms* uniforms_host, uin
     ENSURE(cg_unsorted, (size_t)cap * 4);
     if (fused || !aux->tile_id_from_isect) ENSURE(tile_ids_sorted, (size_t)cap * (fused ? 8 : 4));
     const uint32_t tile_bits = bits_for(num_tiles);
-    SortScratch ss;
+    // Sort scratch.  The status words of BOTH sorts live behind the control block in one allocation, so one
+    // launch zero-fills everything a forward needs zeroed (12 fills in the first version of this path).
+    SortScratch ss_depth, ss_tile;
+    size_t zero_total = 0;
     {
         uint32_t mx = N > cap32 ? N : cap32;
-        int r = sort_scratch(ctx, mx, fused ? 8 : 4, fused ? 32 + tile_bits : 32, &ss);
+        int r = sort_scratch(ctx, mx, fused ? 8 : 4, fused ? 32 + tile_bits : 32, &ss_tile);  // keys_tmp / vals_tmp
         if (r != BRUSH_OK) return r;
+        ss_depth = ss_tile;
+        const size_t tile_passes = ((((fused ? 32 + tile_bits : tile_bits) + 3) / 4) * 4 + 7) / 8;
+        const size_t lb_depth = 4 * sort_tiles(N, 4) * 256 * 4;
+        const size_t lb_tile = (tile_passes ? tile_passes : 1) * sort_tiles(cap32, fused ? 8 : 4) * 256 * 4;
+        size_t off = (cl.total + 255) / 256 * 256;
+        const size_t o_hist_d = off; off += 8 * 256 * 4;
+        const size_t o_hist_t = off; off += 8 * 256 * 4;
+        const size_t o_tick_d = off; off += 64;
+        const size_t o_tick_t = off; off += 64;
+        const size_t o_lb_d = off; off += lb_depth;
+        const size_t o_lb_t = off; off += lb_tile;
+        zero_total = off;
+        ENSURE(control, zero_total);
+        char* base = (char*)ctx->control.p;
+        ss_depth.hist = (uint32_t*)(base + o_hist_d); ss_depth.tickets = (uint32_t*)(base + o_tick_d);
+        ss_depth.lb = (uint32_t*)(base + o_lb_d); ss_depth.pre_zeroed = true;
+        ss_tile.hist = (uint32_t*)(base + o_hist_t); ss_tile.tickets = (uint32_t*)(base + o_tick_t);
+        ss_tile.lb = (uint32_t*)(base + o_lb_t); ss_tile.pre_zeroed = true;
     }
     for (int i = 0; i <= BRUSH_STAGE_RASTERIZE; i++) ctx->ev_used[i] = false;
 
@@ -273,12 +295,16 @@ int brush_render_forward(brush_ctx* ctx, const BrushUniforms* uniforms_host, uin
             ctx->uni_cache.emplace_back(aux->uniforms_buffer, u);
         }
     }
-    CU(zero_async(ctl, cl.total, st));
+    {
+        ZeroSegs z{};
+        z.p[0] = ctl; z.bytes[0] = zero_total;
+        z.p[1] = aux->num_visible; z.bytes[1] = 4;
+        z.p[2] = aux->num_intersections; z.bytes[2] = 4;
+        z.p[3] = gfc; z.bytes[3] = (size_t)N * 4;  // int_zeros, render.rs:124
+        CU(zero_multi_async(z, st));
+    }
     g_launch_count++;
     write_uniforms_kernel<<<1, 32, 0, st>>>(u, aux->uniforms_buffer);
-    CU(zero_async(aux->num_visible, 4, st));
-    CU(zero_async(aux->num_intersections, 4, st));
-    if (N) CU(zero_async(gfc, (size_t)N * 4, st));  // int_zeros, render.rs:124
 
     {   // render.rs:127-142
         StageTimer t(ctx, st, BRUSH_STAGE_PROJECT_SPLATS);
@@ -290,7 +316,7 @@ int brush_render_forward(brush_ctx* ctx, const BrushUniforms* uniforms_host, uin
     {   // render.rs:151-156
         StageTimer t(ctx, st, BRUSH_STAGE_DEPTH_SORT);
         launch_radix_sort_u32((uint32_t*)ctx->depth_bits.p, (uint32_t*)ctx->presort_gid.p, aux->num_visible, N, 32,
-                              (uint32_t*)ctx->depth_sorted.p, gfc, ss, st);
+                              (uint32_t*)ctx->depth_sorted.p, gfc, ss_depth, st);
     }
     {   // render.rs:168-184
         StageTimer t(ctx, st, BRUSH_STAGE_PROJECT_VISIBLE);
@@ -319,10 +345,10 @@ int brush_render_forward(brush_ctx* ctx, const BrushUniforms* uniforms_host, uin
             if (fused)
                 launch_radix_sort_u64((uint64_t*)tid_unsorted, (uint32_t*)ctx->cg_unsorted.p, aux->num_intersections,
                                       cap32, 32 + tile_bits, (uint64_t*)tid_sorted,
-                                      (uint32_t*)aux->compact_gid_from_isect, ss, st);
+                                      (uint32_t*)aux->compact_gid_from_isect, ss_tile, st);
             else
                 launch_radix_sort_u32(tid_unsorted, (uint32_t*)ctx->cg_unsorted.p, aux->num_intersections, cap32,
-                                      tile_bits, tid_sorted, (uint32_t*)aux->compact_gid_from_isect, ss, st);
+                                      tile_bits, tid_sorted, (uint32_t*)aux->compact_gid_from_isect, ss_tile, st);
         }
     }
     {   // render.rs:239-262

@@ -54,6 +54,7 @@ struct SortScratch {
     uint32_t* hist;        // passes * 256
     uint32_t* lb;          // passes * tiles * 256 status words
     uint32_t* tickets;     // passes
+    bool pre_zeroed;       // hist, lb and tickets were zero-filled by the caller (one launch for a whole forward)
 };
 size_t sort_tiles(uint32_t max_n, int key_bytes);
 // Zeroes what the sort needs (hist, lb, tickets) itself.  Result lands in keys_out/vals_out.
@@ -140,6 +141,9 @@ int launch_views_adam(const ViewsLaunch& X, uint32_t N, uint32_t K, const float*
 // step: driver memsets and small copies may be routed through a copy engine, where they queue behind a concurrent
 // host->device upload of the next training view on another stream and stall the compute stream.
 cudaError_t zero_async(void* p, size_t bytes, cudaStream_t st);
+// Up to four 4-byte-aligned regions in ONE launch.
+struct ZeroSegs { void* p[4]; size_t bytes[4]; };
+cudaError_t zero_multi_async(const ZeroSegs& z, cudaStream_t st);
 extern std::atomic<uint64_t> g_launch_count;  // kernels launched by this library (bench.py's gpu_launches)
 struct AdamSeg {
     float* param;

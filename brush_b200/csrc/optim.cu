@@ -226,4 +226,32 @@ cudaError_t zero_async(void* p, size_t bytes, cudaStream_t st) {
     return cudaGetLastError();
 }
 
+__global__ void __launch_bounds__(256)
+zero_multi_kernel(const __grid_constant__ ZeroSegs z) {
+    const size_t stride = (size_t)gridDim.x * 256u, t0 = (size_t)blockIdx.x * 256u + threadIdx.x;
+#pragma unroll
+    for (int s = 0; s < 4; s++) {
+        if (!z.bytes[s]) continue;
+        const uintptr_t a = (uintptr_t)z.p[s];
+        const size_t head = (16 - (a & 15u)) & 15u;  // bytes before the first 16-byte boundary (multiple of 4)
+        const size_t hb = head < z.bytes[s] ? head : z.bytes[s];
+        uint32_t* w = (uint32_t*)z.p[s];
+        if (t0 < hb / 4) w[t0] = 0u;
+        const size_t rest = z.bytes[s] - hb, n16 = rest / 16;
+        uint4* p16 = (uint4*)((char*)z.p[s] + hb);
+        for (size_t i = t0; i < n16; i += stride) p16[i] = make_uint4(0u, 0u, 0u, 0u);
+        uint32_t* tail = (uint32_t*)(p16 + n16);
+        if (t0 < (rest - n16 * 16) / 4) tail[t0] = 0u;
+    }
+}
+cudaError_t zero_multi_async(const ZeroSegs& z, cudaStream_t st) {
+    size_t mx = 0;
+    for (int s = 0; s < 4; s++) mx = z.bytes[s] > mx ? z.bytes[s] : mx;
+    if (!mx) return cudaSuccess;
+    size_t blocks = (mx / 16 + 255) / 256;
+    blocks = blocks < 1 ? 1 : (blocks > 148 * 8 ? 148 * 8 : blocks);
+    zero_multi_kernel<<<(uint32_t)blocks, 256, 0, st>>>(z);
+    return cudaGetLastError();
+}
+
 }  // namespace brush

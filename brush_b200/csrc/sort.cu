@@ -288,9 +288,13 @@ static void radix_sort_impl(const KeyT* keys, const uint32_t* vals, const int32_
         return;
     }
     const uint32_t tiles = (uint32_t)sort_tiles(max_n, sizeof(KeyT));
-    zero_async(s.hist, (size_t)plan.passes * RS_RADIX * 4, st);
-    zero_async(s.lb, (size_t)plan.passes * tiles * RS_RADIX * 4, st);
-    zero_async(s.tickets, RS_MAX_PASSES * 4, st);
+    if (!s.pre_zeroed) {
+        ZeroSegs z{};
+        z.p[0] = s.hist; z.bytes[0] = (size_t)plan.passes * RS_RADIX * 4;
+        z.p[1] = s.lb; z.bytes[1] = (size_t)plan.passes * tiles * RS_RADIX * 4;
+        z.p[2] = s.tickets; z.bytes[2] = RS_MAX_PASSES * 4;
+        zero_multi_async(z, st);
+    }
     uint32_t hist_blocks = (max_n + RS_THREADS * 4 - 1) / (RS_THREADS * 4);
     if (hist_blocks > 148 * 4) hist_blocks = 148 * 4;  // every block ends with up to passes*256 global atomics
     g_launch_count += 1 + plan.passes;

@@ -239,6 +239,21 @@ def test_many_splats_per_tile_and_depth_ties(oracle):
         grads_close(gt.cpu().numpy(), ref_grads[gname], gname)
 
 
+@pytest.mark.parametrize("fused", [False, True])
+def test_large_splats_boxes_beyond_the_hit_mask(oracle, fused):
+    """Splats whose tile boxes span 1 .. ~300 tiles: hit masks of more than 32 bits, boxes beyond 64 tiles (the
+    per-tile fallback in map_intersects) and warps whose candidate lists need many passes.  Tile counts, the
+    intersection list and tile_bins must stay bit-exact."""
+    from brush_b200 import scene
+
+    w, h = 400, 272
+    sc = scene.make_scene(1_500, w, h, 1, 91, sigma_px=(1.0, 60.0))
+    img, aux, ref_img, ref_aux, _, _ = _run_both(oracle, sc, w, h, fused=fused)
+    hits = np.diff(np.concatenate([[0], ref_aux.cum_tiles_hit[:ref_aux.num_visible].astype(np.int64)]))
+    assert hits.max() > 64 and (hits > 32).sum() > 10 and (hits <= 4).sum() > 10  # all three paths are exercised
+    _check_forward(img, aux, ref_img, ref_aux, fused=fused)
+
+
 def test_raster_u32(oracle):
     """Packed RGBA8 output (rasterize.wgsl:106-109): equal up to 1 LSB per channel (exp rounding)."""
     from brush_b200 import make_uniforms, render_forward, scene
