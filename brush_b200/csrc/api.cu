@@ -709,8 +709,13 @@ int brush_xy_grad_stats(brush_ctx* ctx, const float* v_xy, const BrushAux* aux, 
     if (!ctx) return BRUSH_E_INVALID;
     if (!aux || (n && (!v_xy || !grad_norm || !visible))) return fail(ctx, BRUSH_E_INVALID, "null argument");
     CU(cudaSetDevice(ctx->device));
-    launch_xy_grad_stats(v_xy, (const uint32_t*)aux->global_from_compact_gid, aux->num_visible, n, 0.5f * width,
-                         0.5f * height, accumulate, grad_norm, visible, (cudaStream_t)stream);
+    const uint8_t* mask = nullptr;
+    if (n) {
+        int r = visible_mask_for(ctx, aux, n, (cudaStream_t)stream, &mask);
+        if (r != BRUSH_OK) return r;
+    }
+    launch_xy_grad_stats(v_xy, mask, n, 0.5f * width, 0.5f * height, accumulate, grad_norm, visible,
+                         (cudaStream_t)stream);
     CU(cudaGetLastError());
     return BRUSH_OK;
 }

@@ -171,9 +171,8 @@ void launch_image_loss_backward(const float* pred, const float* gt, uint32_t H, 
 void launch_image_u8_to_f32(const unsigned char* src, size_t n, float* dst, cudaStream_t st);
 void launch_quat_normalize(const float* q, uint32_t n, float* out, cudaStream_t st);
 void launch_quat_normalize_vjp(const float* q, uint32_t n, float* v_inout, cudaStream_t st);
-void launch_xy_grad_stats(const float* v_xy, const uint32_t* gfc, const int32_t* num_visible_dev, uint32_t n,
-                          float half_w, float half_h, int accumulate, float* grad_norm, float* visible,
-                          cudaStream_t st);
+void launch_xy_grad_stats(const float* v_xy, const uint8_t* visible_mask, uint32_t n, float half_w, float half_h,
+                          int accumulate, float* grad_norm, float* visible, cudaStream_t st);
 
 
 // ---- dp_adam.cu: view-parallel optimizer step over NVLink peer memory ----

@@ -141,23 +141,17 @@ quat_normalize_vjp_kernel(const float4* __restrict__ q, uint32_t n, float4* __re
 // Refine statistics of one view (train.rs:284-316): grad_norm[g] (+)= |v_xy[g] * (w/2, h/2)|,
 // visible[g] (+)= 1 for the view's visible splats.  accumulate = 0 overwrites (first view of a batch).
 __global__ void __launch_bounds__(256)
-xy_grad_stats_kernel(const float2* __restrict__ v_xy, const uint32_t* __restrict__ global_from_compact,
-                     const int32_t* __restrict__ num_visible_dev, uint32_t n, float half_w, float half_h,
-                     int accumulate, float* __restrict__ grad_norm, float* __restrict__ visible) {
+xy_grad_stats_kernel(const float2* __restrict__ v_xy, const uint8_t* __restrict__ visible_mask, uint32_t n,
+                     float half_w, float half_h, int accumulate, float* __restrict__ grad_norm,
+                     float* __restrict__ visible) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float2 g = v_xy[i];
     const float gx = g.x * half_w, gy = g.y * half_h;
     const float nrm = sqrtf(gx * gx + gy * gy);
+    const float vis = (float)visible_mask[i];
     grad_norm[i] = accumulate ? grad_norm[i] + nrm : nrm;
-    if (!accumulate) visible[i] = 0.f;
-}
-__global__ void __launch_bounds__(256)
-visible_flags_kernel(const uint32_t* __restrict__ global_from_compact, const int32_t* __restrict__ num_visible_dev,
-                     float* __restrict__ visible) {
-    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= (uint32_t)*num_visible_dev) return;
-    visible[global_from_compact[c]] += 1.0f;  // compact ids are unique: no race
+    visible[i] = accumulate ? visible[i] + vis : vis;
 }
 
 // == image_to_tensor's u8 -> f32 / 255 (crates/brush-dataset/src/lib.rs), done after the upload instead of before
@@ -193,14 +187,12 @@ void launch_quat_normalize_vjp(const float* q, uint32_t n, float* v_inout, cudaS
     g_launch_count++;
     quat_normalize_vjp_kernel<<<(n + 255) / 256, 256, 0, st>>>((const float4*)q, n, (float4*)v_inout);
 }
-void launch_xy_grad_stats(const float* v_xy, const uint32_t* gfc, const int32_t* num_visible_dev, uint32_t n,
-                          float half_w, float half_h, int accumulate, float* grad_norm, float* visible,
-                          cudaStream_t st) {
+void launch_xy_grad_stats(const float* v_xy, const uint8_t* visible_mask, uint32_t n, float half_w, float half_h,
+                          int accumulate, float* grad_norm, float* visible, cudaStream_t st) {
     if (!n) return;
-    g_launch_count += 2;
-    xy_grad_stats_kernel<<<(n + 255) / 256, 256, 0, st>>>((const float2*)v_xy, gfc, num_visible_dev, n, half_w,
-                                                          half_h, accumulate, grad_norm, visible);
-    visible_flags_kernel<<<(n + 255) / 256, 256, 0, st>>>(gfc, num_visible_dev, visible);
+    g_launch_count++;
+    xy_grad_stats_kernel<<<(n + 255) / 256, 256, 0, st>>>((const float2*)v_xy, visible_mask, n, half_w, half_h,
+                                                          accumulate, grad_norm, visible);
 }
 
 __global__ void __launch_bounds__(256)

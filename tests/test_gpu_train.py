@@ -284,6 +284,18 @@ def test_views_step_two_views_on_one_device(k):
         ref_norm += 0.5 * gn
         ref_vis += gv
         ref_g = [a.clone() for a in g] if ref_g is None else [a + b for a, b in zip(ref_g, g)]
+    # statistics of an OLDER forward: the ctx no longer holds its visibility mask and rebuilds it from the aux
+    pred0, aux0 = keep[0]
+    g0 = render_backward(aux0, params["means"], params["log_scales"], norm_rot, params["sh_coeffs"].shape,
+                         params["raw_opacity"], pred0, v_out[0], ctx=ctx)
+    gn0, gv0 = torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)
+    caux0 = aux0._c()
+    ctx.check(L.brush_xy_grad_stats(ctx.handle, g0[1].data_ptr(), C.byref(caux0), n, w, h, 0, gn0.data_ptr(),
+                                    gv0.data_ptr(), None))
+    V0 = aux0.read_num_visible()
+    vis0 = torch.zeros(n, device=DEV)
+    vis0[aux0.global_from_compact_gid[:V0].long()] = 1
+    assert torch.equal(gv0, vis0) and 0 < V0 < n
     v_means, _, v_scales, v_quats, v_sh, v_opac = ref_g
     ctx.check(L.brush_quat_normalize_vjp(ctx.handle, raw_rot.data_ptr(), n, v_quats.data_ptr(), None))
     # reference: brush_adam_step on clones
