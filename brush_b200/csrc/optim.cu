@@ -206,6 +206,7 @@ cudaError_t zero_async(void* p, size_t bytes, cudaStream_t st) {
     unsigned char* b = (unsigned char*)p;
     if (((uintptr_t)b & 15u) || bytes < 16) {  // unaligned or tiny: byte-wise through the tail path when it fits
         if (bytes <= 256) {
+            g_launch_count++;
             zero_fill_kernel<<<1, 256, 0, st>>>(nullptr, 0, b, (uint32_t)bytes);
             return cudaGetLastError();
         }
@@ -214,6 +215,7 @@ cudaError_t zero_async(void* p, size_t bytes, cudaStream_t st) {
     const size_t n16 = bytes / 16;
     size_t blocks = (n16 + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
+    g_launch_count++;
     zero_fill_kernel<<<(uint32_t)blocks, 256, 0, st>>>((uint4*)b, n16, b + n16 * 16, (uint32_t)(bytes - n16 * 16));
     return cudaGetLastError();
 }
@@ -242,6 +244,7 @@ cudaError_t zero_multi_async(const ZeroSegs& z, cudaStream_t st) {
     if (!mx) return cudaSuccess;
     size_t blocks = (mx / 16 + 255) / 256;
     blocks = blocks < 1 ? 1 : (blocks > 148 * 8 ? 148 * 8 : blocks);
+    g_launch_count++;
     zero_multi_kernel<<<(uint32_t)blocks, 256, 0, st>>>(z);
     return cudaGetLastError();
 }
