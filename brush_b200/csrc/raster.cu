@@ -339,31 +339,38 @@ __device__ __forceinline__ void flush_rows(uint32_t dummy_addr, uint32_t pair_ad
     const uint32_t row = pair_addr + r_idx * BW_ROW + half * 128u;
     const uint32_t pix = pix_addr + half * 256u;
     const float by_h = by + (float)(2u * half);
-    float s0 = 0.f, sx = 0.f, sy = 0.f, sxx = 0.f, sxy = 0.f, syy = 0.f, r = 0.f, g = 0.f, b = 0.f;
+    // Moments of va about the splat centre.  Along a pixel row dy is constant, so only the x-moments
+    // (1, dx, dx^2) are accumulated per pixel; dy and dy^2 are applied once per row.
+    float r = 0.f, g = 0.f, b = 0.f;
+    float m0[2], m1[2], m2[2];
+    const float dx0 = g0.x - bx;
 #pragma unroll
     for (int py = 0; py < 2; py++) {
-        const float dy = g0.y - (by_h + (float)py);
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f;
 #pragma unroll
         for (int kx = 0; kx < 8; kx += 2) {
             const int p = py * 8 + kx;
             const float4 e = lds128(row + p * 8);  // va, fac of pixels p and p+1
             const float4 o0 = lds128(pix + p * 16), o1 = lds128(pix + p * 16 + 16);
             {
-                const float dx = g0.x - (bx + (float)kx);
-                const float t1 = e.x * dx, t2 = e.x * dy;
-                s0 += e.x; sx += t1; sy += t2;
-                sxx = fmaf(t1, dx, sxx); sxy = fmaf(t1, dy, sxy); syy = fmaf(t2, dy, syy);
+                const float dx = dx0 - (float)kx;
+                const float t1 = e.x * dx;
+                a0 += e.x; a1 = fmaf(e.x, dx, a1); a2 = fmaf(t1, dx, a2);
                 r = fmaf(e.y, o0.x, r); g = fmaf(e.y, o0.y, g); b = fmaf(e.y, o0.z, b);
             }
             {
-                const float dx = g0.x - (bx + (float)(kx + 1));
-                const float t1 = e.z * dx, t2 = e.z * dy;
-                s0 += e.z; sx += t1; sy += t2;
-                sxx = fmaf(t1, dx, sxx); sxy = fmaf(t1, dy, sxy); syy = fmaf(t2, dy, syy);
+                const float dx = dx0 - (float)(kx + 1);
+                const float t1 = e.z * dx;
+                a0 += e.z; a1 = fmaf(e.z, dx, a1); a2 = fmaf(t1, dx, a2);
                 r = fmaf(e.w, o1.x, r); g = fmaf(e.w, o1.y, g); b = fmaf(e.w, o1.z, b);
             }
         }
+        m0[py] = a0; m1[py] = a1; m2[py] = a2;
     }
+    const float dy0 = g0.y - by_h, dy1 = dy0 - 1.0f;
+    float s0 = m0[0] + m0[1], sx = m1[0] + m1[1], sxx = m2[0] + m2[1];
+    float sy = fmaf(dy1, m0[1], dy0 * m0[0]), sxy = fmaf(dy1, m1[1], dy0 * m1[0]);
+    float syy = fmaf(dy1 * dy1, m0[1], (dy0 * dy0) * m0[0]);
     const uint32_t F = 0xffffffffu;
     s0 += __shfl_xor_sync(F, s0, 16); sx += __shfl_xor_sync(F, sx, 16); sy += __shfl_xor_sync(F, sy, 16);
     sxx += __shfl_xor_sync(F, sxx, 16); sxy += __shfl_xor_sync(F, sxy, 16); syy += __shfl_xor_sync(F, syy, 16);
