@@ -105,6 +105,21 @@ static ControlLayout control_layout(uint32_t N) {
     return l;
 }
 
+// Host copy of the uniforms a forward wrote into aux.uniforms_buffer (part of the autodiff state, render.rs:436-446):
+// from the ctx's cache, or read back (synchronises) when the aux comes from another ctx / process.
+static int uniforms_of(brush_ctx* ctx, const BrushAux* aux, uint32_t N, uint32_t K, cudaStream_t st, BrushUniforms* out) {
+    bool cached = false;
+    for (auto& e : ctx->uni_cache)
+        if (e.first == aux->uniforms_buffer) { *out = e.second; cached = true; }
+    if (!cached) {
+        CU(cudaMemcpyAsync(out, aux->uniforms_buffer, sizeof(*out), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+    }
+    if (out->total_splats != N || out->sh_degree != degree_of(K))
+        return fail(ctx, BRUSH_E_INVALID, "aux.uniforms_buffer does not match N / K");
+    return BRUSH_OK;
+}
+
 extern "C" {
 #pragma GCC visibility push(default)
 
@@ -378,15 +393,10 @@ int brush_render_backward(brush_ctx* ctx, uint32_t N, uint32_t K, const float* m
     cudaStream_t st = (cudaStream_t)stream;
     CU(cudaSetDevice(ctx->device));
     BrushUniforms u;
-    bool cached = false;
-    for (auto& e : ctx->uni_cache)
-        if (e.first == aux->uniforms_buffer) { u = e.second; cached = true; }
-    if (!cached) {  // aux from another ctx / process: read the 112 bytes back (synchronises)
-        CU(cudaMemcpyAsync(&u, aux->uniforms_buffer, sizeof(u), cudaMemcpyDeviceToHost, st));
-        CU(cudaStreamSynchronize(st));
+    {
+        int r = uniforms_of(ctx, aux, N, K, st, &u);
+        if (r != BRUSH_OK) return r;
     }
-    if (u.total_splats != N || u.sh_degree != degree_of(K))
-        return fail(ctx, BRUSH_E_INVALID, "aux.uniforms_buffer does not match N / K");
     const Cam cam = make_cam(u);
     ENSURE(v_projected, (size_t)N * VP_STRIDE * 4 + 16);
     ctx->ev_used[BRUSH_STAGE_RASTERIZE_BWD] = ctx->ev_used[BRUSH_STAGE_GATHER_PROJECT_BWD] = false;
@@ -472,15 +482,10 @@ int brush_render_backward_rows(brush_ctx* ctx, uint32_t N, uint32_t K, const flo
     cudaStream_t st = (cudaStream_t)stream;
     CU(cudaSetDevice(ctx->device));
     BrushUniforms u;
-    bool cached = false;
-    for (auto& e : ctx->uni_cache)
-        if (e.first == aux->uniforms_buffer) { u = e.second; cached = true; }
-    if (!cached) {
-        CU(cudaMemcpyAsync(&u, aux->uniforms_buffer, sizeof(u), cudaMemcpyDeviceToHost, st));
-        CU(cudaStreamSynchronize(st));
+    {
+        int r = uniforms_of(ctx, aux, N, K, st, &u);
+        if (r != BRUSH_OK) return r;
     }
-    if (u.total_splats != N || u.sh_degree != degree_of(K))
-        return fail(ctx, BRUSH_E_INVALID, "aux.uniforms_buffer does not match N / K");
     const Cam cam = make_cam(u);
     float* rows = x->rows[x->rank];
     ctx->ev_used[BRUSH_STAGE_RASTERIZE_BWD] = ctx->ev_used[BRUSH_STAGE_GATHER_PROJECT_BWD] = false;
@@ -541,15 +546,10 @@ int brush_render_backward_adam(brush_ctx* ctx, uint32_t N, uint32_t K, const Bru
     cudaStream_t st = (cudaStream_t)stream;
     CU(cudaSetDevice(ctx->device));
     BrushUniforms u;
-    bool cached = false;
-    for (auto& e : ctx->uni_cache)
-        if (e.first == aux->uniforms_buffer) { u = e.second; cached = true; }
-    if (!cached) {
-        CU(cudaMemcpyAsync(&u, aux->uniforms_buffer, sizeof(u), cudaMemcpyDeviceToHost, st));
-        CU(cudaStreamSynchronize(st));
+    {
+        int r = uniforms_of(ctx, aux, N, K, st, &u);
+        if (r != BRUSH_OK) return r;
     }
-    if (u.total_splats != N || u.sh_degree != degree_of(K))
-        return fail(ctx, BRUSH_E_INVALID, "aux.uniforms_buffer does not match N / K");
     const Cam cam = make_cam(u);
     ENSURE(v_projected, (size_t)N * VP_STRIDE * 4 + 16);
     ctx->ev_used[BRUSH_STAGE_RASTERIZE_BWD] = ctx->ev_used[BRUSH_STAGE_GATHER_PROJECT_BWD] = false;
