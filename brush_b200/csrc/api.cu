@@ -153,7 +153,8 @@ void brush_ctx_destroy(brush_ctx* ctx) {
     Buf* bufs[] = {&ctx->control, &ctx->presort_gid, &ctx->depth_bits, &ctx->depth_sorted, &ctx->num_tiles_hit,
                    &ctx->keys_tmp, &ctx->vals_tmp, &ctx->hist, &ctx->lb, &ctx->tickets, &ctx->tile_ids_unsorted,
                    &ctx->cg_unsorted, &ctx->tile_ids_sorted, &ctx->v_projected, &ctx->sticky, &ctx->loss_scratch, &ctx->h_means, &ctx->h_lscales,
-                   &ctx->h_quats, &ctx->h_sh, &ctx->h_opac, &ctx->h_img};
+                   &ctx->h_quats, &ctx->h_sh, &ctx->h_opac, &ctx->h_img, &ctx->visible_mask, &ctx->tile_masks,
+                   &ctx->tile_boxes};
     for (Buf* b : bufs)
         if (b->p) cudaFree(b->p);
     for (Buf& b : ctx->h_aux)
