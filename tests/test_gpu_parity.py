@@ -339,3 +339,76 @@ def test_full_size_config4_vs_oracle(oracle):
         a, b = gt.cpu().numpy().astype(np.float64), ref_grads[gname].astype(np.float64)
         bad = np.abs(a - b) > 1e-3 * np.abs(b) + 2e-5 * np.abs(b).max()
         assert bad.mean() < 1e-5, f"{gname}: {bad.sum()} of {bad.size}"
+
+
+@pytest.mark.parametrize("name", ["cfg2_100k_1024", "cfg3_300k_800"])
+def test_baseline_configs_2_and_3_vs_oracle(oracle, name):
+    """BASELINE.json configs[1] and [2] at full size (100k Gaussians at 1024^2, SH 0; 300k at 800^2, SH 3)."""
+    from brush_b200 import scene
+
+    oracle.set_threads(oracle.max_threads())
+    try:
+        sc = scene.make_config_scene(name)
+        w, h = sc.width, sc.height
+        rng = np.random.default_rng(17)
+        v_out = (rng.uniform(-1, 1, (h, w, 4)) / (h * w)).astype(np.float32)
+        img, aux, ref_img, ref_aux, grads, ref_grads = _run_both(oracle, sc, w, h, v_out=v_out)
+    finally:
+        oracle.set_threads(1)
+    _check_forward(img, aux, ref_img, ref_aux)
+    for gname, gt in zip(["v_means", "v_xy", "v_log_scales", "v_quats", "v_coeffs", "v_raw_opac"], grads):
+        a, b = gt.cpu().numpy().astype(np.float64), ref_grads[gname].astype(np.float64)
+        bad = np.abs(a - b) > 1e-3 * np.abs(b) + 2e-5 * np.abs(b).max()
+        # a pair sitting on the alpha = 1/255 threshold is kept by one machine only (see _check_forward): the splats
+        # of those few pairs see a different gradient; counted and bounded
+        assert bad.mean() < 5e-5, f"{gname}: {bad.sum()} of {bad.size}"
+
+
+def test_config5_6m_4k_properties():
+    """BASELINE.json configs[4]: 6M Gaussians, SH 3, 3840x2160, ~10^8 (tile, depth) keys -- too slow for the CPU
+    oracle inside the suite, so the size-independent properties of the path are checked instead: the scan total is
+    the intersection count, the intersection list is sorted by tile and, inside a tile, by compact (= depth) order,
+    tile_bins are exactly the run boundaries of the sorted tile ids, the compact order is (depth, gid) ascending,
+    and a second forward reproduces every output bit for bit."""
+    from brush_b200 import get_context, make_uniforms, render_forward, scene
+
+    sc = scene.make_config_scene("cfg5_6m_4k")
+    w, h, n = sc.width, sc.height, sc.means.shape[0]
+    vm, focal, center = reference_camera(w, h)
+    u = make_uniforms(vm, focal, (w, h), center)
+    args = [T(sc.means), T(sc.log_scales), T(sc.quats), T(sc.sh_coeffs), T(sc.raw_opacity)]
+    cap = 160 << 20
+    img, aux = render_forward(u, *args, False, isect_capacity=cap, keep_tile_ids=True)
+    get_context(DEV).sync_check()  # raises on intersection-capacity overflow
+    V, I = aux.read_num_visible(), aux.read_num_intersections()
+    assert 0 < V <= n and 50_000_000 < I < cap, (V, I)
+    cum = aux.cum_tiles_hit[:V].long()
+    assert int(cum[-1]) == I and bool((cum[1:] >= cum[:-1]).all())
+    tid = aux.tile_id_from_isect[:I].long()
+    cg = aux.compact_gid_from_isect[:I].long()
+    assert bool((tid[1:] >= tid[:-1]).all())                                   # sorted by tile
+    same = tid[1:] == tid[:-1]
+    assert bool((cg[1:][same] > cg[:-1][same]).all())                          # stable: depth order inside a tile
+    assert int(cg.max()) < V
+    tiles = ((w + 15) // 16) * ((h + 15) // 16)
+    counts = torch.bincount(tid, minlength=tiles)
+    ends = torch.cumsum(counts, 0)
+    bins = aux.tile_bins.view(-1, 2).long()
+    nz = counts > 0
+    assert bool((bins[nz, 1] == ends[nz]).all()) and bool((bins[nz, 0] == (ends - counts)[nz]).all())
+    assert bool(((bins[~nz, 1] - bins[~nz, 0]) == 0).all())
+    # compact order = ascending (depth, gid)
+    gfc = aux.global_from_compact_gid[:V].long()
+    vmt = torch.as_tensor(np.asarray(vm, np.float32), device=DEV)  # row-major world-to-camera
+    depth = args[0][gfc] @ vmt[2, :3] + vmt[2, 3]
+    d = depth[1:] - depth[:-1]
+    assert float(d.min()) > -1e-4                                               # float re-evaluation noise only
+    assert int(torch.unique(gfc).numel()) == V
+    out = img.float()
+    # (colours are SH + 0.5 unclamped, so only alpha is bounded)
+    assert bool(torch.isfinite(out).all()) and float(out[..., 3].max()) <= 1.0 + 1e-6 and float(out[..., 3].min()) >= 0.0
+    # determinism: every output of a second forward is identical
+    img2, aux2 = render_forward(u, *args, False, isect_capacity=cap, keep_tile_ids=True)
+    assert torch.equal(img, img2) and torch.equal(aux.final_index, aux2.final_index)
+    assert torch.equal(aux.compact_gid_from_isect[:I], aux2.compact_gid_from_isect[:I])
+    assert torch.equal(aux.tile_bins, aux2.tile_bins) and torch.equal(aux.global_from_compact_gid, aux2.global_from_compact_gid)
