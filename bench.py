@@ -166,7 +166,7 @@ def run_ours(args):
     gt_dev = torch.empty((N_VIEWS, H, W, 3), dtype=torch.float32, device=dev)
     with torch.no_grad():
         for v, cam in enumerate(cams):
-            img, _ = splats.render(cam, (W, H), False)
+            img, _ = splats.render(cam, (W, H), False, isect_capacity=args.capacity)
             gt_dev[v] = img[..., :3].clamp_(0.0, 1.0)
         # the data set holds 8-bit images (as the reference's does before image_to_tensor); both timed loops train on
         # the same quantised targets, the end-to-end loop uploads the bytes and converts on the device

@@ -280,43 +280,79 @@ map_intersects_kernel(const __grid_constant__ Cam cam, const float* __restrict__
                       uint32_t* __restrict__ compact_gid_from_isect, const uint32_t* __restrict__ depth_sorted_bits,
                       uint64_t* __restrict__ key64_from_isect, const uint64_t* __restrict__ tile_masks,
                       const uint32_t* __restrict__ tile_boxes) {
-    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t FULL = 0xffffffffu;
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31u;
     const uint32_t V = (uint32_t)*num_visible_dev;
-    if (c >= V) return;
-    uint64_t isect = c > 0 ? cum_tiles_hit[c - 1] : 0u;
-    const uint64_t depth_lo = key64_from_isect ? (uint64_t)depth_sorted_bits[c] : 0ull;
-    auto emit = [&](uint32_t tx, uint32_t ty) {
+    const bool valid = c < V;
+    if (__all_sync(FULL, !valid)) return;
+    const uint64_t first = valid && c > 0 ? cum_tiles_hit[c - 1] : 0u;
+    const uint32_t depth_bits = valid && key64_from_isect ? depth_sorted_bits[c] : 0u;
+    auto emit = [&](uint64_t isect, uint32_t cg, uint32_t dbits, uint32_t tx, uint32_t ty) {
         if (isect < capacity) {
             const uint32_t tile_id = tx + ty * cam.tiles_x;
-            if (key64_from_isect) key64_from_isect[isect] = ((uint64_t)tile_id << 32) | depth_lo;
+            if (key64_from_isect) key64_from_isect[isect] = ((uint64_t)tile_id << 32) | (uint64_t)dbits;
             else tile_id_from_isect[isect] = tile_id;
-            compact_gid_from_isect[isect] = c;
-            isect++;
+            compact_gid_from_isect[isect] = cg;
         }
     };
-    const uint32_t box = tile_boxes[c];
-    if (!(box & BOX_BIG)) {  // expand project_visible's hit mask: row-major order, as the reference's loop
-        uint64_t m = tile_masks[c];
+    const uint32_t box = valid ? tile_boxes[c] : 0u;
+    const bool big = valid && (box & BOX_BIG);
+    if (valid && !big) {  // expand project_visible's hit mask: row-major order, as the reference's loop
+        uint64_t m = tile_masks[c], isect = first;
         const uint32_t minx = box & 1023u, miny = (box >> 10) & 1023u, w = box >> 20;
         const float fw = (float)w;
         while (m) {
             const uint32_t j = (uint32_t)__ffsll((long long)m) - 1u;
             m &= m - 1ull;
             const uint32_t row = (uint32_t)__float2uint_rz(__fdividef((float)j + 0.5f, fw));
-            emit(minx + j - row * w, miny + row);
+            emit(isect++, c, depth_bits, minx + j - row * w, miny + row);
         }
-        return;
     }
-    const float* p = projected + (size_t)c * 9;
-    V2 xy = {p[0], p[1]};
-    V3 conic = {p[2], p[3], p[4]};
-    float opac = p[8];
-    uint32_t radius = radius_from_conic(conic);
-    TileBox b = get_tile_bbox(xy, radius, cam.tiles_x, cam.tiles_y);
-    VisTest vt = make_vis_test(xy, conic, opac);
-    for (uint32_t ty = b.miny; ty < b.maxy; ty++)
-        for (uint32_t tx = b.minx; tx < b.maxx; tx++)
-            if (can_be_visible(vt, tx, ty)) emit(tx, ty);
+    // Boxes beyond the 64-tile mask: the whole warp walks one such splat at a time, 32 tiles per pass, with the
+    // reference's test; the ballot gives every hit its position in the splat's row-major run.
+    uint32_t pending = __ballot_sync(FULL, big);
+    if (!pending) return;
+    VisTest vt{};
+    TileBox b{0u, 0u, 0u, 0u};
+    if (big) {
+        const float* p = projected + (size_t)c * 9;
+        const V2 xy = {p[0], p[1]};
+        const V3 conic = {p[2], p[3], p[4]};
+        b = get_tile_bbox(xy, radius_from_conic(conic), cam.tiles_x, cam.tiles_y);
+        vt = make_vis_test(xy, conic, p[8]);
+    }
+    while (pending) {
+        const int src = __ffs((int)pending) - 1;
+        pending &= pending - 1u;
+        VisTest ot;
+        ot.any = __shfl_sync(FULL, (int)vt.any, src) != 0;
+        ot.conic_scaled.c[0].x = __shfl_sync(FULL, vt.conic_scaled.c[0].x, src);
+        ot.conic_scaled.c[0].y = __shfl_sync(FULL, vt.conic_scaled.c[0].y, src);
+        ot.conic_scaled.c[1].y = __shfl_sync(FULL, vt.conic_scaled.c[1].y, src);
+        ot.conic_scaled.c[1].x = ot.conic_scaled.c[0].y;
+        ot.xy.x = __shfl_sync(FULL, vt.xy.x, src);
+        ot.xy.y = __shfl_sync(FULL, vt.xy.y, src);
+        const uint32_t minx = __shfl_sync(FULL, b.minx, src), miny = __shfl_sync(FULL, b.miny, src);
+        const uint32_t bw = __shfl_sync(FULL, b.maxx, src) - minx, bh = __shfl_sync(FULL, b.maxy, src) - miny;
+        const uint32_t cg = __shfl_sync(FULL, c, src), dbits = __shfl_sync(FULL, depth_bits, src);
+        uint64_t isect = __shfl_sync(FULL, (unsigned long long)first, src);
+        const uint32_t total = bw * bh;
+        const float fw = (float)bw;
+        for (uint32_t base = 0; base < total; base += 32) {
+            const uint32_t j = base + lane;
+            bool pass = false;
+            uint32_t tx = 0, ty = 0;
+            if (j < total) {
+                const uint32_t row = (uint32_t)__float2uint_rz(__fdividef((float)j + 0.5f, fw));
+                tx = minx + j - row * bw;
+                ty = miny + row;
+                pass = can_be_visible(ot, tx, ty);
+            }
+            const uint32_t ballot = __ballot_sync(FULL, pass);
+            if (pass) emit(isect + __popc(ballot & ((1u << lane) - 1u)), cg, dbits, tx, ty);
+            isect += __popc(ballot);
+        }
+    }
 }
 
 void launch_map_intersects(const Cam& cam, uint32_t N, const float* projected, const uint32_t* cum_tiles_hit,
