@@ -59,9 +59,9 @@ constexpr uint32_t SM_SLOTS = TILE_SIZE + 1;          // slot 256 is a dummy spl
 constexpr uint32_t SM_G0 = 0;                         // float4[257]: x, y, A, B
 constexpr uint32_t SM_G1 = SM_G0 + 16 * SM_SLOTS;     // float4[257]: C, L, opacity, compact gid (bits)
 constexpr uint32_t SM_COL = SM_G1 + 16 * SM_SLOTS;    // float4[257]: r, g, b, mask of the 8x4 blocks the splat reaches
-constexpr uint32_t SM_LIST = SM_COL + 16 * SM_SLOTS;  // u32[8][260]: per warp, shared-window addresses of the survivors' G0 entries
+constexpr uint32_t SM_LIST = SM_COL + 16 * SM_SLOTS;  // u16[8][260]: per warp, LOW HALVES of the shared-window addresses of the survivors' G0 entries
 constexpr uint32_t LIST_PAD = 4;                      // lists are padded with the dummy slot to a multiple of 4
-constexpr uint32_t LIST_STRIDE = 4 * (TILE_SIZE + LIST_PAD);
+constexpr uint32_t LIST_STRIDE = 2 * (TILE_SIZE + LIST_PAD);
 constexpr uint32_t SM_BYTES = SM_LIST + LIST_STRIDE * (TILE_SIZE / 32);
 
 constexpr float LOG2E = 1.4426950408889634f;
@@ -98,6 +98,28 @@ __device__ __forceinline__ void sts128(uint32_t a, float4 v) {
 }
 __device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v) {
     asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ void sts_u16(uint32_t a, uint32_t v) {
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"((unsigned short)v) : "memory");
+}
+__device__ __forceinline__ uint2 lds64u(uint32_t a) {
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a));
+    return v;
+}
+// Four consecutive entries of a survivor list -> full shared-window addresses.  The lists hold 16-bit halves
+// (half the shared memory of u32 entries: what lets a fourth backward CTA fit on an SM); the staged splats all
+// lie within one 64 KB window of the CTA's shared memory (checked once per CTA), so one PRMT per entry puts
+// the common upper half back.
+__device__ __forceinline__ void list_load4(uint32_t addr, uint32_t sbase, uint32_t (&aa)[4]) {
+    const uint2 l = lds64u(addr);
+    aa[0] = __byte_perm(l.x, sbase, 0x7610);
+    aa[1] = __byte_perm(l.x, sbase, 0x7632);
+    aa[2] = __byte_perm(l.y, sbase, 0x7610);
+    aa[3] = __byte_perm(l.y, sbase, 0x7632);
+}
+__device__ __forceinline__ void check_list_window(uint32_t sbase) {
+    if (((sbase ^ (sbase + SM_LIST)) >> 16) != 0u) __trap();
 }
 // The dummy slot: L = -inf, so q = -inf fails the visibility test for every pixel.
 __device__ __forceinline__ void init_dummy_slot(uint32_t sbase) {
@@ -180,16 +202,16 @@ __device__ __forceinline__ uint32_t cull_to_list(uint32_t sbase, uint32_t list_a
         bool hit = false;
         if (mine >= t_lo && mine < t_max) hit = (lds_u32(sbase + SM_COL + mine * 16u + 12u) >> warp) & 1u;
         const uint32_t mask = __ballot_sync(0xffffffffu, hit);
-        if (hit) sts_u32(list_addr + 4u * (n_list + __popc(mask & ((1u << lane) - 1u))), sbase + mine * 16u);
+        if (hit) sts_u16(list_addr + 2u * (n_list + __popc(mask & ((1u << lane) - 1u))), sbase + mine * 16u);
         n_list += __popc(mask);
     }
-    if (lane < LIST_PAD) sts_u32(list_addr + 4u * (n_list + lane), sbase + TILE_SIZE * 16u);
+    if (lane < LIST_PAD) sts_u16(list_addr + 2u * (n_list + lane), sbase + TILE_SIZE * 16u);
     __syncwarp();
     return n_list;
 }
 
-template <bool RASTER_U32>
-__global__ void __launch_bounds__(TILE_SIZE)
+template <bool RASTER_U32, int MIN_CTAS, bool VOTE_SKIP>
+__global__ void __launch_bounds__(TILE_SIZE, MIN_CTAS)
 rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ compact_gid_from_isect,
                  const uint32_t* __restrict__ tile_bins, const float* __restrict__ projected,
                  void* __restrict__ out_img, uint32_t* __restrict__ final_index) {
@@ -202,19 +224,24 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
     const uint32_t px = bx0 + (lane & 7u), py = by0 + (lane >> 3);
     const bool inside = px < cam.img_w && py < cam.img_h;
     const float pcx = (float)px + 0.5f, pcy = (float)py + 0.5f;
-    bool done = !inside;
 
     const uint2 range = __ldg(reinterpret_cast<const uint2*>(tile_bins) + tile_id);
     const uint32_t num_batches = (range.y - range.x + TILE_SIZE - 1) / TILE_SIZE;
-    float T = 1.0f;
+    // Transmittance; a pixel that is finished (or outside the image) carries it NEGATED, so "still compositing"
+    // is the single test T > 0 and no separate flag has to be kept and combined per splat.  T stays > 1e-4
+    // while a pixel is live (rasterize.wgsl stops before going below), so the sign is free.
+    float T = inside ? 1.0f : -1.0f;
     float pr = 0.f, pg = 0.f, pb = 0.f;
     uint32_t final_idx = 0;
-    if (tid == 0) init_dummy_slot(sbase);
+    if (tid == 0) {
+        check_list_window(sbase);
+        init_dummy_slot(sbase);
+    }
 
     for (uint32_t b = 0; b < num_batches; b++) {
         // barrier before the batch buffer is overwritten + whole-tile early exit (the reference keeps
         // finished threads spinning through every batch)
-        if (__syncthreads_and(done)) break;
+        if (__syncthreads_and(T <= 0.0f)) break;
         const uint32_t batch_start = range.x + b * TILE_SIZE;
         const uint32_t remaining = min(TILE_SIZE, range.y - batch_start);
         if (tid < remaining) {
@@ -222,15 +249,15 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
             stage_splat(sbase, tid, projected, cg, cg, (float)(blockIdx.x * TILE_WIDTH), (float)(blockIdx.y * TILE_WIDTH));
         }
         __syncthreads();
-        if (__all_sync(0xffffffffu, done)) continue;
+        if (__all_sync(0xffffffffu, T <= 0.0f)) continue;
         const uint32_t n_list = cull_to_list(sbase, list_addr, lane, warp, 0u, remaining);
         // Four survivors per iteration: their geometry (sp, q, alpha) is independent of the compositing state, so
         // the four chains overlap; the order-dependent part is then applied in depth order, predicated (no
         // divergent branch).  The list is padded with the dummy slot, which no pixel sees.
         uint32_t final_a = 0;
         for (uint32_t i = 0; i < n_list; i += LIST_PAD) {
-            const uint4 a4 = lds128u(list_addr + 4u * i);
-            const uint32_t aa[4] = {a4.x, a4.y, a4.z, a4.w};
+            uint32_t aa[4];
+            list_load4(list_addr + 2u * i, sbase, aa);
             bool act[4];
             float alpha[4];
 #pragma unroll
@@ -245,26 +272,26 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
             }
 #pragma unroll
             for (int j = 0; j < 4; j++) {
-                const bool live = act[j] && !done;
-                if (__any_sync(0xffffffffu, live)) {
+                const bool live = act[j] && T > 0.0f;
+                if (!VOTE_SKIP || __any_sync(0xffffffffu, live)) {
                     const float4 c = lds128(aa[j] + SM_COL);
                     const float next_T = T * (1.0f - alpha[j]);
                     const bool stop = live && next_T <= 1e-4f;  // rasterize.wgsl: stop BEFORE adding this splat
-                    const bool contrib = live && !stop;
-                    done = done || stop;
+                    const bool contrib = live && !(next_T <= 1e-4f);
                     const float fac = contrib ? alpha[j] * T : 0.0f;
                     pr = fmaf(c.x, fac, pr); pg = fmaf(c.y, fac, pg); pb = fmaf(c.z, fac, pb);
                     T = contrib ? next_T : T;
+                    T = stop ? -T : T;
                     final_a = contrib ? aa[j] : final_a;
                 }
             }
-            if (__all_sync(0xffffffffu, done)) break;
+            if (__all_sync(0xffffffffu, T <= 0.0f)) break;
         }
         if (final_a) final_idx = batch_start + ((final_a - sbase) >> 4);
     }
     if (inside) {
         const size_t pix_id = (size_t)px + (size_t)py * cam.img_w;
-        const float a = 1.0f - T;
+        const float a = 1.0f - fabsf(T);
         if (RASTER_U32) {  // rasterize.wgsl:106-109
             uint32_t r8 = __float2uint_rz(fminf(fmaxf(pr * 255.0f, 0.f), 255.f));
             uint32_t g8 = __float2uint_rz(fminf(fmaxf(pg * 255.0f, 0.f), 255.f));
@@ -284,12 +311,26 @@ void launch_rasterize(const Cam& cam, const uint32_t* compact_gid_from_isect, co
     if (cam.tiles_x == 0 || cam.tiles_y == 0) return;
     dim3 grid(cam.tiles_x, cam.tiles_y);
     g_launch_count++;
-    if (raster_u32)
-        rasterize_kernel<true><<<grid, TILE_SIZE, 0, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
-                                                           out_img, final_index);
-    else
-        rasterize_kernel<false><<<grid, TILE_SIZE, 0, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
-                                                            out_img, final_index);
+    // A/B switch while the variants are being measured: BRUSH_RASTER_FWD = 0 (4 CTAs/SM, vote-skip),
+    // 1 (5 CTAs/SM, vote-skip), 2 (5 CTAs/SM, no vote-skip),
+    // 3 (6 CTAs/SM, vote-skip)
+    const char* env = getenv("BRUSH_RASTER_FWD");  // read per launch so that one process can compare them
+    const int variant = env ? atoi(env) : 1;
+#define BRUSH_RASTER_LAUNCH(U32, CTAS, VOTE)                                                                  \
+    rasterize_kernel<U32, CTAS, VOTE><<<grid, TILE_SIZE, 0, st>>>(cam, compact_gid_from_isect, tile_bins, projected, \
+                                                                  out_img, final_index)
+    if (raster_u32) {
+        BRUSH_RASTER_LAUNCH(true, 5, true);
+    } else if (variant == 0) {
+        BRUSH_RASTER_LAUNCH(false, 4, true);
+    } else if (variant == 2) {
+        BRUSH_RASTER_LAUNCH(false, 5, false);
+    } else if (variant == 3) {
+        BRUSH_RASTER_LAUNCH(false, 6, true);
+    } else {
+        BRUSH_RASTER_LAUNCH(false, 5, true);
+    }
+#undef BRUSH_RASTER_LAUNCH
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -390,7 +431,8 @@ __device__ __forceinline__ void flush_rows(uint32_t dummy_addr, uint32_t pair_ad
     __syncwarp();
 }
 
-__global__ void __launch_bounds__(TILE_SIZE, 3)
+template <int MIN_CTAS>
+__global__ void __launch_bounds__(TILE_SIZE, MIN_CTAS)
 rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ compact_gid_from_isect,
                           const uint32_t* __restrict__ tile_bins, const float* __restrict__ projected,
                           const uint32_t* __restrict__ global_from_compact,
@@ -413,7 +455,10 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
 
     const uint2 range = __ldg(reinterpret_cast<const uint2*>(tile_bins) + tile_id);
     if (range.y <= range.x) return;
-    if (tid == 0) init_dummy_slot(sbase);
+    if (tid == 0) {
+        check_list_window(sbase);
+        init_dummy_slot(sbase);
+    }
 
     float T_final = 1.0f;
     float4 v_out = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -459,8 +504,8 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
                 k = 0;
             }
             if (end) break;
-            const uint4 a4 = lds128u(list_addr + 4u * i);
-            const uint32_t aa[BW_GROUP] = {a4.x, a4.y, a4.z, a4.w};
+            uint32_t aa[BW_GROUP];
+            list_load4(list_addr + 2u * i, sbase, aa);
             bool act[BW_GROUP];
             float alpha[BW_GROUP], ra[BW_GROUP], visra[BW_GROUP];
             // geometry of the four splats: independent of the running state, so the four chains overlap
@@ -502,16 +547,26 @@ void launch_rasterize_backward(const Cam& cam, const uint32_t* compact_gid_from_
                                const float* v_out_img, float* v_projected, cudaStream_t st) {
     const uint32_t tiles = cam.tiles_x * cam.tiles_y;
     if (tiles == 0) return;
+    // A/B switch while the variants are being measured: BRUSH_RASTER_BWD = 3 (80 registers, 3 CTAs/SM) or
+    // 4 (64 registers, 4 CTAs/SM; the 16-bit survivor lists are what makes the fourth CTA's shared memory fit)
+    const char* env = getenv("BRUSH_RASTER_BWD");
+    const int variant = env ? atoi(env) : 4;
+    static_assert(4 * (BW_BYTES + 1024) <= 228 * 1024, "four backward CTAs must fit in one SM's shared memory");
     static uint64_t configured_devices = 0;  // the opt-in to > 48 KB of shared memory is per device
     int dev = 0;
     cudaGetDevice(&dev);
     if (!(configured_devices >> dev & 1ull)) {
-        cudaFuncSetAttribute(rasterize_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BW_BYTES);
+        cudaFuncSetAttribute(rasterize_backward_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BW_BYTES);
+        cudaFuncSetAttribute(rasterize_backward_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BW_BYTES);
         configured_devices |= 1ull << dev;
     }
     g_launch_count++;
-    rasterize_backward_kernel<<<tiles, TILE_SIZE, BW_BYTES, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
-                                                                 global_from_compact, final_index, out_img, v_out_img, v_projected);
+    if (variant == 3)
+        rasterize_backward_kernel<3><<<tiles, TILE_SIZE, BW_BYTES, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
+                                                                        global_from_compact, final_index, out_img, v_out_img, v_projected);
+    else
+        rasterize_backward_kernel<4><<<tiles, TILE_SIZE, BW_BYTES, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
+                                                                        global_from_compact, final_index, out_img, v_out_img, v_projected);
 }
 
 }  // namespace brush
