@@ -102,6 +102,11 @@ __device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v) {
 __device__ __forceinline__ void sts_u16(uint32_t a, uint32_t v) {
     asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"((unsigned short)v) : "memory");
 }
+__device__ __forceinline__ uint32_t lds_u16(uint32_t a) {
+    unsigned short v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a));
+    return v;
+}
 __device__ __forceinline__ uint2 lds64u(uint32_t a) {
     uint2 v;
     asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a));
@@ -311,24 +316,23 @@ void launch_rasterize(const Cam& cam, const uint32_t* compact_gid_from_isect, co
     if (cam.tiles_x == 0 || cam.tiles_y == 0) return;
     dim3 grid(cam.tiles_x, cam.tiles_y);
     g_launch_count++;
-    // A/B switch while the variants are being measured: BRUSH_RASTER_FWD = 0 (4 CTAs/SM, vote-skip),
-    // 1 (5 CTAs/SM, vote-skip), 2 (5 CTAs/SM, no vote-skip),
-    // 3 (6 CTAs/SM, vote-skip)
+    // A/B switch while the variants are being measured: BRUSH_RASTER_FWD = 10 * (CTAs per SM: 4, 5, 6) + vote-skip
     const char* env = getenv("BRUSH_RASTER_FWD");  // read per launch so that one process can compare them
-    const int variant = env ? atoi(env) : 1;
+    const int variant = env ? atoi(env) : 50;
 #define BRUSH_RASTER_LAUNCH(U32, CTAS, VOTE)                                                                  \
     rasterize_kernel<U32, CTAS, VOTE><<<grid, TILE_SIZE, 0, st>>>(cam, compact_gid_from_isect, tile_bins, projected, \
                                                                   out_img, final_index)
     if (raster_u32) {
-        BRUSH_RASTER_LAUNCH(true, 5, true);
-    } else if (variant == 0) {
-        BRUSH_RASTER_LAUNCH(false, 4, true);
-    } else if (variant == 2) {
-        BRUSH_RASTER_LAUNCH(false, 5, false);
-    } else if (variant == 3) {
-        BRUSH_RASTER_LAUNCH(false, 6, true);
+        BRUSH_RASTER_LAUNCH(true, 5, false);
     } else {
-        BRUSH_RASTER_LAUNCH(false, 5, true);
+        switch (variant) {
+            case 40: BRUSH_RASTER_LAUNCH(false, 4, false); break;
+            case 41: BRUSH_RASTER_LAUNCH(false, 4, true); break;
+            case 51: BRUSH_RASTER_LAUNCH(false, 5, true); break;
+            case 60: BRUSH_RASTER_LAUNCH(false, 6, false); break;
+            case 61: BRUSH_RASTER_LAUNCH(false, 6, true); break;
+            default: BRUSH_RASTER_LAUNCH(false, 5, false); break;
+        }
     }
 #undef BRUSH_RASTER_LAUNCH
 }
@@ -368,13 +372,17 @@ __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, 
 // Phase 2 for the first k (<= 16) rows of the warp's pair tile: lane l and lane l+16 share row l, the low lane
 // sums pixel rows 0-1 of the 8x4 block, the high lane rows 2-3; one xor-16 exchange completes the nine sums.
 // (bx, by) = pixel-centre coordinates of the warp's first pixel.
+template <bool FROM_LIST>
 __device__ __forceinline__ void flush_rows(uint32_t dummy_addr, uint32_t pair_addr, uint32_t pix_addr,
                                            uint32_t chunk_addr, uint32_t lane, uint32_t k, float bx, float by,
                                            float* __restrict__ v_projected) {
     __syncwarp();
     const uint32_t r_idx = lane & 15u, half = lane >> 4;
-    const bool valid = r_idx < k;
-    const uint32_t a = valid ? lds_u32(chunk_addr + 4u * r_idx) : dummy_addr;
+    bool valid = r_idx < k;
+    // FROM_LIST: row r belongs to entry r of the survivor list at chunk_addr (16-bit halves, see list_load4)
+    const uint32_t a = !valid ? dummy_addr
+                              : FROM_LIST ? __byte_perm(lds_u16(chunk_addr + 2u * r_idx), dummy_addr, 0x7610)
+                                          : lds_u32(chunk_addr + 4u * r_idx);
     const float4 g0 = lds128(a + SM_G0);  // x, y, A, B
     const float4 g1 = lds128(a + SM_G1);  // C, L, opacity, compact gid
     const uint32_t row = pair_addr + r_idx * BW_ROW + half * 128u;
@@ -416,6 +424,8 @@ __device__ __forceinline__ void flush_rows(uint32_t dummy_addr, uint32_t pair_ad
     s0 += __shfl_xor_sync(F, s0, 16); sx += __shfl_xor_sync(F, sx, 16); sy += __shfl_xor_sync(F, sy, 16);
     sxx += __shfl_xor_sync(F, sxx, 16); sxy += __shfl_xor_sync(F, sxy, 16); syy += __shfl_xor_sync(F, syy, 16);
     r += __shfl_xor_sync(F, r, 16); g += __shfl_xor_sync(F, g, 16); b += __shfl_xor_sync(F, b, 16);
+    // rows without a single active pixel (every entry is an exact zero) add nothing; NaNs still propagate
+    if (FROM_LIST) valid = valid && !(fabsf(s0) + fabsf(sxx) + fabsf(syy) + fabsf(r) + fabsf(g) + fabsf(b) == 0.0f);
     if (valid) {
         // v_sigma = -opac*va; conic = -ln2 * (2A, B, 2C) in log2 form
         const float opac = g1.z, w = LN2 * opac;
@@ -431,7 +441,10 @@ __device__ __forceinline__ void flush_rows(uint32_t dummy_addr, uint32_t pair_ad
     __syncwarp();
 }
 
-template <int MIN_CTAS>
+#ifdef BRUSH_DBG_COUNT
+__device__ unsigned long long g_dbg[4];
+#endif
+template <int MIN_CTAS, bool ALWAYS_ROW>
 __global__ void __launch_bounds__(TILE_SIZE, MIN_CTAS)
 rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ compact_gid_from_isect,
                           const uint32_t* __restrict__ tile_bins, const float* __restrict__ projected,
@@ -496,11 +509,54 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
         const uint32_t a_lo = !inside ? 0xffffffffu
                                       : sbase + (batch_end - 1u > final_isect ? (batch_end - 1u - final_isect) * 16u : 0u);
         const uint32_t n_list = cull_to_list(sbase, list_addr, lane, warp, t_lo_warp, remaining);
+#ifdef BRUSH_DBG_COUNT
+        if (lane == 0) atomicAdd(&g_dbg[0], (unsigned long long)n_list);
+#endif
+        if (ALWAYS_ROW) {
+            // Every survivor takes a row, active pixels or not (96% have some: the cull is exact per block), so
+            // rows sit at compile-time offsets, the row -> splat map is the list itself and the four groups of a
+            // round of 16 carry no votes or branches; a row of zeros is dropped by the flush.
+            for (uint32_t g = 0; g < n_list; g += BW_ROWS) {
+#pragma unroll
+                for (uint32_t u = 0; u < BW_ROWS / BW_GROUP; u++) {
+                    if (g + BW_GROUP * u >= n_list) break;
+                    uint32_t aa[BW_GROUP];
+                    list_load4(list_addr + 2u * (g + BW_GROUP * u), sbase, aa);
+                    float alpha[BW_GROUP], ra[BW_GROUP], visra[BW_GROUP];
+#pragma unroll
+                    for (int j = 0; j < (int)BW_GROUP; j++) {
+                        const float4 g0 = lds128(aa[j] + SM_G0);
+                        const float4 g1 = lds128(aa[j] + SM_G1);
+                        const float dx = g0.x - pcx, dy = g0.y - pcy;
+                        const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);
+                        const float q = sp + g1.y;
+                        const bool act = aa[j] >= a_lo && sp <= 0.0f && q >= LOG2_INV255;
+                        const float vis = act ? ex2_approx(sp) : 0.0f;
+                        alpha[j] = fminf(0.99f, g1.z * vis);
+                        ra[j] = rcp_approx(1.0f - alpha[j]);
+                        visra[j] = vis * ra[j];
+                    }
+#pragma unroll
+                    for (int j = 0; j < (int)BW_GROUP; j++) {
+                        const float4 c = lds128(aa[j] + SM_COL);
+                        const float uu = fmaf(c.z, v_out.z, fmaf(c.y, v_out.y, c.x * v_out.x));
+                        const float va = visra[j] * fmaf(uu, T, D);
+                        T *= ra[j];
+                        const float fac = alpha[j] * T;
+                        D = fmaf(-fac, uu, D);
+                        sts64(pair_addr + (BW_GROUP * u + (uint32_t)j) * BW_ROW + lane * 8u, va, fac);
+                    }
+                }
+                flush_rows<true>(sbase + TILE_SIZE * 16u, pair_addr, pix_addr, list_addr + 2u * g, lane,
+                                 min(BW_ROWS, n_list - g), rx0, ry0, v_projected);
+            }
+            continue;
+        }
         uint32_t k = 0;  // rows of the pair tile in use (warp-uniform); flushed before the batch buffer is reused
         for (uint32_t i = 0;; i += BW_GROUP) {
             const bool end = i >= n_list;
             if (k > BW_ROWS - BW_GROUP || (end && k != 0u)) {
-                flush_rows(sbase + TILE_SIZE * 16u, pair_addr, pix_addr, chunk_addr, lane, k, rx0, ry0, v_projected);
+                flush_rows<false>(sbase + TILE_SIZE * 16u, pair_addr, pix_addr, chunk_addr, lane, k, rx0, ry0, v_projected);
                 k = 0;
             }
             if (end) break;
@@ -525,6 +581,12 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
             }
 #pragma unroll
             for (int j = 0; j < (int)BW_GROUP; j++) {
+#ifdef BRUSH_DBG_COUNT
+                {
+                    const uint32_t bal = __ballot_sync(0xffffffffu, act[j]);
+                    if (lane == 0) { atomicAdd(&g_dbg[2], (unsigned long long)__popc(bal)); if (bal) atomicAdd(&g_dbg[1], 1ull); }
+                }
+#endif
                 if (__any_sync(0xffffffffu, act[j])) {
                     const float4 c = lds128(aa[j] + SM_COL);
                     const float u = fmaf(c.z, v_out.z, fmaf(c.y, v_out.y, c.x * v_out.x));
@@ -547,26 +609,40 @@ void launch_rasterize_backward(const Cam& cam, const uint32_t* compact_gid_from_
                                const float* v_out_img, float* v_projected, cudaStream_t st) {
     const uint32_t tiles = cam.tiles_x * cam.tiles_y;
     if (tiles == 0) return;
-    // A/B switch while the variants are being measured: BRUSH_RASTER_BWD = 3 (80 registers, 3 CTAs/SM) or
-    // 4 (64 registers, 4 CTAs/SM; the 16-bit survivor lists are what makes the fourth CTA's shared memory fit)
+    // A/B switch while the variants are being measured: BRUSH_RASTER_BWD = 10 * (CTAs per SM) + always-row
     const char* env = getenv("BRUSH_RASTER_BWD");
-    const int variant = env ? atoi(env) : 4;
+    const int variant = env ? atoi(env) : 31;
     static_assert(4 * (BW_BYTES + 1024) <= 228 * 1024, "four backward CTAs must fit in one SM's shared memory");
     static uint64_t configured_devices = 0;  // the opt-in to > 48 KB of shared memory is per device
     int dev = 0;
     cudaGetDevice(&dev);
     if (!(configured_devices >> dev & 1ull)) {
-        cudaFuncSetAttribute(rasterize_backward_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BW_BYTES);
-        cudaFuncSetAttribute(rasterize_backward_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BW_BYTES);
+        cudaFuncSetAttribute(rasterize_backward_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BW_BYTES);
+        cudaFuncSetAttribute(rasterize_backward_kernel<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BW_BYTES);
+        cudaFuncSetAttribute(rasterize_backward_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BW_BYTES);
         configured_devices |= 1ull << dev;
     }
     g_launch_count++;
-    if (variant == 3)
-        rasterize_backward_kernel<3><<<tiles, TILE_SIZE, BW_BYTES, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
-                                                                        global_from_compact, final_index, out_img, v_out_img, v_projected);
-    else
-        rasterize_backward_kernel<4><<<tiles, TILE_SIZE, BW_BYTES, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
-                                                                        global_from_compact, final_index, out_img, v_out_img, v_projected);
+#define BRUSH_BWD_LAUNCH(CTAS, ROW)                                                                                    \
+    rasterize_backward_kernel<CTAS, ROW><<<tiles, TILE_SIZE, BW_BYTES, st>>>(cam, compact_gid_from_isect, tile_bins, projected, \
+                                                                             global_from_compact, final_index, out_img, v_out_img, v_projected)
+    switch (variant) {
+        case 30: BRUSH_BWD_LAUNCH(3, false); break;
+        case 41: BRUSH_BWD_LAUNCH(4, true); break;
+        default: BRUSH_BWD_LAUNCH(3, true); break;
+    }
+#undef BRUSH_BWD_LAUNCH
 }
 
 }  // namespace brush
+
+#ifdef BRUSH_DBG_COUNT
+extern "C" __attribute__((visibility("default"))) void brush_debug_counters(unsigned long long* out4, int reset) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out4, brush::g_dbg, 32);
+    if (reset) {
+        unsigned long long z[4] = {0, 0, 0, 0};
+        cudaMemcpyToSymbol(brush::g_dbg, z, 32);
+    }
+}
+#endif

@@ -43,7 +43,7 @@ for _ in range(10):
     step()
 ctx.sync_check()
 results = []
-combos = [(0, 3), (1, 3), (3, 3), (2, 3), (1, 4), (3, 4), (0, 3), (3, 4)]
+combos = [tuple(int(x) for x in c.split(":")) for c in os.environ.get("AB_COMBOS", "50:3").split(",")]
 for fwd, bwd in combos:
     os.environ["BRUSH_RASTER_FWD"], os.environ["BRUSH_RASTER_BWD"] = str(fwd), str(bwd)
     for _ in range(3):
@@ -67,3 +67,14 @@ for fwd, bwd in combos:
          "Rasterize": round(acc["Rasterize"], 4), "RasterizeBackwards": round(acc["RasterizeBackwards"], 4)}
     print(json.dumps(r), flush=True)
     results.append(r)
+
+if os.environ.get("BRUSH_DBG"):
+    import ctypes as C
+    from brush_b200 import _lib
+    L = C.CDLL(_lib.SO_PATH)
+    out = (C.c_ulonglong * 4)()
+    L.brush_debug_counters(out, 1)
+    st = step()
+    L.brush_debug_counters(out, 1)
+    print("dbg: survivors", out[0], "rows", out[1], "active pairs", out[2], "rows/survivors", out[1] / max(out[0], 1),
+          "active lanes per row", out[2] / max(out[1], 1))
