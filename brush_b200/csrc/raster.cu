@@ -63,6 +63,9 @@ constexpr uint32_t SM_LIST = SM_COL + 16 * SM_SLOTS;  // u16[8][260]: per warp, 
 constexpr uint32_t LIST_PAD = 4;                      // lists are padded with the dummy slot to a multiple of 4
 constexpr uint32_t LIST_STRIDE = 2 * (TILE_SIZE + LIST_PAD);
 constexpr uint32_t SM_BYTES = SM_LIST + LIST_STRIDE * (TILE_SIZE / 32);
+// The forward has shared memory to spare and keeps full 32-bit entries (no PRMT per entry).
+constexpr uint32_t LIST_STRIDE32 = 4 * (TILE_SIZE + LIST_PAD);
+constexpr uint32_t SM_BYTES_FWD = SM_LIST + LIST_STRIDE32 * (TILE_SIZE / 32);
 
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
@@ -199,6 +202,7 @@ __device__ __forceinline__ void stage_splat(uint32_t sbase, uint32_t slot, const
 // addresses of the survivors' G0 entries are appended, in depth order, to the warp's list, which is then padded
 // with the dummy slot to a multiple of LIST_PAD.  Returns the list length (without padding).
 // Only slots in [t_lo, t_max) take part.
+template <bool LIST16>
 __device__ __forceinline__ uint32_t cull_to_list(uint32_t sbase, uint32_t list_addr, uint32_t lane, uint32_t warp,
                                                  uint32_t t_lo, uint32_t t_max) {
     uint32_t n_list = 0;
@@ -207,10 +211,17 @@ __device__ __forceinline__ uint32_t cull_to_list(uint32_t sbase, uint32_t list_a
         bool hit = false;
         if (mine >= t_lo && mine < t_max) hit = (lds_u32(sbase + SM_COL + mine * 16u + 12u) >> warp) & 1u;
         const uint32_t mask = __ballot_sync(0xffffffffu, hit);
-        if (hit) sts_u16(list_addr + 2u * (n_list + __popc(mask & ((1u << lane) - 1u))), sbase + mine * 16u);
+        if (hit) {
+            const uint32_t pos = n_list + __popc(mask & ((1u << lane) - 1u));
+            if (LIST16) sts_u16(list_addr + 2u * pos, sbase + mine * 16u);
+            else sts_u32(list_addr + 4u * pos, sbase + mine * 16u);
+        }
         n_list += __popc(mask);
     }
-    if (lane < LIST_PAD) sts_u16(list_addr + 2u * (n_list + lane), sbase + TILE_SIZE * 16u);
+    if (lane < LIST_PAD) {
+        if (LIST16) sts_u16(list_addr + 2u * (n_list + lane), sbase + TILE_SIZE * 16u);
+        else sts_u32(list_addr + 4u * (n_list + lane), sbase + TILE_SIZE * 16u);
+    }
     __syncwarp();
     return n_list;
 }
@@ -220,10 +231,10 @@ __global__ void __launch_bounds__(TILE_SIZE, MIN_CTAS)
 rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ compact_gid_from_isect,
                  const uint32_t* __restrict__ tile_bins, const float* __restrict__ projected,
                  void* __restrict__ out_img, uint32_t* __restrict__ final_index) {
-    __shared__ __align__(16) unsigned char smem[SM_BYTES];
+    __shared__ __align__(16) unsigned char smem[SM_BYTES_FWD];
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(smem);
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-    const uint32_t list_addr = sbase + SM_LIST + warp * LIST_STRIDE;
+    const uint32_t list_addr = sbase + SM_LIST + warp * LIST_STRIDE32;
     const uint32_t tile_id = blockIdx.x + blockIdx.y * cam.tiles_x;
     const uint32_t bx0 = blockIdx.x * TILE_WIDTH + (warp & 1u) * 8u, by0 = blockIdx.y * TILE_WIDTH + (warp >> 1) * 4u;
     const uint32_t px = bx0 + (lane & 7u), py = by0 + (lane >> 3);
@@ -238,10 +249,7 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
     float T = inside ? 1.0f : -1.0f;
     float pr = 0.f, pg = 0.f, pb = 0.f;
     uint32_t final_idx = 0;
-    if (tid == 0) {
-        check_list_window(sbase);
-        init_dummy_slot(sbase);
-    }
+    if (tid == 0) init_dummy_slot(sbase);
 
     for (uint32_t b = 0; b < num_batches; b++) {
         // barrier before the batch buffer is overwritten + whole-tile early exit (the reference keeps
@@ -255,14 +263,14 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
         }
         __syncthreads();
         if (__all_sync(0xffffffffu, T <= 0.0f)) continue;
-        const uint32_t n_list = cull_to_list(sbase, list_addr, lane, warp, 0u, remaining);
+        const uint32_t n_list = cull_to_list<false>(sbase, list_addr, lane, warp, 0u, remaining);
         // Four survivors per iteration: their geometry (sp, q, alpha) is independent of the compositing state, so
         // the four chains overlap; the order-dependent part is then applied in depth order, predicated (no
         // divergent branch).  The list is padded with the dummy slot, which no pixel sees.
         uint32_t final_a = 0;
         for (uint32_t i = 0; i < n_list; i += LIST_PAD) {
-            uint32_t aa[4];
-            list_load4(list_addr + 2u * i, sbase, aa);
+            const uint4 a4 = lds128u(list_addr + 4u * i);
+            const uint32_t aa[4] = {a4.x, a4.y, a4.z, a4.w};
             bool act[4];
             float alpha[4];
 #pragma unroll
@@ -508,7 +516,7 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
         const uint32_t t_lo_warp = batch_end - 1u > warp_final ? batch_end - 1u - warp_final : 0u;
         const uint32_t a_lo = !inside ? 0xffffffffu
                                       : sbase + (batch_end - 1u > final_isect ? (batch_end - 1u - final_isect) * 16u : 0u);
-        const uint32_t n_list = cull_to_list(sbase, list_addr, lane, warp, t_lo_warp, remaining);
+        const uint32_t n_list = cull_to_list<true>(sbase, list_addr, lane, warp, t_lo_warp, remaining);
 #ifdef BRUSH_DBG_COUNT
         if (lane == 0) atomicAdd(&g_dbg[0], (unsigned long long)n_list);
 #endif
