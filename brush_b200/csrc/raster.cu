@@ -61,7 +61,8 @@ constexpr uint32_t SM_G1 = SM_G0 + 16 * SM_SLOTS;     // float4[257]: C, L, opac
 constexpr uint32_t SM_COL = SM_G1 + 16 * SM_SLOTS;    // float4[257]: r, g, b, mask of the 8x4 blocks the splat reaches
 constexpr uint32_t SM_LIST = SM_COL + 16 * SM_SLOTS;  // u16[8][260]: per warp, LOW HALVES of the shared-window addresses of the survivors' G0 entries
 constexpr uint32_t LIST_PAD = 4;                      // lists are padded with the dummy slot to a multiple of 4
-constexpr uint32_t LIST_STRIDE = 2 * (TILE_SIZE + LIST_PAD);
+constexpr uint32_t LIST_SLACK = 4;                    // entries past the padding that may be read (never used) by a load-ahead
+constexpr uint32_t LIST_STRIDE = 2 * (TILE_SIZE + LIST_PAD + LIST_SLACK);
 constexpr uint32_t SM_BYTES = SM_LIST + LIST_STRIDE * (TILE_SIZE / 32);
 // The forward has shared memory to spare and keeps full 32-bit entries (no PRMT per entry).
 constexpr uint32_t LIST_STRIDE32 = 4 * (TILE_SIZE + LIST_PAD);
@@ -84,6 +85,21 @@ __device__ __forceinline__ float rcp_approx(float x) {
 __device__ __forceinline__ float4 lds128(uint32_t a) {
     float4 v;
     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+    return v;
+}
+// Loads of data that does not change while a batch is processed (the staged splats, the survivor lists).  Not
+// volatile, so the compiler may hoist them over the stores of the pair tile and overlap them with the math of
+// the previous group; `token` is a value that only exists after the barrier / __syncwarp that published the
+// data (it differs from batch to batch), which keeps the loads below that point and stops values of different
+// batches from being merged.
+__device__ __forceinline__ float4 lds128_ro(uint32_t a, uint32_t token) {
+    float4 v;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4]; // %5" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a), "r"(token));
+    return v;
+}
+__device__ __forceinline__ uint2 lds64u_ro(uint32_t a, uint32_t token) {
+    uint2 v;
+    asm("ld.shared.v2.u32 {%0, %1}, [%2]; // %3" : "=r"(v.x), "=r"(v.y) : "r"(a), "r"(token));
     return v;
 }
 __device__ __forceinline__ uint32_t lds_u32(uint32_t a) {
@@ -119,8 +135,8 @@ __device__ __forceinline__ uint2 lds64u(uint32_t a) {
 // (half the shared memory of u32 entries: what lets a fourth backward CTA fit on an SM); the staged splats all
 // lie within one 64 KB window of the CTA's shared memory (checked once per CTA), so one PRMT per entry puts
 // the common upper half back.
-__device__ __forceinline__ void list_load4(uint32_t addr, uint32_t sbase, uint32_t (&aa)[4]) {
-    const uint2 l = lds64u(addr);
+__device__ __forceinline__ void list_load4(uint32_t addr, uint32_t sbase, uint32_t (&aa)[4], uint32_t token) {
+    const uint2 l = lds64u_ro(addr, token);
     aa[0] = __byte_perm(l.x, sbase, 0x7610);
     aa[1] = __byte_perm(l.x, sbase, 0x7632);
     aa[2] = __byte_perm(l.y, sbase, 0x7610);
@@ -226,7 +242,7 @@ __device__ __forceinline__ uint32_t cull_to_list(uint32_t sbase, uint32_t list_a
     return n_list;
 }
 
-template <bool RASTER_U32, int MIN_CTAS, bool VOTE_SKIP>
+template <bool RASTER_U32, int MIN_CTAS>
 __global__ void __launch_bounds__(TILE_SIZE, MIN_CTAS)
 rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ compact_gid_from_isect,
                  const uint32_t* __restrict__ tile_bins, const float* __restrict__ projected,
@@ -264,15 +280,25 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
         __syncthreads();
         if (__all_sync(0xffffffffu, T <= 0.0f)) continue;
         const uint32_t n_list = cull_to_list<false>(sbase, list_addr, lane, warp, 0u, remaining);
-        // Four survivors per iteration: their geometry (sp, q, alpha) is independent of the compositing state, so
-        // the four chains overlap; the order-dependent part is then applied in depth order, predicated (no
-        // divergent branch).  The list is padded with the dummy slot, which no pixel sees.
+        // Four survivors per iteration, composited OPTIMISTICALLY: a pixel stops at most once, so the group is
+        // first run without the stop logic -- alpha is zeroed for pairs that fail the visibility test or belong to
+        // a finished pixel, and the transmittance chain T0..T4 is formed unconditionally.  Only when some pixel
+        // of the warp would cross T <= 1e-4 inside the group (T4 tells: T never grows) is the group redone with
+        // the per-splat stop test (rasterize.wgsl: stop BEFORE adding the crossing splat).  The common path
+        // has no per-splat compare / select on the compositing state: the ALU pipe (compares, selects, min)
+        // was this kernel's limiter (ncu: 61% ALU at 78% issue).  Same arithmetic in both paths, so the result
+        // does not depend on which one ran.
         uint32_t final_a = 0;
         for (uint32_t i = 0; i < n_list; i += LIST_PAD) {
             const uint4 a4 = lds128u(list_addr + 4u * i);
             const uint32_t aa[4] = {a4.x, a4.y, a4.z, a4.w};
+            const bool live0 = T > 0.0f;
+            // a finished pixel sees nothing: its visibility threshold is +inf (one select per group instead of a
+            // third compare per pair)
+            const float q_min = live0 ? LOG2_INV255 : __int_as_float(0x7f800000);
             bool act[4];
-            float alpha[4];
+            float alpha[4], Tj[5];
+            Tj[0] = T;
 #pragma unroll
             for (int j = 0; j < 4; j++) {
                 const float4 g0 = lds128(aa[j] + SM_G0);
@@ -280,23 +306,33 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
                 const float dx = g0.x - pcx, dy = g0.y - pcy;
                 const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);  // -sigma * log2(e)
                 const float q = sp + g1.y;                                              // log2(opac * exp(-sigma))
-                act[j] = sp <= 0.0f && q >= LOG2_INV255;
-                alpha[j] = fminf(0.999f, ex2_approx(q));
+                act[j] = sp <= 0.0f && q >= q_min;
+                alpha[j] = act[j] ? fminf(0.999f, ex2_approx(q)) : 0.0f;
+                Tj[j + 1] = Tj[j] * (1.0f - alpha[j]);
+            }
+            if (!__any_sync(0xffffffffu, live0 && Tj[4] <= 1e-4f)) {
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const float4 c = lds128(aa[j] + SM_COL);
+                    const float fac = alpha[j] * Tj[j];
+                    pr = fmaf(c.x, fac, pr); pg = fmaf(c.y, fac, pg); pb = fmaf(c.z, fac, pb);
+                    final_a = act[j] ? aa[j] : final_a;
+                }
+                T = Tj[4];
+                continue;
             }
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
+            for (int j = 0; j < 4; j++) {  // some pixel finishes in this group (at most 32 times per warp and tile)
                 const bool live = act[j] && T > 0.0f;
-                if (!VOTE_SKIP || __any_sync(0xffffffffu, live)) {
-                    const float4 c = lds128(aa[j] + SM_COL);
-                    const float next_T = T * (1.0f - alpha[j]);
-                    const bool stop = live && next_T <= 1e-4f;  // rasterize.wgsl: stop BEFORE adding this splat
-                    const bool contrib = live && !(next_T <= 1e-4f);
-                    const float fac = contrib ? alpha[j] * T : 0.0f;
-                    pr = fmaf(c.x, fac, pr); pg = fmaf(c.y, fac, pg); pb = fmaf(c.z, fac, pb);
-                    T = contrib ? next_T : T;
-                    T = stop ? -T : T;
-                    final_a = contrib ? aa[j] : final_a;
-                }
+                const float4 c = lds128(aa[j] + SM_COL);
+                const float next_T = T * (1.0f - alpha[j]);
+                const bool stop = live && next_T <= 1e-4f;
+                const bool contrib = live && !(next_T <= 1e-4f);
+                const float fac = contrib ? alpha[j] * T : 0.0f;
+                pr = fmaf(c.x, fac, pr); pg = fmaf(c.y, fac, pg); pb = fmaf(c.z, fac, pb);
+                T = contrib ? next_T : T;
+                T = stop ? -T : T;
+                final_a = contrib ? aa[j] : final_a;
             }
             if (__all_sync(0xffffffffu, T <= 0.0f)) break;
         }
@@ -324,23 +360,18 @@ void launch_rasterize(const Cam& cam, const uint32_t* compact_gid_from_isect, co
     if (cam.tiles_x == 0 || cam.tiles_y == 0) return;
     dim3 grid(cam.tiles_x, cam.tiles_y);
     g_launch_count++;
-    // A/B switch while the variants are being measured: BRUSH_RASTER_FWD = 10 * (CTAs per SM: 4, 5, 6) + vote-skip
+    // A/B switch while the variants are being measured: BRUSH_RASTER_FWD = CTAs per SM (4, 5)
     const char* env = getenv("BRUSH_RASTER_FWD");  // read per launch so that one process can compare them
-    const int variant = env ? atoi(env) : 50;
-#define BRUSH_RASTER_LAUNCH(U32, CTAS, VOTE)                                                                  \
-    rasterize_kernel<U32, CTAS, VOTE><<<grid, TILE_SIZE, 0, st>>>(cam, compact_gid_from_isect, tile_bins, projected, \
-                                                                  out_img, final_index)
+    const int variant = env ? atoi(env) : 4;
+#define BRUSH_RASTER_LAUNCH(U32, CTAS)                                                                  \
+    rasterize_kernel<U32, CTAS><<<grid, TILE_SIZE, 0, st>>>(cam, compact_gid_from_isect, tile_bins, projected, \
+                                                            out_img, final_index)
     if (raster_u32) {
-        BRUSH_RASTER_LAUNCH(true, 5, false);
+        BRUSH_RASTER_LAUNCH(true, 4);
+    } else if (variant == 5) {
+        BRUSH_RASTER_LAUNCH(false, 5);
     } else {
-        switch (variant) {
-            case 40: BRUSH_RASTER_LAUNCH(false, 4, false); break;
-            case 41: BRUSH_RASTER_LAUNCH(false, 4, true); break;
-            case 51: BRUSH_RASTER_LAUNCH(false, 5, true); break;
-            case 60: BRUSH_RASTER_LAUNCH(false, 6, false); break;
-            case 61: BRUSH_RASTER_LAUNCH(false, 6, true); break;
-            default: BRUSH_RASTER_LAUNCH(false, 5, false); break;
-        }
+        BRUSH_RASTER_LAUNCH(false, 4);
     }
 #undef BRUSH_RASTER_LAUNCH
 }
@@ -520,21 +551,24 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
 #ifdef BRUSH_DBG_COUNT
         if (lane == 0) atomicAdd(&g_dbg[0], (unsigned long long)n_list);
 #endif
+        const uint32_t token = n_list ^ b;  // exists only after cull_to_list's __syncwarp (see lds128_ro)
         if (ALWAYS_ROW) {
             // Every survivor takes a row, active pixels or not (96% have some: the cull is exact per block), so
             // rows sit at compile-time offsets, the row -> splat map is the list itself and the four groups of a
             // round of 16 carry no votes or branches; a row of zeros is dropped by the flush.
+            uint32_t an[BW_GROUP];  // the next group's list entries, loaded one group ahead (the list is padded)
+            list_load4(list_addr, sbase, an, token);
             for (uint32_t g = 0; g < n_list; g += BW_ROWS) {
 #pragma unroll
                 for (uint32_t u = 0; u < BW_ROWS / BW_GROUP; u++) {
                     if (g + BW_GROUP * u >= n_list) break;
-                    uint32_t aa[BW_GROUP];
-                    list_load4(list_addr + 2u * (g + BW_GROUP * u), sbase, aa);
+                    const uint32_t aa[BW_GROUP] = {an[0], an[1], an[2], an[3]};
+                    list_load4(list_addr + 2u * (g + BW_GROUP * (u + 1u)), sbase, an, token);
                     float alpha[BW_GROUP], ra[BW_GROUP], visra[BW_GROUP];
 #pragma unroll
                     for (int j = 0; j < (int)BW_GROUP; j++) {
-                        const float4 g0 = lds128(aa[j] + SM_G0);
-                        const float4 g1 = lds128(aa[j] + SM_G1);
+                        const float4 g0 = lds128_ro(aa[j] + SM_G0, token);
+                        const float4 g1 = lds128_ro(aa[j] + SM_G1, token);
                         const float dx = g0.x - pcx, dy = g0.y - pcy;
                         const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);
                         const float q = sp + g1.y;
@@ -546,7 +580,7 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
                     }
 #pragma unroll
                     for (int j = 0; j < (int)BW_GROUP; j++) {
-                        const float4 c = lds128(aa[j] + SM_COL);
+                        const float4 c = lds128_ro(aa[j] + SM_COL, token);
                         const float uu = fmaf(c.z, v_out.z, fmaf(c.y, v_out.y, c.x * v_out.x));
                         const float va = visra[j] * fmaf(uu, T, D);
                         T *= ra[j];
@@ -569,7 +603,7 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
             }
             if (end) break;
             uint32_t aa[BW_GROUP];
-            list_load4(list_addr + 2u * i, sbase, aa);
+            list_load4(list_addr + 2u * i, sbase, aa, token);
             bool act[BW_GROUP];
             float alpha[BW_GROUP], ra[BW_GROUP], visra[BW_GROUP];
             // geometry of the four splats: independent of the running state, so the four chains overlap
