@@ -126,11 +126,6 @@ __device__ __forceinline__ uint32_t lds_u16(uint32_t a) {
     asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a));
     return v;
 }
-__device__ __forceinline__ uint2 lds64u(uint32_t a) {
-    uint2 v;
-    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a));
-    return v;
-}
 // Four consecutive entries of a survivor list -> full shared-window addresses.  The lists hold 16-bit halves
 // (half the shared memory of u32 entries: what lets a fourth backward CTA fit on an SM); the staged splats all
 // lie within one 64 KB window of the CTA's shared memory (checked once per CTA), so one PRMT per entry puts
@@ -242,8 +237,8 @@ __device__ __forceinline__ uint32_t cull_to_list(uint32_t sbase, uint32_t list_a
     return n_list;
 }
 
-template <bool RASTER_U32, int MIN_CTAS>
-__global__ void __launch_bounds__(TILE_SIZE, MIN_CTAS)
+template <bool RASTER_U32>
+__global__ void __launch_bounds__(TILE_SIZE, 5)  // 48 registers: five CTAs per SM (measured best of 4 / 5 / 6)
 rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ compact_gid_from_isect,
                  const uint32_t* __restrict__ tile_bins, const float* __restrict__ projected,
                  void* __restrict__ out_img, uint32_t* __restrict__ final_index) {
@@ -360,20 +355,12 @@ void launch_rasterize(const Cam& cam, const uint32_t* compact_gid_from_isect, co
     if (cam.tiles_x == 0 || cam.tiles_y == 0) return;
     dim3 grid(cam.tiles_x, cam.tiles_y);
     g_launch_count++;
-    // A/B switch while the variants are being measured: BRUSH_RASTER_FWD = CTAs per SM (4, 5)
-    const char* env = getenv("BRUSH_RASTER_FWD");  // read per launch so that one process can compare them
-    const int variant = env ? atoi(env) : 4;
-#define BRUSH_RASTER_LAUNCH(U32, CTAS)                                                                  \
-    rasterize_kernel<U32, CTAS><<<grid, TILE_SIZE, 0, st>>>(cam, compact_gid_from_isect, tile_bins, projected, \
-                                                            out_img, final_index)
-    if (raster_u32) {
-        BRUSH_RASTER_LAUNCH(true, 4);
-    } else if (variant == 5) {
-        BRUSH_RASTER_LAUNCH(false, 5);
-    } else {
-        BRUSH_RASTER_LAUNCH(false, 4);
-    }
-#undef BRUSH_RASTER_LAUNCH
+    if (raster_u32)
+        rasterize_kernel<true><<<grid, TILE_SIZE, 0, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
+                                                           out_img, final_index);
+    else
+        rasterize_kernel<false><<<grid, TILE_SIZE, 0, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
+                                                            out_img, final_index);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -383,22 +370,24 @@ void launch_rasterize(const Cam& cam, const uint32_t* compact_gid_from_isect, co
 // butterfly per step makes this kernel issue-bound (ncu, profiles/r1a: ~107 of ~130 instructions per step
 // were reduction and gradient math on half-empty warps), so the work is split in two phases:
 //
-//  phase 1 (lane = pixel): walk the warp's survivor list in depth order; per (pixel, splat) pair keep only
-//      the two scalars that depend on the compositing order, va = vis * v_alpha and fac = alpha * T, in a
-//      per-warp shared-memory tile [32 splats][32 pixels]; splats with no active pixel take no row.
-//  phase 2 (lane = splat): each lane owns one row and accumulates, in registers and without any
-//      cross-lane traffic, the moments of va about its splat centre (1, dx, dy, dx^2, dx dy, dy^2) and
-//      fac * v_out.rgb over the 32 pixels; the nine gradient terms are linear in those sums
-//      (v_sigma = -opac * va).  Each lane then issues two red.global.add.v4.f32 and one scalar red for its
-//      own splat -- the native replacement for the reference's CAS loops.
+//  phase 1 (lane = pixel): walk the warp's survivor list in depth order, 16 survivors per round in four groups of
+//      four; per (pixel, splat) pair keep only the two scalars that depend on the compositing order,
+//      va = vis * v_alpha and fac = alpha * T, in a per-warp shared-memory tile [16 splats][32 pixels].  EVERY
+//      survivor takes a row, active pixels or not (measured: 96% have some, the cull is exact per block), so the
+//      rows sit at compile-time offsets, the row -> splat map is the list itself and a group carries no vote,
+//      branch or address arithmetic (0.775 -> 0.714 ms against rows handed out on demand).
+//  phase 2 (lane = half a splat row): accumulates, in registers and without any cross-lane traffic, the
+//      moments of va about the splat centre (1, dx, dy, dx^2, dx dy, dy^2) and fac * v_out.rgb over its 16
+//      pixels; the nine gradient terms are linear in those sums (v_sigma = -opac * va).  One xor-16 exchange,
+//      then two red.global.add.v4.f32 and one scalar red per row -- the native replacement for the reference's
+//      CAS loops; a row of zeros is dropped.
 constexpr uint32_t BW_ROW = 32u * 8u + 16u;  // one row: 32 x (va, fac) + pad => conflict-free LDS.128 at lane stride
 constexpr uint32_t BW_ROWS = 16;             // rows per warp; phase 2 gives each row to two lanes (16 pixels each)
 constexpr uint32_t BW_GROUP = 4;             // survivors examined per phase-1 iteration (independent geometry => ILP)
 constexpr uint32_t BW_PAIR = SM_BYTES;
 constexpr uint32_t BW_PAIR_WARP = BW_ROWS * BW_ROW;
 constexpr uint32_t BW_PIX = BW_PAIR + (TILE_SIZE / 32u) * BW_PAIR_WARP;  // per warp float4[32]: v_out of its pixels
-constexpr uint32_t BW_CHUNK = BW_PIX + (TILE_SIZE / 32u) * 512u;         // per warp u32[BW_ROWS]: G0 address of each row's splat
-constexpr uint32_t BW_BYTES = BW_CHUNK + (TILE_SIZE / 32u) * 4u * BW_ROWS;
+constexpr uint32_t BW_BYTES = BW_PIX + (TILE_SIZE / 32u) * 512u;
 
 __device__ __forceinline__ void sts64(uint32_t a, float x, float y) {
     asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(a), "f"(x), "f"(y) : "memory");
@@ -411,17 +400,14 @@ __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, 
 // Phase 2 for the first k (<= 16) rows of the warp's pair tile: lane l and lane l+16 share row l, the low lane
 // sums pixel rows 0-1 of the 8x4 block, the high lane rows 2-3; one xor-16 exchange completes the nine sums.
 // (bx, by) = pixel-centre coordinates of the warp's first pixel.
-template <bool FROM_LIST>
+// Row r belongs to entry r of the survivor list at `entries` (16-bit halves, see list_load4).
 __device__ __forceinline__ void flush_rows(uint32_t dummy_addr, uint32_t pair_addr, uint32_t pix_addr,
-                                           uint32_t chunk_addr, uint32_t lane, uint32_t k, float bx, float by,
+                                           uint32_t entries, uint32_t lane, uint32_t k, float bx, float by,
                                            float* __restrict__ v_projected) {
     __syncwarp();
     const uint32_t r_idx = lane & 15u, half = lane >> 4;
     bool valid = r_idx < k;
-    // FROM_LIST: row r belongs to entry r of the survivor list at chunk_addr (16-bit halves, see list_load4)
-    const uint32_t a = !valid ? dummy_addr
-                              : FROM_LIST ? __byte_perm(lds_u16(chunk_addr + 2u * r_idx), dummy_addr, 0x7610)
-                                          : lds_u32(chunk_addr + 4u * r_idx);
+    const uint32_t a = !valid ? dummy_addr : __byte_perm(lds_u16(entries + 2u * r_idx), dummy_addr, 0x7610);
     const float4 g0 = lds128(a + SM_G0);  // x, y, A, B
     const float4 g1 = lds128(a + SM_G1);  // C, L, opacity, compact gid
     const uint32_t row = pair_addr + r_idx * BW_ROW + half * 128u;
@@ -464,7 +450,7 @@ __device__ __forceinline__ void flush_rows(uint32_t dummy_addr, uint32_t pair_ad
     sxx += __shfl_xor_sync(F, sxx, 16); sxy += __shfl_xor_sync(F, sxy, 16); syy += __shfl_xor_sync(F, syy, 16);
     r += __shfl_xor_sync(F, r, 16); g += __shfl_xor_sync(F, g, 16); b += __shfl_xor_sync(F, b, 16);
     // rows without a single active pixel (every entry is an exact zero) add nothing; NaNs still propagate
-    if (FROM_LIST) valid = valid && !(fabsf(s0) + fabsf(sxx) + fabsf(syy) + fabsf(r) + fabsf(g) + fabsf(b) == 0.0f);
+    valid = valid && !(fabsf(s0) + fabsf(sxx) + fabsf(syy) + fabsf(r) + fabsf(g) + fabsf(b) == 0.0f);
     if (valid) {
         // v_sigma = -opac*va; conic = -ln2 * (2A, B, 2C) in log2 form
         const float opac = g1.z, w = LN2 * opac;
@@ -480,11 +466,7 @@ __device__ __forceinline__ void flush_rows(uint32_t dummy_addr, uint32_t pair_ad
     __syncwarp();
 }
 
-#ifdef BRUSH_DBG_COUNT
-__device__ unsigned long long g_dbg[4];
-#endif
-template <int MIN_CTAS, bool ALWAYS_ROW>
-__global__ void __launch_bounds__(TILE_SIZE, MIN_CTAS)
+__global__ void __launch_bounds__(TILE_SIZE, 3)  // 80 registers; a fourth CTA at 64 registers measured 4% slower
 rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ compact_gid_from_isect,
                           const uint32_t* __restrict__ tile_bins, const float* __restrict__ projected,
                           const uint32_t* __restrict__ global_from_compact,
@@ -496,7 +478,6 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
     const uint32_t list_addr = sbase + SM_LIST + warp * LIST_STRIDE;
     const uint32_t pair_addr = sbase + BW_PAIR + warp * BW_PAIR_WARP;
     const uint32_t pix_addr = sbase + BW_PIX + warp * 512u;
-    const uint32_t chunk_addr = sbase + BW_CHUNK + warp * (4u * BW_ROWS);
     const uint32_t tile_id = blockIdx.x;
     const uint32_t tile_x = tile_id % cam.tiles_x, tile_y = tile_id / cam.tiles_x;
     const uint32_t bx0 = tile_x * TILE_WIDTH + (warp & 1u) * 8u, by0 = tile_y * TILE_WIDTH + (warp >> 1) * 4u;
@@ -548,99 +529,43 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
         const uint32_t a_lo = !inside ? 0xffffffffu
                                       : sbase + (batch_end - 1u > final_isect ? (batch_end - 1u - final_isect) * 16u : 0u);
         const uint32_t n_list = cull_to_list<true>(sbase, list_addr, lane, warp, t_lo_warp, remaining);
-#ifdef BRUSH_DBG_COUNT
-        if (lane == 0) atomicAdd(&g_dbg[0], (unsigned long long)n_list);
-#endif
         const uint32_t token = n_list ^ b;  // exists only after cull_to_list's __syncwarp (see lds128_ro)
-        if (ALWAYS_ROW) {
-            // Every survivor takes a row, active pixels or not (96% have some: the cull is exact per block), so
-            // rows sit at compile-time offsets, the row -> splat map is the list itself and the four groups of a
-            // round of 16 carry no votes or branches; a row of zeros is dropped by the flush.
-            uint32_t an[BW_GROUP];  // the next group's list entries, loaded one group ahead (the list is padded)
-            list_load4(list_addr, sbase, an, token);
-            for (uint32_t g = 0; g < n_list; g += BW_ROWS) {
+        uint32_t an[BW_GROUP];  // the next group's list entries, loaded one group ahead (the list is padded)
+        list_load4(list_addr, sbase, an, token);
+        for (uint32_t g = 0; g < n_list; g += BW_ROWS) {
 #pragma unroll
-                for (uint32_t u = 0; u < BW_ROWS / BW_GROUP; u++) {
-                    if (g + BW_GROUP * u >= n_list) break;
-                    const uint32_t aa[BW_GROUP] = {an[0], an[1], an[2], an[3]};
-                    list_load4(list_addr + 2u * (g + BW_GROUP * (u + 1u)), sbase, an, token);
-                    float alpha[BW_GROUP], ra[BW_GROUP], visra[BW_GROUP];
+            for (uint32_t u = 0; u < BW_ROWS / BW_GROUP; u++) {
+                if (g + BW_GROUP * u >= n_list) break;
+                const uint32_t aa[BW_GROUP] = {an[0], an[1], an[2], an[3]};
+                list_load4(list_addr + 2u * (g + BW_GROUP * (u + 1u)), sbase, an, token);
+                float alpha[BW_GROUP], ra[BW_GROUP], visra[BW_GROUP];
 #pragma unroll
-                    for (int j = 0; j < (int)BW_GROUP; j++) {
-                        const float4 g0 = lds128_ro(aa[j] + SM_G0, token);
-                        const float4 g1 = lds128_ro(aa[j] + SM_G1, token);
-                        const float dx = g0.x - pcx, dy = g0.y - pcy;
-                        const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);
-                        const float q = sp + g1.y;
-                        const bool act = aa[j] >= a_lo && sp <= 0.0f && q >= LOG2_INV255;
-                        const float vis = act ? ex2_approx(sp) : 0.0f;
-                        alpha[j] = fminf(0.99f, g1.z * vis);
-                        ra[j] = rcp_approx(1.0f - alpha[j]);
-                        visra[j] = vis * ra[j];
-                    }
-#pragma unroll
-                    for (int j = 0; j < (int)BW_GROUP; j++) {
-                        const float4 c = lds128_ro(aa[j] + SM_COL, token);
-                        const float uu = fmaf(c.z, v_out.z, fmaf(c.y, v_out.y, c.x * v_out.x));
-                        const float va = visra[j] * fmaf(uu, T, D);
-                        T *= ra[j];
-                        const float fac = alpha[j] * T;
-                        D = fmaf(-fac, uu, D);
-                        sts64(pair_addr + (BW_GROUP * u + (uint32_t)j) * BW_ROW + lane * 8u, va, fac);
-                    }
+                for (int j = 0; j < (int)BW_GROUP; j++) {
+                    const float4 g0 = lds128_ro(aa[j] + SM_G0, token);
+                    const float4 g1 = lds128_ro(aa[j] + SM_G1, token);
+                    const float dx = g0.x - pcx, dy = g0.y - pcy;
+                    const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);
+                    const float q = sp + g1.y;
+                    // the same predicate, on the same instruction sequence, as the forward
+                    const bool act = aa[j] >= a_lo && sp <= 0.0f && q >= LOG2_INV255;
+                    const float vis = act ? ex2_approx(sp) : 0.0f;  // inactive: alpha = 0, ra = 1, a row of zeros
+                    alpha[j] = fminf(0.99f, g1.z * vis);            // 0.99 here, 0.999 forward (reference quirk)
+                    ra[j] = rcp_approx(1.0f - alpha[j]);
+                    visra[j] = vis * ra[j];
                 }
-                flush_rows<true>(sbase + TILE_SIZE * 16u, pair_addr, pix_addr, list_addr + 2u * g, lane,
-                                 min(BW_ROWS, n_list - g), rx0, ry0, v_projected);
-            }
-            continue;
-        }
-        uint32_t k = 0;  // rows of the pair tile in use (warp-uniform); flushed before the batch buffer is reused
-        for (uint32_t i = 0;; i += BW_GROUP) {
-            const bool end = i >= n_list;
-            if (k > BW_ROWS - BW_GROUP || (end && k != 0u)) {
-                flush_rows<false>(sbase + TILE_SIZE * 16u, pair_addr, pix_addr, chunk_addr, lane, k, rx0, ry0, v_projected);
-                k = 0;
-            }
-            if (end) break;
-            uint32_t aa[BW_GROUP];
-            list_load4(list_addr + 2u * i, sbase, aa, token);
-            bool act[BW_GROUP];
-            float alpha[BW_GROUP], ra[BW_GROUP], visra[BW_GROUP];
-            // geometry of the four splats: independent of the running state, so the four chains overlap
 #pragma unroll
-            for (int j = 0; j < (int)BW_GROUP; j++) {
-                const float4 g0 = lds128(aa[j] + SM_G0);
-                const float4 g1 = lds128(aa[j] + SM_G1);
-                const float dx = g0.x - pcx, dy = g0.y - pcy;
-                const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);
-                const float q = sp + g1.y;
-                // the same predicate, on the same instruction sequence, as the forward
-                act[j] = aa[j] >= a_lo && sp <= 0.0f && q >= LOG2_INV255;
-                const float vis = act[j] ? ex2_approx(sp) : 0.0f;  // inactive: alpha = 0, ra = 1, everything below is a no-op
-                alpha[j] = fminf(0.99f, g1.z * vis);               // 0.99 here, 0.999 forward (reference quirk)
-                ra[j] = rcp_approx(1.0f - alpha[j]);
-                visra[j] = vis * ra[j];
-            }
-#pragma unroll
-            for (int j = 0; j < (int)BW_GROUP; j++) {
-#ifdef BRUSH_DBG_COUNT
-                {
-                    const uint32_t bal = __ballot_sync(0xffffffffu, act[j]);
-                    if (lane == 0) { atomicAdd(&g_dbg[2], (unsigned long long)__popc(bal)); if (bal) atomicAdd(&g_dbg[1], 1ull); }
-                }
-#endif
-                if (__any_sync(0xffffffffu, act[j])) {
-                    const float4 c = lds128(aa[j] + SM_COL);
-                    const float u = fmaf(c.z, v_out.z, fmaf(c.y, v_out.y, c.x * v_out.x));
-                    const float va = visra[j] * fmaf(u, T, D);  // vis * v_alpha
+                for (int j = 0; j < (int)BW_GROUP; j++) {
+                    const float4 c = lds128_ro(aa[j] + SM_COL, token);
+                    const float uu = fmaf(c.z, v_out.z, fmaf(c.y, v_out.y, c.x * v_out.x));
+                    const float va = visra[j] * fmaf(uu, T, D);
                     T *= ra[j];
                     const float fac = alpha[j] * T;
-                    D = fmaf(-fac, u, D);
-                    sts64(pair_addr + k * BW_ROW + lane * 8u, va, fac);
-                    sts_u32(chunk_addr + 4u * k, aa[j]);
-                    k++;
+                    D = fmaf(-fac, uu, D);
+                    sts64(pair_addr + (BW_GROUP * u + (uint32_t)j) * BW_ROW + lane * 8u, va, fac);
                 }
             }
+            flush_rows(sbase + TILE_SIZE * 16u, pair_addr, pix_addr, list_addr + 2u * g, lane, min(BW_ROWS, n_list - g),
+                       rx0, ry0, v_projected);
         }
     }
 }
@@ -651,40 +576,16 @@ void launch_rasterize_backward(const Cam& cam, const uint32_t* compact_gid_from_
                                const float* v_out_img, float* v_projected, cudaStream_t st) {
     const uint32_t tiles = cam.tiles_x * cam.tiles_y;
     if (tiles == 0) return;
-    // A/B switch while the variants are being measured: BRUSH_RASTER_BWD = 10 * (CTAs per SM) + always-row
-    const char* env = getenv("BRUSH_RASTER_BWD");
-    const int variant = env ? atoi(env) : 31;
-    static_assert(4 * (BW_BYTES + 1024) <= 228 * 1024, "four backward CTAs must fit in one SM's shared memory");
     static uint64_t configured_devices = 0;  // the opt-in to > 48 KB of shared memory is per device
     int dev = 0;
     cudaGetDevice(&dev);
     if (!(configured_devices >> dev & 1ull)) {
-        cudaFuncSetAttribute(rasterize_backward_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BW_BYTES);
-        cudaFuncSetAttribute(rasterize_backward_kernel<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BW_BYTES);
-        cudaFuncSetAttribute(rasterize_backward_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BW_BYTES);
+        cudaFuncSetAttribute(rasterize_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BW_BYTES);
         configured_devices |= 1ull << dev;
     }
     g_launch_count++;
-#define BRUSH_BWD_LAUNCH(CTAS, ROW)                                                                                    \
-    rasterize_backward_kernel<CTAS, ROW><<<tiles, TILE_SIZE, BW_BYTES, st>>>(cam, compact_gid_from_isect, tile_bins, projected, \
-                                                                             global_from_compact, final_index, out_img, v_out_img, v_projected)
-    switch (variant) {
-        case 30: BRUSH_BWD_LAUNCH(3, false); break;
-        case 41: BRUSH_BWD_LAUNCH(4, true); break;
-        default: BRUSH_BWD_LAUNCH(3, true); break;
-    }
-#undef BRUSH_BWD_LAUNCH
+    rasterize_backward_kernel<<<tiles, TILE_SIZE, BW_BYTES, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
+                                                                 global_from_compact, final_index, out_img, v_out_img, v_projected);
 }
 
 }  // namespace brush
-
-#ifdef BRUSH_DBG_COUNT
-extern "C" __attribute__((visibility("default"))) void brush_debug_counters(unsigned long long* out4, int reset) {
-    cudaDeviceSynchronize();
-    cudaMemcpyFromSymbol(out4, brush::g_dbg, 32);
-    if (reset) {
-        unsigned long long z[4] = {0, 0, 0, 0};
-        cudaMemcpyToSymbol(brush::g_dbg, z, 32);
-    }
-}
-#endif
