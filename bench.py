@@ -65,16 +65,52 @@ def view_cameras(width, height):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    """SM clock and throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe).  NVML in a thread
+    (a sample every 20 ms: the default timed region lasts about 0.2 s, less than `nvidia-smi -lms` needs to print its
+    first line); falls back to the nvidia-smi loop when the NVML binding is missing."""
 
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20),
+               ("sw_power_cap", 0x4))
 
     def __init__(self, gpu_index):
         self.rows, self.proc, self.gpu = [], None, gpu_index
+        self.nvml, self.handle, self.samples, self.run = None, None, [], False
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            try:
+                import torch
+
+                uuid = str(torch.cuda.get_device_properties(gpu_index).uuid)
+                self.handle = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid).encode())
+            except Exception:
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = None
+
+    def _sample_nvml(self):
+        n, h = self.nvml, self.handle
+        while self.run:
+            try:
+                sm = n.nvmlDeviceGetClockInfo(h, n.NVML_CLOCK_SM)
+                mx = n.nvmlDeviceGetMaxClockInfo(h, n.NVML_CLOCK_SM)
+                get = getattr(n, "nvmlDeviceGetCurrentClocksEventReasons", None) or n.nvmlDeviceGetCurrentClocksThrottleReasons
+                self.samples.append((float(sm), float(mx), int(get(h))))
+            except Exception:
+                pass
+            time.sleep(0.02)
 
     def start(self):
+        if self.nvml is not None:
+            self.run = True
+            self.thread = threading.Thread(target=self._sample_nvml, daemon=True)
+            self.thread.start()
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
@@ -88,23 +124,31 @@ class ClockSampler:
             self.rows.append(line.strip())
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
         sm, mx, reasons = [], None, set()
-        for r in self.rows:
-            c = [x.strip() for x in r.split(",")]
-            if len(c) < 7:
-                continue
-            try:
-                sm.append(float(c[0]))
-                mx = float(c[1])
-            except ValueError:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
+        if self.nvml is not None:
+            self.run = False
+            self.thread.join(timeout=1.0)
+            for s_, m_, bits in self.samples:
+                sm.append(s_)
+                mx = m_
+                reasons.update(name for name, bit in self.REASONS if bits & bit)
+        elif self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        else:
+            time.sleep(0.15)
+            self.proc.terminate()
+            for r in self.rows:
+                c = [x.strip() for x in r.split(",")]
+                if len(c) < 7:
+                    continue
+                try:
+                    sm.append(float(c[0]))
+                    mx = float(c[1])
+                except ValueError:
+                    continue
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
         busy = [x for x in sm if mx and x > 0.5 * mx] or sm
         return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
                 "samples": len(sm)}
