@@ -349,7 +349,9 @@ def test_views_step_two_views_on_one_device(k):
         assert float(diff.max()) <= 2.01 * group_lr[name] and float((diff <= 1e-6).float().mean()) > 0.999, name
 
 
-@pytest.mark.parametrize("channels,h,w", [(3, 37, 53), (4, 64, 48), (3, 16, 16)])
+# (700, 40): many row segments per column strip (the seams of the row-streaming kernels); (3, 5): smaller than the
+# window; (20, 300): ten strips, the last one ragged
+@pytest.mark.parametrize("channels,h,w", [(3, 37, 53), (4, 64, 48), (3, 16, 16), (3, 700, 40), (4, 3, 5), (3, 20, 300)])
 def test_image_loss_ssim_forward_and_gradient(channels, h, w):
     """brush_image_loss_backward vs the numpy oracle (loss value) and torch autograd of the same definition
     (gradient; float64 on the CPU).  Tolerances: loss 2e-6 abs, gradient 1e-4 relative to its largest entry."""
