@@ -45,6 +45,21 @@ class BrushTrainState(C.Structure):
             "lr_mean", "lr_scale", "lr_rotation", "lr_coeffs_dc", "lr_opac", "sh_rest_lr_scale")]
 
 
+class BrushSplatParams(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("means", "rotation", "sh_coeffs", "raw_opacity", "log_scales")]
+
+
+class BrushRefineConfig(C.Structure):
+    _fields_ = [("densify_grad_thresh", C.c_float), ("densify_size_thresh", C.c_float),
+                ("cull_alpha_thresh", C.c_float), ("cull_scale_thresh", C.c_float), ("reset_alpha", C.c_int32),
+                ("reset_alpha_value", C.c_float)]
+
+
+class BrushRefineCounts(C.Structure):
+    _fields_ = [("num_split", C.c_uint32), ("num_cloned", C.c_uint32), ("alpha_pruned", C.c_uint32),
+                ("scale_pruned", C.c_uint32), ("num_out", C.c_uint32), ("reserved", C.c_uint32 * 3)]
+
+
 DP_MAX_WORLD = 8
 
 
@@ -115,6 +130,12 @@ _SIGS = {
     "brush_adam_step": (C.c_int, [C.c_void_p, C.POINTER(BrushAdamGroup), C.c_int, C.c_float, C.c_float, C.c_float,
                                   C.c_uint32, C.c_float, C.c_void_p]),
     "brush_launch_count": (C.c_uint64, []),
+    "brush_refine_plan": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.POINTER(BrushSplatParams),
+                                    C.POINTER(BrushSplatParams), C.POINTER(BrushRefineConfig),
+                                    C.POINTER(BrushRefineCounts), C.c_void_p]),
+    "brush_refine_apply": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(BrushSplatParams),
+                                     C.POINTER(BrushSplatParams), C.c_void_p, C.POINTER(BrushRefineConfig),
+                                     C.POINTER(BrushSplatParams), C.c_void_p]),
     "brush_dp_adam_step": (C.c_int, [C.c_void_p, C.POINTER(BrushDpStep), C.POINTER(BrushDpSegment), C.c_int,
                                      C.c_float, C.c_float, C.c_float, C.c_uint32, C.c_float, C.c_void_p]),
     "brush_dp_owned_range": (None, [C.c_uint64, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),

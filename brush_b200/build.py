@@ -29,6 +29,7 @@ UNITS = {
     "optim.cu": [],
     "dp_adam.cu": [],
     "ssim.cu": [],
+    "refine.cu": [],
     "api.cu": [],
 }
 

@@ -23,7 +23,9 @@ struct brush_ctx {
     int timing = 0;
     // scratch, grown on demand (growth synchronises; steady state never allocates)
     Buf control, presort_gid, depth_bits, depth_sorted, num_tiles_hit, keys_tmp, vals_tmp, hist, lb, tickets,
-        tile_ids_unsorted, cg_unsorted, tile_ids_sorted, v_projected, sticky, loss_scratch, visible_mask, tile_masks, tile_boxes;
+        tile_ids_unsorted, cg_unsorted, tile_ids_sorted, v_projected, sticky, loss_scratch, visible_mask, tile_masks, tile_boxes,
+        refine_scratch;
+    uint32_t refine_n = 0;  // n of the last brush_refine_plan (brush_refine_apply must match)
     const void* visible_owner = nullptr;  // aux.uniforms_buffer of the forward whose visibility visible_mask holds
     // host-staged path
     Buf h_means, h_lscales, h_quats, h_sh, h_opac, h_img, h_aux[9];
@@ -154,7 +156,7 @@ void brush_ctx_destroy(brush_ctx* ctx) {
                    &ctx->keys_tmp, &ctx->vals_tmp, &ctx->hist, &ctx->lb, &ctx->tickets, &ctx->tile_ids_unsorted,
                    &ctx->cg_unsorted, &ctx->tile_ids_sorted, &ctx->v_projected, &ctx->sticky, &ctx->loss_scratch, &ctx->h_means, &ctx->h_lscales,
                    &ctx->h_quats, &ctx->h_sh, &ctx->h_opac, &ctx->h_img, &ctx->visible_mask, &ctx->tile_masks,
-                   &ctx->tile_boxes};
+                   &ctx->tile_boxes, &ctx->refine_scratch};
     for (Buf* b : bufs)
         if (b->p) cudaFree(b->p);
     for (Buf& b : ctx->h_aux)
@@ -677,6 +679,71 @@ int brush_render_forward_host(brush_ctx* ctx, const BrushUniforms* uniforms_host
     return brush_ctx_check(ctx, st);
 }
 
+
+static RefineLaunchCfg refine_cfg(const BrushRefineConfig* c) {
+    RefineLaunchCfg r;
+    r.grad_thresh = c->densify_grad_thresh;
+    r.log_size_thresh = logf(c->densify_size_thresh);
+    r.logit_alpha = std::log((double)c->cull_alpha_thresh / (1.0 - (double)c->cull_alpha_thresh));
+    r.log_scale_cull = logf(c->cull_scale_thresh);
+    r.reset_alpha = c->reset_alpha;
+    r.reset_alpha_raw = (float)std::log((double)c->reset_alpha_value / (1.0 - (double)c->reset_alpha_value));
+    return r;
+}
+static bool params_ok(const BrushSplatParams* p) {
+    return p && p->means && p->rotation && p->sh_coeffs && p->raw_opacity && p->log_scales;
+}
+
+int brush_refine_plan(brush_ctx* ctx, uint32_t n, const float* grad_2d_accum, const float* xy_grad_counts,
+                      const BrushSplatParams* pre_step, const BrushSplatParams* post_step,
+                      const BrushRefineConfig* config, BrushRefineCounts* counts_host, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (!grad_2d_accum || !xy_grad_counts || !params_ok(pre_step) || !params_ok(post_step) || !config || !counts_host)
+        return fail(ctx, BRUSH_E_INVALID, "null argument");
+    if (!(config->cull_alpha_thresh > 0.f && config->cull_alpha_thresh < 1.f) || !(config->densify_size_thresh > 0.f) ||
+        !(config->cull_scale_thresh > 0.f))
+        return fail(ctx, BRUSH_E_INVALID, "refine: thresholds out of range");
+    memset(counts_host, 0, sizeof(*counts_host));
+    ctx->refine_n = n;
+    if (n == 0) return BRUSH_OK;
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    ENSURE(refine_scratch, refine_scratch_bytes(n));
+    uint32_t* totals_dev = nullptr;
+    launch_refine_plan(n, grad_2d_accum, xy_grad_counts, pre_step->log_scales, pre_step->raw_opacity,
+                       post_step->log_scales, post_step->raw_opacity, refine_cfg(config), ctx->refine_scratch.p,
+                       &totals_dev, st);
+    CU(cudaGetLastError());
+    uint32_t t[6];
+    CU(cudaMemcpyAsync(t, totals_dev, sizeof(t), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));  // the caller allocates the new set from these counts (train.rs awaits argwhere)
+    counts_host->num_out = t[0] + t[1] + t[2];
+    counts_host->num_split = t[3];
+    counts_host->alpha_pruned = t[4];
+    counts_host->scale_pruned = t[4] + t[5];  // cumulative, train.rs:555
+    // every row is either kept or counted by one of the two prune tests: n + clones + splits = kept + pruned
+    counts_host->num_cloned = counts_host->num_out + t[4] + t[5] - n - t[3];
+    return BRUSH_OK;
+}
+
+int brush_refine_apply(brush_ctx* ctx, uint32_t n, uint32_t K, const BrushSplatParams* pre_step,
+                       const BrushSplatParams* post_step, const float* samples, const BrushRefineConfig* config,
+                       const BrushSplatParams* out, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (!params_ok(pre_step) || !params_ok(post_step) || !config) return fail(ctx, BRUSH_E_INVALID, "null argument");
+    if (!valid_k(K)) return fail(ctx, BRUSH_E_INVALID, "Invalid nr. of sh bases");
+    if (n != ctx->refine_n || (n && !ctx->refine_scratch.p))
+        return fail(ctx, BRUSH_E_INVALID, "brush_refine_apply must follow brush_refine_plan with the same n");
+    if (n == 0) return BRUSH_OK;
+    if (!out) return fail(ctx, BRUSH_E_INVALID, "null argument");
+    CU(cudaSetDevice(ctx->device));
+    const float* pre[5] = {pre_step->means, pre_step->rotation, pre_step->sh_coeffs, pre_step->raw_opacity, pre_step->log_scales};
+    const float* post[5] = {post_step->means, post_step->rotation, post_step->sh_coeffs, post_step->raw_opacity, post_step->log_scales};
+    float* o[5] = {out->means, out->rotation, out->sh_coeffs, out->raw_opacity, out->log_scales};
+    launch_refine_apply(n, K, pre, post, samples, refine_cfg(config), ctx->refine_scratch.p, o, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
 
 uint64_t brush_launch_count(void) { return g_launch_count.load(); }
 

@@ -175,6 +175,25 @@ void launch_xy_grad_stats(const float* v_xy, const uint8_t* visible_mask, uint32
                           int accumulate, float* grad_norm, float* visible, cudaStream_t st);
 
 
+// ---- refine.cu: densify / prune (train.rs:395-553) ----
+struct RefineLaunchCfg {
+    float grad_thresh, log_size_thresh;
+    double logit_alpha;
+    float log_scale_cull;
+    int reset_alpha;
+    float reset_alpha_raw;
+};
+size_t refine_scratch_bytes(uint32_t N);
+// totals_dev: u32[6] = rows kept of (post-step splats, clones, split copies), split candidates, rows failing the
+// opacity test, rows failing the scale test after passing the opacity test
+void launch_refine_plan(uint32_t N, const float* grad_accum, const float* grad_counts, const float* pre_log_scales,
+                        const float* pre_opac, const float* post_log_scales, const float* post_opac,
+                        const RefineLaunchCfg& c, void* scratch, uint32_t** totals_dev, cudaStream_t st);
+// pre / post / out: means, rotation, sh, raw_opacity, log_scales
+void launch_refine_apply(uint32_t N, uint32_t K, const float* const pre[5], const float* const post[5],
+                         const float* samples, const RefineLaunchCfg& c, void* scratch, float* const out[5],
+                         cudaStream_t st);
+
 // ---- dp_adam.cu: view-parallel optimizer step over NVLink peer memory ----
 struct DpSeg {
     uint64_t src_off, dst_off, count;  // floats; multiples of 4

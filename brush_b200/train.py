@@ -343,46 +343,47 @@ class SplatTrainer:
         applied to clones that are then dropped (train.rs:401-402,481-507 vs :519): only the appended copies
         carry them.  Every rank takes the same decisions: the statistics are the reduced ones and the split
         offsets come from a generator seeded with (config.seed, iter).  `samples` [num_split, 3] overrides the
-        N(0, 0.5) draws (tests)."""
-        cfg = self.config
-        pre_means, pre_sh, pre_rot, pre_opac, pre_scales = pre_step
-        p_means, p_sh, p_rot = post.means.detach(), post.sh_coeffs.detach(), post.rotation.detach()
-        p_opac, p_scales = post.raw_opacity.detach(), post.log_scales.detach()
-        grads = self.grad_2d_accum / self.xy_grad_counts.clamp_min(1.0)
-        big_grad = grads >= cfg.densify_grad_thresh
-        small = torch.exp(p_scales).amax(dim=1) < cfg.densify_size_thresh
-        clone_inds = torch.nonzero(small & big_grad).squeeze(1)
-        split_inds = torch.nonzero(~small & big_grad).squeeze(1)
-        n_clone, n_split = int(clone_inds.numel()), int(split_inds.numel())
-        app = [[], [], [], [], []]  # means, rotation, sh, opacity, log_scales
-        if n_clone:
-            for dst, src in zip(app, (pre_means, pre_rot, pre_sh, pre_opac, pre_scales)):
-                dst.append(src[clone_inds])
-        if n_split:
-            cur_rot, cur_scale = p_rot[split_inds], torch.exp(p_scales[split_inds])
+        N(0, 0.5) draws (tests).  The arithmetic runs in three kernels behind brush_refine_plan /
+        brush_refine_apply (csrc/refine.cu); torch only allocates the new tensors and draws the samples."""
+        cfg, dev, L = self.config, self.device, _lib.lib()
+        ctx = get_context(dev)
+        st = C.c_void_p(_stream_ptr(dev))
+        f32 = lambda t: t.detach().contiguous().float()
+        pre = [f32(t) for t in pre_step]  # means, sh, rotation, raw_opacity, log_scales
+        post = [f32(t) for t in (post.means, post.sh_coeffs, post.rotation, post.raw_opacity, post.log_scales)]
+
+        def params(ts):  # BrushSplatParams order: means, rotation, sh, raw_opacity, log_scales
+            return _lib.BrushSplatParams(ts[0].data_ptr(), ts[2].data_ptr(), ts[1].data_ptr(), ts[3].data_ptr(),
+                                         ts[4].data_ptr())
+
+        refine_step = (self.iter - 1) // cfg.refine_every  # self.iter was already incremented
+        rcfg = _lib.BrushRefineConfig(cfg.densify_grad_thresh, cfg.densify_size_thresh, cfg.cull_alpha_thresh,
+                                      cfg.cull_scale_thresh, int(refine_step % cfg.reset_alpha_every_refine == 0),
+                                      cfg.reset_alpha_value)
+        counts = _lib.BrushRefineCounts()
+        c_pre, c_post = params(pre), params(post)
+        with torch.cuda.device(dev):
+            # decisions + prune tests + counts on the device; synchronises like the reference's argwhere().await
+            ctx.check(L.brush_refine_plan(ctx.handle, self.n, self.grad_2d_accum.data_ptr(),
+                                          self.xy_grad_counts.data_ptr(), C.byref(c_pre), C.byref(c_post),
+                                          C.byref(rcfg), C.byref(counts), st))
+            n_split, n_out = int(counts.num_split), int(counts.num_out)
             if samples is None:
-                gen = torch.Generator(device=self.device)
+                gen = torch.Generator(device=dev)
                 gen.manual_seed((cfg.seed << 20) + self.iter)
-                samples = torch.randn((n_split, 3), device=self.device, generator=gen) * 0.5
-            offset = quaternion_vec_multiply(cur_rot, samples * cur_scale)
-            app[0].append(pre_means[split_inds] + offset)
-            app[1].append(cur_rot)
-            app[2].append(p_sh[split_inds])
-            app[3].append(p_opac[split_inds])
-            app[4].append(torch.log(cur_scale / 1.6))
-        new = [p_means, p_rot, p_sh, p_opac, p_scales]
-        if n_clone or n_split:
-            new = [torch.cat([base] + extra, 0) for base, extra in zip(new, app)]
-        start = new[0].shape[0]
-        keep = ~(torch.sigmoid(new[3]) < cfg.cull_alpha_thresh)          # prune_points, train.rs:530-531
-        new = [t[keep] for t in new]
-        alpha_pruned = start - new[0].shape[0]
-        keep = ~(torch.exp(new[4]).amax(dim=1) > cfg.cull_scale_thresh)  # train.rs:536-541
-        new = [t[keep] for t in new]
-        scale_pruned = start - new[0].shape[0]                           # cumulative, as train.rs:543
-        refine_step = (self.iter - 1) // cfg.refine_every                # self.iter was already incremented
-        if refine_step % cfg.reset_alpha_every_refine == 0:              # train.rs:545-548
-            new[3] = torch.full_like(new[3], math.log(cfg.reset_alpha_value / (1.0 - cfg.reset_alpha_value)))
+                samples = torch.randn((max(n_split, 1), 3), device=dev, generator=gen) * 0.5
+            samples = f32(samples)
+            if n_split and tuple(samples.shape) != (n_split, 3):
+                raise ValueError(f"samples must be [{n_split}, 3]")
+            k = post[1].shape[1]
+            f = dict(dtype=torch.float32, device=dev)
+            new = [torch.empty((n_out, 3), **f), torch.empty((n_out, k, 3), **f), torch.empty((n_out, 4), **f),
+                   torch.empty((n_out,), **f), torch.empty((n_out, 3), **f)]
+            c_out = params(new)
+            ctx.check(L.brush_refine_apply(ctx.handle, self.n, k, C.byref(c_pre), C.byref(c_post), samples.data_ptr(),
+                                           C.byref(rcfg), C.byref(c_out), st))
+        n_clone, alpha_pruned, scale_pruned = int(counts.num_cloned), int(counts.alpha_pruned), int(counts.scale_pruned)
+        new = [new[0], new[2], new[1], new[3], new[4]]  # -> means, rotation, sh, opacity, log_scales (as below)
         it = self.iter
         self._alloc(new[0].shape[0], self.k)  # reset_stats + a fresh optimizer (train.rs:550-554)
         self.iter = it

@@ -277,6 +277,44 @@ int brush_dp_adam_step(brush_ctx* ctx, const BrushDpStep* step_host, const Brush
 /* The slice [begin, end) of a segment of `count` floats that `rank` owns (host helper, no GPU needed). */
 void brush_dp_owned_range(uint64_t count, int world, int rank, uint64_t* begin, uint64_t* end);
 
+/* ---- densify / prune: the arithmetic of SplatTrainer::refine_splats, crates/brush-train/src/train.rs:395-553
+ * (with prune_points :560-596, concat_splats :598-621, quaternion_vec_multiply :140-177, reset_opacity :205-209).
+ * Two calls, because the caller has to allocate the output between them (the reference awaits argwhere twice):
+ *   brush_refine_plan   classifies every splat (clone: small & high 2-D gradient; split: large & high gradient),
+ *                       applies the two prune tests (opacity < cull_alpha_thresh, max scale > cull_scale_thresh) to
+ *                       every row the refine yields, and returns the counts -- it synchronises the stream.
+ *   brush_refine_apply  writes the new splat set: surviving post-step splats, then surviving clones (PRE-step values),
+ *                       then surviving split copies (pre-step mean + R(q) (sample * scale), scale / 1.6), each in
+ *                       index order -- the order of the reference's concat + two order-preserving prunes.
+ * brush_refine_apply must follow brush_refine_plan on the same ctx with the same n and buffers.  samples:
+ * f32[num_split, 3], the N(0, 0.5) draws of train.rs:497-499 in split-candidate order (an input, so that every rank
+ * of a view-parallel run uses the same ones).  reset_alpha != 0: every output opacity = inverse_sigmoid(
+ * reset_alpha_value) (train.rs:557-560). */
+typedef struct BrushSplatParams {   /* device pointers */
+    float* means;         /* [n,3] */
+    float* rotation;      /* [n,4] */
+    float* sh_coeffs;     /* [n,K,3] */
+    float* raw_opacity;   /* [n] */
+    float* log_scales;    /* [n,3] */
+} BrushSplatParams;
+typedef struct BrushRefineConfig {  /* TrainConfig fields, train.rs:48-71 */
+    float densify_grad_thresh;
+    float densify_size_thresh;
+    float cull_alpha_thresh;
+    float cull_scale_thresh;
+    int32_t reset_alpha;
+    float reset_alpha_value;
+} BrushRefineConfig;
+typedef struct BrushRefineCounts {  /* == RefineStats (train.rs:112-118) + the size of the new set */
+    uint32_t num_split, num_cloned, alpha_pruned, scale_pruned, num_out, reserved[3];
+} BrushRefineCounts;
+int brush_refine_plan(brush_ctx* ctx, uint32_t n, const float* grad_2d_accum, const float* xy_grad_counts,
+                      const BrushSplatParams* pre_step, const BrushSplatParams* post_step,
+                      const BrushRefineConfig* config, BrushRefineCounts* counts_host, void* stream);
+int brush_refine_apply(brush_ctx* ctx, uint32_t n, uint32_t K, const BrushSplatParams* pre_step,
+                       const BrushSplatParams* post_step, const float* samples, const BrushRefineConfig* config,
+                       const BrushSplatParams* out, void* stream);
+
 /* Number of kernels this library has launched in this process (all contexts). */
 uint64_t brush_launch_count(void);
 

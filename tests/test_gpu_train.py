@@ -434,6 +434,74 @@ def test_refine_splats_matches_oracle():
         assert tr.n == out.means.shape[0] and float(tr.grad_2d_accum.abs().sum()) == 0.0 and tr.state == {}
 
 
+def test_refine_abi_edge_cases():
+    """brush_refine_plan / brush_refine_apply through the C ABI: nothing to densify or prune (the set comes back
+    unchanged), SH degree 0 rows (12 bytes: the scalar copy path), everything pruned (empty output), and apply
+    without a matching plan (error, as the header says)."""
+    import ctypes as C
+
+    from brush_b200 import _lib, get_context, scene
+    from oracle import refine_oracle as ro
+
+    ctx, L = get_context(DEV), _lib.lib()
+    st = C.c_void_p(torch.cuda.current_stream(DEV).cuda_stream)
+    n = 777
+    sc = scene.make_scene(n, 64, 64, 0, 3)
+    t = lambda a: torch.as_tensor(np.ascontiguousarray(a, dtype=np.float32), device=DEV)
+    names = ("means", "rotation", "sh", "raw_opacity", "log_scales")  # BrushSplatParams order
+    host = dict(means=sc.means, rotation=sc.quats, sh=sc.sh_coeffs, raw_opacity=sc.raw_opacity, log_scales=sc.log_scales)
+    dev = {k: t(v) for k, v in host.items()}
+    P = lambda d: _lib.BrushSplatParams(*[d[k].data_ptr() for k in names])
+    accum, cnt = t(np.zeros(n)), t(np.ones(n))
+    counts = _lib.BrushRefineCounts()
+
+    class Cfg:  # TrainConfig fields the oracle reads
+        densify_grad_thresh, densify_size_thresh, cull_alpha_thresh, cull_scale_thresh = 2e-4, 0.01, 1e-9, 1e9
+        refine_every, reset_alpha_every_refine, reset_alpha_value = 100, 30, 0.01
+
+    def run(cfg, accum_t, reset):
+        rc = _lib.BrushRefineConfig(cfg.densify_grad_thresh, cfg.densify_size_thresh, cfg.cull_alpha_thresh,
+                                    cfg.cull_scale_thresh, int(reset), cfg.reset_alpha_value)
+        p = P(dev)
+        ctx.check(L.brush_refine_plan(ctx.handle, n, accum_t.data_ptr(), cnt.data_ptr(), C.byref(p), C.byref(p),
+                                      C.byref(rc), C.byref(counts), st))
+        m = int(counts.num_out)
+        out = dict(means=torch.empty((m, 3), device=DEV), rotation=torch.empty((m, 4), device=DEV),
+                   sh=torch.empty((m, 1, 3), device=DEV), raw_opacity=torch.empty((m,), device=DEV),
+                   log_scales=torch.empty((m, 3), device=DEV))
+        samples = torch.zeros((max(int(counts.num_split), 1), 3), device=DEV)
+        po = P(out)
+        ctx.check(L.brush_refine_apply(ctx.handle, n, 1, C.byref(p), C.byref(p), samples.data_ptr(), C.byref(rc),
+                                       C.byref(po), st))
+        return out
+
+    out = run(Cfg, accum, False)  # no gradient statistics, thresholds that prune nothing
+    assert (counts.num_split, counts.num_cloned, counts.alpha_pruned, counts.scale_pruned, counts.num_out) == (0, 0, 0, 0, n)
+    for k in names:
+        assert torch.equal(out[k].reshape(dev[k].shape), dev[k]), k
+    # every splat has a large gradient: clones and splits of 12-byte SH rows, checked against the oracle
+    big = t(np.full(n, 1.0))
+    out = run(Cfg, big, True)
+    hd = {("sh" if k == "sh" else k): v for k, v in host.items()}
+    ref, ref_stats = ro.refine(hd, hd, np.full(n, 1.0, np.float32), np.ones(n, np.float32),
+                               np.zeros((int(counts.num_split), 3), np.float32), 3000, Cfg)
+    assert (counts.num_split, counts.num_cloned, counts.alpha_pruned, counts.scale_pruned) == ref_stats
+    assert counts.num_out == 2 * n and counts.num_split + counts.num_cloned == n
+    for k in names:
+        assert np.allclose(out[k].cpu().numpy().reshape(ref[k].shape), ref[k], rtol=1e-5, atol=1e-6), k
+
+    class PruneAll(Cfg):
+        cull_alpha_thresh = 1.0 - 1e-7
+
+    out = run(PruneAll, accum, False)
+    assert counts.num_out == 0 and counts.alpha_pruned == n
+    p = P(dev)
+    rc = _lib.BrushRefineConfig(2e-4, 0.01, 0.005, 5.0, 0, 0.01)
+    with pytest.raises(_lib.BrushError):  # n differs from the plan's
+        ctx.check(L.brush_refine_apply(ctx.handle, n - 1, 1, C.byref(p), C.byref(p), accum.data_ptr(), C.byref(rc),
+                                       C.byref(p), st))
+
+
 def test_training_loop_survives_refinement():
     """A short run with refinement every 5 steps: the splat count changes, buffers are re-made, training goes on."""
     from brush_b200 import Camera, Splats, scene
