@@ -208,6 +208,30 @@ BD TileHits warp_tile_hits(const VisTest& vt, const TileBox& b, bool valid, uint
     return out;
 }
 
+// The reference walks the bounding box of a CIRCLE of radius ceil(3 sqrt(lambda_max)) (helpers.wgsl:192-201,55-71)
+// and tests every tile of it against the alpha >= 1/255 ELLIPSE (can_be_visible).  The candidates outside the
+// ellipse's own axis-aligned extent can never pass, so the box handed to the tile test is first clipped to that
+// extent: for {d : d^T C d <= 1}, |dx| <= sqrt(c / det C), |dy| <= sqrt(a / det C).  The margin (0.02 px + 0.1 %)
+// is two orders above the rounding error of the exact test at 8K coordinates, so only tiles the exact test
+// rejects are dropped: the hit lists stay bit-identical (row-major order inside a sub-box is the order inside
+// the box), with a quarter fewer candidates on the 1 M scene and more on larger splats.
+BD void shrink_to_ellipse(TileBox& b, const VisTest& vt) {
+    if (!vt.any) return;
+    const float a = vt.conic_scaled.c[0].x, h = vt.conic_scaled.c[0].y, c = vt.conic_scaled.c[1].y;
+    const float det = a * c - h * h;
+    if (!(det > 0.0f) || !(a > 0.0f) || !(c > 0.0f)) return;
+    const float ex = sqrtf(c / det), ey = sqrtf(a / det);
+    if (!(ex < 1e7f) || !(ey < 1e7f)) return;
+    const float mx = ex * 1.001f + 0.02f, my = ey * 1.001f + 0.02f;
+    const float inv = 1.0f / (float)TILE_WIDTH;
+    const float lo_x = floorf((vt.xy.x - mx) * inv), hi_x = floorf((vt.xy.x + mx) * inv) + 1.0f;
+    const float lo_y = floorf((vt.xy.y - my) * inv), hi_y = floorf((vt.xy.y + my) * inv) + 1.0f;
+    const uint32_t minx = max(b.minx, (uint32_t)fmaxf(lo_x, 0.0f)), maxx = min(b.maxx, (uint32_t)fmaxf(hi_x, 0.0f));
+    const uint32_t miny = max(b.miny, (uint32_t)fmaxf(lo_y, 0.0f)), maxy = min(b.maxy, (uint32_t)fmaxf(hi_y, 0.0f));
+    b.minx = minx; b.miny = miny;
+    b.maxx = max(maxx, minx); b.maxy = max(maxy, miny);
+}
+
 template <int K>
 __global__ void __launch_bounds__(256)
 project_visible_kernel(const __grid_constant__ Cam cam, const float* __restrict__ means,
@@ -241,6 +265,7 @@ project_visible_kernel(const __grid_constant__ Cam cam, const float* __restrict_
         uint32_t radius = radius_from_conic(conic);
         b = get_tile_bbox(xy, radius, cam.tiles_x, cam.tiles_y);
         vt = make_vis_test(xy, conic, opac);
+        shrink_to_ellipse(b, vt);
         float* p = projected + (size_t)c * 9;
         p[0] = xy.x; p[1] = xy.y; p[2] = conic.x; p[3] = conic.y; p[4] = conic.z;
         p[5] = color.x; p[6] = color.y; p[7] = color.z; p[8] = opac;
