@@ -94,10 +94,19 @@ radix_hist_kernel(const KeyT* __restrict__ keys, const int32_t* __restrict__ n_d
             const KeyT k = k4[u];
             for (uint32_t p = 0; p < plan.passes; p++) {
                 const uint32_t d = (uint32_t)(k >> plan.shift[p]) & plan.mask[p];
-                // warp-aggregated shared atomics: clustered keys (tile ids, depth exponents) would
-                // otherwise serialise 32-way on one bank.
-                const uint32_t peers = match_digit(d, valid);
-                if (valid && lane == (uint32_t)(31 - __clz(peers))) atomicAdd(&s_hist[p * RS_RADIX + d], __popc(peers));
+                // Clustered digits (tile-row bits, depth exponents) would serialise up to 32-way on one shared
+                // word, so they are counted warp-aggregated (nine ballots); scattered digits (mantissa bytes, tile
+                // columns) go straight to a shared atomic.  The warp picks per digit by looking at how many lanes
+                // agree with their neighbour.
+                const uint32_t nb = __shfl_down_sync(0xffffffffu, d, 1);
+                const uint32_t same = __ballot_sync(0xffffffffu, valid && nb == d);
+                if (__popc(same) >= 8) {
+                    const uint32_t peers = match_digit(d, valid);
+                    if (valid && lane == (uint32_t)(31 - __clz(peers)))
+                        atomicAdd(&s_hist[p * RS_RADIX + d], __popc(peers));
+                } else if (valid) {
+                    atomicAdd(&s_hist[p * RS_RADIX + d], 1u);
+                }
             }
         }
     }
