@@ -390,6 +390,9 @@ def run_ours(args):
                     "peak_source": "148 SMs x 128 FP32 lanes x 2 x max SM clock (no tensor-core or HBM roofline applies: "
                                    "the kernel is FP32-issue-bound, ncu in profiles/)",
                     "pairs": r_bwd if dom["stage"] == "RasterizeBackwards" else r_fwd,
+                    # the same kernel against the HBM roofline, in the base contract's shape
+                    "hbm_view": {"bound": "hbm", "achieved": dom["gbs"], "peak": peak, "unit": "GB/s",
+                                 "frac": dom["frac_hbm"], "traffic": traffic, "peak_source": peak_src},
                     "note": "achieved = 64 (bwd) / 26 (fwd) algorithmic flop per reference-evaluated (pixel, splat) "
                             "pair / kernel time; pairs the kernel culls before evaluating them still count as work "
                             "done. HBM view of the same kernel: "
