@@ -255,6 +255,8 @@ def run_ours(args):
 
     loss_slots = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)]
     loss_events = [torch.cuda.Event(), torch.cuda.Event()]
+    step_done = [torch.cuda.Event(), torch.cuda.Event()]
+    readback = torch.cuda.Stream(dev)
 
     def e2e_steps(n_steps, first_idx):
         """The user-facing loop: every step's view comes from pinned host memory (copy started one step ahead on
@@ -269,8 +271,14 @@ def run_ours(args):
                 if s + 1 < n_steps:
                     nxt = trainer.prefetch(make_batch(first_idx + s + 1, host_in))
                 continue
-            loss_slots[s & 1].copy_(stats.loss, non_blocking=True)
-            loss_events[s & 1].record()
+            # the device->host read of the loss runs on its own stream behind the step (a copy-engine operation
+            # on the compute stream costs a bubble between two kernels: measured 0.02 ms per step); the trainer
+            # keeps a step's loss scalar valid while the next step runs
+            step_done[s & 1].record()
+            with torch.cuda.stream(readback):
+                readback.wait_event(step_done[s & 1])
+                loss_slots[s & 1].copy_(stats.loss, non_blocking=True)
+                loss_events[s & 1].record(readback)
             if s + 1 < n_steps:
                 nxt = trainer.prefetch(make_batch(first_idx + s + 1, host_in))
             if s >= 1:

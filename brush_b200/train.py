@@ -148,8 +148,10 @@ class SplatTrainer:
         self.xy_grad_counts = torch.zeros(n, **f)
         self.norm_rot = torch.empty((n, 4), **f)
         self.state = {}
-        self.loss_buf = torch.zeros(1, **f)
-        self.loss_total = torch.zeros(1, **f)
+        # two sets of loss scalars, alternating by step: the loss a step returns stays valid while the NEXT step
+        # runs, so a caller may read it back from another stream, one step behind, without a copy on this one
+        self._loss_sets = [(torch.zeros(1, **f), torch.zeros(1, **f)) for _ in range(2)]
+        self.loss_total, self.loss_buf = self._loss_sets[0]
         self.v_out = None
         self.gt_dev = None
         self.render_bufs: List = []
@@ -214,6 +216,7 @@ class SplatTrainer:
         cfg, dev, L = self.config, self.device, _lib.lib()
         ctx = get_context(dev)
         st = C.c_void_p(_stream_ptr(dev))
+        self.loss_total, self.loss_buf = self._loss_sets[self.iter & 1]
         B = len(batch.gt_views)
         _, H, W, Cc = batch.gt_images.shape
         if self.v_out is None or tuple(self.v_out.shape[:2]) != (H, W):
