@@ -167,6 +167,10 @@ def algorithmic_bytes(stage, N, V, I, P, T, K):
         "Rasterize": 40 * I + 20 * P,
         "RasterizeBackwards": 40 * I + 36 * P + 36 * V,
         "GatherProjectBackwards": (84 + 52 + 12 * K) * V + (52 + 12 * K) * N,
+        # the kernel that runs in the single-GPU step is the FUSED tail (gather_grads + project_backwards +
+        # normalisation VJP + Adam + refine statistics): it reads the 48-byte rows and reads + writes parameters and
+        # both moments once, (44 + 12 K) B each, plus 9 B of statistics per splat; no dense gradient exists
+        "GatherProjectBackwards+Adam (fused)": 48 * N + 6 * (44 + 12 * K) * N + 9 * N,
     }[stage]
 
 
@@ -174,6 +178,7 @@ def run_ours(args):
     import torch
 
     from brush_b200 import Splats, _lib, get_context, scene
+    from brush_b200.parallel import view_for_rank
     from brush_b200.train import SceneBatch, SplatTrainer, TrainConfig
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -227,9 +232,14 @@ def run_ours(args):
     if world == 1:
         exchange = "nccl"  # single device: the fused tail, no exchange
     # reference defaults, except that refinement is off: the benchmark times a fixed number of splats
-    trainer = SplatTrainer(N, TrainConfig(max_refine_step=0), dev, sh_coeffs_per_channel=K, process_group=pg,
+    # (max_refine_step = 0), and warmup_steps = 0 so the refine statistics (train.rs:284-316) are accumulated in every
+    # timed step, as in the reference's steady state after its 500 warm-up iterations
+    train_cfg = TrainConfig(max_refine_step=0, warmup_steps=0)
+    trainer = SplatTrainer(N, train_cfg, dev, sh_coeffs_per_channel=K, process_group=pg,
                            isect_capacity=args.capacity, optimize=not args.no_optim,
                            exchange=exchange)
+    start_params = [p.detach().clone() for p in (splats.means, splats.sh_coeffs, splats.rotation, splats.raw_opacity,
+                                                 splats.log_scales)] if world > 1 else None
     splats = trainer.adopt(splats)  # peer exchange: parameters live in the peer-mapped replica
     if world > 1 and trainer.exchange == "views":
         exchange_desc = ("no gradient exchange: every rank publishes its view's nine per-splat sums (48 B rows) in NVLink "
@@ -245,7 +255,7 @@ def run_ours(args):
     loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
 
     def make_batch(step_idx, host_inputs):
-        v = (step_idx * world + rank) % N_VIEWS
+        v = view_for_rank(step_idx, world, rank, N_VIEWS)
         src = gt_host if host_inputs else gt_dev
         return SceneBatch(src[v:v + 1], [cams[v]], 1.0)
 
@@ -348,9 +358,19 @@ def run_ours(args):
             acc[k_] = acc.get(k_, 0.0) + v_ / reps
     ctx.set_timing(False)
     stage_ms = acc
+    # one more step with the rasterizers counting the (pixel, splat) pairs they evaluate after culling (diagnostic
+    # build of the forward kernel; outside every timed region)
+    ctx.set_pair_counting(True)
+    ctx.read_pair_counts(torch.cuda.current_stream().cuda_stream)
+    stats = one_step(2000, False)
+    pairs_eval_fwd, pairs_eval_bwd = ctx.read_pair_counts(torch.cuda.current_stream().cuda_stream)
+    ctx.set_pair_counting(False)
     if rank == 0:
         counts = (stats.auxes[0].read_num_visible(), stats.auxes[0].read_num_intersections())
+    check = None
     if world > 1:
+        barrier()
+        check = multi_gpu_self_check(args, trainer, splats, start_params, cams, gt_dev, N, K, dev, pg, world, rank)
         barrier()
 
     if rank != 0:
@@ -359,14 +379,19 @@ def run_ours(args):
         return
     V, I = counts
     peak, peak_src = load_peaks()
+    fp32_peak_measured, mufu_peak_measured = ctx.measure_peaks(torch.cuda.current_stream().cuda_stream)
+    fused_tail = world == 1 and not args.no_optim
     stages = []
     for name, ms in stage_ms.items():
-        b = algorithmic_bytes(name, N, V, I, P, T, K)
-        stages.append({"stage": name, "ms": round(ms, 4), "alg_bytes": b,
+        label = name
+        if name == "GatherProjectBackwards" and fused_tail:
+            label = "GatherProjectBackwards+Adam (fused)"
+        b = algorithmic_bytes(label, N, V, I, P, T, K)
+        stages.append({"stage": label, "ms": round(ms, 4), "alg_bytes": b,
                        "gbs": round(b / (ms * 1e-3) / 1e9, 1) if ms > 0 else None,
                        "frac_hbm": round(b / (ms * 1e-3) / 1e9 / peak, 4) if ms > 0 else None})
-    # ---- evaluated (pixel, splat) pairs of the two compositors, as the REFERENCE loops would count them
-    # (R_fwd, R_bwd), from the last step's aux tensors; outside every timed region ----
+    # ---- (pixel, splat) pairs of the two compositors as the REFERENCE loops evaluate them (R_fwd, R_bwd),
+    # from the last step's aux tensors; outside every timed region ----
     aux = stats.auxes[0]
     fi = aux.final_index.to(torch.int64)
     tb = aux.tile_bins.to(torch.int64)
@@ -378,13 +403,36 @@ def run_ours(args):
     opaque = stats.pred_images[0][..., 3] > 0.9998  # the pixel stopped early (T <= 1e-4): walked to final_index + 1
     r_fwd = int(torch.where(nonempty, torch.where(opaque, torch.minimum(fi - start + 2, end - start), end - start),
                             torch.zeros_like(fi)).sum().item())
-    fp32_peak = 148 * 128 * 2 * (clocks.get("sm_max_mhz") or 1965.0) * 1e6 / 1e12  # TFLOP/s, FMA = 2
+    fp32_nominal = 148 * 128 * 2 * ((clocks or {}).get("sm_max_mhz") or 1965.0) * 1e6 / 1e12  # TFLOP/s, FMA = 2
+    fp32_peak = fp32_peak_measured
     flops = {"Rasterize": 26 * r_fwd, "RasterizeBackwards": 64 * r_bwd}  # SURVEY 8d per-pair figures
+    pairs_ref = {"Rasterize": r_fwd, "RasterizeBackwards": r_bwd}
+    pairs_eval = {"Rasterize": pairs_eval_fwd, "RasterizeBackwards": pairs_eval_bwd}
+    # executed FFMA / FMUL / FADD thread-instructions per launch from the committed ncu capture of this workload
+    # (profiles/executed.json, written by profiles/ncu_executed.py); FFMA counts two flops
+    executed = {}
+    try:
+        with open(os.path.join(ROOT, "profiles", "executed.json")) as f:
+            executed = json.load(f)
+    except (OSError, ValueError):
+        pass
     for s_ in stages:
-        if s_["stage"] in flops and s_["ms"] > 0:
-            s_["alg_flops"] = flops[s_["stage"]]
-            s_["tflops"] = round(flops[s_["stage"]] / (s_["ms"] * 1e-3) / 1e12, 2)
-            s_["frac_fp32"] = round(s_["tflops"] / fp32_peak, 4)
+        nm = s_["stage"]
+        if nm in flops and s_["ms"] > 0:
+            sec = s_["ms"] * 1e-3
+            s_["alg_flops"] = flops[nm]
+            s_["tflops"] = round(flops[nm] / sec / 1e12, 2)
+            s_["frac_fp32"] = round(s_["tflops"] / fp32_peak, 4)            # algorithmic: reference pairs x 26 / 64
+            s_["pairs_reference"] = pairs_ref[nm]
+            s_["pairs_evaluated"] = pairs_eval[nm]                           # after the kernel's culling
+            s_["culled_pair_ratio"] = round(pairs_eval[nm] / max(pairs_ref[nm], 1), 4)
+            ex = executed.get(nm) if executed.get("workload") == args.workload else None
+            if ex:
+                ex_flop = 2 * ex["ffma"] + ex["fmul"] + ex["fadd"]
+                s_["executed_flops"] = ex_flop
+                s_["frac_executed"] = round(ex_flop / sec / 1e12 / fp32_peak, 4)  # what the FP32 pipe really did
+                if ex.get("mufu"):
+                    s_["frac_mufu"] = round(ex["mufu"] / sec / 1e12 / mufu_peak_measured, 4)
     dom = max(stages, key=lambda s_: s_["ms"])
     traffic = None
     try:
@@ -393,18 +441,21 @@ def run_ours(args):
     except OSError:
         pass
     if "tflops" in dom:
-        roofline = {"kernel": dom["stage"], "bound": "fp32", "achieved": dom["tflops"], "peak": round(fp32_peak, 1),
-                    "unit": "TFLOP/s", "frac": dom["frac_fp32"], "traffic": traffic,
-                    "peak_source": "148 SMs x 128 FP32 lanes x 2 x max SM clock (no tensor-core or HBM roofline applies: "
-                                   "the kernel is FP32-issue-bound, ncu in profiles/)",
-                    "pairs": r_bwd if dom["stage"] == "RasterizeBackwards" else r_fwd,
+        roofline = {"kernel": dom["stage"], "bound": "fp32", "achieved": dom["tflops"], "peak": round(fp32_peak, 2),
+                    "unit": "TFLOP/s", "frac": dom["frac_fp32"], "frac_executed": dom.get("frac_executed"),
+                    "traffic": traffic,
+                    "peak_source": "measured: FFMA micro-kernel on this device in this run (brush_measure_peaks); "
+                                   f"nominal 148 SMs x 128 lanes x 2 x max clock = {fp32_nominal:.1f}",
+                    "mufu_peak_tops": round(mufu_peak_measured, 3), "frac_mufu": dom.get("frac_mufu"),
+                    "pairs_reference": dom["pairs_reference"], "pairs_evaluated": dom["pairs_evaluated"],
+                    "culled_pair_ratio": dom["culled_pair_ratio"],
                     # the same kernel against the HBM roofline, in the base contract's shape
                     "hbm_view": {"bound": "hbm", "achieved": dom["gbs"], "peak": peak, "unit": "GB/s",
                                  "frac": dom["frac_hbm"], "traffic": traffic, "peak_source": peak_src},
-                    "note": "achieved = 64 (bwd) / 26 (fwd) algorithmic flop per reference-evaluated (pixel, splat) "
-                            "pair / kernel time; pairs the kernel culls before evaluating them still count as work "
-                            "done. HBM view of the same kernel: "
-                            f"{dom['gbs']} GB/s of algorithmic bytes = {dom['frac_hbm']} of {peak} GB/s ({peak_src})"}
+                    "note": "frac = ALGORITHMIC flops (64 bwd / 26 fwd per pair the reference loop evaluates) / kernel "
+                            "time / measured FP32 peak: pairs the kernel culls before evaluating still count, so it can "
+                            "exceed the hardware fraction; frac_executed = executed FFMA*2 + FMUL + FADD thread "
+                            "instructions (ncu, profiles/executed.json) / kernel time / the same peak"}
     else:
         roofline = {"kernel": dom["stage"], "bound": "hbm", "achieved": dom["gbs"], "peak": peak, "unit": "GB/s",
                     "frac": dom["frac_hbm"], "traffic": traffic, "peak_source": peak_src}
@@ -414,8 +465,8 @@ def run_ours(args):
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {N} random Gaussians, SH degree {sc.sh_degree}, {W}x{H}, one view per "
                                f"GPU per step ({N_VIEWS} views; targets = the scene's own renders, start = colours and opacities perturbed), loss 0.8 L1 - 0.2 SSIM "
-                               f"(reference default), {'fused Adam' if not args.no_optim else 'no optimizer'}, "
-                               f"{exchange_desc}",
+                               f"(reference default), {'fused Adam' if not args.no_optim else 'no optimizer'}, refine "
+                               f"statistics accumulated every step (warmup_steps = 0), {exchange_desc}",
                    "num_visible": V, "num_intersections": I, "views": N_VIEWS, "isect_capacity": args.capacity,
                    "l2": "inputs larger than L2 (236 MB of parameters + 472 MB of Adam moments per step vs 126 MB L2)"},
         "e2e": {"value": round(world * 1000.0 / ms_e2e_step, 3), "unit": UNIT, "ms_per_step": round(ms_e2e_step, 4),
@@ -423,13 +474,96 @@ def run_ours(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": roofline,
+        "peaks_measured": {"fp32_tflops": round(fp32_peak_measured, 2), "mufu_tops": round(mufu_peak_measured, 3),
+                           "fp32_nominal_tflops": round(fp32_nominal, 1), "hbm_gbs": peak, "hbm_source": peak_src},
         "stages": stages,
     }
+    if check is not None:
+        out.update(check)
     if not args.no_cpu_baseline and world == 1:
-        out["cpu_baseline"] = cpu_baseline_sample(args, sc, 1)
+        out["cpu_baseline"] = cpu_baseline_sample(args, sc)
     print(json.dumps(out))
     if world > 1:
         torch.distributed.destroy_process_group()
+
+
+def _checksum64(t):
+    """Two order-sensitive 64-bit sums of a tensor's bit pattern (device side; wraps mod 2^64)."""
+    import torch
+
+    bits = t.detach().contiguous().view(torch.int32).reshape(-1).to(torch.int64) & 0xFFFFFFFF
+    idx = torch.arange(bits.numel(), device=bits.device, dtype=torch.int64) % 65521 + 1
+    return torch.stack([bits.sum(), (bits * idx).sum()])
+
+
+def multi_gpu_self_check(args, trainer, splats, start_params, cams, gt_dev, N, K, dev, pg, world, rank):
+    """world > 1, outside every timed region.  (a) The replicas the timed run left behind must be bit-identical on
+    every rank (64-bit checksums of every parameter group, all-gathered).  (b) The exchange mode under test and the
+    plain NCCL all-reduce + replicated Adam are each run for the same few steps from the same start (the parameters
+    the bench started from) on fresh trainers; the maximum relative parameter difference, the fraction of parameters
+    within 2e-5 relative + 2e-6 absolute (the tolerance of tests/test_gpu_peer.py: Adam normalises the step, so a
+    gradient within atomics-order noise of zero may flip its sign) and the loss difference are reported.  The
+    reference is single-device (train.rs:216-219 asserts one view), so the NCCL path -- the mean over the batch of
+    train.rs:229-268 done with a library collective -- is the oracle of the exchange kernels."""
+    import torch
+    import torch.distributed as dist
+
+    from brush_b200 import Splats
+    from brush_b200.parallel import view_for_rank
+    from brush_b200.train import SceneBatch, SplatTrainer, TrainConfig
+
+    names = ("means", "sh_coeffs", "rotation", "raw_opacity", "log_scales")
+    mine = torch.stack([_checksum64(p) for p in (splats.means, splats.sh_coeffs, splats.rotation, splats.raw_opacity,
+                                                 splats.log_scales)])
+    every = [torch.zeros_like(mine) for _ in range(world)]
+    dist.all_gather(every, mine, group=pg)
+    identical = all(bool(torch.equal(every[0], e)) for e in every)
+    mode = trainer.exchange
+    steps = max(2, min(args.steps, 6))
+    results = {}
+    for m in (mode, "nccl"):
+        sp = Splats(*[p.clone() for p in start_params])
+        tr = SplatTrainer(N, TrainConfig(max_refine_step=0, warmup_steps=0), dev, sh_coeffs_per_channel=K,
+                          process_group=pg, isect_capacity=args.capacity, exchange=m)
+        sp = tr.adopt(sp)
+        loss = None
+        for s in range(steps):
+            v = view_for_rank(s, world, rank, N_VIEWS)
+            sp, st = tr.step(SceneBatch(gt_dev[v:v + 1], [cams[v]], 1.0), sp)
+            loss = st.loss
+        torch.cuda.synchronize(dev)
+        results[m] = ([p.detach().clone() for p in sp.params()], float(loss),
+                      tr.grad_2d_accum.clone(), tr.xy_grad_counts.clone())
+        del tr, sp
+    a, b = results[mode], results["nccl"]
+    max_rel, close_frac, n_all = 0.0, 0.0, 0
+    per_group = {}
+    for name, pa, pb in zip(names, a[0], b[0]):
+        d = (pa - pb).abs()
+        rel = d / pb.abs().clamp_min(1e-3)
+        close = d <= 2e-5 * pb.abs() + 2e-6
+        per_group[name] = {"max_rel": float(rel.max()), "frac_close": float(close.float().mean())}
+        max_rel = max(max_rel, float(rel.max()))
+        close_frac += float(close.sum())
+        n_all += pa.numel()
+    mine2 = torch.stack([_checksum64(p) for p in a[0]])
+    every2 = [torch.zeros_like(mine2) for _ in range(world)]
+    dist.all_gather(every2, mine2, group=pg)
+    identical2 = all(bool(torch.equal(every2[0], e)) for e in every2)
+    out = {
+        "replicas_identical": bool(identical and identical2),
+        "exchange_check": {
+            "mode": mode, "against": "nccl all-reduce + replicated Adam", "steps": steps,
+            "replicas_identical_after_timed_run": bool(identical),
+            "replicas_identical_after_check_run": bool(identical2),
+            "max_rel_param_diff": max_rel, "frac_params_close": close_frac / max(n_all, 1),
+            "loss": a[1], "loss_nccl": b[1], "loss_abs_diff": abs(a[1] - b[1]),
+            "visible_counts_equal": bool(torch.equal(a[3], b[3])),
+            "grad_norm_stat_frac_close": float(torch.isclose(a[2], b[2], rtol=1e-4, atol=1e-9).float().mean()),
+            "per_group": per_group,
+        },
+    }
+    return out
 
 
 def _oracle_iteration(O, u, sc, v_out, capacity):
@@ -440,12 +574,22 @@ def _oracle_iteration(O, u, sc, v_out, capacity):
     return aux
 
 
+def _cpu_threads():
+    """Every host core this process may run on -- NOT omp_get_max_threads(): torchrun exports OMP_NUM_THREADS=1 to
+    its workers, which would silently turn the reference arm into a one-thread run at N > 1."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def _oracle_setup(args, sc):
     from oracle import pyoracle as O  # the ONLY place bench.py touches oracle/: the CPU baseline legs
 
     O.build()
-    threads = O.max_threads()
-    O.set_threads(threads)
+    O.use_timed()  # -O3 -march=native build made on THIS machine (oracle/Makefile `timed`, BASELINE.md section 3)
+    threads = _cpu_threads()
+    O.set_threads(threads)  # num_threads(...) clause on every parallel region: overrides OMP_NUM_THREADS
     W, H = sc.width, sc.height
     vm = np.eye(4, dtype=np.float32)
     vm[2, 3] = 8.0  # bench camera (0,0,-8), identity (benches/render_bench.rs:163-174)
@@ -454,22 +598,40 @@ def _oracle_setup(args, sc):
     return O, u, v_out, threads
 
 
-def cpu_baseline_sample(args, sc, iters):
+def _timed_samples(fn, n_samples, inner):
+    """divan's shape (benches/render_bench.rs:29-30,199): n_samples samples of `inner` back-to-back iterations;
+    returns the per-iteration seconds of every sample."""
+    out = []
+    for _ in range(n_samples):
+        t0 = time.perf_counter()
+        for _ in range(inner):
+            fn()
+        out.append((time.perf_counter() - t0) / inner)
+    return out
+
+
+def cpu_baseline_sample(args, sc):
     O, u, v_out, threads = _oracle_setup(args, sc)
-    _oracle_iteration(O, u, sc, v_out, args.capacity)  # warm (page-in, allocator)
     t0 = time.perf_counter()
-    for _ in range(iters):
-        _oracle_iteration(O, u, sc, v_out, args.capacity)
-    dt = (time.perf_counter() - t0) / iters
+    _oracle_iteration(O, u, sc, v_out, args.capacity)  # warm (page-in, allocator) + probe
+    probe = time.perf_counter() - t0
+    inner = 4 if probe < 0.5 else 1               # small configs: the reference's 4 inner iterations per sample
+    n_samples = 5 if probe * 5 * inner <= 40.0 else max(1, int(40.0 / (probe * inner)))
+    per_it = _timed_samples(lambda: _oracle_iteration(O, u, sc, v_out, args.capacity), n_samples, inner)
+    dt = statistics.median(per_it)
     return {"value": round(1.0 / dt, 4), "unit": UNIT, "cores": threads, "kind": "port",
-            "sample": f"{iters} full fwd+bwd iteration(s) of the whole workload ({sc.means.shape[0]} Gaussians, "
-                      f"{sc.width}x{sc.height}, bench camera, v_out = 1/(4P)) by the C++ oracle with OpenMP on "
-                      f"{threads} threads; {dt:.2f} s per iteration"}
+            "stage_ms": {k: round(v * 1e3, 2) for k, v in O.stage_seconds().items()},
+            "sample": f"median of {n_samples} sample(s) x {inner} full fwd+bwd iteration(s) of the whole workload "
+                      f"({sc.means.shape[0]} Gaussians, {sc.width}x{sc.height}, bench camera, v_out = 1/(4P)) by the "
+                      f"timed build of the C++ oracle port (-O3 -march=native, thread-private f32 accumulators) with "
+                      f"OpenMP on {threads} threads; {dt:.3f} s per iteration (min {min(per_it):.3f}, max {max(per_it):.3f})"}
 
 
 def run_reference(args):
     """The reference arm: the reference's own implementation of the path is WGSL through wgpu, which cannot run on
-    this box (no Rust toolchain, no graphics stack), so this times the oracle port of it on all host cores."""
+    this box (no Rust toolchain, no graphics stack), so this times the oracle port of it on all host cores.  Always
+    the WHOLE workload: if K + W full iterations do not fit the time budget, fewer iterations are timed (and the
+    line says so); the workload is never made smaller."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -477,41 +639,41 @@ def run_reference(args):
 
     sc = scene.make_config_scene(args.workload, args.n_override)
     O, u, v_out, threads = _oracle_setup(args, sc)
-    # bounded sample: keep the whole run within a few minutes whatever K and W are
     t0 = time.perf_counter()
-    _oracle_iteration(O, u, sc, v_out, args.capacity)
+    aux = _oracle_iteration(O, u, sc, v_out, args.capacity)  # untimed: page-in + the probe that sizes the run
     probe = time.perf_counter() - t0
     budget = float(os.environ.get("BRUSH_REF_BUDGET_S", "240"))
-    stride = 1
-    while probe / stride * (args.steps + args.warmup) > budget and stride < 64:
-        stride *= 2
-    if stride > 1:  # every stride-th Gaussian: fewer splats at the same resolution; value is it/s ON THAT SAMPLE
-        sc.means, sc.log_scales, sc.quats = sc.means[::stride].copy(), sc.log_scales[::stride].copy(), sc.quats[::stride].copy()
-        sc.sh_coeffs, sc.raw_opacity = sc.sh_coeffs[::stride].copy(), sc.raw_opacity[::stride].copy()
-    for _ in range(max(args.warmup - 1, 0)):
+    affordable = max(1, int(budget / max(probe, 1e-6)))
+    warm = max(0, min(args.warmup - 1, affordable - 1))  # the probe was the first warm-up iteration
+    steps = max(1, min(args.steps, affordable - warm))
+    for _ in range(warm):
         _oracle_iteration(O, u, sc, v_out, args.capacity)
-    t0 = time.perf_counter()
-    aux = None
-    for _ in range(args.steps):
+    per_it = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
         aux = _oracle_iteration(O, u, sc, v_out, args.capacity)
-    dt = (time.perf_counter() - t0) / args.steps
+        per_it.append(time.perf_counter() - t0)
+    dt = sum(per_it) / len(per_it)
     val = round(1.0 / dt, 4)
     N, K = sc.means.shape[0], sc.sh_coeffs.shape[1]
+    reduced = "" if steps == args.steps else (f"; only {steps} of the requested {args.steps} steps were timed to stay "
+                                              f"within {budget:.0f} s (the workload itself is never reduced)")
     out = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": round(dt * 1e3, 2), "higher_is_better": True, "scaling": "weak",
+        "steps_timed": steps, "warmup": args.warmup, "ms_per_step": round(dt * 1e3, 2),
+        "ms_per_step_median": round(statistics.median(per_it) * 1e3, 2), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {N} random Gaussians, SH degree {sc.sh_degree}, {sc.width}x"
                                f"{sc.height}, fwd+bwd of one view per step on the host CPU (no optimizer; the "
                                "reference bench shape, benches/render_bench.rs:176-184)",
                    "num_visible": aux.num_visible, "num_intersections": aux.num_intersections},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": (f"every step = one full fwd+bwd of the whole workload by the C++ oracle (OpenMP, "
-                                    f"{threads} threads); the reference's wgpu path is unavailable on this box"
-                                    + (f"; SUBSAMPLED to every {stride}th Gaussian to fit the time budget" if stride > 1
-                                       else ""))},
+                         "sample": (f"every step = one full fwd+bwd of the whole workload by the timed build of the C++ "
+                                    f"oracle port (-O3 -march=native, OpenMP, {threads} threads = every core this "
+                                    f"process may use); the reference's wgpu path is unavailable on this box" + reduced)},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        "stage_ms": {k: round(v * 1e3, 2) for k, v in O.stage_seconds().items()},
     }
     print(json.dumps(out))
 

@@ -104,6 +104,9 @@ _SIGS = {
     "brush_ctx_set_timing": (C.c_int, [C.c_void_p, C.c_int]),
     "brush_stage_times_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.c_int, C.c_void_p]),
     "brush_ctx_check": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "brush_measure_peaks": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_void_p]),
+    "brush_ctx_set_pair_counting": (C.c_int, [C.c_void_p, C.c_int]),
+    "brush_ctx_read_pair_counts": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64), C.c_void_p]),
     "brush_render_forward": (C.c_int, [C.c_void_p, C.POINTER(BrushUniforms), C.c_uint32, C.c_uint32] +
                              [C.c_void_p] * 5 + [C.c_int, C.c_void_p, C.POINTER(BrushAux), C.c_void_p]),
     "brush_render_backward": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32] + [C.c_void_p] * 6 +
@@ -208,6 +211,21 @@ class Context:
         arr = (C.c_float * len(STAGE_NAMES))()
         self.check(lib().brush_stage_times_ms(self._h, arr, len(STAGE_NAMES), C.c_void_p(stream)))
         return dict(zip(STAGE_NAMES, list(arr)))
+
+    def measure_peaks(self, stream=0):
+        """(FP32 TFLOP/s, 1e12 ex2/s) of this device, measured by micro-kernels; synchronises."""
+        f, m = C.c_float(), C.c_float()
+        self.check(lib().brush_measure_peaks(self._h, C.byref(f), C.byref(m), C.c_void_p(stream)))
+        return float(f.value), float(m.value)
+
+    def set_pair_counting(self, enabled: bool):
+        self.check(lib().brush_ctx_set_pair_counting(self._h, int(enabled)))
+
+    def read_pair_counts(self, stream=0):
+        """{forward, backward} (pixel, splat) pairs the rasterizers evaluated since the last read; synchronises."""
+        arr = (C.c_uint64 * 2)()
+        self.check(lib().brush_ctx_read_pair_counts(self._h, arr, C.c_void_p(stream)))
+        return int(arr[0]), int(arr[1])
 
     def sync_check(self, stream=0):
         """Synchronises and raises CapacityError if any forward since the last check overflowed."""

@@ -30,6 +30,7 @@ UNITS = {
     "dp_adam.cu": [],
     "ssim.cu": [],
     "refine.cu": [],
+    "peaks.cu": [],
     "api.cu": [],
 }
 
@@ -79,7 +80,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     with ThreadPoolExecutor(max_workers=8) as ex:
         objs = list(ex.map(compile_one, units.items()))
-    cmd = [nvcc, *ARCH, "-shared", "-o", SO, *objs, "-Xcompiler", "-fPIC"]
+    # -cudart shared: one CUDA runtime per process (the host framework's), and no runtime code inside the product .so
+    cmd = [nvcc, *ARCH, "-shared", "-cudart", "shared", "-o", SO, *objs, "-Xcompiler", "-fPIC", "-ldl"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

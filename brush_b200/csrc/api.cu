@@ -7,9 +7,22 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>  // header-only; ranges cost nothing unless a tool (nsys, ncu --nvtx) is attached
+
 #include "internal.h"
 
 using namespace brush;
+
+// NVTX range names == the reference's tracing spans (crates/brush-render/src/render.rs:127-267,515-577, collected by
+// crates/sync-span/src/lib.rs:26-41), spelling included ("ProjectVisibile", "Tile sort").  The fused per-splat
+// backward covers the reference's "GatherGrads" and "ProjectBackwards" spans.
+static const char* const kStageSpan[BRUSH_STAGE_COUNT] = {
+    "ProjectSplats", "DepthSort", "ProjectVisibile", "PrefixSum", "MapGaussiansToIntersect", "Tile sort",
+    "GetTileBinEdges", "Rasterize", "RasterizeBackwards", "GatherGrads+ProjectBackwards"};
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
 
 struct Buf {
     void* p = nullptr;
@@ -21,6 +34,7 @@ struct brush_ctx {
     std::string err;
     int fused64 = 0;
     int timing = 0;
+    int pair_counting = 0;  // diagnostic: the rasterizers count the pairs they evaluate (sticky block, bytes 128..143)
     // scratch, grown on demand (growth synchronises; steady state never allocates)
     Buf control, presort_gid, depth_bits, depth_sorted, num_tiles_hit, keys_tmp, vals_tmp, hist, lb, tickets,
         tile_ids_unsorted, cg_unsorted, tile_ids_sorted, v_projected, sticky, loss_scratch, visible_mask, tile_masks, tile_boxes,
@@ -71,6 +85,7 @@ struct StageTimer {
     cudaStream_t st;
     int stage;
     StageTimer(brush_ctx* c_, cudaStream_t s, int stage_) : c(c_), st(s), stage(stage_) {
+        nvtxRangePushA(kStageSpan[stage]);
         if (c->timing) {
             cudaEventRecord(c->ev[stage][0], st);
             c->ev_used[stage] = true;
@@ -78,12 +93,12 @@ struct StageTimer {
     }
     ~StageTimer() {
         if (c->timing) cudaEventRecord(c->ev[stage][1], st);
+        nvtxRangePop();
     }
 };
 
-__global__ void write_uniforms_kernel(const __grid_constant__ BrushUniforms u, int32_t* dst) {
-    const int32_t* src = reinterpret_cast<const int32_t*>(&u);
-    if (threadIdx.x < 28) dst[threadIdx.x] = src[threadIdx.x];
+static unsigned long long* pair_counter_of(brush_ctx* c, int which) {
+    return c->pair_counting ? reinterpret_cast<unsigned long long*>((char*)c->sticky.p + 128) + which : nullptr;
 }
 
 static bool valid_k(uint32_t K) { return K == 1 || K == 4 || K == 9 || K == 16 || K == 25; }
@@ -182,6 +197,27 @@ int brush_ctx_set_timing(brush_ctx* ctx, int enabled) {
     return BRUSH_OK;
 }
 
+int brush_ctx_set_pair_counting(brush_ctx* ctx, int enabled) {
+    if (!ctx) return BRUSH_E_INVALID;
+    ctx->pair_counting = enabled ? 1 : 0;
+    return BRUSH_OK;
+}
+int brush_ctx_read_pair_counts(brush_ctx* ctx, uint64_t* out_host, void* stream) {
+    if (!ctx || !out_host) return BRUSH_E_INVALID;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize((cudaStream_t)stream));
+    CU(cudaMemcpy(out_host, (char*)ctx->sticky.p + 128, 16, cudaMemcpyDeviceToHost));
+    CU(cudaMemset((char*)ctx->sticky.p + 128, 0, 16));
+    return BRUSH_OK;
+}
+int brush_measure_peaks(brush_ctx* ctx, float* fp32_tflops_host, float* mufu_tops_host, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    CU(cudaSetDevice(ctx->device));
+    int r = measure_peaks(fp32_tflops_host, mufu_tops_host, (float*)((char*)ctx->sticky.p + 192), (cudaStream_t)stream);
+    if (r != 0) return cuda_fail(ctx, (cudaError_t)r, "measure_peaks");
+    return BRUSH_OK;
+}
+
 int brush_stage_times_ms(brush_ctx* ctx, float* out_host, int n, void* stream) {
     if (!ctx || !out_host) return BRUSH_E_INVALID;
     CU(cudaStreamSynchronize((cudaStream_t)stream));
@@ -241,6 +277,7 @@ int brush_render_forward(brush_ctx* ctx, const BrushUniforms* uniforms_host, uin
         return fail(ctx, BRUSH_E_INVALID, "N and isect_capacity must be < 2^30");
     cudaStream_t st = (cudaStream_t)stream;
     CU(cudaSetDevice(ctx->device));
+    NvtxRange span("render_forward");  // render.rs:71
 
     BrushUniforms u = *uniforms_host;
     u.tile_bounds[0] = (u.img_size[0] + TILE_WIDTH - 1) / TILE_WIDTH;  // render.rs:82-85
@@ -319,10 +356,11 @@ int brush_render_forward(brush_ctx* ctx, const BrushUniforms* uniforms_host, uin
         z.p[1] = aux->num_visible; z.bytes[1] = 4;
         z.p[2] = aux->num_intersections; z.bytes[2] = 4;
         z.p[3] = gfc; z.bytes[3] = (size_t)N * 4;  // int_zeros, render.rs:124
+        z.p[4] = aux->tile_bins; z.bytes[4] = (size_t)num_tiles * 8;  // int_zeros, render.rs:241-244
+        z.words_dst = (uint32_t*)aux->uniforms_buffer; z.n_words = 28;  // the uniform upload, render.rs:102-116
+        memcpy(z.words, &u, sizeof(u));
         CU(zero_multi_async(z, st));
     }
-    g_launch_count++;
-    write_uniforms_kernel<<<1, 32, 0, st>>>(u, aux->uniforms_buffer);
 
     {   // render.rs:127-142
         StageTimer t(ctx, st, BRUSH_STAGE_PROJECT_SPLATS);
@@ -377,7 +415,8 @@ int brush_render_forward(brush_ctx* ctx, const BrushUniforms* uniforms_host, uin
     {   // render.rs:267-307
         StageTimer t(ctx, st, BRUSH_STAGE_RASTERIZE);
         launch_rasterize(cam, (uint32_t*)aux->compact_gid_from_isect, (uint32_t*)aux->tile_bins,
-                         aux->projected_splats, raster_u32, out_img, (uint32_t*)aux->final_index, st);
+                         aux->projected_splats, raster_u32, out_img, (uint32_t*)aux->final_index,
+                         pair_counter_of(ctx, 0), st);
     }
     CU(cudaGetLastError());
     return BRUSH_OK;
@@ -395,6 +434,7 @@ int brush_render_backward(brush_ctx* ctx, uint32_t N, uint32_t K, const float* m
         return fail(ctx, BRUSH_E_INVALID, "null argument");
     cudaStream_t st = (cudaStream_t)stream;
     CU(cudaSetDevice(ctx->device));
+    NvtxRange span("render_gaussians backwards");  // render.rs:474
     BrushUniforms u;
     {
         int r = uniforms_of(ctx, aux, N, K, st, &u);
@@ -413,7 +453,8 @@ int brush_render_backward(brush_ctx* ctx, uint32_t N, uint32_t K, const float* m
         StageTimer t(ctx, st, BRUSH_STAGE_RASTERIZE_BWD);
         launch_rasterize_backward(cam, (uint32_t*)aux->compact_gid_from_isect, (uint32_t*)aux->tile_bins,
                                   aux->projected_splats, (uint32_t*)aux->global_from_compact_gid,
-                                  (uint32_t*)aux->final_index, out_img, v_out_img, (float*)ctx->v_projected.p, st);
+                                  (uint32_t*)aux->final_index, out_img, v_out_img, (float*)ctx->v_projected.p,
+                                  pair_counter_of(ctx, 1), st);
     }
     {   // render.rs:542-594
         StageTimer t(ctx, st, BRUSH_STAGE_GATHER_PROJECT_BWD);
@@ -497,7 +538,7 @@ int brush_render_backward_rows(brush_ctx* ctx, uint32_t N, uint32_t K, const flo
         StageTimer t(ctx, st, BRUSH_STAGE_RASTERIZE_BWD);
         launch_rasterize_backward(cam, (uint32_t*)aux->compact_gid_from_isect, (uint32_t*)aux->tile_bins,
                                   aux->projected_splats, (uint32_t*)aux->global_from_compact_gid,
-                                  (uint32_t*)aux->final_index, out_img, v_out_img, rows, st);
+                                  (uint32_t*)aux->final_index, out_img, v_out_img, rows, pair_counter_of(ctx, 1), st);
     }
     const uint8_t* mask = nullptr;
     r = visible_mask_for(ctx, aux, N, st, &mask);
@@ -561,7 +602,8 @@ int brush_render_backward_adam(brush_ctx* ctx, uint32_t N, uint32_t K, const Bru
         StageTimer t(ctx, st, BRUSH_STAGE_RASTERIZE_BWD);
         launch_rasterize_backward(cam, (uint32_t*)aux->compact_gid_from_isect, (uint32_t*)aux->tile_bins,
                                   aux->projected_splats, (uint32_t*)aux->global_from_compact_gid,
-                                  (uint32_t*)aux->final_index, out_img, v_out_img, (float*)ctx->v_projected.p, st);
+                                  (uint32_t*)aux->final_index, out_img, v_out_img, (float*)ctx->v_projected.p,
+                                  pair_counter_of(ctx, 1), st);
     }
     const FusedAdamLaunch A = fused_adam_launch(s, beta1, beta2, eps, step, grad_scale);
     {   // gather_grads + project_backwards + normalisation VJP + Adam in one pass

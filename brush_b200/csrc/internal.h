@@ -70,11 +70,15 @@ void launch_tile_bins(const uint32_t* sorted_tile_ids, const uint64_t* sorted_ke
                       uint64_t capacity, uint32_t num_tiles, uint32_t* tile_bins, cudaStream_t st);
 void launch_rasterize(const Cam& cam, const uint32_t* compact_gid_from_isect, const uint32_t* tile_bins,
                       const float* projected, int raster_u32, void* out_img, uint32_t* final_index,
-                      cudaStream_t st);
+                      unsigned long long* pair_counter /* diagnostic, normally null */, cudaStream_t st);
 void launch_rasterize_backward(const Cam& cam, const uint32_t* compact_gid_from_isect, const uint32_t* tile_bins,
                                const float* projected, const uint32_t* global_from_compact,
                                const uint32_t* final_index, const float* out_img, const float* v_out_img,
-                               float* v_projected /* [N,VP_STRIDE] by GLOBAL id, zeroed */, cudaStream_t st);
+                               float* v_projected /* [N,VP_STRIDE] by GLOBAL id, zeroed */,
+                               unsigned long long* pair_counter /* diagnostic, normally null */, cudaStream_t st);
+
+// ---- peaks.cu: FP32 / MUFU micro-kernels, the measured roofline denominators of the rasterizers ----
+int measure_peaks(float* fp32_tflops, float* mufu_tops, float* sink, cudaStream_t st);
 
 // ---- backward.cu ----
 void launch_gather_project_backward(const Cam& cam, uint32_t N, uint32_t K, const float* means,
@@ -141,8 +145,16 @@ int launch_views_adam(const ViewsLaunch& X, uint32_t N, uint32_t K, const float*
 // step: driver memsets and small copies may be routed through a copy engine, where they queue behind a concurrent
 // host->device upload of the next training view on another stream and stall the compute stream.
 cudaError_t zero_async(void* p, size_t bytes, cudaStream_t st);
-// Up to four 4-byte-aligned regions in ONE launch.
-struct ZeroSegs { void* p[4]; size_t bytes[4]; };
+// Up to six 4-byte-aligned regions in ONE launch, plus (optionally) up to 32 words copied from the launch
+// parameters to words_dst: a forward's RenderUniforms ride along with its zero-fills (render.rs:102-124).
+constexpr int ZERO_MAX_SEGS = 6;
+struct ZeroSegs {
+    void* p[ZERO_MAX_SEGS];
+    size_t bytes[ZERO_MAX_SEGS];
+    uint32_t* words_dst;
+    uint32_t n_words;
+    uint32_t words[32];
+};
 cudaError_t zero_multi_async(const ZeroSegs& z, cudaStream_t st);
 extern std::atomic<uint64_t> g_launch_count;  // kernels launched by this library (bench.py's gpu_launches)
 struct AdamSeg {

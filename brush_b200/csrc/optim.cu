@@ -223,8 +223,9 @@ cudaError_t zero_async(void* p, size_t bytes, cudaStream_t st) {
 __global__ void __launch_bounds__(256)
 zero_multi_kernel(const __grid_constant__ ZeroSegs z) {
     const size_t stride = (size_t)gridDim.x * 256u, t0 = (size_t)blockIdx.x * 256u + threadIdx.x;
+    if (z.words_dst && t0 < z.n_words) z.words_dst[t0] = z.words[t0];
 #pragma unroll
-    for (int s = 0; s < 4; s++) {
+    for (int s = 0; s < ZERO_MAX_SEGS; s++) {
         if (!z.bytes[s]) continue;
         const uintptr_t a = (uintptr_t)z.p[s];
         const size_t head = (16 - (a & 15u)) & 15u;  // bytes before the first 16-byte boundary (multiple of 4)
@@ -240,8 +241,8 @@ zero_multi_kernel(const __grid_constant__ ZeroSegs z) {
 }
 cudaError_t zero_multi_async(const ZeroSegs& z, cudaStream_t st) {
     size_t mx = 0;
-    for (int s = 0; s < 4; s++) mx = z.bytes[s] > mx ? z.bytes[s] : mx;
-    if (!mx) return cudaSuccess;
+    for (int s = 0; s < ZERO_MAX_SEGS; s++) mx = z.bytes[s] > mx ? z.bytes[s] : mx;
+    if (!mx && !z.words_dst) return cudaSuccess;
     size_t blocks = (mx / 16 + 255) / 256;
     blocks = blocks < 1 ? 1 : (blocks > 148 * 8 ? 148 * 8 : blocks);
     g_launch_count++;

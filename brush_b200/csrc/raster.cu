@@ -30,7 +30,8 @@ tile_bins_kernel(const uint32_t* __restrict__ tile_ids, const uint64_t* __restri
 
 void launch_tile_bins(const uint32_t* sorted_tile_ids, const uint64_t* sorted_keys64, const int32_t* n_isect_dev,
                       uint64_t capacity, uint32_t num_tiles, uint32_t* tile_bins, cudaStream_t st) {
-    cudaMemsetAsync(tile_bins, 0, (size_t)num_tiles * 2 * sizeof(uint32_t), st);  // render.rs:241-244
+    // tile_bins was zero-filled by the forward's single init launch (int_zeros, render.rs:241-244)
+    (void)num_tiles;
     if (capacity == 0) return;
     uint64_t blocks = (capacity + 255) / 256;
     if (blocks > 148 * 16) blocks = 148 * 16;
@@ -67,6 +68,8 @@ constexpr uint32_t SM_BYTES = SM_LIST + LIST_STRIDE * (TILE_SIZE / 32);
 // The forward has shared memory to spare and keeps full 32-bit entries (no PRMT per entry).
 constexpr uint32_t LIST_STRIDE32 = 4 * (TILE_SIZE + LIST_PAD);
 constexpr uint32_t SM_BYTES_FWD = SM_LIST + LIST_STRIDE32 * (TILE_SIZE / 32);
+
+constexpr uint32_t NO_CONTRIBUTOR = 0xffffffffu;      // "no splat of this batch contributed" (never a shared-window address)
 
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
@@ -237,11 +240,15 @@ __device__ __forceinline__ uint32_t cull_to_list(uint32_t sbase, uint32_t list_a
     return n_list;
 }
 
-template <bool RASTER_U32>
+// COUNT: the diagnostic build of the kernel that also counts the (pixel, splat) pairs it evaluates (32 lanes x the
+// list entries each warp walks, padding included) into *pair_counter; launched only while brush_ctx_set_pair_counting
+// is on (bench.py's "pairs_evaluated", outside every timed region).
+template <bool RASTER_U32, bool COUNT>
 __global__ void __launch_bounds__(TILE_SIZE, 5)  // 48 registers: five CTAs per SM (measured best of 4 / 5 / 6)
 rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ compact_gid_from_isect,
                  const uint32_t* __restrict__ tile_bins, const float* __restrict__ projected,
-                 void* __restrict__ out_img, uint32_t* __restrict__ final_index) {
+                 void* __restrict__ out_img, uint32_t* __restrict__ final_index,
+                 unsigned long long* __restrict__ pair_counter) {
     __shared__ __align__(16) unsigned char smem[SM_BYTES_FWD];
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(smem);
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
@@ -260,6 +267,7 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
     float T = inside ? 1.0f : -1.0f;
     float pr = 0.f, pg = 0.f, pb = 0.f;
     uint32_t final_idx = 0;
+    uint32_t groups_walked = 0;
     if (tid == 0) init_dummy_slot(sbase);
 
     for (uint32_t b = 0; b < num_batches; b++) {
@@ -283,8 +291,9 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
         // has no per-splat compare / select on the compositing state: the ALU pipe (compares, selects, min)
         // was this kernel's limiter (ncu: 61% ALU at 78% issue).  Same arithmetic in both paths, so the result
         // does not depend on which one ran.
-        uint32_t final_a = 0;
+        uint32_t final_a = NO_CONTRIBUTOR;
         for (uint32_t i = 0; i < n_list; i += LIST_PAD) {
+            if (COUNT) groups_walked++;
             const uint4 a4 = lds128u(list_addr + 4u * i);
             const uint32_t aa[4] = {a4.x, a4.y, a4.z, a4.w};
             const bool live0 = T > 0.0f;
@@ -331,8 +340,9 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
             }
             if (__all_sync(0xffffffffu, T <= 0.0f)) break;
         }
-        if (final_a) final_idx = batch_start + ((final_a - sbase) >> 4);
+        if (final_a != NO_CONTRIBUTOR) final_idx = batch_start + ((final_a - sbase) >> 4);
     }
+    if (COUNT && lane == 0 && groups_walked) atomicAdd(pair_counter, (unsigned long long)groups_walked * (LIST_PAD * 32u));
     if (inside) {
         const size_t pix_id = (size_t)px + (size_t)py * cam.img_w;
         const float a = 1.0f - fabsf(T);
@@ -351,16 +361,16 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
 
 void launch_rasterize(const Cam& cam, const uint32_t* compact_gid_from_isect, const uint32_t* tile_bins,
                       const float* projected, int raster_u32, void* out_img, uint32_t* final_index,
-                      cudaStream_t st) {
+                      unsigned long long* pair_counter, cudaStream_t st) {
     if (cam.tiles_x == 0 || cam.tiles_y == 0) return;
     dim3 grid(cam.tiles_x, cam.tiles_y);
     g_launch_count++;
-    if (raster_u32)
-        rasterize_kernel<true><<<grid, TILE_SIZE, 0, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
-                                                           out_img, final_index);
-    else
-        rasterize_kernel<false><<<grid, TILE_SIZE, 0, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
-                                                            out_img, final_index);
+#define RK_ARGS cam, compact_gid_from_isect, tile_bins, projected, out_img, final_index, pair_counter
+    if (raster_u32 && pair_counter) rasterize_kernel<true, true><<<grid, TILE_SIZE, 0, st>>>(RK_ARGS);
+    else if (raster_u32) rasterize_kernel<true, false><<<grid, TILE_SIZE, 0, st>>>(RK_ARGS);
+    else if (pair_counter) rasterize_kernel<false, true><<<grid, TILE_SIZE, 0, st>>>(RK_ARGS);
+    else rasterize_kernel<false, false><<<grid, TILE_SIZE, 0, st>>>(RK_ARGS);
+#undef RK_ARGS
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -471,7 +481,8 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
                           const uint32_t* __restrict__ tile_bins, const float* __restrict__ projected,
                           const uint32_t* __restrict__ global_from_compact,
                           const uint32_t* __restrict__ final_index, const float* __restrict__ out_img,
-                          const float* __restrict__ v_out_img, float* __restrict__ v_projected) {
+                          const float* __restrict__ v_out_img, float* __restrict__ v_projected,
+                          unsigned long long* __restrict__ pair_counter) {
     extern __shared__ __align__(16) unsigned char smem[];
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(smem);
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
@@ -529,6 +540,8 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
         const uint32_t a_lo = !inside ? 0xffffffffu
                                       : sbase + (batch_end - 1u > final_isect ? (batch_end - 1u - final_isect) * 16u : 0u);
         const uint32_t n_list = cull_to_list<true>(sbase, list_addr, lane, warp, t_lo_warp, remaining);
+        if (pair_counter && lane == 0 && n_list)  // diagnostic (brush_ctx_set_pair_counting), per batch, not per pair
+            atomicAdd(pair_counter, (unsigned long long)((n_list + BW_GROUP - 1u) / BW_GROUP) * (BW_GROUP * 32u));
         const uint32_t token = n_list ^ b;  // exists only after cull_to_list's __syncwarp (see lds128_ro)
         uint32_t an[BW_GROUP];  // the next group's list entries, loaded one group ahead (the list is padded)
         list_load4(list_addr, sbase, an, token);
@@ -573,19 +586,21 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
 void launch_rasterize_backward(const Cam& cam, const uint32_t* compact_gid_from_isect, const uint32_t* tile_bins,
                                const float* projected, const uint32_t* global_from_compact,
                                const uint32_t* final_index, const float* out_img,
-                               const float* v_out_img, float* v_projected, cudaStream_t st) {
+                               const float* v_out_img, float* v_projected, unsigned long long* pair_counter,
+                               cudaStream_t st) {
     const uint32_t tiles = cam.tiles_x * cam.tiles_y;
     if (tiles == 0) return;
-    static uint64_t configured_devices = 0;  // the opt-in to > 48 KB of shared memory is per device
+    static std::atomic<uint64_t> configured_devices{0};  // the opt-in to > 48 KB of shared memory is per device
     int dev = 0;
     cudaGetDevice(&dev);
-    if (!(configured_devices >> dev & 1ull)) {
+    if (!(configured_devices.load(std::memory_order_acquire) >> dev & 1ull)) {  // idempotent: a race only repeats the call
         cudaFuncSetAttribute(rasterize_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BW_BYTES);
-        configured_devices |= 1ull << dev;
+        configured_devices.fetch_or(1ull << dev, std::memory_order_release);
     }
     g_launch_count++;
     rasterize_backward_kernel<<<tiles, TILE_SIZE, BW_BYTES, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
-                                                                 global_from_compact, final_index, out_img, v_out_img, v_projected);
+                                                                 global_from_compact, final_index, out_img, v_out_img, v_projected,
+                                                                 pair_counter);
 }
 
 }  // namespace brush

@@ -12,6 +12,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 from dataclasses import dataclass
 from typing import Optional, Tuple
 
@@ -23,6 +24,23 @@ from ._lib import BrushAux, BrushUniforms, Context
 
 TILE_WIDTH = 16
 REFERENCE_MAX_INTERSECTS = 128 * 65535  # render.rs:204-206
+
+
+def poison_enabled() -> bool:
+    """BRUSH_POISON=1: every caller-allocated aux / output buffer is noise-filled before the library call, the way
+    the reference's `create_tensor` does under test (crates/brush-kernel/src/lib.rs:134-147 fills "empty" buffers
+    with -12345), so a kernel that relies on zero-initialised memory fails loudly."""
+    return os.environ.get("BRUSH_POISON", "0") == "1"
+
+
+def poison_(*tensors):
+    for t in tensors:
+        if t is None:
+            continue
+        if t.dtype.is_floating_point:
+            t.fill_(-12345.0)
+        else:
+            t.view(torch.int32).fill_(-0x30303031)  # 0xCFCFCFCF
 
 
 def fov_to_focal(fov_rad: float, pixels: int) -> float:  # camera.rs:52-54
@@ -111,6 +129,11 @@ class RenderAux:
     global_from_compact_gid: torch.Tensor  # i32[N]
     tile_id_from_isect: Optional[torch.Tensor] = None  # i32[capacity], sorted (not in the reference's RenderAux)
 
+    def tensors(self):
+        return (self.projected_splats, self.uniforms_buffer, self.num_intersections, self.num_visible,
+                self.final_index, self.cum_tiles_hit, self.tile_bins, self.compact_gid_from_isect,
+                self.global_from_compact_gid, self.tile_id_from_isect)
+
     def read_num_visible(self) -> int:  # lib.rs:42-47
         return int(self.num_visible.item())
 
@@ -192,6 +215,8 @@ def render_forward(uniforms: BrushUniforms, means, log_scales, quats, sh_coeffs,
         if (aux.projected_splats.shape[0] != N or aux.final_index.shape != (H, W)
                 or aux.compact_gid_from_isect.numel() != cap or out.shape[-1] != (1 if raster_u32 else 4)):
             raise ValueError("render_forward: `reuse` buffers do not match this call's shapes")
+        if poison_enabled():
+            poison_(out, *aux.tensors())
         caux = aux._c()
         with torch.cuda.device(dev):
             rc = _lib.lib().brush_render_forward(
@@ -216,6 +241,8 @@ def render_forward(uniforms: BrushUniforms, means, log_scales, quats, sh_coeffs,
         out = torch.empty((H, W, 1), dtype=torch.int32, device=dev)  # packed RGBA8 (render.rs:269-280)
     else:
         out = torch.empty((H, W, 4), dtype=torch.float32, device=dev)
+    if poison_enabled():
+        poison_(out, *aux.tensors())
     caux = aux._c()
     with torch.cuda.device(dev):
         rc = _lib.lib().brush_render_forward(
@@ -244,6 +271,8 @@ def render_backward(aux: RenderAux, means, log_scales, quats, sh_coeffs_shape, r
         v_sh = torch.empty((N, K, 3), **f32)
         v_opac = torch.empty((N,), **f32)
     v_out_img = v_out_img.contiguous()
+    if poison_enabled():
+        poison_(v_means, v_xy, v_scales, v_quats, v_sh, v_opac)
     caux = aux._c()
     with torch.cuda.device(dev):
         rc = _lib.lib().brush_render_backward(

@@ -23,7 +23,8 @@ import torch
 
 from . import _lib
 from .parallel import ViewBuffers, FlatGradLayout, FlatParamLayout, PeerBuffers, allreduce_flat, global_grad_scale
-from .render import Camera, RenderAux, Splats, _stream_ptr, get_context, make_uniforms, render_backward, render_forward
+from .render import (Camera, RenderAux, Splats, _stream_ptr, get_context, make_uniforms, poison_, poison_enabled,
+                     render_backward, render_forward)
 
 
 @dataclass
@@ -68,20 +69,6 @@ class RefineStats:  # train.rs:112-118
     num_cloned: int
     num_transparent_pruned: int
     num_scale_pruned: int
-
-
-def quaternion_vec_multiply(q: torch.Tensor, v: torch.Tensor) -> torch.Tensor:
-    """train.rs:140-177: rotates v[n,3] by the (w, x, y, z) quaternions q[n,4], term for term."""
-    qw, qx, qy, qz = q[:, 0:1], q[:, 1:2], q[:, 2:3], q[:, 3:4]
-    vx, vy, vz = v[:, 0:1], v[:, 1:2], v[:, 2:3]
-    t1 = qw * vx + qy * vz - qz * vy
-    t2 = qw * vy - qx * vz + qz * vx
-    t3 = qw * vz + qx * vy - qy * vx
-    t4 = qx * vx + qy * vy + qz * vz
-    rx = vx + (qw * t1 + qx * t4 - qy * t3 + qz * t2) * 2.0
-    ry = vy + (qw * t2 - qx * t3 + qy * t4 + qz * t1) * 2.0
-    rz = vz + (qw * t3 + qx * t2 - qy * t1 + qz * t4) * 2.0
-    return torch.cat([rx, ry, rz], 1)
 
 
 @dataclass
@@ -130,6 +117,9 @@ class SplatTrainer:
     def _alloc(self, n: int, k: int):
         f = dict(dtype=torch.float32, device=self.device)
         self.n, self.k = n, k
+        # Adam's bias-correction time: restarts with the optimizer state (train.rs:568 re-creates the optimizer in
+        # refine_splats, so Burn's per-parameter `time` is 1 again on the first step after a refine)
+        self.opt_step = 0
         self.layout = FlatGradLayout(n, k)
         self.param_layout = FlatParamLayout(n, k)
         if self.exchange == "peer":
@@ -147,6 +137,8 @@ class SplatTrainer:
         self.grad_2d_accum = torch.zeros(n, **f)   # train.rs:195-196
         self.xy_grad_counts = torch.zeros(n, **f)
         self.norm_rot = torch.empty((n, 4), **f)
+        if poison_enabled():
+            poison_(self.norm_rot)
         self.state = {}
         # two sets of loss scalars, alternating by step: the loss a step returns stays valid while the NEXT step
         # runs, so a caller may read it back from another stream, one step behind, without a copy on this one
@@ -221,6 +213,8 @@ class SplatTrainer:
         _, H, W, Cc = batch.gt_images.shape
         if self.v_out is None or tuple(self.v_out.shape[:2]) != (H, W):
             self.v_out = torch.empty((H, W, 4), dtype=torch.float32, device=dev)
+            if poison_enabled():
+                poison_(self.v_out)
             self.render_bufs = []
         world = self.pg.size() if self.pg is not None else 1
         p_means, p_scales = splats.means.detach(), splats.log_scales.detach()
@@ -306,6 +300,7 @@ class SplatTrainer:
                 ctx.check(L.brush_quat_normalize_vjp(ctx.handle, p_rot.data_ptr(), self.n, self.g_quats.data_ptr(),
                                                      st))
             self.iter += 1
+            self.opt_step += 1
             if views:
                 with_stats = self.iter - 1 > cfg.warmup_steps  # train.rs:286-316
                 self._views_step(ctx, splats, vx, lr_mean, grad_scale, with_stats, st)
@@ -370,6 +365,9 @@ class SplatTrainer:
             ctx.check(L.brush_refine_plan(ctx.handle, self.n, self.grad_2d_accum.data_ptr(),
                                           self.xy_grad_counts.data_ptr(), C.byref(c_pre), C.byref(c_post),
                                           C.byref(rcfg), C.byref(counts), st))
+            # brush_refine_plan has just synchronised the stream: the cheap place to surface an intersection
+            # overflow of any forward since the last refine (raises CapacityError; the reference truncates silently)
+            ctx.sync_check(_stream_ptr(dev))
             n_split, n_out = int(counts.num_split), int(counts.num_out)
             if samples is None:
                 gen = torch.Generator(device=dev)
@@ -421,7 +419,7 @@ class SplatTrainer:
         sp.loss_offset, sp.loss_out = gl.offset("loss"), self.loss_buf.data_ptr()
         sp.epoch = self.epoch
         ctx.check(_lib.lib().brush_dp_adam_step(ctx.handle, C.byref(sp), segs, len(segs), cfg.adam_beta1,
-                                                cfg.adam_beta2, cfg.adam_eps, self.iter, grad_scale, st))
+                                                cfg.adam_beta2, cfg.adam_eps, self.opt_step, grad_scale, st))
         views = pl.views(peer.param)
         return views[5], views[6]
 
@@ -454,7 +452,7 @@ class SplatTrainer:
         accum = (self.grad_2d_accum.data_ptr(), self.xy_grad_counts.data_ptr()) if with_stats else (None, None)
         ctx.check(_lib.lib().brush_views_adam_step(
             ctx.handle, self.n, self.k, C.byref(S), self.norm_rot.data_ptr(), C.byref(vx), accum[0], accum[1],
-            self.loss_buf.data_ptr(), cfg.adam_beta1, cfg.adam_beta2, cfg.adam_eps, self.iter, grad_scale, st))
+            self.loss_buf.data_ptr(), cfg.adam_beta1, cfg.adam_beta2, cfg.adam_eps, self.opt_step, grad_scale, st))
 
     def _backward_adam(self, ctx, splats: Splats, aux, pred, lr_mean: float, with_stats: bool, st):
         cfg = self.config
@@ -463,7 +461,7 @@ class SplatTrainer:
         accum = (self.grad_2d_accum.data_ptr(), self.xy_grad_counts.data_ptr()) if with_stats else (None, None)
         ctx.check(_lib.lib().brush_render_backward_adam(
             ctx.handle, self.n, self.k, C.byref(S), self.norm_rot.data_ptr(), pred.data_ptr(), self.v_out.data_ptr(),
-            C.byref(caux), None, accum[0], accum[1], cfg.adam_beta1, cfg.adam_beta2, cfg.adam_eps, self.iter + 1, 1.0,
+            C.byref(caux), None, accum[0], accum[1], cfg.adam_beta1, cfg.adam_beta2, cfg.adam_eps, self.opt_step + 1, 1.0,
             st))
 
     def _adam(self, ctx, splats: Splats, lr_mean: float, grad_scale: float, st):
@@ -483,4 +481,4 @@ class SplatTrainer:
             groups[i].sh_coeffs_per_channel = shk
             groups[i].sh_rest_lr_scale = 1.0 / cfg.lr_coeffs_sh_scale
         ctx.check(_lib.lib().brush_adam_step(ctx.handle, groups, 5, cfg.adam_beta1, cfg.adam_beta2, cfg.adam_eps,
-                                             self.iter, grad_scale, st))
+                                             self.opt_step, grad_scale, st))

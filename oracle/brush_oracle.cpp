@@ -14,10 +14,17 @@
 // intersection-capacity behaviour.
 //
 // All citations are relative to /root/reference/.
-// Build: see oracle/Makefile (-O2 -ffp-contract=off, no fast-math).
+// Build: see oracle/Makefile.  Two targets from this one file:
+//   libbrush_oracle.so               the PARITY oracle: -O2 -ffp-contract=off, no fast-math, f64 accumulation of the
+//                                    rasterize_backwards sums (independent of the thread count).
+//   _timed/libbrush_oracle_timed.so  the TIMED CPU baseline (-DORACLE_TIMED -O3 -march=native, built on the machine
+//                                    that runs bench.py): same algorithm and results to rounding, but the
+//                                    rasterize_backwards sums go to thread-private f32 accumulators (no atomics) and
+//                                    the LSD sorts take 8-bit digits (half the passes, identical output).
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <ctime>
 #include <vector>
 #ifdef _OPENMP
 #include <omp.h>
@@ -298,8 +305,28 @@ static int threads_env() {
 #define OMP_FOR
 #endif
 static int g_threads = 1;
+// Wall-clock seconds of each stage of the last oracle_render_forward / oracle_render_backward call, in the order of
+// the reference's tracing spans (render.rs:127-267,515-577): ProjectSplats, DepthSort, ProjectVisibile, PrefixSum,
+// MapGaussiansToIntersect, Tile sort, GetTileBinEdges, Rasterize, RasterizeBackwards, GatherGrads, ProjectBackwards.
+static double g_stage_s[11];
+static inline double now_s() {
+#ifdef _OPENMP
+    return omp_get_wtime();
+#else
+    return (double)clock() / CLOCKS_PER_SEC;
+#endif
+}
+struct StageClock {
+    int i;
+    double t0;
+    explicit StageClock(int i_) : i(i_), t0(now_s()) {}
+    ~StageClock() { g_stage_s[i] = now_s() - t0; }
+};
 
 extern "C" {
+void oracle_stage_seconds(double* out11) {
+    for (int i = 0; i < 11; i++) out11[i] = g_stage_s[i];
+}
 
 // Number of worker threads for the timed CPU baseline. 1 (default) = the strictly
 // serial parity oracle.
@@ -366,6 +393,23 @@ int oracle_radix_argsort_u32(const uint32_t* keys, const uint32_t* vals, uint32_
                              uint32_t* keys_out, uint32_t* vals_out) {
     if (bits > 32) return -1;
     std::vector<uint32_t> k0(keys, keys + n), v0(vals, vals + n), k1(n), v1(n);
+#ifdef ORACLE_TIMED
+    // timed build: the same stable LSD sort over the same 4*ceil(bits/4) key bits, 8 bits per pass
+    const uint32_t rb = ((bits + 3) / 4) * 4;
+    for (uint32_t shift = 0; shift < rb; shift += 8) {
+        const uint32_t nb = rb - shift < 8 ? rb - shift : 8, mask = (1u << nb) - 1u;
+        size_t cnt[257] = {0};
+        for (uint32_t i = 0; i < n; i++) cnt[((uint32_t)(k0[i] >> shift) & mask) + 1]++;
+        for (int b = 0; b < 256; b++) cnt[b + 1] += cnt[b];
+        for (uint32_t i = 0; i < n; i++) {
+            size_t d = cnt[(uint32_t)(k0[i] >> shift) & mask]++;
+            k1[d] = k0[i];
+            v1[d] = v0[i];
+        }
+        k0.swap(k1);
+        v0.swap(v1);
+    }
+#else
     uint32_t passes = (bits + 3) / 4;
     for (uint32_t pass = 0; pass < passes; pass++) {
         uint32_t shift = pass * 4;
@@ -380,6 +424,7 @@ int oracle_radix_argsort_u32(const uint32_t* keys, const uint32_t* vals, uint32_
         k0.swap(k1);
         v0.swap(v1);
     }
+#endif
     std::copy(k0.begin(), k0.end(), keys_out);
     std::copy(v0.begin(), v0.end(), vals_out);
     return 0;
@@ -391,6 +436,23 @@ int oracle_radix_argsort_u64(const uint64_t* keys, const uint32_t* vals, uint32_
     if (bits > 64) return -1;
     std::vector<uint64_t> k0(keys, keys + n), k1(n);
     std::vector<uint32_t> v0(vals, vals + n), v1(n);
+#ifdef ORACLE_TIMED
+    // timed build: the same stable LSD sort over the same 4*ceil(bits/4) key bits, 8 bits per pass
+    const uint32_t rb = ((bits + 3) / 4) * 4;
+    for (uint32_t shift = 0; shift < rb; shift += 8) {
+        const uint32_t nb = rb - shift < 8 ? rb - shift : 8, mask = (1u << nb) - 1u;
+        size_t cnt[257] = {0};
+        for (uint32_t i = 0; i < n; i++) cnt[((uint32_t)(k0[i] >> shift) & mask) + 1]++;
+        for (int b = 0; b < 256; b++) cnt[b + 1] += cnt[b];
+        for (uint32_t i = 0; i < n; i++) {
+            size_t d = cnt[(uint32_t)(k0[i] >> shift) & mask]++;
+            k1[d] = k0[i];
+            v1[d] = v0[i];
+        }
+        k0.swap(k1);
+        v0.swap(v1);
+    }
+#else
     uint32_t passes = (bits + 3) / 4;
     for (uint32_t pass = 0; pass < passes; pass++) {
         uint32_t shift = pass * 4;
@@ -405,6 +467,7 @@ int oracle_radix_argsort_u64(const uint64_t* keys, const uint32_t* vals, uint32_
         k0.swap(k1);
         v0.swap(v1);
     }
+#endif
     std::copy(k0.begin(), k0.end(), keys_out);
     std::copy(v0.begin(), v0.end(), vals_out);
     return 0;
@@ -512,7 +575,9 @@ int oracle_rasterize(const Uniforms* up, const uint32_t* compact_gid_from_isect,
     const Uniforms& u = *up;
     uint32_t Wd = u.img_size[0], Hd = u.img_size[1];
     int64_t ntiles = (int64_t)u.tile_bounds[0] * u.tile_bounds[1];
-    OMP_FOR
+#ifdef _OPENMP
+#pragma omp parallel for schedule(dynamic, 2) num_threads(g_threads)
+#endif
     for (int64_t tile_id = 0; tile_id < ntiles; tile_id++) {
         uint32_t tx = tile_id % u.tile_bounds[0], ty = tile_id / u.tile_bounds[0];
         uint32_t r0 = tile_bins[tile_id * 2], r1 = tile_bins[tile_id * 2 + 1];
@@ -569,9 +634,29 @@ int oracle_rasterize_backwards(const Uniforms* up, const uint32_t* compact_gid_f
     const Uniforms& u = *up;
     uint32_t Wd = u.img_size[0], Hd = u.img_size[1];
     int64_t ntiles = (int64_t)u.tile_bounds[0] * u.tile_bounds[1];
+#ifdef ORACLE_TIMED
+    // timed build: one f32 accumulator array per thread (no atomics), summed per splat afterwards
+    const int nthr = g_threads;
+    const size_t acc_rows = u.num_visible < num_points ? u.num_visible : num_points;  // rows are compact ids < V
+    const size_t acc_len = acc_rows * 9;
+    std::vector<std::vector<float>> acc_thr(nthr);
+#else
     std::vector<double> acc((size_t)num_points * 9, 0.0);
+#endif
 #ifdef _OPENMP
-#pragma omp parallel for schedule(dynamic, 16) num_threads(g_threads)
+#pragma omp parallel num_threads(g_threads)
+#endif
+    {
+#ifdef ORACLE_TIMED
+#ifdef _OPENMP
+    std::vector<float>& acc = acc_thr[omp_get_thread_num()];
+#else
+    std::vector<float>& acc = acc_thr[0];
+#endif
+    acc.assign(acc_len, 0.0f);
+#endif
+#ifdef _OPENMP
+#pragma omp for schedule(dynamic, 2)
 #endif
     for (int64_t tile_id = 0; tile_id < ntiles; tile_id++) {
         uint32_t tx = tile_id % u.tile_bounds[0], ty = tile_id / u.tile_bounds[0];
@@ -629,6 +714,10 @@ int oracle_rasterize_backwards(const Uniforms* up, const uint32_t* compact_gid_f
                 s[8] += vis * v_alpha;
             }
             if (any) {
+#ifdef ORACLE_TIMED
+                float* a = &acc[(size_t)cg * 9];
+                for (int k = 0; k < 9; k++) a[k] += s[k];
+#else
                 double* a = &acc[(size_t)cg * 9];
                 for (int k = 0; k < 9; k++) {
 #ifdef _OPENMP
@@ -636,15 +725,30 @@ int oracle_rasterize_backwards(const Uniforms* up, const uint32_t* compact_gid_f
 #endif
                     a[k] += (double)s[k];
                 }
+#endif
             }
         }
     }
+    }  // omp parallel
+#ifdef ORACLE_TIMED
+    OMP_FOR
+    for (int64_t c = 0; c < (int64_t)acc_rows; c++) {
+        float a[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+        for (int t = 0; t < nthr; t++)
+            if (!acc_thr[t].empty())
+                for (int k = 0; k < 9; k++) a[k] += acc_thr[t][(size_t)c * 9 + k];
+        v_xy[c * 2] += a[0]; v_xy[c * 2 + 1] += a[1];
+        v_conic[c * 3] += a[2]; v_conic[c * 3 + 1] += a[3]; v_conic[c * 3 + 2] += a[4];
+        for (int k = 0; k < 4; k++) v_colors[c * 4 + k] += a[5 + k];
+    }
+#else
     for (size_t c = 0; c < num_points; c++) {
         const double* a = &acc[c * 9];
         v_xy[c * 2] += (float)a[0]; v_xy[c * 2 + 1] += (float)a[1];
         v_conic[c * 3] += (float)a[2]; v_conic[c * 3 + 1] += (float)a[3]; v_conic[c * 3 + 2] += (float)a[4];
         for (int k = 0; k < 4; k++) v_colors[c * 4 + k] += (float)a[5 + k];
     }
+#endif
     return 0;
 }
 
@@ -803,18 +907,30 @@ int oracle_render_forward(const Uniforms* uin, uint32_t N, uint32_t K, const flo
     std::vector<uint32_t> presort(N, 0u), depth_bits(N), sorted_depth(N);
     std::vector<float> depths(N);
     uint32_t V = 0;
-    oracle_project_forward(&u, means, log_scales, quats, presort.data(), depths.data(), &V);
+    {
+        StageClock c(0);
+        oracle_project_forward(&u, means, log_scales, quats, presort.data(), depths.data(), &V);
+    }
     u.num_visible = V;
-    for (uint32_t i = 0; i < V; i++) depth_bits[i] = f2bits(depths[i]);
-    std::fill(global_from_compact_gid, global_from_compact_gid + N, 0u);
-    oracle_radix_argsort_u32(depth_bits.data(), presort.data(), V, 32, sorted_depth.data(), global_from_compact_gid);
+    {
+        StageClock c(1);
+        for (uint32_t i = 0; i < V; i++) depth_bits[i] = f2bits(depths[i]);
+        std::fill(global_from_compact_gid, global_from_compact_gid + N, 0u);
+        oracle_radix_argsort_u32(depth_bits.data(), presort.data(), V, 32, sorted_depth.data(), global_from_compact_gid);
+    }
 
     // render.rs:161-184: ProjectVisible (num_tiles_hit zeroed)
     std::vector<uint32_t> num_tiles_hit(N, 0u);
-    oracle_project_visible(&u, K, means, log_scales, quats, coeffs, raw_opacities, global_from_compact_gid, V,
-                           projected, num_tiles_hit.data());
+    {
+        StageClock c(2);
+        oracle_project_visible(&u, K, means, log_scales, quats, coeffs, raw_opacities, global_from_compact_gid, V,
+                               projected, num_tiles_hit.data());
+    }
     // render.rs:186-192: PrefixSum over all N
-    oracle_prefix_sum_u32(num_tiles_hit.data(), N, cum_tiles_hit);
+    {
+        StageClock c(3);
+        oracle_prefix_sum_u32(num_tiles_hit.data(), N, cum_tiles_hit);
+    }
     uint32_t I = N > 0 ? cum_tiles_hit[N - 1] : 0u;
     int status = 0;
     if ((uint64_t)I > capacity) {
@@ -823,15 +939,28 @@ int oracle_render_forward(const Uniforms* uin, uint32_t N, uint32_t K, const flo
     }
     // render.rs:211-237: MapGaussiansToIntersect + tile sort
     uint32_t num_tiles = u.tile_bounds[0] * u.tile_bounds[1];
-    std::vector<uint32_t> tid(capacity ? capacity : 1), cg(capacity ? capacity : 1);
-    oracle_map_gaussian_to_intersects(&u, V, projected, cum_tiles_hit, capacity, tid.data(), cg.data());
+    // only the first I entries are ever written or read (the reference allocates `max_intersects` uninitialised)
+    std::vector<uint32_t> tid(I ? I : 1), cg(I ? I : 1);
+    {
+        StageClock c(4);
+        oracle_map_gaussian_to_intersects(&u, V, projected, cum_tiles_hit, I, tid.data(), cg.data());
+    }
     uint32_t bits = 32 - (num_tiles ? __builtin_clz(num_tiles) : 32);
-    oracle_radix_argsort_u32(tid.data(), cg.data(), I, bits, tile_id_from_isect, compact_gid_from_isect);
+    {
+        StageClock c(5);
+        oracle_radix_argsort_u32(tid.data(), cg.data(), I, bits, tile_id_from_isect, compact_gid_from_isect);
+    }
     // render.rs:239-262: GetTileBinEdges
-    std::fill(tile_bins, tile_bins + (size_t)num_tiles * 2, 0u);
-    oracle_get_tile_bin_edges(tile_id_from_isect, I, tile_bins);
+    {
+        StageClock c(6);
+        std::fill(tile_bins, tile_bins + (size_t)num_tiles * 2, 0u);
+        oracle_get_tile_bin_edges(tile_id_from_isect, I, tile_bins);
+    }
     // render.rs:267-307: Rasterize
-    oracle_rasterize(&u, compact_gid_from_isect, tile_bins, projected, raster_u32, out_img, final_index);
+    {
+        StageClock c(7);
+        oracle_rasterize(&u, compact_gid_from_isect, tile_bins, projected, raster_u32, out_img, final_index);
+    }
     *uniforms_out = u;
     *num_visible_out = V;
     *num_intersections = I;
@@ -853,18 +982,27 @@ int oracle_render_backward(const Uniforms* up, uint32_t N, uint32_t K, const flo
     const Uniforms& u = *up;
     uint32_t V = u.num_visible;
     std::vector<float> v_xy_local((size_t)N * 2, 0.f), v_conics((size_t)N * 3, 0.f), v_colors((size_t)N * 4, 0.f);
-    oracle_rasterize_backwards(&u, compact_gid_from_isect, tile_bins, projected, final_index, out_img, v_out_img, N,
-                               v_xy_local.data(), v_conics.data(), v_colors.data());
-    std::fill(v_coeffs, v_coeffs + (size_t)N * K * 3, 0.f);
-    std::fill(v_raw_opac, v_raw_opac + N, 0.f);
-    std::fill(v_xy, v_xy + (size_t)N * 2, 0.f);
-    oracle_gather_grads(&u, K, global_from_compact_gid, V, raw_opacities, means, v_colors.data(), v_xy_local.data(),
-                        v_coeffs, v_raw_opac, v_xy);
-    std::fill(v_means, v_means + (size_t)N * 3, 0.f);
-    std::fill(v_log_scales, v_log_scales + (size_t)N * 3, 0.f);
-    std::fill(v_quats, v_quats + (size_t)N * 4, 0.f);
-    oracle_project_backwards(&u, means, log_scales, quats, global_from_compact_gid, V, v_xy_local.data(),
-                             v_conics.data(), v_means, v_log_scales, v_quats);
+    {
+        StageClock c(8);
+        oracle_rasterize_backwards(&u, compact_gid_from_isect, tile_bins, projected, final_index, out_img, v_out_img, N,
+                                   v_xy_local.data(), v_conics.data(), v_colors.data());
+    }
+    {
+        StageClock c(9);
+        std::fill(v_coeffs, v_coeffs + (size_t)N * K * 3, 0.f);
+        std::fill(v_raw_opac, v_raw_opac + N, 0.f);
+        std::fill(v_xy, v_xy + (size_t)N * 2, 0.f);
+        oracle_gather_grads(&u, K, global_from_compact_gid, V, raw_opacities, means, v_colors.data(),
+                            v_xy_local.data(), v_coeffs, v_raw_opac, v_xy);
+    }
+    {
+        StageClock c(10);
+        std::fill(v_means, v_means + (size_t)N * 3, 0.f);
+        std::fill(v_log_scales, v_log_scales + (size_t)N * 3, 0.f);
+        std::fill(v_quats, v_quats + (size_t)N * 4, 0.f);
+        oracle_project_backwards(&u, means, log_scales, quats, global_from_compact_gid, V, v_xy_local.data(),
+                                 v_conics.data(), v_means, v_log_scales, v_quats);
+    }
     return 0;
 }
 

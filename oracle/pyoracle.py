@@ -47,6 +47,57 @@ def build(force: bool = False) -> str:
     return _SO
 
 
+_TIMED_DIR = os.path.join(_HERE, "_timed")
+_TIMED_SO = os.path.join(_TIMED_DIR, "libbrush_oracle_timed.so")
+
+
+def _cpu_tag() -> str:
+    """Identifies the CPU a -march=native build is valid for (model name + ISA flags of /proc/cpuinfo)."""
+    import hashlib
+
+    model, flags = "", ""
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("model name") and not model:
+                    model = line.split(":", 1)[1].strip()
+                elif line.startswith("flags") and not flags:
+                    flags = " ".join(sorted(line.split(":", 1)[1].split()))
+                if model and flags:
+                    break
+    except OSError:
+        pass
+    return hashlib.sha256((model + "|" + flags).encode()).hexdigest()[:16]
+
+
+def use_timed() -> str:
+    """Switches this module to the TIMED build (oracle/Makefile `timed`: -O3 -march=native, thread-private f32
+    accumulators, 8-bit sort digits) -- the CPU baseline bench.py times.  Built on the machine that runs it: a copy
+    built for another CPU (the tag differs) is rebuilt, never executed."""
+    global _lib
+    tag_path = os.path.join(_TIMED_DIR, "cpu.tag")
+    tag = _cpu_tag()
+    src = [os.path.join(_HERE, f) for f in ("brush_oracle.cpp", "oracle_math.h", "Makefile")]
+    stale = (not os.path.exists(_TIMED_SO) or not os.path.exists(tag_path) or open(tag_path).read().strip() != tag
+             or any(os.path.getmtime(s_) > os.path.getmtime(_TIMED_SO) for s_ in src))
+    if stale:
+        if os.path.exists(_TIMED_SO):
+            os.remove(_TIMED_SO)
+        subprocess.check_call(["make", "-C", _HERE, "-s", "timed"])
+        with open(tag_path, "w") as f:
+            f.write(tag + "\n")
+    _lib = C.CDLL(_TIMED_SO)
+    _bind(_lib)
+    return _TIMED_SO
+
+
+def _bind(l):
+    l.oracle_det_expf.restype = C.c_float
+    l.oracle_det_expf.argtypes = [C.c_float]
+    l.oracle_det_logf.restype = C.c_float
+    l.oracle_det_logf.argtypes = [C.c_float]
+
+
 _lib = None
 
 
@@ -56,10 +107,7 @@ def lib():
         if not os.path.exists(_SO):
             build()
         _lib = C.CDLL(_SO)
-        _lib.oracle_det_expf.restype = C.c_float
-        _lib.oracle_det_expf.argtypes = [C.c_float]
-        _lib.oracle_det_logf.restype = C.c_float
-        _lib.oracle_det_logf.argtypes = [C.c_float]
+        _bind(_lib)
     return _lib
 
 
@@ -81,6 +129,17 @@ def set_threads(n: int):
 
 def max_threads() -> int:
     return int(lib().oracle_max_threads())
+
+
+STAGE_NAMES = ("ProjectSplats", "DepthSort", "ProjectVisibile", "PrefixSum", "MapGaussiansToIntersect", "Tile sort",
+               "GetTileBinEdges", "Rasterize", "RasterizeBackwards", "GatherGrads", "ProjectBackwards")
+
+
+def stage_seconds() -> dict:
+    """Wall-clock seconds per stage of the last render_forward / render_backward (the reference's span names)."""
+    arr = (C.c_double * 11)()
+    lib().oracle_stage_seconds(arr)
+    return dict(zip(STAGE_NAMES, [float(x) for x in arr]))
 
 
 def make_uniforms(viewmat, focal, img_size, pixel_center, sh_degree=0, total_splats=0) -> Uniforms:

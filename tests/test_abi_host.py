@@ -81,3 +81,45 @@ def test_scene_generator_deterministic():
     b = scene.make_scene(1000, 256, 256, 0, 1001)
     assert np.array_equal(a.means, b.means) and a.sh_coeffs.shape == (1000, 1, 3)
     assert np.allclose(np.linalg.norm(a.quats, axis=1), 1.0, atol=1e-5)
+
+
+def test_rust_ffi_block_matches_the_header():
+    """rust/brush-b200-sys/src/ffi.rs is generated from include/brush_b200.h (rust/gen_ffi.py): the committed file must
+    be what the generator produces now, declare every prototype of the header with the same number of parameters, and
+    the ctypes table of brush_b200/_lib.py must agree on the parameter counts too -- so neither binding can drift from
+    the header the way a hand-written snippet once did."""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("gen_ffi", os.path.join(ROOT, "rust", "gen_ffi.py"))
+    gen = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gen)
+    committed = open(os.path.join(ROOT, "rust", "brush-b200-sys", "src", "ffi.rs")).read()
+    assert committed == gen.generate(), "ffi.rs is stale: run `python rust/gen_ffi.py`"
+    hdr = open(os.path.join(ROOT, "include", "brush_b200.h")).read()
+    _, _, structs, funcs = gen.parse(hdr)
+    declared = set(re.findall(r"\b(brush_[a-z0-9_]+)\s*\(", gen.strip_comments(hdr)))
+    assert {f[0] for f in funcs} == declared
+    from brush_b200 import _lib
+
+    for name, params, _ in funcs:
+        m = re.search(r"pub fn " + name + r"\((.*?)\)", committed, flags=re.S)
+        assert m is not None, name
+        n_rust = len([p for p in m.group(1).split(",") if p.strip()])
+        assert n_rust == len(params), name
+        if name in _lib._SIGS:
+            assert len(_lib._SIGS[name][1]) == len(params), f"ctypes signature of {name} disagrees with the header"
+    assert set(_lib._SIGS) == declared  # the Python binding covers the whole ABI
+    # struct sizes: the ctypes mirrors and the header-derived field lists agree on the field count
+    import ctypes
+
+    by_name = dict(structs)
+    for cname in ("BrushUniforms", "BrushAux", "BrushAdamGroup", "BrushTrainState", "BrushViewExchange", "BrushDpSegment",
+                  "BrushDpStep", "BrushSplatParams", "BrushRefineConfig", "BrushRefineCounts"):
+        cls = getattr(_lib, cname)
+        assert [f[0] for f in cls._fields_] == [f[0] for f in by_name[cname]], cname
+        assert issubclass(cls, ctypes.Structure)
+    # the Burn-facing glue names every call it makes through the safe wrappers of the sys crate
+    glue = open(os.path.join(ROOT, "rust", "brush-render-b200", "render_b200.rs")).read()
+    sys_lib = open(os.path.join(ROOT, "rust", "brush-b200-sys", "src", "lib.rs")).read()
+    for fn in ("render_forward", "render_backward"):
+        assert f"ctx.{fn}(" in glue and f"ffi::brush_{fn}(" in sys_lib

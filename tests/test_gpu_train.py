@@ -2,6 +2,7 @@
 PyTorch fp32 statement of the same arithmetic, and of SplatTrainer.step end to end."""
 import ctypes as C
 import math
+import os
 
 import numpy as np
 import pytest
@@ -349,6 +350,86 @@ def test_views_step_two_views_on_one_device(k):
         assert float(diff.max()) <= 2.01 * group_lr[name] and float((diff <= 1e-6).float().mean()) > 0.999, name
 
 
+def test_views_step_two_views_against_oracle():
+    """The multi-view exchange kernel against the ORACLE (not a sibling GPU path): world = 2 emulated on one GPU as in
+    the test above, expected values from tests/helpers.py::oracle_multi_view_step -- per-view oracle fwd + bwd,
+    gradients summed in view order, per-view refine statistics (train.rs:300-314), Adam at t = 1.  The same expected
+    step is reproduced over two gloo ranks on CPU in tests/test_parallel_gloo.py."""
+    import ctypes as C
+    import sys
+
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import helpers as Hh
+    from test_parallel_gloo import _two_view_inputs
+
+    from brush_b200 import _lib, get_context
+    from brush_b200.render import make_uniforms, render_forward
+    from oracle import pyoracle as O
+
+    O.build()
+    O.set_threads(4)
+    L = _lib.lib()
+    ctx = get_context(DEV)
+    sc, cams, cam_args, v_outs, raw_rot_np, lrs, k = _two_view_inputs()
+    w, h, n = sc.width, sc.height, sc.means.shape[0]
+    ref = Hh.oracle_multi_view_step(O, sc, cam_args, raw_rot_np, v_outs, lrs, k, 0.05)
+    t = lambda a: torch.as_tensor(np.ascontiguousarray(a), device=DEV)
+    raw_rot = t(raw_rot_np)
+    norm_rot = torch.empty_like(raw_rot)
+    ctx.check(L.brush_quat_normalize(ctx.handle, raw_rot.data_ptr(), n, norm_rot.data_ptr(), None))
+    params = {"means": t(sc.means), "log_scales": t(sc.log_scales), "rotation": raw_rot, "sh_coeffs": t(sc.sh_coeffs),
+              "raw_opacity": t(sc.raw_opacity)}
+    block = n * 12 + 32
+    rows = torch.zeros(2 * block, device=DEV)
+    flags = torch.zeros(64, dtype=torch.int32, device=DEV)
+    keep = []
+    for r, cam in enumerate(cams):
+        u = make_uniforms(cam.world_to_local(), cam.focal((w, h)), (w, h), cam.center((w, h)))
+        pred, aux = render_forward(u, params["means"], params["log_scales"], norm_rot, params["sh_coeffs"],
+                                   params["raw_opacity"], False, ctx=ctx)
+        keep.append((pred, aux))
+        x = _lib.BrushViewExchange()
+        x.world, x.rank, x.epoch = 2, r, 1
+        for i in range(2):
+            x.rows[i], x.flags[i] = rows.data_ptr() + 4 * block * i, flags.data_ptr()
+        caux = aux._c()
+        loss_term = torch.full((1,), 0.25 * (r + 1), device=DEV)
+        ctx.check(L.brush_render_backward_rows(ctx.handle, n, k, pred.data_ptr(), t(v_outs[r]).data_ptr(),
+                                               C.byref(caux), loss_term.data_ptr(), C.byref(x), None))
+    S = _lib.BrushTrainState()
+    state = {}
+    for name, p in params.items():
+        state[name] = (torch.zeros_like(p), torch.zeros_like(p))
+        setattr(S, name, p.data_ptr())
+        setattr(S, "m_" + name, state[name][0].data_ptr())
+        setattr(S, "v_" + name, state[name][1].data_ptr())
+    S.lr_mean, S.lr_scale, S.lr_rotation = lrs["means"], lrs["log_scales"], lrs["rotation"]
+    S.lr_coeffs_dc, S.lr_opac, S.sh_rest_lr_scale = lrs["sh_coeffs"], lrs["raw_opacity"], 0.05
+    x = _lib.BrushViewExchange()
+    x.world, x.rank, x.epoch = 2, 0, 1
+    for i in range(2):
+        x.rows[i], x.flags[i] = rows.data_ptr() + 4 * block * i, flags.data_ptr()
+    acc_norm, acc_vis, loss = torch.zeros(n, device=DEV), torch.zeros(n, device=DEV), torch.zeros(1, device=DEV)
+    ctx.check(L.brush_views_adam_step(ctx.handle, n, k, C.byref(S), norm_rot.data_ptr(), C.byref(x),
+                                      acc_norm.data_ptr(), acc_vis.data_ptr(), loss.data_ptr(), 0.9, 0.999, 1e-15, 1,
+                                      0.5, None))
+    torch.cuda.synchronize()
+    assert abs(float(loss) - 0.375) < 1e-6
+    assert np.array_equal(acc_vis.cpu().numpy(), ref["visible"]) and float(acc_vis.max()) == 2.0
+    gn, rn = acc_norm.cpu().numpy().astype(np.float64), ref["grad_norm"].astype(np.float64)
+    assert (np.abs(gn - rn) <= 1e-3 * np.abs(rn) + 2e-5 * np.abs(rn).max()).all()
+    # first-step Adam is sign-like in the parameters, so the moments carry the comparison: m = 0.1 * g_sum / 2.
+    # north_star tolerance for gradients: 1e-3 relative (+ the atomics-order floor the parity tests use)
+    for name in params:
+        m = state[name][0].cpu().numpy().astype(np.float64)
+        rm = ref["m"][name]
+        assert np.abs(rm).max() > 0
+        assert (np.abs(m - rm) <= 1e-3 * np.abs(rm) + 2e-5 * np.abs(rm).max()).all(), name
+        diff = np.abs(params[name].cpu().numpy().astype(np.float64) - ref["params"][name])
+        lr = lrs[name]
+        assert diff.max() <= 2.01 * lr and (diff <= 1e-5 * max(lr, 1e-3) + 1e-6).mean() > 0.995, name
+
+
 # (700, 40): many row segments per column strip (the seams of the row-streaming kernels); (3, 5): smaller than the
 # window; (20, 300): ten strips, the last one ragged
 @pytest.mark.parametrize("channels,h,w", [(3, 37, 53), (4, 64, 48), (3, 16, 16), (3, 700, 40), (4, 3, 5), (3, 20, 300)])
@@ -523,6 +604,46 @@ def test_training_loop_survives_refinement():
         refines += stats.refine is not None
         assert np.isfinite(float(stats.loss))
     assert refines == 3 and counts[-1] != n and tr.n == counts[-1]  # iters 1, 6, 11
+
+
+@pytest.mark.parametrize("fused", [True, False])
+def test_adam_time_restarts_after_refine(fused):
+    """train.rs:568 re-creates the optimizer in refine_splats, so Burn's Adam `time` is 1 on the next step: with
+    m = v = 0 the first update is lr * sign(g) (bias corrections cancel), not ~2 lr.  The step after a refine must
+    equal the first step of a brand-new trainer on the refined splats."""
+    from brush_b200 import Camera, Splats, scene
+    from brush_b200.scene import bench_camera_params
+    from brush_b200.train import SceneBatch, SplatTrainer, TrainConfig
+
+    w, h, n = 128, 96, 2000
+    sc = scene.make_scene(n, w, h, 0, 5)
+    t = lambda a: torch.as_tensor(a, device=DEV)
+    cam = Camera(*bench_camera_params(w, h))
+    splats = Splats(t(sc.means), t(sc.sh_coeffs), t(sc.quats), t(sc.raw_opacity), t(sc.log_scales))
+    gt = torch.rand((1, h, w, 3), generator=torch.Generator(device=DEV).manual_seed(1), device=DEV)
+    cfg = TrainConfig(warmup_steps=0, refine_every=5, densify_grad_thresh=1e-7, reset_alpha_value=0.05)
+    tr = SplatTrainer(n, cfg, DEV, sh_coeffs_per_channel=1, fused_tail=fused)
+    for i in range(7):  # refine happens at the end of the step with iter == 6 (iter % 5 == 1)
+        splats, stats = tr.step(SceneBatch(gt, [cam], 1.0), splats)
+        if stats.refine is not None and i > 1:
+            break
+    assert stats.refine is not None and tr.opt_step == 0 and tr.iter == 7
+    before = [p.detach().clone() for p in splats.params()]
+    fresh = SplatTrainer(tr.n, TrainConfig(warmup_steps=0, max_refine_step=0), DEV, sh_coeffs_per_channel=1,
+                         fused_tail=fused)
+    twin = Splats(*[p.detach().clone() for p in (splats.means, splats.sh_coeffs, splats.rotation, splats.raw_opacity,
+                                                 splats.log_scales)])
+    splats, _ = tr.step(SceneBatch(gt, [cam], 1.0), splats)
+    twin, _ = fresh.step(SceneBatch(gt, [cam], 1.0), twin)
+    torch.cuda.synchronize()
+    assert tr.opt_step == 1
+    for a, b, p0, lr in zip(splats.params(), twin.params(), before,
+                            (cfg.lr_mean, cfg.lr_coeffs_dc, cfg.lr_rotation, cfg.lr_opac, cfg.lr_scale)):
+        assert torch.equal(a.detach(), b.detach())
+        step = (a.detach() - p0).abs()
+        moved = step > 0
+        # t = 1: |update| = lr * |g| / (|g| + eps) ~= lr for every element with a gradient (never ~2 lr)
+        assert moved.any() and float(step[moved].max()) <= lr * 1.01
 
 
 def test_eval_stats_and_loader_driven_training():
