@@ -246,8 +246,12 @@ def run_ours(args):
                          "peer memory, then redoes the per-splat backward of all views + Adam on its own replica in ONE "
                          "kernel (brush_views_adam_step)")
     elif world > 1 and trainer.exchange == "peer":
-        exchange_desc = ("gradient sum + Adam + parameter broadcast as ONE brush_dp_adam_step launch per rank over "
-                         f"NVLink peer memory ({'NVSwitch multimem.ld_reduce/st' if trainer.peer.grad_mc else 'peer loads/stores'})")
+        exchange_desc = ("gradient sum + Adam + parameter broadcast fused in brush_dp_adam_step over NVLink peer memory "
+                         f"({'NVSwitch multimem.ld_reduce/st' if trainer.peer.grad_mc else 'peer loads/stores'}); "
+                         + ("two launches per step: the small groups on the step's stream, the SH group on a side "
+                            "stream under the next step's projection / sorts / binning (exact parameters: the next "
+                            "forward evaluates colours last and waits for the SH exchange there)"
+                            if trainer.overlap_exchange else "one launch per step, not overlapped"))
     elif world > 1:
         exchange_desc = "NCCL all-reduce of the flat dense gradient, replicated Adam"
     else:
@@ -312,6 +316,7 @@ def run_ours(args):
         else:
             for s in range(n_steps):
                 one_step(first_idx + s, False)
+        trainer.finish()  # an overlapped SH exchange of the last step belongs to the timed region
         e1.record()
         barrier()
         ms = e0.elapsed_time(e1)

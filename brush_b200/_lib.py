@@ -6,7 +6,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "lib", "libbrush_b200.so")
+# BRUSH_B200_LIB: another build of the SAME library (e.g. a profiling build made with BRUSH_NVCC_EXTRA); never a fallback
+SO_PATH = os.environ.get("BRUSH_B200_LIB") or os.path.join(_HERE, "lib", "libbrush_b200.so")
 
 BRUSH_OK, BRUSH_E_INVALID, BRUSH_E_CAPACITY, BRUSH_E_CUDA = 0, -1, -2, -3
 STAGE_NAMES = ["ProjectSplats", "DepthSort", "ProjectVisible", "PrefixSum", "MapGaussiansToIntersect", "TileSort",
@@ -77,7 +78,8 @@ class BrushDpStep(C.Structure):
     _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("src", C.c_void_p * DP_MAX_WORLD),
                 ("dst", C.c_void_p * DP_MAX_WORLD), ("src_multicast", C.c_void_p), ("dst_multicast", C.c_void_p),
                 ("flags", C.c_void_p * DP_MAX_WORLD), ("m", C.c_void_p), ("v", C.c_void_p),
-                ("loss_offset", C.c_uint64), ("loss_out", C.c_void_p), ("epoch", C.c_uint32)]
+                ("loss_offset", C.c_uint64), ("loss_out", C.c_void_p), ("epoch", C.c_uint32), ("lane", C.c_int32),
+                ("ctas_per_sm", C.c_int32)]
 
 
 assert C.sizeof(BrushUniforms) == 112
@@ -102,6 +104,8 @@ _SIGS = {
     "brush_version": (C.c_char_p, []),
     "brush_ctx_set_sort_mode": (C.c_int, [C.c_void_p, C.c_int]),
     "brush_ctx_set_timing": (C.c_int, [C.c_void_p, C.c_int]),
+    "brush_ctx_set_sh_ready_event": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "brush_ctx_set_split_colors": (C.c_int, [C.c_void_p, C.c_int]),
     "brush_stage_times_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.c_int, C.c_void_p]),
     "brush_ctx_check": (C.c_int, [C.c_void_p, C.c_void_p]),
     "brush_measure_peaks": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_void_p]),
@@ -203,6 +207,13 @@ class Context:
 
     def set_sort_mode(self, fused64: bool):
         self.check(lib().brush_ctx_set_sort_mode(self._h, int(fused64)))
+
+    def set_sh_ready_event(self, event_ptr):
+        """The next forward reads sh_coeffs only behind this CUDA event (a raw cudaEvent_t; None cancels)."""
+        self.check(lib().brush_ctx_set_sh_ready_event(self._h, C.c_void_p(event_ptr) if event_ptr else None))
+
+    def set_split_colors(self, enabled: bool):
+        self.check(lib().brush_ctx_set_split_colors(self._h, int(enabled)))
 
     def set_timing(self, enabled: bool):
         self.check(lib().brush_ctx_set_timing(self._h, int(enabled)))

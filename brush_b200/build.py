@@ -56,7 +56,18 @@ def needs_build() -> bool:
     return any(os.path.getmtime(d) > t for d in _sources())
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, tag: str = "") -> str:
+    """tag: build a VARIANT (extra flags from BRUSH_NVCC_EXTRA) to lib/libbrush_b200_<tag>.so next to the product
+    library, for A/B and profiling runs (select it with BRUSH_B200_LIB); the product build has no tag."""
+    global SO, OBJDIR
+    if tag:
+        so, objdir = os.path.join(LIBDIR, f"libbrush_b200_{tag}.so"), os.path.join(HERE, f"build_{tag}")
+        saved = (SO, OBJDIR)
+        SO, OBJDIR = so, objdir
+        try:
+            return build(force=True, verbose=verbose)
+        finally:
+            SO, OBJDIR = saved
     if not force and not needs_build():
         return SO
     nvcc = _nvcc()
@@ -89,4 +100,5 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    _tag = next((a.split("=", 1)[1] for a in sys.argv if a.startswith("--tag=")), "")
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, tag=_tag))

@@ -34,6 +34,8 @@ struct brush_ctx {
     std::string err;
     int fused64 = 0;
     int timing = 0;
+    void* sh_ready = nullptr;  // cudaEvent_t: the NEXT forward defers its first read of sh_coeffs behind it (one-shot)
+    int split_colors = 0;      // always run the deferred-colour forward (A/B measurements)
     int pair_counting = 0;  // diagnostic: the rasterizers count the pairs they evaluate (sticky block, bytes 128..143)
     // scratch, grown on demand (growth synchronises; steady state never allocates)
     Buf control, presort_gid, depth_bits, depth_sorted, num_tiles_hit, keys_tmp, vals_tmp, hist, lb, tickets,
@@ -197,6 +199,16 @@ int brush_ctx_set_timing(brush_ctx* ctx, int enabled) {
     return BRUSH_OK;
 }
 
+int brush_ctx_set_sh_ready_event(brush_ctx* ctx, void* event) {
+    if (!ctx) return BRUSH_E_INVALID;
+    ctx->sh_ready = event;
+    return BRUSH_OK;
+}
+int brush_ctx_set_split_colors(brush_ctx* ctx, int enabled) {
+    if (!ctx) return BRUSH_E_INVALID;
+    ctx->split_colors = enabled ? 1 : 0;
+    return BRUSH_OK;
+}
 int brush_ctx_set_pair_counting(brush_ctx* ctx, int enabled) {
     if (!ctx) return BRUSH_E_INVALID;
     ctx->pair_counting = enabled ? 1 : 0;
@@ -374,11 +386,17 @@ int brush_render_forward(brush_ctx* ctx, const BrushUniforms* uniforms_host, uin
         launch_radix_sort_u32((uint32_t*)ctx->depth_bits.p, (uint32_t*)ctx->presort_gid.p, aux->num_visible, N, 32,
                               (uint32_t*)ctx->depth_sorted.p, gfc, ss_depth, st);
     }
+    // Deferred colours: when the caller announced that sh_coeffs is still being written on another stream
+    // (brush_ctx_set_sh_ready_event), nothing before the rasterizer reads it; the SH evaluation runs as its own
+    // kernel behind the event.  Same arithmetic, same bits as the fused kernel.
+    void* const sh_ready = ctx->sh_ready;
+    ctx->sh_ready = nullptr;
+    const bool defer_colors = sh_ready != nullptr || ctx->split_colors;
     {   // render.rs:168-184
         StageTimer t(ctx, st, BRUSH_STAGE_PROJECT_VISIBLE);
         launch_project_visible(cam, N, K, means, log_scales, quats, sh_coeffs, raw_opacity, gfc, aux->num_visible,
                                aux->projected_splats, (uint32_t*)ctx->num_tiles_hit.p, (uint64_t*)ctx->tile_masks.p,
-                               (uint32_t*)ctx->tile_boxes.p, st);
+                               (uint32_t*)ctx->tile_boxes.p, !defer_colors, st);
     }
     {   // render.rs:186-192
         StageTimer t(ctx, st, BRUSH_STAGE_PREFIX_SUM);
@@ -411,6 +429,11 @@ int brush_render_forward(brush_ctx* ctx, const BrushUniforms* uniforms_host, uin
         StageTimer t(ctx, st, BRUSH_STAGE_TILE_BINS);
         launch_tile_bins(fused ? nullptr : tid_sorted, fused ? (uint64_t*)tid_sorted : nullptr,
                          aux->num_intersections, cap, num_tiles, (uint32_t*)aux->tile_bins, st);
+    }
+    if (defer_colors) {
+        if (sh_ready) CU(cudaStreamWaitEvent(st, (cudaEvent_t)sh_ready, 0));
+        NvtxRange span("ProjectColors");
+        launch_project_colors(cam, N, K, means, sh_coeffs, gfc, aux->num_visible, aux->projected_splats, st);
     }
     {   // render.rs:267-307
         StageTimer t(ctx, st, BRUSH_STAGE_RASTERIZE);
@@ -909,8 +932,12 @@ int brush_dp_adam_step(brush_ctx* ctx, const BrushDpStep* sp, const BrushDpSegme
     L.src_mc = sp->src_multicast; L.dst_mc = sp->dst_multicast;
     L.m = sp->m; L.v = sp->v;
     L.loss_off = sp->loss_offset; L.loss_out = sp->loss_out;
-    L.arrive = (uint32_t*)ctx->sticky.p + 16;
+    if (sp->lane < 0 || sp->lane > 1 || sp->ctas_per_sm < 0 || sp->ctas_per_sm > 16)
+        return fail(ctx, BRUSH_E_INVALID, "dp_adam: lane must be 0 or 1, ctas_per_sm 0..16");
+    L.arrive = (uint32_t*)ctx->sticky.p + 16 + sp->lane;
     L.epoch = sp->epoch;
+    L.lane = sp->lane;
+    L.ctas_per_sm = sp->ctas_per_sm;
     for (int i = 0; i < n_segs; i++) {
         const BrushDpSegment& g = segs[i];
         if ((g.src_offset | g.dst_offset | g.count) & 3u)

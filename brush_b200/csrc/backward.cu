@@ -303,6 +303,7 @@ backward_adam_kernel(const __grid_constant__ Cam cam, const float* __restrict__ 
     __shared__ float s_sh[256][ROW + 1];  // basis[K], v_rgb[3]
     const uint32_t N = cam.total_splats;
     const uint32_t g = blockIdx.x * 256u + threadIdx.x;
+    PDL_ENTER();
     if (g < N) {
         const float4* vp = reinterpret_cast<const float4*>(v_projected + (size_t)g * VP_STRIDE);
         const float4 vp0 = vp[0], vp1 = vp[1];
@@ -353,16 +354,16 @@ void launch_backward_adam(const Cam& cam, uint32_t N, uint32_t K, const float* n
     dim3 grid((N + 255) / 256), block(256);
     g_launch_count++;
     switch (K) {
-        case 1: backward_adam_kernel<1><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy, visible_mask,
-                                                                 grad_norm_accum, visible_accum); break;
-        case 4: backward_adam_kernel<4><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy, visible_mask,
-                                                                 grad_norm_accum, visible_accum); break;
-        case 9: backward_adam_kernel<9><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy, visible_mask,
-                                                                 grad_norm_accum, visible_accum); break;
-        case 16: backward_adam_kernel<16><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy, visible_mask,
-                                                                 grad_norm_accum, visible_accum); break;
-        case 25: backward_adam_kernel<25><<<grid, block, 0, st>>>(cam, norm_quats, v_projected, A, v_xy, visible_mask,
-                                                                 grad_norm_accum, visible_accum); break;
+        case 1: launch_k(backward_adam_kernel<1>, grid, block, 0, st, cam, norm_quats, v_projected, A, v_xy, visible_mask,
+                         grad_norm_accum, visible_accum); break;
+        case 4: launch_k(backward_adam_kernel<4>, grid, block, 0, st, cam, norm_quats, v_projected, A, v_xy, visible_mask,
+                         grad_norm_accum, visible_accum); break;
+        case 9: launch_k(backward_adam_kernel<9>, grid, block, 0, st, cam, norm_quats, v_projected, A, v_xy, visible_mask,
+                         grad_norm_accum, visible_accum); break;
+        case 16: launch_k(backward_adam_kernel<16>, grid, block, 0, st, cam, norm_quats, v_projected, A, v_xy, visible_mask,
+                         grad_norm_accum, visible_accum); break;
+        case 25: launch_k(backward_adam_kernel<25>, grid, block, 0, st, cam, norm_quats, v_projected, A, v_xy, visible_mask,
+                         grad_norm_accum, visible_accum); break;
     }
 }
 

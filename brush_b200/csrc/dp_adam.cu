@@ -36,12 +36,13 @@ template <bool MM_LD, bool MM_ST>
 __global__ void __launch_bounds__(256)
 dp_adam_kernel(const __grid_constant__ DpLaunch L) {
     const int world = L.world, rank = L.rank;
-    uint32_t* my_flags = L.flags[rank];
+    const int lane_off = L.lane * 2 * DP_MAX_WORLD;
+    uint32_t* my_flags = L.flags[rank] + lane_off;
     // ---- barrier 0: every rank's gradient buffer is complete (the producing kernels precede this launch in
     // stream order on their own GPU; the fence + release publishes them at system scope) ----
     if (blockIdx.x == 0 && threadIdx.x < (uint32_t)world) {
         __threadfence_system();
-        st_release_sys(L.flags[threadIdx.x] + 0 * DP_MAX_WORLD + rank, L.epoch);
+        st_release_sys(L.flags[threadIdx.x] + lane_off + 0 * DP_MAX_WORLD + rank, L.epoch);
     }
     wait_flags(my_flags, 0, world, L.epoch);
 
@@ -137,14 +138,20 @@ dp_adam_kernel(const __grid_constant__ DpLaunch L) {
     if (threadIdx.x == 0) *L.arrive = 0u;
     if (threadIdx.x < (uint32_t)world) {
         __threadfence_system();
-        st_release_sys(L.flags[threadIdx.x] + 1 * DP_MAX_WORLD + rank, L.epoch);
+        st_release_sys(L.flags[threadIdx.x] + lane_off + 1 * DP_MAX_WORLD + rank, L.epoch);
     }
     wait_flags(my_flags, 1, world, L.epoch);
 }
 
 void launch_dp_adam(const DpLaunch& L, cudaStream_t st) {
     g_launch_count++;
-    const int blocks = 148 * 6;
+    int sms = 148;
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    const int blocks = sms * (L.ctas_per_sm > 0 ? L.ctas_per_sm : 6);
     const bool mm_ld = L.src_mc != nullptr, mm_st = L.dst_mc != nullptr;
     if (mm_ld && mm_st) dp_adam_kernel<true, true><<<blocks, 256, 0, st>>>(L);
     else if (mm_ld) dp_adam_kernel<true, false><<<blocks, 256, 0, st>>>(L);

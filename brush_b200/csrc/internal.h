@@ -33,7 +33,12 @@ void launch_project_forward(const Cam& cam, uint32_t N, const float* means, cons
 void launch_project_visible(const Cam& cam, uint32_t N, uint32_t K, const float* means, const float* log_scales,
                             const float* quats, const float* coeffs, const float* raw_opac,
                             const uint32_t* global_from_compact, const int32_t* num_visible_dev, float* projected,
-                            uint32_t* num_tiles_hit, uint64_t* tile_masks, uint32_t* tile_boxes, cudaStream_t st);
+                            uint32_t* num_tiles_hit, uint64_t* tile_masks, uint32_t* tile_boxes, bool with_colors,
+                            cudaStream_t st);
+// The colour columns of `projected` when launch_project_visible ran with with_colors = false.
+void launch_project_colors(const Cam& cam, uint32_t N, uint32_t K, const float* means, const float* coeffs,
+                           const uint32_t* global_from_compact, const int32_t* num_visible_dev, float* projected,
+                           cudaStream_t st);
 void launch_map_intersects(const Cam& cam, uint32_t N, const float* projected, const uint32_t* cum_tiles_hit,
                            const int32_t* num_visible_dev, uint64_t capacity, uint32_t* tile_id_from_isect,
                            uint32_t* compact_gid_from_isect, const uint32_t* depth_sorted_bits,
@@ -86,7 +91,42 @@ void launch_gather_project_backward(const Cam& cam, uint32_t N, uint32_t K, cons
                                     const float* v_projected, float* v_means, float* v_xy, float* v_log_scales,
                                     float* v_quats, float* v_coeffs, float* v_raw_opac, cudaStream_t st);
 
+// ---- programmatic dependent launch (PDL) ----
+// A training step is ~22 short kernels on one stream; with plain launches each boundary costs a full drain of the
+// GPU, the launch latency and the ramp-up of the next grid (13 boundaries between the two rasterizers alone).
+// Every kernel of the step starts with PDL_ENTER(): griddepcontrol.wait (all memory of the preceding grid is
+// visible; a no-op for a plain launch) followed by griddepcontrol.launch_dependents (the next grid on the stream
+// may be scheduled as soon as every CTA of this one has got this far), and is launched through launch_k with the
+// programmatic-stream-serialization attribute: the next kernel's CTAs become resident while this kernel's last
+// wave drains and fall through their wait the moment it retires.  Nothing before PDL_ENTER() touches global
+// memory, so read-after-write and write-after-read order between kernels is exactly the stream order.
+// BRUSH_PDL=0 in the environment turns the attribute off (A/B measurements).
+bool pdl_enabled();
 #ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#define PDL_ENTER()              \
+    do {                         \
+        pdl_wait();              \
+        pdl_launch_dependents(); \
+    } while (0)
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                   Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // The one Adam update every optimizer kernel uses (adam_kernel, dp_adam_kernel, backward_adam_kernel), so the three
 // step paths give the same bits on the same gradients.  == AdamState::step of Burn 0.16 as brush-train calls it
 // (train.rs:318-359): bias-corrected moments, p -= lr * m_hat / (sqrt(v_hat) + eps).  div.approx / sqrt.approx
@@ -227,6 +267,8 @@ struct DpLaunch {
     float* loss_out;
     uint32_t* arrive;
     uint32_t epoch;
+    int lane;         // flag words [lane * 2 * DP_MAX_WORLD, ...) of every rank's flag block
+    int ctas_per_sm;  // 0 = default
     float beta1, beta2, eps, inv_bc1, inv_bc2, grad_scale;
     DpSeg seg[8];
 };

@@ -2,11 +2,21 @@
 // v_out_img directly, and a fused multi-tensor Adam over the five parameter groups.
 //   loss  == (pred_compare - gt).abs().mean()                  crates/brush-train/src/train.rs:255
 //   Adam  == AdamConfig::new().with_epsilon(1e-15) (Burn 0.16) crates/brush-train/src/train.rs:184,318-359
+#include <cstdlib>
+
 #include "internal.h"
 
 namespace brush {
 
 std::atomic<uint64_t> g_launch_count{0};
+
+bool pdl_enabled() {
+    static const bool on = [] {
+        const char* e = getenv("BRUSH_PDL");
+        return !(e && e[0] == '0');
+    }();
+    return on;
+}
 
 // pred f32[P,4]; gt f32[P,C] (C = 3: RGB compare, C = 4: RGBA compare).  v_out[P,4] = d mean|pred-gt| / d pred.
 // loss_out[0] += sum |pred-gt| / (P*C)   (must be zeroed by the caller; one atomic per CTA)
@@ -119,6 +129,7 @@ void launch_adam(const AdamLaunch& L, cudaStream_t st) {
 // both directions to Burn's elementwise ops + autodiff) ----
 __global__ void __launch_bounds__(256)
 quat_normalize_kernel(const float4* __restrict__ q, uint32_t n, float4* __restrict__ out) {
+    PDL_ENTER();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float4 v = q[i];
@@ -180,7 +191,7 @@ void launch_image_u8_to_f32(const unsigned char* src, size_t n, float* dst, cuda
 void launch_quat_normalize(const float* q, uint32_t n, float* out, cudaStream_t st) {
     if (!n) return;
     g_launch_count++;
-    quat_normalize_kernel<<<(n + 255) / 256, 256, 0, st>>>((const float4*)q, n, (float4*)out);
+    launch_k(quat_normalize_kernel, (n + 255) / 256, 256, 0, st, (const float4*)q, n, (float4*)out);
 }
 void launch_quat_normalize_vjp(const float* q, uint32_t n, float* v_inout, cudaStream_t st) {
     if (!n) return;
@@ -197,6 +208,7 @@ void launch_xy_grad_stats(const float* v_xy, const uint8_t* visible_mask, uint32
 
 __global__ void __launch_bounds__(256)
 zero_fill_kernel(uint4* __restrict__ p16, size_t n16, unsigned char* __restrict__ tail, uint32_t ntail) {
+    PDL_ENTER();
     const size_t stride = (size_t)gridDim.x * 256u;
     for (size_t i = (size_t)blockIdx.x * 256u + threadIdx.x; i < n16; i += stride) p16[i] = make_uint4(0u, 0u, 0u, 0u);
     if (blockIdx.x == 0 && threadIdx.x < ntail) tail[threadIdx.x] = 0;
@@ -207,7 +219,7 @@ cudaError_t zero_async(void* p, size_t bytes, cudaStream_t st) {
     if (((uintptr_t)b & 15u) || bytes < 16) {  // unaligned or tiny: byte-wise through the tail path when it fits
         if (bytes <= 256) {
             g_launch_count++;
-            zero_fill_kernel<<<1, 256, 0, st>>>(nullptr, 0, b, (uint32_t)bytes);
+            launch_k(zero_fill_kernel, 1, 256, 0, st, (uint4*)nullptr, (size_t)0, b, (uint32_t)bytes);
             return cudaGetLastError();
         }
         return cudaMemsetAsync(p, 0, bytes, st);
@@ -216,12 +228,13 @@ cudaError_t zero_async(void* p, size_t bytes, cudaStream_t st) {
     size_t blocks = (n16 + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
     g_launch_count++;
-    zero_fill_kernel<<<(uint32_t)blocks, 256, 0, st>>>((uint4*)b, n16, b + n16 * 16, (uint32_t)(bytes - n16 * 16));
+    launch_k(zero_fill_kernel, (uint32_t)blocks, 256, 0, st, (uint4*)b, n16, b + n16 * 16, (uint32_t)(bytes - n16 * 16));
     return cudaGetLastError();
 }
 
 __global__ void __launch_bounds__(256)
 zero_multi_kernel(const __grid_constant__ ZeroSegs z) {
+    PDL_ENTER();
     const size_t stride = (size_t)gridDim.x * 256u, t0 = (size_t)blockIdx.x * 256u + threadIdx.x;
     if (z.words_dst && t0 < z.n_words) z.words_dst[t0] = z.words[t0];
 #pragma unroll
@@ -246,7 +259,7 @@ cudaError_t zero_multi_async(const ZeroSegs& z, cudaStream_t st) {
     size_t blocks = (mx / 16 + 255) / 256;
     blocks = blocks < 1 ? 1 : (blocks > 148 * 8 ? 148 * 8 : blocks);
     g_launch_count++;
-    zero_multi_kernel<<<(uint32_t)blocks, 256, 0, st>>>(z);
+    launch_k(zero_multi_kernel, (uint32_t)blocks, 256, 0, st, z);
     return cudaGetLastError();
 }
 

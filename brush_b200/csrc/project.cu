@@ -39,6 +39,7 @@ project_forward_kernel(const __grid_constant__ Cam cam, const float* __restrict_
     __shared__ uint32_t s_tile, s_base;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t N = cam.total_splats;
+    PDL_ENTER();
     if (tid == 0) s_tile = atomicAdd(ticket, 1u);
     __syncthreads();
     const uint32_t tile = s_tile;
@@ -108,9 +109,8 @@ void launch_project_forward(const Cam& cam, uint32_t N, const float* means, cons
     if (N == 0) return;
     uint32_t tiles = (N + PF_THREADS - 1) / PF_THREADS;
     g_launch_count++;
-    project_forward_kernel<<<tiles, PF_THREADS, 0, st>>>(cam, means, log_scales, quats, presort_gid, depth_bits,
-                                                         lb_status, ticket, uniforms_dev, num_visible_out,
-                                                         visible_mask);
+    launch_k(project_forward_kernel, tiles, PF_THREADS, 0, st, cam, means, log_scales, quats, presort_gid, depth_bits,
+             lb_status, ticket, uniforms_dev, num_visible_out, visible_mask);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -232,7 +232,10 @@ BD void shrink_to_ellipse(TileBox& b, const VisTest& vt) {
     b.maxx = max(maxx, minx); b.maxy = max(maxy, miny);
 }
 
-template <int K>
+// COLOR = false: the SH evaluation is left to project_colors_kernel (same arithmetic, same bits), so that everything
+// up to the rasterizer runs without reading sh_coeffs -- in the view-parallel step the SH part of the parameter
+// exchange is still in flight on another stream while the next forward projects, sorts and bins (api.cu).
+template <int K, bool COLOR>
 __global__ void __launch_bounds__(256)
 project_visible_kernel(const __grid_constant__ Cam cam, const float* __restrict__ means,
                        const float* __restrict__ log_scales, const float* __restrict__ quats,
@@ -241,6 +244,7 @@ project_visible_kernel(const __grid_constant__ Cam cam, const float* __restrict_
                        float* __restrict__ projected, uint32_t* __restrict__ num_tiles_hit,
                        uint64_t* __restrict__ tile_masks, uint32_t* __restrict__ tile_boxes) {
     const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    PDL_ENTER();
     const uint32_t V = (uint32_t)*num_visible_dev;
     const bool valid = c < V;  // V <= total_splats
     if (c < cam.total_splats && !valid) num_tiles_hit[c] = 0u;  // the scan runs over all N (render.rs:164-165,187)
@@ -259,16 +263,18 @@ project_visible_kernel(const __grid_constant__ Cam cam, const float* __restrict_
         V3 cov2d = calc_cov2d(cam, p_view, scale, V4{q4.x, q4.y, q4.z, q4.w});
         V3 conic = cov_to_conic(cov2d);
         V2 xy = project_pix(cam, p_view);
-        V3 viewdir = normalize3(mean - cam.t);  // project_visible.wgsl:232-233
-        V3 color = eval_sh_color<K>(cam.sh_degree, viewdir, coeffs, g);
-        color = {color.x + 0.5f, color.y + 0.5f, color.z + 0.5f};
         uint32_t radius = radius_from_conic(conic);
         b = get_tile_bbox(xy, radius, cam.tiles_x, cam.tiles_y);
         vt = make_vis_test(xy, conic, opac);
         shrink_to_ellipse(b, vt);
         float* p = projected + (size_t)c * 9;
         p[0] = xy.x; p[1] = xy.y; p[2] = conic.x; p[3] = conic.y; p[4] = conic.z;
-        p[5] = color.x; p[6] = color.y; p[7] = color.z; p[8] = opac;
+        p[8] = opac;
+        if (COLOR) {
+            V3 viewdir = normalize3(mean - cam.t);  // project_visible.wgsl:232-233
+            V3 color = eval_sh_color<K>(cam.sh_degree, viewdir, coeffs, g);
+            p[5] = color.x + 0.5f; p[6] = color.y + 0.5f; p[7] = color.z + 0.5f;
+        }
     }
     const TileHits hits = warp_tile_hits(vt, b, valid, threadIdx.x & 31u);
     if (valid) {
@@ -278,23 +284,61 @@ project_visible_kernel(const __grid_constant__ Cam cam, const float* __restrict_
     }
 }
 
+// == the colour half of project_visible.wgsl:163-258 (sh_coeffs_to_color, :51-147) for the deferred-colour forward:
+// projected[c][5..8) = SH(degree, normalize(mean - viewmat[3].xyz)) + 0.5 for every compact id c < num_visible.
+template <int K>
+__global__ void __launch_bounds__(256)
+project_colors_kernel(const __grid_constant__ Cam cam, const float* __restrict__ means,
+                      const float* __restrict__ coeffs, const uint32_t* __restrict__ global_from_compact,
+                      const int32_t* __restrict__ num_visible_dev, float* __restrict__ projected) {
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    PDL_ENTER();
+    if (c >= (uint32_t)*num_visible_dev) return;
+    const uint32_t g = global_from_compact[c];
+    const V3 mean = {__ldg(means + 3 * (size_t)g), __ldg(means + 3 * (size_t)g + 1), __ldg(means + 3 * (size_t)g + 2)};
+    const V3 viewdir = normalize3(mean - cam.t);
+    const V3 color = eval_sh_color<K>(cam.sh_degree, viewdir, coeffs, g);
+    float* p = projected + (size_t)c * 9;
+    p[5] = color.x + 0.5f; p[6] = color.y + 0.5f; p[7] = color.z + 0.5f;
+}
+
 void launch_project_visible(const Cam& cam, uint32_t N, uint32_t K, const float* means, const float* log_scales,
                             const float* quats, const float* coeffs, const float* raw_opac,
                             const uint32_t* global_from_compact, const int32_t* num_visible_dev, float* projected,
-                            uint32_t* num_tiles_hit, uint64_t* tile_masks, uint32_t* tile_boxes, cudaStream_t st) {
+                            uint32_t* num_tiles_hit, uint64_t* tile_masks, uint32_t* tile_boxes, bool with_colors,
+                            cudaStream_t st) {
     if (N == 0) return;
     dim3 grid((N + 255) / 256), block(256);
     g_launch_count++;
 #define PV_ARGS cam, means, log_scales, quats, coeffs, raw_opac, global_from_compact, num_visible_dev, projected, \
                 num_tiles_hit, tile_masks, tile_boxes
+#define PV_CASE(k)                                                                                   \
+    case k:                                                                                          \
+        if (with_colors) launch_k(project_visible_kernel<k, true>, grid, block, 0, st, PV_ARGS);     \
+        else launch_k(project_visible_kernel<1, false>, grid, block, 0, st, PV_ARGS);                \
+        break;
     switch (K) {
-        case 1: project_visible_kernel<1><<<grid, block, 0, st>>>(PV_ARGS); break;
-        case 4: project_visible_kernel<4><<<grid, block, 0, st>>>(PV_ARGS); break;
-        case 9: project_visible_kernel<9><<<grid, block, 0, st>>>(PV_ARGS); break;
-        case 16: project_visible_kernel<16><<<grid, block, 0, st>>>(PV_ARGS); break;
-        case 25: project_visible_kernel<25><<<grid, block, 0, st>>>(PV_ARGS); break;
+        PV_CASE(1) PV_CASE(4) PV_CASE(9) PV_CASE(16) PV_CASE(25)
     }
+#undef PV_CASE
 #undef PV_ARGS
+}
+
+void launch_project_colors(const Cam& cam, uint32_t N, uint32_t K, const float* means, const float* coeffs,
+                           const uint32_t* global_from_compact, const int32_t* num_visible_dev, float* projected,
+                           cudaStream_t st) {
+    if (N == 0) return;
+    dim3 grid((N + 255) / 256), block(256);
+    g_launch_count++;
+#define PC_ARGS cam, means, coeffs, global_from_compact, num_visible_dev, projected
+    switch (K) {
+        case 1: launch_k(project_colors_kernel<1>, grid, block, 0, st, PC_ARGS); break;
+        case 4: launch_k(project_colors_kernel<4>, grid, block, 0, st, PC_ARGS); break;
+        case 9: launch_k(project_colors_kernel<9>, grid, block, 0, st, PC_ARGS); break;
+        case 16: launch_k(project_colors_kernel<16>, grid, block, 0, st, PC_ARGS); break;
+        case 25: launch_k(project_colors_kernel<25>, grid, block, 0, st, PC_ARGS); break;
+    }
+#undef PC_ARGS
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -307,6 +351,7 @@ map_intersects_kernel(const __grid_constant__ Cam cam, const float* __restrict__
                       const uint32_t* __restrict__ tile_boxes) {
     const uint32_t FULL = 0xffffffffu;
     const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31u;
+    PDL_ENTER();
     const uint32_t V = (uint32_t)*num_visible_dev;
     const bool valid = c < V;
     if (__all_sync(FULL, !valid)) return;
@@ -387,10 +432,8 @@ void launch_map_intersects(const Cam& cam, uint32_t N, const float* projected, c
                            const uint32_t* tile_boxes, cudaStream_t st) {
     if (N == 0) return;
     g_launch_count++;
-    map_intersects_kernel<<<(N + 255) / 256, 256, 0, st>>>(cam, projected, cum_tiles_hit, num_visible_dev, capacity,
-                                                           tile_id_from_isect, compact_gid_from_isect,
-                                                           depth_sorted_bits, key64_from_isect, tile_masks,
-                                                           tile_boxes);
+    launch_k(map_intersects_kernel, (N + 255) / 256, 256, 0, st, cam, projected, cum_tiles_hit, num_visible_dev, capacity,
+             tile_id_from_isect, compact_gid_from_isect, depth_sorted_bits, key64_from_isect, tile_masks, tile_boxes);
 }
 
 }  // namespace brush

@@ -12,6 +12,7 @@ namespace brush {
 __global__ void __launch_bounds__(256)
 tile_bins_kernel(const uint32_t* __restrict__ tile_ids, const uint64_t* __restrict__ keys64,
                  const int32_t* __restrict__ n_dev, uint64_t capacity, uint32_t* __restrict__ tile_bins) {
+    PDL_ENTER();
     const uint32_t n = (uint32_t)min((uint64_t)max(*n_dev, 0), capacity);
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const uint32_t cur = keys64 ? (uint32_t)(keys64[i] >> 32) : tile_ids[i];
@@ -36,8 +37,8 @@ void launch_tile_bins(const uint32_t* sorted_tile_ids, const uint64_t* sorted_ke
     uint64_t blocks = (capacity + 255) / 256;
     if (blocks > 148 * 16) blocks = 148 * 16;
     g_launch_count++;
-    tile_bins_kernel<<<(uint32_t)blocks, 256, 0, st>>>(sorted_tile_ids, sorted_keys64, n_isect_dev, capacity,
-                                                       tile_bins);
+    launch_k(tile_bins_kernel, (uint32_t)blocks, 256, 0, st, sorted_tile_ids, sorted_keys64, n_isect_dev, capacity,
+             tile_bins);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -259,6 +260,7 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
     const bool inside = px < cam.img_w && py < cam.img_h;
     const float pcx = (float)px + 0.5f, pcy = (float)py + 0.5f;
 
+    PDL_ENTER();
     const uint2 range = __ldg(reinterpret_cast<const uint2*>(tile_bins) + tile_id);
     const uint32_t num_batches = (range.y - range.x + TILE_SIZE - 1) / TILE_SIZE;
     // Transmittance; a pixel that is finished (or outside the image) carries it NEGATED, so "still compositing"
@@ -366,10 +368,10 @@ void launch_rasterize(const Cam& cam, const uint32_t* compact_gid_from_isect, co
     dim3 grid(cam.tiles_x, cam.tiles_y);
     g_launch_count++;
 #define RK_ARGS cam, compact_gid_from_isect, tile_bins, projected, out_img, final_index, pair_counter
-    if (raster_u32 && pair_counter) rasterize_kernel<true, true><<<grid, TILE_SIZE, 0, st>>>(RK_ARGS);
-    else if (raster_u32) rasterize_kernel<true, false><<<grid, TILE_SIZE, 0, st>>>(RK_ARGS);
-    else if (pair_counter) rasterize_kernel<false, true><<<grid, TILE_SIZE, 0, st>>>(RK_ARGS);
-    else rasterize_kernel<false, false><<<grid, TILE_SIZE, 0, st>>>(RK_ARGS);
+    if (raster_u32 && pair_counter) launch_k(rasterize_kernel<true, true>, grid, TILE_SIZE, 0, st, RK_ARGS);
+    else if (raster_u32) launch_k(rasterize_kernel<true, false>, grid, TILE_SIZE, 0, st, RK_ARGS);
+    else if (pair_counter) launch_k(rasterize_kernel<false, true>, grid, TILE_SIZE, 0, st, RK_ARGS);
+    else launch_k(rasterize_kernel<false, false>, grid, TILE_SIZE, 0, st, RK_ARGS);
 #undef RK_ARGS
 }
 
@@ -497,6 +499,7 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
     const float pcx = (float)px + 0.5f, pcy = (float)py + 0.5f;
     const float rx0 = (float)bx0 + 0.5f, ry0 = (float)by0 + 0.5f;  // pixel centre of the warp's first pixel
 
+    PDL_ENTER();
     const uint2 range = __ldg(reinterpret_cast<const uint2*>(tile_bins) + tile_id);
     if (range.y <= range.x) return;
     if (tid == 0) {
@@ -519,16 +522,27 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
     // D = T_final * v_a - dot(buffer, v_rgb) is carried, not the three buffer channels.
     float T = T_final;
     float D = T_final * v_out.w;
-    // Splats behind every pixel's last contributor are skipped warp-wide.
+    // Splats behind every pixel's last contributor are skipped warp-wide, and batches (and slots of the first
+    // batch) behind the last contributor of the WHOLE tile are not even staged: at 4K / 6 M splats most of a tile's
+    // list lies behind the point where its pixels saturate (13.6 evaluated pairs per staged intersection before).
     const uint32_t warp_final = __reduce_max_sync(0xffffffffu, inside ? final_isect : 0u);
     const bool warp_any_inside = __any_sync(0xffffffffu, inside);
+    __shared__ uint32_t s_warp_final[TILE_SIZE / 32];
+    if (lane == 0) s_warp_final[warp] = warp_final;
+    __syncthreads();
+    uint32_t tile_final = 0;
+#pragma unroll
+    for (uint32_t w2 = 0; w2 < TILE_SIZE / 32; w2++) tile_final = max(tile_final, s_warp_final[w2]);
+    if (tile_final < range.x) return;  // no pixel of the tile has a contributor (final_index is 0 then)
+    tile_final = min(tile_final, range.y - 1u);
 
     const uint32_t num_batches = (range.y - range.x + TILE_SIZE - 1) / TILE_SIZE;
-    for (uint32_t b = 0; b < num_batches; b++) {
+    for (uint32_t b = (range.y - 1u - tile_final) / TILE_SIZE; b < num_batches; b++) {
         __syncthreads();
         const uint32_t batch_end = range.y - b * TILE_SIZE;  // slot t of this batch <-> isect batch_end-1-t
         const uint32_t remaining = min(TILE_SIZE, batch_end - range.x);
-        if (tid < remaining) {  // gradient rows are indexed by GLOBAL splat id, so the per-splat backward is coalesced
+        const uint32_t t_lo_tile = batch_end - 1u > tile_final ? batch_end - 1u - tile_final : 0u;
+        if (tid >= t_lo_tile && tid < remaining) {  // gradient rows are indexed by GLOBAL splat id, so the per-splat backward is coalesced
             const uint32_t cg = __ldg(compact_gid_from_isect + batch_end - 1u - tid);
             stage_splat(sbase, tid, projected, cg, __ldg(global_from_compact + cg), (float)(tile_x * TILE_WIDTH),
                         (float)(tile_y * TILE_WIDTH));
@@ -598,9 +612,8 @@ void launch_rasterize_backward(const Cam& cam, const uint32_t* compact_gid_from_
         configured_devices.fetch_or(1ull << dev, std::memory_order_release);
     }
     g_launch_count++;
-    rasterize_backward_kernel<<<tiles, TILE_SIZE, BW_BYTES, st>>>(cam, compact_gid_from_isect, tile_bins, projected,
-                                                                 global_from_compact, final_index, out_img, v_out_img, v_projected,
-                                                                 pair_counter);
+    launch_k(rasterize_backward_kernel, tiles, TILE_SIZE, BW_BYTES, st, cam, compact_gid_from_isect, tile_bins, projected,
+             global_from_compact, final_index, out_img, v_out_img, v_projected, pair_counter);
 }
 
 }  // namespace brush

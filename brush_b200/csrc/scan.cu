@@ -18,6 +18,7 @@ inclusive_scan_kernel(const uint32_t* __restrict__ in, uint32_t n, uint32_t* __r
     __shared__ uint32_t s_warp[SC_THREADS / 32];
     __shared__ uint32_t s_tile, s_base;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    PDL_ENTER();
     if (tid == 0) s_tile = atomicAdd(ticket, 1u);
     __syncthreads();
     const uint32_t tile = s_tile;
@@ -79,7 +80,7 @@ void launch_inclusive_scan(const uint32_t* in, uint32_t n, uint32_t* out, uint64
     if (n == 0) return;
     uint32_t tiles = (n + SC_TILE - 1) / SC_TILE;
     g_launch_count++;
-    inclusive_scan_kernel<<<tiles, SC_THREADS, 0, st>>>(in, n, out, lb_status, ticket, total_out, cap, status_word);
+    launch_k(inclusive_scan_kernel, tiles, SC_THREADS, 0, st, in, n, out, lb_status, ticket, total_out, cap, status_word);
 }
 
 }  // namespace brush

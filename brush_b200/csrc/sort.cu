@@ -8,6 +8,8 @@
 // is sized for max_n and tiles past *n_dev exit at once.
 // Sort order contract: stable, ascending on the low 4*ceil(bits/4) key bits (exactly the bits the
 // reference's ceil(bits/4) passes look at).
+#include <cstdlib>
+
 #include "internal.h"
 
 namespace brush {
@@ -39,12 +41,22 @@ __device__ unsigned long long g_sort_prof[16];
 #define PROF_MARK(i) do { } while (0)
 #endif
 
+// Keys per thread.  BRUSH_SORT_ITEMS=8|16 overrides the 32-bit-key default (A/B: 8 halves the registers and doubles
+// the resident CTAs, at twice the look-back work per key).
 template <typename KeyT> struct SortCfg;
 template <> struct SortCfg<uint32_t> { static constexpr int ITEMS = 16; };
 template <> struct SortCfg<uint64_t> { static constexpr int ITEMS = 8; };
+static int items_u32() {
+    static const int v = [] {
+        const char* e = getenv("BRUSH_SORT_ITEMS");
+        const int x = e ? atoi(e) : 0;
+        return (x == 8 || x == 16) ? x : SortCfg<uint32_t>::ITEMS;
+    }();
+    return v;
+}
 
 size_t sort_tiles(uint32_t max_n, int key_bytes) {
-    uint32_t tile = RS_THREADS * (key_bytes == 8 ? SortCfg<uint64_t>::ITEMS : SortCfg<uint32_t>::ITEMS);
+    uint32_t tile = RS_THREADS * (key_bytes == 8 ? SortCfg<uint64_t>::ITEMS : items_u32());
     return ((size_t)max_n + tile - 1) / tile;
 }
 
@@ -72,8 +84,9 @@ __global__ void __launch_bounds__(RS_THREADS)
 radix_hist_kernel(const KeyT* __restrict__ keys, const int32_t* __restrict__ n_dev, uint32_t max_n,
                   const __grid_constant__ PassPlan plan, uint32_t* __restrict__ hist) {
     __shared__ uint32_t s_hist[RS_MAX_PASSES * RS_RADIX];
-    const uint32_t n = min((uint32_t)max(*n_dev, 0), max_n);
     for (uint32_t i = threadIdx.x; i < plan.passes * RS_RADIX; i += RS_THREADS) s_hist[i] = 0;
+    PDL_ENTER();
+    const uint32_t n = min((uint32_t)max(*n_dev, 0), max_n);
     __syncthreads();
     const uint32_t lane = threadIdx.x & 31u;
     // warp-uniform loop bound so match_any always sees the whole warp
@@ -116,12 +129,11 @@ radix_hist_kernel(const KeyT* __restrict__ keys, const int32_t* __restrict__ n_d
 }
 
 // ---- one onesweep pass ----
-template <typename KeyT>
+template <typename KeyT, int ITEMS>
 __global__ void __launch_bounds__(RS_THREADS)
 onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, KeyT* __restrict__ keys_out,
                 uint32_t* __restrict__ vals_out, const int32_t* __restrict__ n_dev, uint32_t max_n, uint32_t shift,
                 uint32_t mask, const uint32_t* __restrict__ hist, uint32_t* lb, uint32_t* ticket) {
-    constexpr int ITEMS = SortCfg<KeyT>::ITEMS;
     constexpr int TILE = RS_THREADS * ITEMS;
     __shared__ KeyT s_keys[TILE];
     __shared__ uint32_t s_vals[TILE];
@@ -132,14 +144,18 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ v
     __shared__ uint32_t s_tile;
 
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+    PDL_ENTER();
+    // The grid is sized for max_n (the count lives on the device).  CTAs beyond the tiles *n_dev needs leave at once
+    // -- no ticket, no shared-memory set-up: at 3 M intersections in a 16 M-entry buffer that is 3300 of 4096 CTAs --
+    // and the others draw tickets 0 .. tiles-1 in start order, so a tile never waits on one that has not started.
+    const uint32_t n = min((uint32_t)max(*n_dev, 0), max_n);
+    if ((uint64_t)blockIdx.x * TILE >= n) return;
 #pragma unroll
     for (int w = 0; w < RS_WARPS; w++) s_whist[w][tid] = 0;
+    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
     __syncthreads();
     const uint32_t tile = s_tile;
-    const uint32_t n = min((uint32_t)max(*n_dev, 0), max_n);
     const uint64_t tile_start = (uint64_t)tile * TILE;
-    if (tile_start >= n) return;
     const uint32_t count = (uint32_t)min((uint64_t)TILE, (uint64_t)n - tile_start);
 
     PROF_MARK(0);
@@ -297,6 +313,7 @@ static void radix_sort_impl(const KeyT* keys, const uint32_t* vals, const int32_
         return;
     }
     const uint32_t tiles = (uint32_t)sort_tiles(max_n, sizeof(KeyT));
+    const int items = sizeof(KeyT) == 8 ? SortCfg<uint64_t>::ITEMS : items_u32();
     if (!s.pre_zeroed) {
         ZeroSegs z{};
         z.p[0] = s.hist; z.bytes[0] = (size_t)plan.passes * RS_RADIX * 4;
@@ -307,7 +324,7 @@ static void radix_sort_impl(const KeyT* keys, const uint32_t* vals, const int32_
     uint32_t hist_blocks = (max_n + RS_THREADS * 4 - 1) / (RS_THREADS * 4);
     if (hist_blocks > 148 * 4) hist_blocks = 148 * 4;  // every block ends with up to passes*256 global atomics
     g_launch_count += 1 + plan.passes;
-    radix_hist_kernel<KeyT><<<hist_blocks, RS_THREADS, 0, st>>>(keys, n_dev, max_n, plan, s.hist);
+    launch_k(radix_hist_kernel<KeyT>, hist_blocks, RS_THREADS, 0, st, keys, n_dev, max_n, plan, s.hist);
     const KeyT* src_k = keys;
     const uint32_t* src_v = vals;
     KeyT* tmp_k = reinterpret_cast<KeyT*>(s.keys_tmp);
@@ -315,9 +332,14 @@ static void radix_sort_impl(const KeyT* keys, const uint32_t* vals, const int32_
         const bool to_out = ((plan.passes - 1 - p) % 2) == 0;
         KeyT* dst_k = to_out ? keys_out : tmp_k;
         uint32_t* dst_v = to_out ? vals_out : s.vals_tmp;
-        onesweep_kernel<KeyT><<<tiles, RS_THREADS, 0, st>>>(src_k, src_v, dst_k, dst_v, n_dev, max_n, plan.shift[p],
-                                                           plan.mask[p], s.hist + p * RS_RADIX,
-                                                           s.lb + (size_t)p * tiles * RS_RADIX, s.tickets + p);
+        if (items == 8 || sizeof(KeyT) == 8)
+            launch_k(onesweep_kernel<KeyT, 8>, tiles, RS_THREADS, 0, st, src_k, src_v, dst_k, dst_v, n_dev, max_n,
+                     plan.shift[p], plan.mask[p], (const uint32_t*)(s.hist + p * RS_RADIX),
+                     s.lb + (size_t)p * tiles * RS_RADIX, s.tickets + p);
+        else if constexpr (sizeof(KeyT) == 4)
+            launch_k(onesweep_kernel<KeyT, 16>, tiles, RS_THREADS, 0, st, src_k, src_v, dst_k, dst_v, n_dev, max_n,
+                     plan.shift[p], plan.mask[p], (const uint32_t*)(s.hist + p * RS_RADIX),
+                     s.lb + (size_t)p * tiles * RS_RADIX, s.tickets + p);
         src_k = dst_k;
         src_v = dst_v;
     }

@@ -171,6 +171,7 @@ ssim_stats_kernel(const float* __restrict__ pred, const float* __restrict__ gt, 
     __shared__ __align__(16) float s_line[SS_WARPS][SS_DEPTH][2][SS_LINE];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int item = blockIdx.x * SS_WARPS + warp;
+    PDL_ENTER();
     if (item >= G.strips * G.segs * 3) return;  // whole warps only; no CTA-wide barrier below
     StatsRow S;
     const int MW = W + 2, MH = H + 2;
@@ -311,6 +312,7 @@ image_loss_backward_kernel(const float* __restrict__ pred, const float* __restri
                            float* __restrict__ v_out, float* __restrict__ loss_out) {
     __shared__ __align__(16) float s_line[SS_WARPS][SS_DEPTH][5][SS_LINE];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    PDL_ENTER();
     const int item = blockIdx.x * SS_WARPS + warp;
     const int MH = H + 2, MW = W + 2;
     const float inv_l1 = 1.0f / ((float)H * (float)W * (float)C);
@@ -412,14 +414,13 @@ void launch_image_loss_backward(const float* pred, const float* gt, uint32_t H, 
     const SsimGrid GA = plan_grid((int)W + 2, (int)H + 2, (const void*)ssim_stats_kernel);
     const int items_a = GA.strips * GA.segs * 3;
     g_launch_count++;
-    ssim_stats_kernel<<<(items_a + SS_WARPS - 1) / SS_WARPS, 32 * SS_WARPS, 0, st>>>(pred, gt, (int)H, (int)W, (int)C,
-                                                                                    win, GA, maps, sums);
+    launch_k(ssim_stats_kernel, (items_a + SS_WARPS - 1) / SS_WARPS, 32 * SS_WARPS, 0, st, pred, gt, (int)H, (int)W, (int)C,
+             win, GA, maps, sums);
     const SsimGrid GB = plan_grid((int)W, (int)H, (const void*)image_loss_backward_kernel);
     const int items_b = GB.strips * GB.segs * 3;
     g_launch_count++;
-    image_loss_backward_kernel<<<(items_b + SS_WARPS - 1) / SS_WARPS, 32 * SS_WARPS, 0, st>>>(
-        pred, gt, (int)H, (int)W, (int)C, ssim_weight, win, GB, maps, sums, reinterpret_cast<uint32_t*>(sums + 4), v_out,
-        loss_out);
+    launch_k(image_loss_backward_kernel, (items_b + SS_WARPS - 1) / SS_WARPS, 32 * SS_WARPS, 0, st, pred, gt, (int)H, (int)W,
+             (int)C, ssim_weight, win, GB, (const float*)maps, sums, reinterpret_cast<uint32_t*>(sums + 4), v_out, loss_out);
 }
 
 }  // namespace brush

@@ -112,6 +112,12 @@ class SplatTrainer:
         self.views: Optional[ViewBuffers] = None
         self.epoch = 0
         self._copy_stream = None
+        # overlapped peer exchange (see _peer_step); BRUSH_DP_OVERLAP=0 restores the single-launch exchange
+        import os
+
+        self.overlap_exchange = os.environ.get("BRUSH_DP_OVERLAP", "1") != "0"
+        self.side_ctas = int(os.environ.get("BRUSH_DP_SIDE_CTAS", "2"))
+        self._xchg_stream, self._sh_pending = None, False
         self._alloc(num_points, sh_coeffs_per_channel)
 
     def _alloc(self, n: int, k: int):
@@ -227,6 +233,12 @@ class SplatTrainer:
         do_refine = (self.iter < cfg.max_refine_step and self.iter >= cfg.warmup_steps
                      and self.iter % cfg.refine_every == 1 and self.optimize)
         with torch.cuda.device(dev):
+            if self._sh_pending:
+                if do_refine or B != 1:
+                    self.finish()  # this step reads sh_coeffs before its (first) forward gets to the colours
+                else:
+                    ctx.set_sh_ready_event(self._ev_sh.cuda_event)  # the forward waits just before it needs colours
+                    self._sh_pending = False
             pre_step = [p.detach().clone() for p in (splats.means, splats.sh_coeffs, splats.rotation,
                                                      splats.raw_opacity, splats.log_scales)] if do_refine else None
             if batch.ready is not None:
@@ -327,6 +339,7 @@ class SplatTrainer:
                 self._slot_free[batch.slot].record(torch.cuda.current_stream(dev))
             refine = None
             if do_refine:
+                self.finish()
                 loss = loss.clone()
                 splats, refine = self.refine_splats(pre_step, splats)
         stats = TrainStepStats(preds, auxes, loss, lr_mean, cfg.lr_rotation, cfg.lr_scale, cfg.lr_coeffs_dc,
@@ -392,36 +405,73 @@ class SplatTrainer:
         return out, RefineStats(n_split, n_clone, alpha_pruned, scale_pruned)
 
     def _peer_step(self, ctx, lr_mean: float, grad_scale: float, st):
-        """One brush_dp_adam_step launch: sum of the ranks' gradients on the owned slice -> Adam (train.rs:318-359)
-        -> new parameters into every replica; the refine statistics ride along as plain-sum segments."""
+        """brush_dp_adam_step: sum of the ranks' gradients on the owned slice -> Adam (train.rs:318-359) -> new
+        parameters into every replica; the refine statistics ride along as plain-sum segments.
+
+        With `overlap_exchange` (default) the exchange is TWO launches: the small groups (means, opacity, rotation,
+        scales: 11 floats per splat, plus statistics and loss) on the step's stream, and the SH group (3K floats per
+        splat, 81 % of the bytes) on a side stream.  The next forward needs SH only for the colours, which it
+        evaluates last (brush_ctx_set_sh_ready_event): projection, both sorts, scan, intersection lists and tile bins
+        of step t+1 run while step t's SH exchange is still on the wire.  Parameters are exact, never stale."""
         cfg, pl, gl, peer = self.config, self.param_layout, self.layout, self.peer
         lrs = {"means": lr_mean, "opacity": cfg.lr_opac, "sh": cfg.lr_coeffs_dc, "rotation": cfg.lr_rotation,
                "log_scales": cfg.lr_scale}
+
+        def seg_array(names):
+            segs = (_lib.BrushDpSegment * len(names))()
+            for i, name in enumerate(names):
+                segs[i].src_offset = gl.offset(pl.GRAD_OF[name])
+                segs[i].dst_offset = pl.offset(name)
+                segs[i].count = pl.padded_size(name)
+                segs[i].adam = int(name in lrs and self.optimize)
+                segs[i].lr = lrs.get(name, 0.0)
+                segs[i].sh_coeffs_per_channel = self.k if name == "sh" else 0
+                segs[i].sh_rest_lr_scale = 1.0 / cfg.lr_coeffs_sh_scale
+            return segs
+
+        def launch(names, lane, ctas, loss_out, stream_ptr):
+            sp = _lib.BrushDpStep()
+            sp.world, sp.rank = peer.world, peer.rank
+            for r in range(peer.world):
+                sp.src[r], sp.dst[r], sp.flags[r] = peer.grad_ptrs[r], peer.param_ptrs[r], peer.flag_ptrs[r]
+            sp.src_multicast, sp.dst_multicast = peer.grad_mc or None, peer.param_mc or None
+            sp.m, sp.v = self.peer_m.data_ptr(), self.peer_v.data_ptr()
+            sp.loss_offset, sp.loss_out = gl.offset("loss"), loss_out
+            sp.epoch, sp.lane, sp.ctas_per_sm = self.epoch, lane, ctas
+            segs = seg_array(names)
+            ctx.check(_lib.lib().brush_dp_adam_step(ctx.handle, C.byref(sp), segs, len(segs), cfg.adam_beta1,
+                                                    cfg.adam_beta2, cfg.adam_eps, self.opt_step, grad_scale,
+                                                    C.c_void_p(stream_ptr)))
+
         names = list(pl.NAMES)
-        segs = (_lib.BrushDpSegment * len(names))()
-        for i, name in enumerate(names):
-            segs[i].src_offset = gl.offset(pl.GRAD_OF[name])
-            segs[i].dst_offset = pl.offset(name)
-            segs[i].count = pl.padded_size(name)
-            segs[i].adam = int(name in lrs and self.optimize)
-            segs[i].lr = lrs.get(name, 0.0)
-            segs[i].sh_coeffs_per_channel = self.k if name == "sh" else 0
-            segs[i].sh_rest_lr_scale = 1.0 / cfg.lr_coeffs_sh_scale
         if not self.optimize:  # gradients only: leave the parameters alone, still reduce the statistics
-            segs = (_lib.BrushDpSegment * 2)(segs[names.index("grad_norm")], segs[names.index("visible")])
+            names = ["grad_norm", "visible"]
         self.epoch += 1
-        sp = _lib.BrushDpStep()
-        sp.world, sp.rank = peer.world, peer.rank
-        for r in range(peer.world):
-            sp.src[r], sp.dst[r], sp.flags[r] = peer.grad_ptrs[r], peer.param_ptrs[r], peer.flag_ptrs[r]
-        sp.src_multicast, sp.dst_multicast = peer.grad_mc or None, peer.param_mc or None
-        sp.m, sp.v = self.peer_m.data_ptr(), self.peer_v.data_ptr()
-        sp.loss_offset, sp.loss_out = gl.offset("loss"), self.loss_buf.data_ptr()
-        sp.epoch = self.epoch
-        ctx.check(_lib.lib().brush_dp_adam_step(ctx.handle, C.byref(sp), segs, len(segs), cfg.adam_beta1,
-                                                cfg.adam_beta2, cfg.adam_eps, self.opt_step, grad_scale, st))
+        main = torch.cuda.current_stream(self.device)
+        if self.overlap_exchange and self.optimize and "sh" in names:
+            if self._xchg_stream is None:
+                self._xchg_stream = torch.cuda.Stream(self.device)
+                self._ev_grads, self._ev_sh = torch.cuda.Event(), torch.cuda.Event()
+            self._ev_grads.record(main)  # this rank's dense gradients are complete
+            launch([n for n in names if n != "sh"], 0, 0, self.loss_buf.data_ptr(), main.cuda_stream)
+            side = self._xchg_stream
+            side.wait_event(self._ev_grads)
+            launch(["sh"], 1, self.side_ctas, None, side.cuda_stream)
+            self._ev_sh.record(side)
+            self._sh_pending = True
+        else:
+            launch(names, 0, 0, self.loss_buf.data_ptr(), main.cuda_stream)
         views = pl.views(peer.param)
         return views[5], views[6]
+
+    def finish(self):
+        """Makes the current stream wait for an SH exchange that is still in flight on the side stream (overlapped
+        peer exchange).  step() hands the wait to the next forward instead; call this before reading the parameters
+        from any other code (evaluation renders go through the ctx and wait by themselves)."""
+        if self._sh_pending:
+            torch.cuda.current_stream(self.device).wait_event(self._ev_sh)
+            get_context(self.device).set_sh_ready_event(None)
+            self._sh_pending = False
 
     def _lr_mean(self, batch: SceneBatch) -> float:
         """ExponentialLrScheduler (Burn 0.16): step k (1-based) returns initial_lr * gamma^(k-1); train.rs:276-278."""

@@ -95,6 +95,14 @@ const char* brush_version(void);
 /* Tile-sort strategy: 0 = two-stage (depth sort, then stable sort by tile id: the reference's structure,
  * render.rs:151-156,225-237), 1 = single fused 64-bit (tile<<32 | depth_bits) key sort.  Same output. */
 int brush_ctx_set_sort_mode(brush_ctx* ctx, int fused64);
+/* View-parallel overlap (no reference counterpart).  `event` (a cudaEvent_t, or NULL to cancel) marks
+ * the point at which sh_coeffs becomes readable: the NEXT brush_render_forward on this ctx reads sh_coeffs only
+ * behind it (cudaStreamWaitEvent on its stream) and runs everything that does not need colours -- projection, both
+ * sorts, the scan, the intersection lists, the tile bins -- before that.  The SH evaluation then runs as its own
+ * kernel just before the rasterizer: same arithmetic and bits as the fused kernel.  One-shot: consumed by that
+ * forward.  brush_ctx_set_split_colors(1) makes every forward take the deferred-colour route (measurements). */
+int brush_ctx_set_sh_ready_event(brush_ctx* ctx, void* event);
+int brush_ctx_set_split_colors(brush_ctx* ctx, int enabled);
 /* Per-stage CUDA-event timing (the sync-span equivalent, crates/sync-span/src/lib.rs:26-41). Off by default. */
 int brush_ctx_set_timing(brush_ctx* ctx, int enabled);
 /* Synchronises `stream`, then fills out[0..n) with the last call's stage times in ms. */
@@ -255,7 +263,7 @@ int brush_xy_grad_stats(brush_ctx* ctx, const float* v_xy, const BrushAux* aux, 
  * m, v are touched only on the owned slice) or just the sum (adam = 0: refine statistics), and stores the result
  * into every rank's `dst` buffer.  All buffers named here except m, v, loss_out must be peer-mapped on every rank
  * (cudaIpc / CUDA VMM / torch symmetric memory); src[i], dst[i], flags[i] are rank i's buffers as mapped in THIS
- * process.  flags[i]: uint32[2 * BRUSH_DP_MAX_WORLD], zeroed once at allocation.  epoch: the same strictly
+ * process.  flags[i]: uint32[2 * BRUSH_DP_MAX_WORLD] per lane (see `lane`), zeroed once at allocation.  epoch: the same strictly
  * increasing value (>= 1) on every rank for every call.  Every rank must make the matching call. */
 typedef struct BrushDpSegment {
     uint64_t src_offset;   /* floats, multiple of 4 */
@@ -278,6 +286,13 @@ typedef struct BrushDpStep {
     uint64_t loss_offset;         /* float index inside src of the rank's loss term */
     float* loss_out;              /* local f32[1] = grad_scale * sum of the ranks' loss terms, or NULL */
     uint32_t epoch;
+    /* Two exchanges may be in flight at once on different streams (e.g. the small parameter groups on the step's
+     * stream and the SH group on a side stream that the next forward overlaps): each uses its own `lane` (0 or 1) =
+     * its own flag words inside flags[] (which must then hold 4 * BRUSH_DP_MAX_WORLD words) and arrival counter.
+     * Epochs are per lane.  ctas_per_sm = 0 picks the default grid (6 CTAs per SM); an overlapped exchange should
+     * leave room for the kernels it runs beside (2). */
+    int32_t lane;
+    int32_t ctas_per_sm;
 } BrushDpStep;
 int brush_dp_adam_step(brush_ctx* ctx, const BrushDpStep* step_host, const BrushDpSegment* segments_host,
                        int n_segments, float beta1, float beta2, float eps, uint32_t adam_step, float grad_scale,

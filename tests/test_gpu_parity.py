@@ -19,10 +19,40 @@ def T(a, dtype=torch.float32):
     return torch.as_tensor(np.ascontiguousarray(a), device=DEV).to(dtype)
 
 
+def record_counts(**kv):
+    """Appends the exception counts a parity test OBSERVED (pixels over 1e-5, final_index mismatches, gradient entries
+    outside 1e-3 relative) to gpurun_out/parity_counts.json, keyed by the running test; the file of the last full run
+    is committed as profiles/r2_parity_counts.json and quoted in DESIGN.md section 4.  The asserts bound the counts;
+    this records what they actually were."""
+    import json
+    import os
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    path = os.environ.get("BRUSH_PARITY_COUNTS", os.path.join(root, "gpurun_out", "parity_counts.json"))
+    test = os.environ.get("PYTEST_CURRENT_TEST", "?").split(" ")[0].split("::")[-1]
+    try:
+        os.makedirs(os.path.dirname(path), exist_ok=True)
+        data = {}
+        if os.path.exists(path):
+            with open(path) as f:
+                data = json.load(f)
+        entry = data.setdefault(test, {})
+        for k, v in kv.items():
+            if isinstance(v, dict):
+                entry.setdefault(k, {}).update(v)
+            else:
+                entry[k] = v
+        with open(path, "w") as f:
+            json.dump(data, f, indent=1, sort_keys=True)
+    except OSError:
+        pass
+
+
 def grads_close(a, b, name):
     a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
     scale = np.abs(b).max() + 1e-30
     bad = np.abs(a - b) > 1e-3 * np.abs(b) + 2e-5 * scale
+    record_counts(grad_entries_outside_1e_3={name: [int(bad.sum()), int(bad.size)]})
     assert not bad.any(), f"{name}: {bad.sum()} / {bad.size} outside 1e-3 rel; max abs diff {np.abs(a - b).max():.3e}, scale {scale:.3e}"
 
 
@@ -182,10 +212,14 @@ def _check_forward(img, aux, ref_img, ref_aux, fused=False):
     # cut-off and exp() rounds differently on the two machines (the pair is then kept on one side only: an error of
     # at most alpha * T <= 1/255 on that pixel).  Those pixels are counted and bounded, never ignored.
     err = np.abs(img.cpu().numpy() - ref_img).max(axis=2)
-    assert (err > 1e-5).sum() <= max(2, 2e-5 * err.size), f"{(err > 1e-5).sum()} pixels over 1e-5"
-    assert err.max() < 1.0 / 255.0 + 1e-4 and np.median(err) < 1e-6
     fi = aux.final_index.cpu().numpy().view(np.uint32)
-    assert (fi != ref_aux.final_index).mean() < 1e-3  # decided by exp() rounding at the 1/255 threshold
+    record_counts(pixels=int(err.size), pixels_over_1e_5=int((err > 1e-5).sum()), max_abs_err=float(err.max()),
+                  final_index_mismatches=int((fi != ref_aux.final_index).sum()), num_visible=int(V), num_intersections=int(I))
+    # bounds = a few times the counts observed on B200 (profiles/r2_parity_counts.json: at most 1 pixel per megapixel
+    # over 1e-5 and 2 final_index mismatches in any case that goes through here)
+    assert (err > 1e-5).sum() <= max(2, 4e-6 * err.size), f"{(err > 1e-5).sum()} pixels over 1e-5"
+    assert err.max() < 1.0 / 255.0 + 1e-4 and np.median(err) < 1e-6
+    assert (fi != ref_aux.final_index).sum() <= max(2, 1e-5 * err.size)  # decided by exp() rounding at the 1/255 threshold
 
 
 @pytest.mark.parametrize("n,w,h,deg,seed", [(16_384, 256, 256, 0, 1001), (20_000, 333, 200, 3, 7),
@@ -252,6 +286,47 @@ def test_large_splats_boxes_beyond_the_hit_mask(oracle, fused):
     hits = np.diff(np.concatenate([[0], ref_aux.cum_tiles_hit[:ref_aux.num_visible].astype(np.int64)]))
     assert hits.max() > 64 and (hits > 32).sum() > 10 and (hits <= 4).sum() > 10  # all three paths are exercised
     _check_forward(img, aux, ref_img, ref_aux, fused=fused)
+
+
+def test_deferred_colours_forward_is_bit_identical():
+    """brush_ctx_set_sh_ready_event / set_split_colors: the forward that evaluates SH colours in their own kernel just
+    before the rasterizer (so that it can run under an in-flight SH exchange) must reproduce the fused forward bit for
+    bit -- image, projected splats and every aux tensor -- with and without a pending event."""
+    from brush_b200 import get_context, make_uniforms, render_forward, scene
+
+    w, h = 240, 160
+    sc = scene.make_scene(12_000, w, h, 3, 5)
+    vm, focal, center = reference_camera(w, h)
+    u = make_uniforms(vm, focal, (w, h), center)
+    args = [T(sc.means), T(sc.log_scales), T(sc.quats), T(sc.sh_coeffs), T(sc.raw_opacity)]
+    ctx = get_context(DEV)
+    img0, aux0 = render_forward(u, *args, False)
+    ctx.set_split_colors(True)
+    try:
+        img1, aux1 = render_forward(u, *args, False)
+    finally:
+        ctx.set_split_colors(False)
+    # with an event: SH written on a side stream just before; the forward must pick the new values up
+    side = torch.cuda.Stream()
+    ev = torch.cuda.Event()
+    sh2 = args[3].clone()
+    torch.cuda.synchronize()
+    with torch.cuda.stream(side):
+        torch.cuda._sleep(20_000_000)  # ~10 ms: the forward's geometry stages finish long before this
+        sh2.mul_(0.5)
+        ev.record(side)
+    ctx.set_sh_ready_event(ev.cuda_event)
+    img2, aux2 = render_forward(u, args[0], args[1], args[2], sh2, args[4], False)
+    torch.cuda.synchronize()
+    img3, _ = render_forward(u, args[0], args[1], args[2], sh2, args[4], False)  # plain forward on the final values
+    V, I = aux0.read_num_visible(), aux0.read_num_intersections()
+    assert V == aux1.read_num_visible() and I == aux1.read_num_intersections() and V > 1000
+    assert torch.equal(img0, img1) and torch.equal(aux0.projected_splats[:V], aux1.projected_splats[:V])
+    assert torch.equal(aux0.final_index, aux1.final_index) and torch.equal(aux0.tile_bins, aux1.tile_bins)
+    assert torch.equal(aux0.cum_tiles_hit, aux1.cum_tiles_hit)
+    assert torch.equal(aux0.compact_gid_from_isect[:I], aux1.compact_gid_from_isect[:I])
+    assert torch.equal(aux0.global_from_compact_gid, aux1.global_from_compact_gid)
+    assert torch.equal(img2, img3) and not torch.equal(img2, img0)
 
 
 def test_raster_u32(oracle):
@@ -334,11 +409,16 @@ def test_full_size_config4_vs_oracle(oracle):
     err = np.abs(img.cpu().numpy() - ref_img).max(axis=2)
     flips = int((err > 1e-5).sum())
     print(f"full size: V={V} I={I} max err {err.max():.2e}, pixels over 1e-5: {flips} of {err.size}")
-    assert flips <= 1e-4 * err.size and err.max() < 1.0 / 255.0 + 1e-4
+    fi = aux.final_index.cpu().numpy().view(np.uint32)
+    record_counts(pixels=int(err.size), pixels_over_1e_5=flips, max_abs_err=float(err.max()),
+                  final_index_mismatches=int((fi != ref_aux.final_index).sum()), num_visible=int(V), num_intersections=int(I))
+    # observed on B200: 7 pixels of 2 073 600 over 1e-5, 4 final_index mismatches (profiles/r2_parity_counts.json)
+    assert flips <= 16 and err.max() < 1.0 / 255.0 + 1e-4 and int((fi != ref_aux.final_index).sum()) <= 12
     for gname, gt in zip(["v_means", "v_xy", "v_log_scales", "v_quats", "v_coeffs", "v_raw_opac"], grads):
         a, b = gt.cpu().numpy().astype(np.float64), ref_grads[gname].astype(np.float64)
         bad = np.abs(a - b) > 1e-3 * np.abs(b) + 2e-5 * np.abs(b).max()
-        assert bad.mean() < 1e-5, f"{gname}: {bad.sum()} of {bad.size}"
+        record_counts(grad_entries_outside_1e_3={gname: [int(bad.sum()), int(bad.size)]})
+        assert bad.sum() <= 32, f"{gname}: {bad.sum()} of {bad.size}"  # observed: at most 10 entries (v_xy)
 
 
 @pytest.mark.parametrize("name", ["cfg2_100k_1024", "cfg3_300k_800"])
@@ -361,12 +441,50 @@ def test_baseline_configs_2_and_3_vs_oracle(oracle, name):
         bad = np.abs(a - b) > 1e-3 * np.abs(b) + 2e-5 * np.abs(b).max()
         # a pair sitting on the alpha = 1/255 threshold is kept by one machine only (see _check_forward): the splats
         # of those few pairs see a different gradient; counted and bounded
-        assert bad.mean() < 5e-5, f"{gname}: {bad.sum()} of {bad.size}"
+        record_counts(grad_entries_outside_1e_3={gname: [int(bad.sum()), int(bad.size)]})
+        assert bad.sum() <= 32, f"{gname}: {bad.sum()} of {bad.size}"  # observed: at most 9 entries (v_quats, cfg 2)
+
+
+@pytest.mark.parametrize("fused", [False, True])
+def test_config5_6m_4k_digest_vs_oracle(fused):
+    """BASELINE.json configs[4] PINNED: the oracle was run once offline at full size (tests/golden/make_cfg5_digest.py,
+    minutes of CPU) and its integer outputs committed as SHA-256 digests (tests/golden/cfg5_digest.json).  The GPU
+    lists -- depth order, scan, tile bins and the ~77 M-entry tile-sorted intersection list -- must hash to the same
+    values: bit-exact keys AND values at 1e8 sort elements, as crates/brush-sort/src/lib.rs:219-265 demands, in both
+    tile-sort modes."""
+    import json
+    import os
+    import sys
+
+    from brush_b200 import get_context, make_uniforms, render_forward, scene
+
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    sys.path.insert(0, gold)
+    from make_cfg5_digest import CAPACITY, WORKLOAD, digest
+
+    with open(os.path.join(gold, "cfg5_digest.json")) as f:
+        want = json.load(f)
+    sc = scene.make_config_scene(WORKLOAD)
+    w, h = sc.width, sc.height
+    vm, focal, center = reference_camera(w, h)
+    u = make_uniforms(vm, focal, (w, h), center)
+    args = [T(sc.means), T(sc.log_scales), T(sc.quats), T(sc.sh_coeffs), T(sc.raw_opacity)]
+    ctx = get_context(DEV)
+    ctx.set_sort_mode(fused)
+    try:
+        _, aux = render_forward(u, *args, False, isect_capacity=CAPACITY)
+        ctx.sync_check()
+    finally:
+        ctx.set_sort_mode(False)
+    got = digest(aux.read_num_visible(), aux.read_num_intersections(), aux.global_from_compact_gid.cpu().numpy(),
+                 aux.cum_tiles_hit.cpu().numpy(), aux.tile_bins.cpu().numpy(), aux.compact_gid_from_isect.cpu().numpy())
+    for k, v in got.items():
+        assert want[k] == v, k
 
 
 def test_config5_6m_4k_properties():
-    """BASELINE.json configs[4]: 6M Gaussians, SH 3, 3840x2160, ~10^8 (tile, depth) keys -- too slow for the CPU
-    oracle inside the suite, so the size-independent properties of the path are checked instead: the scan total is
+    """BASELINE.json configs[4]: 6M Gaussians, SH 3, 3840x2160, ~10^8 (tile, depth) keys.  Besides the digest
+    comparison above, the size-independent properties of the path are checked: the scan total is
     the intersection count, the intersection list is sorted by tile and, inside a tile, by compact (= depth) order,
     tile_bins are exactly the run boundaries of the sorted tile ids, the compact order is (depth, gid) ascending,
     and a second forward reproduces every output bit for bit."""

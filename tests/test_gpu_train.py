@@ -639,7 +639,10 @@ def test_adam_time_restarts_after_refine(fused):
     assert tr.opt_step == 1
     for a, b, p0, lr in zip(splats.params(), twin.params(), before,
                             (cfg.lr_mean, cfg.lr_coeffs_dc, cfg.lr_rotation, cfg.lr_opac, cfg.lr_scale)):
-        assert torch.equal(a.detach(), b.detach())
+        # the two runs differ only by the order of the rasterizer's atomic adds: a first-step update is lr * sign(g),
+        # so all but the few elements whose gradient is within that noise of zero agree to rounding
+        d = (a.detach() - b.detach()).abs()
+        assert float((d <= 1e-3 * lr + 2e-6).float().mean()) > 0.999 and float(d.max()) <= 2.01 * lr
         step = (a.detach() - p0).abs()
         moved = step > 0
         # t = 1: |update| = lr * |g| / (|g| + eps) ~= lr for every element with a gradient (never ~2 lr)

@@ -125,3 +125,34 @@ def test_det_transcendentals(oracle):
     ref = np.log(xs.astype(np.float64))
     tol = 2 * np.spacing(np.abs(ref).astype(np.float32)).astype(np.float64) + 1e-9
     assert (np.abs(got - ref) <= tol).all()
+
+
+def test_cfg5_digest_file_and_thread_independence(oracle):
+    """tests/golden/cfg5_digest.json (the oracle's integer outputs at BASELINE configs[4], made offline by
+    tests/golden/make_cfg5_digest.py with all cores) is well formed, and the digest of a small scene does not depend
+    on the oracle's thread count -- which is what makes a multi-threaded offline run a valid pin."""
+    import json
+    import os
+    import sys
+
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    sys.path.insert(0, gold)
+    from make_cfg5_digest import digest
+
+    from brush_b200 import scene
+
+    with open(os.path.join(gold, "cfg5_digest.json")) as f:
+        d = json.load(f)
+    assert d["workload"] == "cfg5_6m_4k" and d["n"] == 6_000_000 and 50_000_000 < d["num_intersections"] < d["capacity"]
+    assert all(len(d[k]) == 64 for k in d if k.startswith("sha256_"))
+    sc = scene.make_scene(20_000, 320, 200, 1, 77, sigma_px=(1.0, 8.0))
+    vm, focal, center = reference_camera(sc.width, sc.height)
+    u = oracle.make_uniforms(vm, focal, (sc.width, sc.height), center)
+    got = []
+    for threads in (1, 4):
+        oracle.set_threads(threads)
+        _, aux = oracle.render_forward(u, sc.means, sc.log_scales, sc.quats, sc.sh_coeffs, sc.raw_opacity)
+        got.append(digest(aux.num_visible, aux.num_intersections, aux.global_from_compact_gid, aux.cum_tiles_hit,
+                          aux.tile_bins, aux.compact_gid_from_isect))
+    oracle.set_threads(1)
+    assert got[0] == got[1] and got[0]["num_intersections"] > 20_000
