@@ -108,7 +108,7 @@ _SIGS = {
     "brush_ctx_set_split_colors": (C.c_int, [C.c_void_p, C.c_int]),
     "brush_stage_times_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.c_int, C.c_void_p]),
     "brush_ctx_check": (C.c_int, [C.c_void_p, C.c_void_p]),
-    "brush_measure_peaks": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_void_p]),
+    "brush_measure_peaks": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.c_void_p]),
     "brush_ctx_set_pair_counting": (C.c_int, [C.c_void_p, C.c_int]),
     "brush_ctx_read_pair_counts": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64), C.c_void_p]),
     "brush_render_forward": (C.c_int, [C.c_void_p, C.POINTER(BrushUniforms), C.c_uint32, C.c_uint32] +
@@ -184,6 +184,8 @@ class Context:
         if rc != 0:
             raise BrushError(rc, "brush_ctx_create failed (is a CUDA device present?)")
         self.device = device
+        if os.environ.get("BRUSH_SPLIT_COLORS") == "1":  # A/B: every forward takes the deferred-colour route
+            self.set_split_colors(True)
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:
@@ -224,10 +226,12 @@ class Context:
         return dict(zip(STAGE_NAMES, list(arr)))
 
     def measure_peaks(self, stream=0):
-        """(FP32 TFLOP/s, 1e12 ex2/s) of this device, measured by micro-kernels; synchronises."""
-        f, m = C.c_float(), C.c_float()
-        self.check(lib().brush_measure_peaks(self._h, C.byref(f), C.byref(m), C.c_void_p(stream)))
-        return float(f.value), float(m.value)
+        """Measured by micro-kernels on this device (synchronises): FP32 TFLOP/s of scalar FFMA with constant-bank
+        operands, of scalar FFMA with three register operands and of packed FFMA2, and 1e12 MUFU.EX2 per second."""
+        out = (C.c_float * 4)()
+        self.check(lib().brush_measure_peaks(self._h, out, C.c_void_p(stream)))
+        return {"fp32_ffma_const_tflops": float(out[0]), "fp32_ffma_3reg_tflops": float(out[1]),
+                "fp32_ffma2_packed_tflops": float(out[2]), "mufu_ex2_tops": float(out[3])}
 
     def set_pair_counting(self, enabled: bool):
         self.check(lib().brush_ctx_set_pair_counting(self._h, int(enabled)))

@@ -222,10 +222,10 @@ int brush_ctx_read_pair_counts(brush_ctx* ctx, uint64_t* out_host, void* stream)
     CU(cudaMemset((char*)ctx->sticky.p + 128, 0, 16));
     return BRUSH_OK;
 }
-int brush_measure_peaks(brush_ctx* ctx, float* fp32_tflops_host, float* mufu_tops_host, void* stream) {
-    if (!ctx) return BRUSH_E_INVALID;
+int brush_measure_peaks(brush_ctx* ctx, float* out4_host, void* stream) {
+    if (!ctx || !out4_host) return BRUSH_E_INVALID;
     CU(cudaSetDevice(ctx->device));
-    int r = measure_peaks(fp32_tflops_host, mufu_tops_host, (float*)((char*)ctx->sticky.p + 192), (cudaStream_t)stream);
+    int r = measure_peaks(out4_host, (float*)((char*)ctx->sticky.p + 192), (cudaStream_t)stream);
     if (r != 0) return cuda_fail(ctx, (cudaError_t)r, "measure_peaks");
     return BRUSH_OK;
 }

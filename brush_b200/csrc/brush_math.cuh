@@ -268,6 +268,38 @@ BD bool can_be_visible(const VisTest& v, uint32_t tx, uint32_t ty) {
     return ellipse_intersects_aabb(tc, ext, v.xy, v.conic_scaled);
 }
 
+// The same predicate, decided cheaply wherever that is safe.  can_be_visible asks whether the ellipse
+// {p : (p-c)^T C (p-c) <= 1} meets the tile (helpers.wgsl:238-262: centre inside the box, nearest corner inside the
+// ellipse, or the boundary crossing one of the two edges next to that corner -- two IEEE sqrt and four IEEE divisions
+// per candidate).  Away from its decision boundary that equals "min of the quadratic form over the box < 1", and the
+// minimum of a convex form whose centre lies outside the box is on one of the two edges facing the centre, where it is
+// a clamped 1-D parabola: ~45 instructions, no division.  Whenever that minimum is within a margin of 1 (two orders
+// above the rounding error of either evaluation), or the reference's sign() logic degenerates (centre within 1e-3 px of
+// a tile centre line), or the conic is not positive definite, the reference's exact sequence decides -- so the result
+// is the reference's bit for bit, and only one candidate in ~1e5 pays for it.
+BD bool can_be_visible_fast(const VisTest& v, uint32_t tx, uint32_t ty) {
+    if (!v.any) return false;
+    const float a = v.conic_scaled.c[0].x, b = v.conic_scaled.c[0].y, c = v.conic_scaled.c[1].y;
+    const float bx = (float)(tx * TILE_WIDTH) + 8.0f, by = (float)(ty * TILE_WIDTH) + 8.0f;
+    const float dx = v.xy.x - bx, dy = v.xy.y - by;  // the reference's d (exactly)
+    const float adx = fabsf(dx), ady = fabsf(dy);
+    if (adx <= 8.0f && ady <= 8.0f) return true;     // the reference's first test, same operations
+    bool exact = !(adx > 1e-3f) || !(ady > 1e-3f) || !(a > 0.0f) || !(c > 0.0f) || !(__fmaf_rn(a, c, -b * b) > 0.0f);
+    // the box in ellipse-centred coordinates, and its two edges that face the centre
+    const float x0 = -dx - 8.0f, x1 = -dx + 8.0f, y0 = -dy - 8.0f, y1 = -dy + 8.0f;
+    const float xe = dx > 0.0f ? x1 : x0, ye = dy > 0.0f ? y1 : y0;
+    const float ys = fminf(fmaxf(__fdividef(-b * xe, c), y0), y1);  // minimiser on the edge px = xe
+    const float xs = fminf(fmaxf(__fdividef(-b * ye, a), x0), x1);  // minimiser on the edge py = ye
+    const float q1 = __fmaf_rn(__fmaf_rn(2.0f * b, xe, c * ys), ys, a * xe * xe);
+    const float q2 = __fmaf_rn(__fmaf_rn(2.0f * b, ye, a * xs), xs, c * ye * ye);
+    const float qmin = fminf(q1, q2);
+    const float X = fmaxf(fabsf(x0), fabsf(x1)), Y = fmaxf(fabsf(y0), fabsf(y1));
+    const float mag = __fmaf_rn(a * X, X, __fmaf_rn(c * Y, Y, 2.0f * fabsf(b) * X * Y));
+    exact = exact || !(fabsf(qmin - 1.0f) > __fmaf_rn(8e-6f, mag, 8e-6f));  // also catches NaN / inf
+    if (exact) return can_be_visible(v, tx, ty);
+    return qmin < 1.0f;
+}
+
 BD float sigmoid_det(float x) { return div_rn(1.0f, 1.0f + det_expf(-x)); }  // project_visible.wgsl:149-151
 BD V3 normalize3(V3 v) {
     float l = sqrt_rn(dot3(v, v));

@@ -83,7 +83,7 @@ void launch_rasterize_backward(const Cam& cam, const uint32_t* compact_gid_from_
                                unsigned long long* pair_counter /* diagnostic, normally null */, cudaStream_t st);
 
 // ---- peaks.cu: FP32 / MUFU micro-kernels, the measured roofline denominators of the rasterizers ----
-int measure_peaks(float* fp32_tflops, float* mufu_tops, float* sink, cudaStream_t st);
+int measure_peaks(float* out4, float* sink, cudaStream_t st);
 
 // ---- backward.cu ----
 void launch_gather_project_backward(const Cam& cam, uint32_t N, uint32_t K, const float* means,

@@ -30,6 +30,61 @@ ffma_peak_kernel(float a, float b, int iters, float* __restrict__ sink) {
     if (s == 12345.678f) sink[0] = s;  // keeps the chains alive; never true
 }
 
+// Three REGISTER operands per FFMA (the form real kernels issue: ffma_peak_kernel's multiplier and addend sit in the
+// constant bank), 16 chains per thread.
+__global__ void __launch_bounds__(PEAK_THREADS)
+ffma3_peak_kernel(float a, float b, int iters, float* __restrict__ sink) {
+    float x[PEAK_CHAINS], y[4], z[4];
+#pragma unroll
+    for (int i = 0; i < PEAK_CHAINS; i++) x[i] = (float)(threadIdx.x + i) * 1e-3f;
+#pragma unroll
+    for (int i = 0; i < 4; i++) { y[i] = a - 1e-4f * (float)(threadIdx.x & (i + 1)); z[i] = b + 1e-5f * (float)(threadIdx.x & (i + 3)); }
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+#pragma unroll
+            for (int i = 0; i < PEAK_CHAINS; i++) x[i] = fmaf(x[i], y[(i + u) & 3], z[i & 3]);
+        }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < PEAK_CHAINS; i++) s += x[i];
+    if (s == 12345.678f) sink[0] = s;
+}
+
+// Packed FP32 (fma.rn.f32x2 -> FFMA2, new on sm_100): two FMAs per issued instruction, 8 packed chains per thread.
+__global__ void __launch_bounds__(PEAK_THREADS)
+ffma2_peak_kernel(float a, float b, int iters, float* __restrict__ sink) {
+    unsigned long long x[PEAK_CHAINS / 2], y[2], z[2];
+#pragma unroll
+    for (int i = 0; i < PEAK_CHAINS / 2; i++) {
+        const float lo = (float)(threadIdx.x + i) * 1e-3f, hi = (float)(threadIdx.x + i) * 2e-3f;
+        asm("mov.b64 %0, {%1, %2};" : "=l"(x[i]) : "f"(lo), "f"(hi));
+    }
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+        const float ya = a - 1e-4f * (float)(threadIdx.x & (i + 1)), zb = b + 1e-5f * (float)(threadIdx.x & (i + 3));
+        asm("mov.b64 %0, {%1, %2};" : "=l"(y[i]) : "f"(ya), "f"(ya * 0.999f));
+        asm("mov.b64 %0, {%1, %2};" : "=l"(z[i]) : "f"(zb), "f"(zb * 1.001f));
+    }
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+#pragma unroll
+            for (int i = 0; i < PEAK_CHAINS / 2; i++)
+                asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(x[i]) : "l"(y[(i + u) & 1]), "l"(z[i & 1]));
+        }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < PEAK_CHAINS / 2; i++) {
+        float lo, hi;
+        asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(x[i]));
+        s += lo + hi;
+    }
+    if (s == 12345.678f) sink[0] = s;
+}
+
 __global__ void __launch_bounds__(PEAK_THREADS)
 mufu_peak_kernel(int iters, float* __restrict__ sink) {
     float x[8];
@@ -49,8 +104,10 @@ mufu_peak_kernel(int iters, float* __restrict__ sink) {
     if (s == 12345.678f) sink[0] = s;
 }
 
-// Best of `reps` timed launches each; synchronises `st`.  Returns 0 or a cudaError_t.
-int measure_peaks(float* fp32_tflops, float* mufu_tops, float* sink, cudaStream_t st) {
+// Best of `reps` timed launches each; synchronises `st`.  out[0] = scalar FFMA with constant-bank operands,
+// out[1] = scalar FFMA with three register operands, out[2] = packed FFMA2, all in FP32 TFLOP/s (FMA = 2 flop);
+// out[3] = 1e12 MUFU.EX2 per second.  Returns 0 or a cudaError_t.
+int measure_peaks(float* out4, float* sink, cudaStream_t st) {
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -61,32 +118,31 @@ int measure_peaks(float* fp32_tflops, float* mufu_tops, float* sink, cudaStream_
     err = cudaEventCreate(&e1);
     if (err != cudaSuccess) return (int)err;
     const int ffma_iters = 4096, mufu_iters = 1024, reps = 4;
-    float best_f = 1e30f, best_m = 1e30f;
+    float best[4] = {1e30f, 1e30f, 1e30f, 1e30f};
     for (int r = 0; r < reps + 1; r++) {  // first launch of each is the warm-up
-        g_launch_count += 2;
-        cudaEventRecord(e0, st);
-        ffma_peak_kernel<<<blocks, PEAK_THREADS, 0, st>>>(0.999f, 1e-3f, ffma_iters, sink);
-        cudaEventRecord(e1, st);
-        cudaEventSynchronize(e1);
-        float ms = 0.f;
-        cudaEventElapsedTime(&ms, e0, e1);
-        if (r > 0 && ms < best_f) best_f = ms;
-        cudaEventRecord(e0, st);
-        mufu_peak_kernel<<<blocks, PEAK_THREADS, 0, st>>>(mufu_iters, sink);
-        cudaEventRecord(e1, st);
-        cudaEventSynchronize(e1);
-        cudaEventElapsedTime(&ms, e0, e1);
-        if (r > 0 && ms < best_m) best_m = ms;
+        for (int k = 0; k < 4; k++) {
+            g_launch_count++;
+            cudaEventRecord(e0, st);
+            if (k == 0) ffma_peak_kernel<<<blocks, PEAK_THREADS, 0, st>>>(0.999f, 1e-3f, ffma_iters, sink);
+            else if (k == 1) ffma3_peak_kernel<<<blocks, PEAK_THREADS, 0, st>>>(0.999f, 1e-3f, ffma_iters, sink);
+            else if (k == 2) ffma2_peak_kernel<<<blocks, PEAK_THREADS, 0, st>>>(0.999f, 1e-3f, ffma_iters, sink);
+            else mufu_peak_kernel<<<blocks, PEAK_THREADS, 0, st>>>(mufu_iters, sink);
+            cudaEventRecord(e1, st);
+            cudaEventSynchronize(e1);
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, e0, e1);
+            if (r > 0 && ms < best[k]) best[k] = ms;
+        }
     }
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     err = cudaGetLastError();
     if (err != cudaSuccess) return (int)err;
     const double threads = (double)blocks * PEAK_THREADS;
-    const double flop = threads * (double)ffma_iters * 4.0 * PEAK_CHAINS * 2.0;
+    const double flop = threads * (double)ffma_iters * 4.0 * PEAK_CHAINS * 2.0;  // the same for all three FFMA kernels
     const double ex2 = threads * (double)mufu_iters * 4.0 * 8.0;
-    if (fp32_tflops) *fp32_tflops = (float)(flop / (best_f * 1e-3) / 1e12);
-    if (mufu_tops) *mufu_tops = (float)(ex2 / (best_m * 1e-3) / 1e12);
+    for (int k = 0; k < 3; k++) out4[k] = (float)(flop / (best[k] * 1e-3) / 1e12);
+    out4[3] = (float)(ex2 / (best[3] * 1e-3) / 1e12);
     return 0;
 }
 

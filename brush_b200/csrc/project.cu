@@ -189,7 +189,7 @@ BD TileHits warp_tile_hits(const VisTest& vt, const TileBox& b, bool valid, uint
             // j / o_w for small integers: (j + 0.5) / w is never within rounding distance of an integer
             const uint32_t row = (uint32_t)__float2uint_rz(__fdividef((float)j + 0.5f, (float)o_w));
             const uint32_t col = j - row * o_w;
-            pass = can_be_visible(ot, (o_origin & 0xffffu) + col, (o_origin >> 16) + row);
+            pass = can_be_visible_fast(ot, (o_origin & 0xffffu) + col, (o_origin >> 16) + row);
         }
         const uint32_t ballot = __ballot_sync(FULL, pass);
         if (n) {  // this lane's own candidates inside the pass

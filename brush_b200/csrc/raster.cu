@@ -4,27 +4,45 @@
 //   rasterize_backward == crates/brush-render/src/shaders/rasterize_backwards.wgsl:140-304
 // FP32/MUFU-bound stages: compiled with FMA contraction on and ex2.approx for exp(-sigma); parity is
 // the 1e-5 absolute image tolerance / 1e-3 relative gradient tolerance, not bit equality.
+#include <type_traits>
+
 #include "internal.h"
 
 namespace brush {
 
 // ---------------------------------------------------------------------------------------------
+// Four consecutive intersections per thread (one 16-byte load + the element before them): the first version walked one
+// element per thread per grid-stride iteration, each a dependent pair of loads behind the *n_dev load (13 us for 12 MB).
 __global__ void __launch_bounds__(256)
 tile_bins_kernel(const uint32_t* __restrict__ tile_ids, const uint64_t* __restrict__ keys64,
                  const int32_t* __restrict__ n_dev, uint64_t capacity, uint32_t* __restrict__ tile_bins) {
     PDL_ENTER();
     const uint32_t n = (uint32_t)min((uint64_t)max(*n_dev, 0), capacity);
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const uint32_t cur = keys64 ? (uint32_t)(keys64[i] >> 32) : tile_ids[i];
-        if (i == n - 1) tile_bins[cur * 2 + 1] = n;
-        if (i == 0) {
-            tile_bins[cur * 2] = 0u;
+    auto tile_of = [&](uint32_t i) { return keys64 ? (uint32_t)(keys64[i] >> 32) : tile_ids[i]; };
+    const bool vec = !keys64 && (reinterpret_cast<uintptr_t>(tile_ids) & 15u) == 0;
+    for (uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4u; i0 < n; i0 += gridDim.x * blockDim.x * 4u) {
+        uint32_t t[4];
+        if (vec && i0 + 4u <= n) {
+            const uint4 q = __ldg(reinterpret_cast<const uint4*>(tile_ids + i0));
+            t[0] = q.x; t[1] = q.y; t[2] = q.z; t[3] = q.w;
         } else {
-            const uint32_t prev = keys64 ? (uint32_t)(keys64[i - 1] >> 32) : tile_ids[i - 1];
-            if (prev != cur) {
+#pragma unroll
+            for (uint32_t j = 0; j < 4u; j++) t[j] = i0 + j < n ? tile_of(i0 + j) : 0u;
+        }
+        uint32_t prev = i0 > 0 ? tile_of(i0 - 1u) : 0u;
+#pragma unroll
+        for (uint32_t j = 0; j < 4u; j++) {
+            const uint32_t i = i0 + j;
+            if (i >= n) break;
+            const uint32_t cur = t[j];
+            if (i == n - 1) tile_bins[cur * 2 + 1] = n;
+            if (i == 0) {
+                tile_bins[cur * 2] = 0u;
+            } else if (prev != cur) {
                 tile_bins[prev * 2 + 1] = i;
                 tile_bins[cur * 2] = i;
             }
+            prev = cur;
         }
     }
 }
@@ -34,8 +52,8 @@ void launch_tile_bins(const uint32_t* sorted_tile_ids, const uint64_t* sorted_ke
     // tile_bins was zero-filled by the forward's single init launch (int_zeros, render.rs:241-244)
     (void)num_tiles;
     if (capacity == 0) return;
-    uint64_t blocks = (capacity + 255) / 256;
-    if (blocks > 148 * 16) blocks = 148 * 16;
+    uint64_t blocks = (capacity + 1023) / 1024;
+    if (blocks > 148 * 8) blocks = 148 * 8;
     g_launch_count++;
     launch_k(tile_bins_kernel, (uint32_t)blocks, 256, 0, st, sorted_tile_ids, sorted_keys64, n_isect_dev, capacity,
              tile_bins);
@@ -180,7 +198,12 @@ __device__ __forceinline__ bool ellipse_reaches_block(const CullForm& f, float r
 // per splat by the staging thread, and every warp's list pass is then a bit test.
 // `tag` travels in G1.w: the backward uses it as the row of its gradient accumulator.
 // (tile_px, tile_py) = pixel coordinates of the tile's first pixel.
-__device__ __forceinline__ void stage_splat(uint32_t sbase, uint32_t slot, const float* __restrict__ projected,
+// Returns whether the splat is "plain": opacity <= PLAIN_MAX_OPAC (so neither compositor's alpha clamp, 0.999 forward /
+// 0.99 backward, can bind: alpha <= opacity) and a conic that is positive definite with a margin (so sigma >= 0 for
+// every pixel, in exact arithmetic and under rounding).  A batch of plain splats is composited by the loop variant
+// without the `sigma < 0` test and the clamp: two instructions per pair fewer, the same bits.
+constexpr float PLAIN_MAX_OPAC = 0.989f;
+__device__ __forceinline__ bool stage_splat(uint32_t sbase, uint32_t slot, const float* __restrict__ projected,
                                             uint32_t cg, uint32_t tag, float tile_px, float tile_py) {
     const float* p = projected + (size_t)cg * 9;
     const float x = __ldg(p), y = __ldg(p + 1), cxx = __ldg(p + 2), cxy = __ldg(p + 3), cyy = __ldg(p + 4);
@@ -211,6 +234,8 @@ __device__ __forceinline__ void stage_splat(uint32_t sbase, uint32_t slot, const
         mask |= (hit ? 1u : 0u) << b;
     }
     sts128(sbase + SM_COL + slot * 16, make_float4(__ldg(p + 5), __ldg(p + 6), __ldg(p + 7), __uint_as_float(mask)));
+    // |cxy| <= 0.99 sqrt(cxx cyy): sigma >= 0.01 * (cxx dx^2 + cyy dy^2) / 2, five orders above its rounding error
+    return opac <= PLAIN_MAX_OPAC && cxx > 0.0f && cyy > 0.0f && cxy * cxy <= 0.98f * (cxx * cyy);
 }
 
 // List pass of one warp over the staged batch: one lane per splat tests its block's bit; the shared-window
@@ -239,6 +264,64 @@ __device__ __forceinline__ uint32_t cull_to_list(uint32_t sbase, uint32_t list_a
     }
     __syncwarp();
     return n_list;
+}
+
+// The forward compositing loop of one warp over its survivor list of one batch (see the kernel comment).
+// GENERAL = false: every splat of the batch is "plain" (stage_splat), so sigma >= 0 and alpha <= 0.989 hold for every
+// pair and the `sp <= 0` compare and the 0.999 clamp are dropped -- same values, two instructions per pair fewer.
+template <bool GENERAL, bool COUNT>
+__device__ __forceinline__ uint32_t composite_forward(uint32_t list_addr, uint32_t n_list, float pcx, float pcy, float& T,
+                                                      float& pr, float& pg, float& pb, uint32_t& groups_walked) {
+    uint32_t final_a = NO_CONTRIBUTOR;
+    for (uint32_t i = 0; i < n_list; i += LIST_PAD) {
+        if (COUNT) groups_walked++;
+        const uint4 a4 = lds128u(list_addr + 4u * i);
+        const uint32_t aa[4] = {a4.x, a4.y, a4.z, a4.w};
+        const bool live0 = T > 0.0f;
+        // a finished pixel sees nothing: its visibility threshold is +inf (one select per group instead of a
+        // third compare per pair)
+        const float q_min = live0 ? LOG2_INV255 : __int_as_float(0x7f800000);
+        bool act[4];
+        float alpha[4], Tj[5];
+        Tj[0] = T;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const float4 g0 = lds128(aa[j] + SM_G0);
+            const float4 g1 = lds128(aa[j] + SM_G1);
+            const float dx = g0.x - pcx, dy = g0.y - pcy;
+            const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);  // -sigma * log2(e)
+            const float q = sp + g1.y;                                              // log2(opac * exp(-sigma))
+            act[j] = GENERAL ? (sp <= 0.0f && q >= q_min) : (q >= q_min);
+            alpha[j] = act[j] ? (GENERAL ? fminf(0.999f, ex2_approx(q)) : ex2_approx(q)) : 0.0f;
+            Tj[j + 1] = Tj[j] * (1.0f - alpha[j]);
+        }
+        if (!__any_sync(0xffffffffu, live0 && Tj[4] <= 1e-4f)) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const float4 c = lds128(aa[j] + SM_COL);
+                const float fac = alpha[j] * Tj[j];
+                pr = fmaf(c.x, fac, pr); pg = fmaf(c.y, fac, pg); pb = fmaf(c.z, fac, pb);
+                final_a = act[j] ? aa[j] : final_a;
+            }
+            T = Tj[4];
+            continue;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; j++) {  // some pixel finishes in this group (at most 32 times per warp and tile)
+            const bool live = act[j] && T > 0.0f;
+            const float4 c = lds128(aa[j] + SM_COL);
+            const float next_T = T * (1.0f - alpha[j]);
+            const bool stop = live && next_T <= 1e-4f;
+            const bool contrib = live && !(next_T <= 1e-4f);
+            const float fac = contrib ? alpha[j] * T : 0.0f;
+            pr = fmaf(c.x, fac, pr); pg = fmaf(c.y, fac, pg); pb = fmaf(c.z, fac, pb);
+            T = contrib ? next_T : T;
+            T = stop ? -T : T;
+            final_a = contrib ? aa[j] : final_a;
+        }
+        if (__all_sync(0xffffffffu, T <= 0.0f)) break;
+    }
+    return final_a;
 }
 
 // COUNT: the diagnostic build of the kernel that also counts the (pixel, splat) pairs it evaluates (32 lanes x the
@@ -278,11 +361,12 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
         if (__syncthreads_and(T <= 0.0f)) break;
         const uint32_t batch_start = range.x + b * TILE_SIZE;
         const uint32_t remaining = min(TILE_SIZE, range.y - batch_start);
+        bool odd = false;
         if (tid < remaining) {
             const uint32_t cg = __ldg(compact_gid_from_isect + batch_start + tid);
-            stage_splat(sbase, tid, projected, cg, cg, (float)(blockIdx.x * TILE_WIDTH), (float)(blockIdx.y * TILE_WIDTH));
+            odd = !stage_splat(sbase, tid, projected, cg, cg, (float)(blockIdx.x * TILE_WIDTH), (float)(blockIdx.y * TILE_WIDTH));
         }
-        __syncthreads();
+        const int any_odd = __syncthreads_or(odd);
         if (__all_sync(0xffffffffu, T <= 0.0f)) continue;
         const uint32_t n_list = cull_to_list<false>(sbase, list_addr, lane, warp, 0u, remaining);
         // Four survivors per iteration, composited OPTIMISTICALLY: a pixel stops at most once, so the group is
@@ -293,55 +377,8 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
         // has no per-splat compare / select on the compositing state: the ALU pipe (compares, selects, min)
         // was this kernel's limiter (ncu: 61% ALU at 78% issue).  Same arithmetic in both paths, so the result
         // does not depend on which one ran.
-        uint32_t final_a = NO_CONTRIBUTOR;
-        for (uint32_t i = 0; i < n_list; i += LIST_PAD) {
-            if (COUNT) groups_walked++;
-            const uint4 a4 = lds128u(list_addr + 4u * i);
-            const uint32_t aa[4] = {a4.x, a4.y, a4.z, a4.w};
-            const bool live0 = T > 0.0f;
-            // a finished pixel sees nothing: its visibility threshold is +inf (one select per group instead of a
-            // third compare per pair)
-            const float q_min = live0 ? LOG2_INV255 : __int_as_float(0x7f800000);
-            bool act[4];
-            float alpha[4], Tj[5];
-            Tj[0] = T;
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const float4 g0 = lds128(aa[j] + SM_G0);
-                const float4 g1 = lds128(aa[j] + SM_G1);
-                const float dx = g0.x - pcx, dy = g0.y - pcy;
-                const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);  // -sigma * log2(e)
-                const float q = sp + g1.y;                                              // log2(opac * exp(-sigma))
-                act[j] = sp <= 0.0f && q >= q_min;
-                alpha[j] = act[j] ? fminf(0.999f, ex2_approx(q)) : 0.0f;
-                Tj[j + 1] = Tj[j] * (1.0f - alpha[j]);
-            }
-            if (!__any_sync(0xffffffffu, live0 && Tj[4] <= 1e-4f)) {
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const float4 c = lds128(aa[j] + SM_COL);
-                    const float fac = alpha[j] * Tj[j];
-                    pr = fmaf(c.x, fac, pr); pg = fmaf(c.y, fac, pg); pb = fmaf(c.z, fac, pb);
-                    final_a = act[j] ? aa[j] : final_a;
-                }
-                T = Tj[4];
-                continue;
-            }
-#pragma unroll
-            for (int j = 0; j < 4; j++) {  // some pixel finishes in this group (at most 32 times per warp and tile)
-                const bool live = act[j] && T > 0.0f;
-                const float4 c = lds128(aa[j] + SM_COL);
-                const float next_T = T * (1.0f - alpha[j]);
-                const bool stop = live && next_T <= 1e-4f;
-                const bool contrib = live && !(next_T <= 1e-4f);
-                const float fac = contrib ? alpha[j] * T : 0.0f;
-                pr = fmaf(c.x, fac, pr); pg = fmaf(c.y, fac, pg); pb = fmaf(c.z, fac, pb);
-                T = contrib ? next_T : T;
-                T = stop ? -T : T;
-                final_a = contrib ? aa[j] : final_a;
-            }
-            if (__all_sync(0xffffffffu, T <= 0.0f)) break;
-        }
+        const uint32_t final_a = any_odd ? composite_forward<true, COUNT>(list_addr, n_list, pcx, pcy, T, pr, pg, pb, groups_walked)
+                                         : composite_forward<false, COUNT>(list_addr, n_list, pcx, pcy, T, pr, pg, pb, groups_walked);
         if (final_a != NO_CONTRIBUTOR) final_idx = batch_start + ((final_a - sbase) >> 4);
     }
     if (COUNT && lane == 0 && groups_walked) atomicAdd(pair_counter, (unsigned long long)groups_walked * (LIST_PAD * 32u));
@@ -542,12 +579,13 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
         const uint32_t batch_end = range.y - b * TILE_SIZE;  // slot t of this batch <-> isect batch_end-1-t
         const uint32_t remaining = min(TILE_SIZE, batch_end - range.x);
         const uint32_t t_lo_tile = batch_end - 1u > tile_final ? batch_end - 1u - tile_final : 0u;
+        bool odd = false;
         if (tid >= t_lo_tile && tid < remaining) {  // gradient rows are indexed by GLOBAL splat id, so the per-splat backward is coalesced
             const uint32_t cg = __ldg(compact_gid_from_isect + batch_end - 1u - tid);
-            stage_splat(sbase, tid, projected, cg, __ldg(global_from_compact + cg), (float)(tile_x * TILE_WIDTH),
-                        (float)(tile_y * TILE_WIDTH));
+            odd = !stage_splat(sbase, tid, projected, cg, __ldg(global_from_compact + cg), (float)(tile_x * TILE_WIDTH),
+                               (float)(tile_y * TILE_WIDTH));
         }
-        __syncthreads();
+        const int any_odd = __syncthreads_or(odd);
         if (!warp_any_inside || batch_end - remaining > warp_final) continue;
         // isect <= final  <=>  slot >= batch_end-1-final; compared as shared-window addresses of the G0 entries
         const uint32_t t_lo_warp = batch_end - 1u > warp_final ? batch_end - 1u - warp_final : 0u;
@@ -557,43 +595,51 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
         if (pair_counter && lane == 0 && n_list)  // diagnostic (brush_ctx_set_pair_counting), per batch, not per pair
             atomicAdd(pair_counter, (unsigned long long)((n_list + BW_GROUP - 1u) / BW_GROUP) * (BW_GROUP * 32u));
         const uint32_t token = n_list ^ b;  // exists only after cull_to_list's __syncwarp (see lds128_ro)
-        uint32_t an[BW_GROUP];  // the next group's list entries, loaded one group ahead (the list is padded)
-        list_load4(list_addr, sbase, an, token);
-        for (uint32_t g = 0; g < n_list; g += BW_ROWS) {
-#pragma unroll
-            for (uint32_t u = 0; u < BW_ROWS / BW_GROUP; u++) {
-                if (g + BW_GROUP * u >= n_list) break;
-                const uint32_t aa[BW_GROUP] = {an[0], an[1], an[2], an[3]};
-                list_load4(list_addr + 2u * (g + BW_GROUP * (u + 1u)), sbase, an, token);
-                float alpha[BW_GROUP], ra[BW_GROUP], visra[BW_GROUP];
-#pragma unroll
-                for (int j = 0; j < (int)BW_GROUP; j++) {
-                    const float4 g0 = lds128_ro(aa[j] + SM_G0, token);
-                    const float4 g1 = lds128_ro(aa[j] + SM_G1, token);
-                    const float dx = g0.x - pcx, dy = g0.y - pcy;
-                    const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);
-                    const float q = sp + g1.y;
-                    // the same predicate, on the same instruction sequence, as the forward
-                    const bool act = aa[j] >= a_lo && sp <= 0.0f && q >= LOG2_INV255;
-                    const float vis = act ? ex2_approx(sp) : 0.0f;  // inactive: alpha = 0, ra = 1, a row of zeros
-                    alpha[j] = fminf(0.99f, g1.z * vis);            // 0.99 here, 0.999 forward (reference quirk)
-                    ra[j] = rcp_approx(1.0f - alpha[j]);
-                    visra[j] = vis * ra[j];
+        // GENERAL = false: every splat of the batch is "plain" (stage_splat): sigma >= 0 and alpha <= 0.989 for every
+        // pair, so the `sp <= 0` compare and the clamp are dropped -- same values, two instructions per pair fewer.
+        auto walk_list = [&](auto general_tag) {
+            constexpr bool GENERAL = decltype(general_tag)::value;
+            uint32_t an[BW_GROUP];  // the next group's list entries, loaded one group ahead (the list is padded)
+            list_load4(list_addr, sbase, an, token);
+            for (uint32_t g = 0; g < n_list; g += BW_ROWS) {
+    #pragma unroll
+                for (uint32_t u = 0; u < BW_ROWS / BW_GROUP; u++) {
+                    if (g + BW_GROUP * u >= n_list) break;
+                    const uint32_t aa[BW_GROUP] = {an[0], an[1], an[2], an[3]};
+                    list_load4(list_addr + 2u * (g + BW_GROUP * (u + 1u)), sbase, an, token);
+                    float alpha[BW_GROUP], ra[BW_GROUP], visra[BW_GROUP];
+    #pragma unroll
+                    for (int j = 0; j < (int)BW_GROUP; j++) {
+                        const float4 g0 = lds128_ro(aa[j] + SM_G0, token);
+                        const float4 g1 = lds128_ro(aa[j] + SM_G1, token);
+                        const float dx = g0.x - pcx, dy = g0.y - pcy;
+                        const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);
+                        const float q = sp + g1.y;
+                        // the same predicate, on the same instruction sequence, as the forward
+                        const bool act = GENERAL ? (aa[j] >= a_lo && sp <= 0.0f && q >= LOG2_INV255)
+                                                 : (aa[j] >= a_lo && q >= LOG2_INV255);
+                        const float vis = act ? ex2_approx(sp) : 0.0f;  // inactive: alpha = 0, ra = 1, a row of zeros
+                        alpha[j] = GENERAL ? fminf(0.99f, g1.z * vis) : g1.z * vis;  // clamp 0.99 here, 0.999 forward (reference quirk)
+                        ra[j] = rcp_approx(1.0f - alpha[j]);
+                        visra[j] = vis * ra[j];
+                    }
+    #pragma unroll
+                    for (int j = 0; j < (int)BW_GROUP; j++) {
+                        const float4 c = lds128_ro(aa[j] + SM_COL, token);
+                        const float uu = fmaf(c.z, v_out.z, fmaf(c.y, v_out.y, c.x * v_out.x));
+                        const float va = visra[j] * fmaf(uu, T, D);
+                        T *= ra[j];
+                        const float fac = alpha[j] * T;
+                        D = fmaf(-fac, uu, D);
+                        sts64(pair_addr + (BW_GROUP * u + (uint32_t)j) * BW_ROW + lane * 8u, va, fac);
+                    }
                 }
-#pragma unroll
-                for (int j = 0; j < (int)BW_GROUP; j++) {
-                    const float4 c = lds128_ro(aa[j] + SM_COL, token);
-                    const float uu = fmaf(c.z, v_out.z, fmaf(c.y, v_out.y, c.x * v_out.x));
-                    const float va = visra[j] * fmaf(uu, T, D);
-                    T *= ra[j];
-                    const float fac = alpha[j] * T;
-                    D = fmaf(-fac, uu, D);
-                    sts64(pair_addr + (BW_GROUP * u + (uint32_t)j) * BW_ROW + lane * 8u, va, fac);
-                }
+                flush_rows(sbase + TILE_SIZE * 16u, pair_addr, pix_addr, list_addr + 2u * g, lane, min(BW_ROWS, n_list - g),
+                           rx0, ry0, v_projected);
             }
-            flush_rows(sbase + TILE_SIZE * 16u, pair_addr, pix_addr, list_addr + 2u * g, lane, min(BW_ROWS, n_list - g),
-                       rx0, ry0, v_projected);
-        }
+        };
+        if (any_odd) walk_list(std::true_type{});
+        else walk_list(std::false_type{});
     }
 }
 

@@ -7,8 +7,13 @@
 namespace brush {
 
 constexpr int SC_THREADS = 256;
-constexpr int SC_ITEMS = 4;
+constexpr int SC_VEC = 4;                  // uint4 loads
+constexpr int SC_CHUNKS = 4;               // uint4s per thread: 16 elements, 4096 per tile
+constexpr int SC_ITEMS = SC_VEC * SC_CHUNKS;
 constexpr int SC_TILE = SC_THREADS * SC_ITEMS;
+// Tile size matters more than it looks: at 1 M elements every tile of a 1024-element tiling is resident at once, no
+// predecessor is "inclusive" yet, and the last tile's look-back is 977 / 32 serial rounds of L2 round trips (15 us
+// for 8 MB of traffic).  4096-element tiles: 245 tiles, 8 rounds.
 
 size_t scan_status_words(uint32_t n) { return (size_t)(n + SC_TILE - 1) / SC_TILE + 1; }
 
@@ -22,24 +27,39 @@ inclusive_scan_kernel(const uint32_t* __restrict__ in, uint32_t n, uint32_t* __r
     if (tid == 0) s_tile = atomicAdd(ticket, 1u);
     __syncthreads();
     const uint32_t tile = s_tile;
-    const uint32_t base = tile * SC_TILE + tid * SC_ITEMS;
-    uint32_t v[SC_ITEMS];
+    // warp-striped: chunk j of lane l of warp w = uint4 number (w * SC_CHUNKS + j) * 32 + l of the tile, so every
+    // load and store instruction of a warp covers 512 contiguous bytes
+    const uint32_t tile_base = tile * SC_TILE;
+    uint32_t v[SC_CHUNKS][SC_VEC];
     const bool aligned = ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15u) == 0;
-    if (aligned && base + SC_ITEMS <= n) {
-        uint4 q = __ldg(reinterpret_cast<const uint4*>(in + base));
-        v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
-    } else {
+    const bool full = aligned && (uint64_t)tile_base + SC_TILE <= n;
 #pragma unroll
-        for (int i = 0; i < SC_ITEMS; i++) v[i] = base + i < n ? __ldg(in + base + i) : 0u;
-    }
-    v[1] += v[0]; v[2] += v[1]; v[3] += v[2];
-    uint32_t incl = v[3];
+    for (int j = 0; j < SC_CHUNKS; j++) {
+        const uint32_t e = tile_base + ((warp * SC_CHUNKS + j) * 32u + lane) * SC_VEC;
+        if (full) {
+            const uint4 q = __ldg(reinterpret_cast<const uint4*>(in + e));
+            v[j][0] = q.x; v[j][1] = q.y; v[j][2] = q.z; v[j][3] = q.w;
+        } else {
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= (uint32_t)o) incl += t;
+            for (int i = 0; i < SC_VEC; i++) v[j][i] = e + i < n ? __ldg(in + e + i) : 0u;
+        }
     }
-    if (lane == 31) s_warp[warp] = incl;
+    // per chunk: serial scan of the four elements, warp scan of the chunk totals; chunks of a warp are consecutive
+    uint32_t chunk_off[SC_CHUNKS];
+    uint32_t warp_running = 0;
+#pragma unroll
+    for (int j = 0; j < SC_CHUNKS; j++) {
+        v[j][1] += v[j][0]; v[j][2] += v[j][1]; v[j][3] += v[j][2];
+        uint32_t incl = v[j][3];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= (uint32_t)o) incl += t;
+        }
+        chunk_off[j] = warp_running + incl - v[j][3];
+        warp_running += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    if (lane == 31) s_warp[warp] = warp_running;
     __syncthreads();
     if (warp == 0) {
         uint32_t w = lane < SC_THREADS / 32 ? s_warp[lane] : 0u;
@@ -65,13 +85,18 @@ inclusive_scan_kernel(const uint32_t* __restrict__ in, uint32_t n, uint32_t* __r
         }
     }
     __syncthreads();
-    const uint32_t off = s_base + s_warp[warp] + (incl - v[3]);
-    if (aligned && base + SC_ITEMS <= n) {
-        *reinterpret_cast<uint4*>(out + base) = make_uint4(v[0] + off, v[1] + off, v[2] + off, v[3] + off);
-    } else {
+    const uint32_t base_off = s_base + s_warp[warp];
 #pragma unroll
-        for (int i = 0; i < SC_ITEMS; i++)
-            if (base + i < n) out[base + i] = v[i] + off;
+    for (int j = 0; j < SC_CHUNKS; j++) {
+        const uint32_t e = tile_base + ((warp * SC_CHUNKS + j) * 32u + lane) * SC_VEC;
+        const uint32_t off = base_off + chunk_off[j];
+        if (full) {
+            *reinterpret_cast<uint4*>(out + e) = make_uint4(v[j][0] + off, v[j][1] + off, v[j][2] + off, v[j][3] + off);
+        } else {
+#pragma unroll
+            for (int i = 0; i < SC_VEC; i++)
+                if (e + i < n) out[e + i] = v[j][i] + off;
+        }
     }
 }
 

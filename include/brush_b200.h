@@ -108,11 +108,12 @@ int brush_ctx_set_timing(brush_ctx* ctx, int enabled);
 /* Synchronises `stream`, then fills out[0..n) with the last call's stage times in ms. */
 int brush_stage_times_ms(brush_ctx* ctx, float* out_host, int n, void* stream);
 /* Diagnostics for the roofline report (no reference counterpart; SURVEY.md 6 / 8d "measured on the box").
- * brush_measure_peaks runs an FFMA and a MUFU.EX2 micro-kernel on `stream`, synchronises, and returns the device's
- * measured FP32 TFLOP/s (FMA = 2) and 1e12 ex2/s.  While pair counting is on, the two rasterizers count the (pixel,
+ * brush_measure_peaks runs four micro-kernels on `stream`, synchronises, and fills out4_host with the device's
+ * measured FP32 TFLOP/s (FMA = 2 flop) for scalar FFMA with constant-bank operands [0], scalar FFMA with three register
+ * operands [1] and packed FFMA2 (fma.rn.f32x2) [2], and 1e12 MUFU.EX2 per second [3].  While pair counting is on, the two rasterizers count the (pixel,
  * splat) pairs they evaluate after culling; brush_ctx_read_pair_counts synchronises, writes {forward, backward}
  * totals since the last read into out_host[2] and clears them.  Off by default; never on in a timed region. */
-int brush_measure_peaks(brush_ctx* ctx, float* fp32_tflops_host, float* mufu_tops_host, void* stream);
+int brush_measure_peaks(brush_ctx* ctx, float* out4_host, void* stream);
 int brush_ctx_set_pair_counting(brush_ctx* ctx, int enabled);
 int brush_ctx_read_pair_counts(brush_ctx* ctx, uint64_t* out_host, void* stream);
 /* Synchronises `stream` and returns the sticky device status: BRUSH_OK or BRUSH_E_CAPACITY; clears it. */
