@@ -245,6 +245,11 @@ def run_ours(args):
         exchange_desc = ("no gradient exchange: every rank publishes its view's nine per-splat sums (48 B rows) in NVLink "
                          "peer memory, then redoes the per-splat backward of all views + Adam on its own replica in ONE "
                          "kernel (brush_views_adam_step)")
+    elif world > 1 and trainer.exchange == "hybrid":
+        exchange_desc = ("hybrid exchange: the SH group travels as 16-byte colour rows (v_rgb + visibility) per splat and view, "
+                         "rebuilt and Adam-stepped on every rank (brush_sh_views_adam_step, replicated SH state); the 11 "
+                         "small gradient floats per splat are summed + stepped + broadcast by brush_dp_adam_step over "
+                         f"NVLink peer memory ({'NVSwitch multimem.ld_reduce/st' if trainer.peer.grad_mc else 'peer loads/stores'})")
     elif world > 1 and trainer.exchange == "peer":
         exchange_desc = ("gradient sum + Adam + parameter broadcast fused in brush_dp_adam_step over NVLink peer memory "
                          f"({'NVSwitch multimem.ld_reduce/st' if trainer.peer.grad_mc else 'peer loads/stores'}); "
@@ -701,7 +706,7 @@ def main():
     ap.add_argument("--profile-step", action="store_true",
                     help="run the warm-up, then ONE step between cudaProfilerStart/Stop and exit (for ncu "
                          "--profile-from-start off); prints no bench line")
-    ap.add_argument("--exchange", choices=["auto", "views", "peer", "nccl"], default="auto",
+    ap.add_argument("--exchange", choices=["auto", "views", "peer", "hybrid", "nccl"], default="auto",
                     help="multi-GPU step: per-view rows in peer memory + replicated fused tail (default), dense "
                          "gradient sum fused with Adam over peer memory, or NCCL all-reduce")
     args = ap.parse_args()

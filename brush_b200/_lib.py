@@ -122,6 +122,11 @@ _SIGS = {
     "brush_render_backward_rows": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,
                                              C.POINTER(BrushAux), C.c_void_p, C.POINTER(BrushViewExchange),
                                              C.c_void_p]),
+    "brush_render_backward_hybrid": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32] + [C.c_void_p] * 6 +
+                                     [C.POINTER(BrushAux)] + [C.c_void_p] * 6 + [C.POINTER(BrushViewExchange), C.c_void_p]),
+    "brush_sh_views_adam_step": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32] + [C.c_void_p] * 4 +
+                                 [C.c_float, C.c_float, C.POINTER(BrushViewExchange), C.c_void_p, C.c_float, C.c_float,
+                                  C.c_float, C.c_uint32, C.c_float, C.c_void_p]),
     "brush_views_adam_step": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(BrushTrainState), C.c_void_p,
                                         C.POINTER(BrushViewExchange), C.c_void_p, C.c_void_p, C.c_void_p,
                                         C.c_float, C.c_float, C.c_float, C.c_uint32, C.c_float, C.c_void_p]),

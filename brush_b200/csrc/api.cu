@@ -483,7 +483,7 @@ int brush_render_backward(brush_ctx* ctx, uint32_t N, uint32_t K, const float* m
         StageTimer t(ctx, st, BRUSH_STAGE_GATHER_PROJECT_BWD);
         launch_gather_project_backward(cam, N, K, means, log_scales, quats, raw_opacity,
                                        (float*)ctx->v_projected.p, v_means, v_xy, v_log_scales, v_quats, v_sh_coeffs,
-                                       v_raw_opacity, st);
+                                       v_raw_opacity, nullptr, nullptr, st);
     }
     CU(cudaGetLastError());
     return BRUSH_OK;
@@ -567,6 +567,74 @@ int brush_render_backward_rows(brush_ctx* ctx, uint32_t N, uint32_t K, const flo
     r = visible_mask_for(ctx, aux, N, st, &mask);
     if (r != BRUSH_OK) return r;
     launch_publish_view(rows, N, mask, aux->uniforms_buffer, loss_term, X, st);
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
+
+int brush_render_backward_hybrid(brush_ctx* ctx, uint32_t N, uint32_t K, const float* means, const float* log_scales,
+                                 const float* quats, const float* raw_opacity, const float* out_img,
+                                 const float* v_out_img, const BrushAux* aux, float* v_means, float* v_xy,
+                                 float* v_log_scales, float* v_quats, float* v_raw_opacity, const float* loss_term,
+                                 const BrushViewExchange* x, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (!valid_k(K)) return fail(ctx, BRUSH_E_INVALID, "Invalid nr. of sh bases " + std::to_string(K));
+    if (!aux || !out_img || !v_out_img || N == 0 || !means || !log_scales || !quats || !raw_opacity || !v_means ||
+        !v_xy || !v_log_scales || !v_quats || !v_raw_opacity)
+        return fail(ctx, BRUSH_E_INVALID, "null argument or N == 0");
+    ViewsLaunch X;
+    int r = views_launch(ctx, x, &X);
+    if (r != BRUSH_OK) return r;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(ctx->device));
+    NvtxRange span("render_gaussians backwards");
+    BrushUniforms u;
+    r = uniforms_of(ctx, aux, N, K, st, &u);
+    if (r != BRUSH_OK) return r;
+    const Cam cam = make_cam(u);
+    ENSURE(v_projected, (size_t)N * VP_STRIDE * 4 + 16);
+    ctx->ev_used[BRUSH_STAGE_RASTERIZE_BWD] = ctx->ev_used[BRUSH_STAGE_GATHER_PROJECT_BWD] = false;
+    CU(zero_async(ctx->v_projected.p, (size_t)N * VP_STRIDE * 4, st));
+    {
+        StageTimer t(ctx, st, BRUSH_STAGE_RASTERIZE_BWD);
+        launch_rasterize_backward(cam, (uint32_t*)aux->compact_gid_from_isect, (uint32_t*)aux->tile_bins,
+                                  aux->projected_splats, (uint32_t*)aux->global_from_compact_gid,
+                                  (uint32_t*)aux->final_index, out_img, v_out_img, (float*)ctx->v_projected.p,
+                                  pair_counter_of(ctx, 1), st);
+    }
+    const uint8_t* mask = nullptr;
+    r = visible_mask_for(ctx, aux, N, st, &mask);
+    if (r != BRUSH_OK) return r;
+    float* rows = x->rows[x->rank];
+    {
+        StageTimer t(ctx, st, BRUSH_STAGE_GATHER_PROJECT_BWD);
+        launch_gather_project_backward(cam, N, K, means, log_scales, quats, raw_opacity, (float*)ctx->v_projected.p,
+                                       v_means, v_xy, v_log_scales, v_quats, nullptr, v_raw_opacity, rows, mask, st);
+    }
+    launch_publish_colour_rows(rows, N, aux->uniforms_buffer, loss_term, X, st);
+    CU(cudaGetLastError());
+    return BRUSH_OK;
+}
+
+int brush_sh_views_adam_step(brush_ctx* ctx, uint32_t N, uint32_t K, const float* means, float* sh_coeffs,
+                             float* m_sh_coeffs, float* v_sh_coeffs, float lr_coeffs_dc, float sh_rest_lr_scale,
+                             const BrushViewExchange* x, float* loss_out, float beta1, float beta2, float eps,
+                             uint32_t step, float grad_scale, void* stream) {
+    if (!ctx) return BRUSH_E_INVALID;
+    if (!valid_k(K)) return fail(ctx, BRUSH_E_INVALID, "Invalid nr. of sh bases " + std::to_string(K));
+    if (!means || !sh_coeffs || !m_sh_coeffs || !v_sh_coeffs || N == 0 || step < 1 ||
+        (((uintptr_t)sh_coeffs | (uintptr_t)m_sh_coeffs | (uintptr_t)v_sh_coeffs) & 15u))
+        return fail(ctx, BRUSH_E_INVALID, "null / misaligned argument or N == 0");
+    ViewsLaunch X;
+    int r = views_launch(ctx, x, &X);
+    if (r != BRUSH_OK) return r;
+    X.loss_out = loss_out;
+    CU(cudaSetDevice(ctx->device));
+    const float inv_bc1 = (float)(1.0 / (1.0 - std::pow((double)beta1, (double)step)));
+    const float inv_bc2 = (float)(1.0 / (1.0 - std::pow((double)beta2, (double)step)));
+    if (launch_sh_views_adam(X, N, K, means, sh_coeffs, m_sh_coeffs, v_sh_coeffs, lr_coeffs_dc,
+                             lr_coeffs_dc * sh_rest_lr_scale, beta1, beta2, eps, inv_bc1, inv_bc2, grad_scale,
+                             (cudaStream_t)stream) != 0)
+        return fail(ctx, BRUSH_E_CUDA, "sh_views_adam launch failed");
     CU(cudaGetLastError());
     return BRUSH_OK;
 }

@@ -84,14 +84,19 @@ BD void project_backward_chain(const Cam& cam, V3 mean, V3 scale, V4 quat, V2 v_
     v_quat_out = v_quat;
 }
 
-template <int K>
+// SH_DENSE = false (the hybrid view-parallel step): the SH gradient is not formed here.  The splat's colour gradient
+// v_rgb -- all the SH gradient of one view is made of: v_coeffs[g,k,:] = basis_k(viewdir) * v_rgb, gather_grads.wgsl:
+// 165-232 -- goes to colour_rows[g] = (v_r, v_g, v_b, visible) instead, 16 bytes instead of 12 K, for
+// sh_views_adam_kernel on every rank to expand.
+template <int K, bool SH_DENSE>
 __global__ void __launch_bounds__(256)
 gather_project_backward_kernel(const __grid_constant__ Cam cam, const float* __restrict__ means,
                                const float* __restrict__ log_scales, const float* __restrict__ quats,
                                const float* __restrict__ raw_opac, const float* __restrict__ v_projected,
                                float* __restrict__ v_means, float* __restrict__ v_xy_out,
                                float* __restrict__ v_log_scales, float* __restrict__ v_quats,
-                               float* __restrict__ v_coeffs, float* __restrict__ v_raw_opac) {
+                               float* __restrict__ v_coeffs, float* __restrict__ v_raw_opac,
+                               float4* __restrict__ colour_rows, const uint8_t* __restrict__ visible_mask) {
     // One thread per splat in GLOBAL id order: the rasterizer accumulated its nine sums into row g, so every
     // read and write here is coalesced and every output row is written exactly once (dense gradients, zero
     // for splats no pixel saw: render.rs:598-624), with no separate zero-fill pass.
@@ -103,12 +108,14 @@ gather_project_backward_kernel(const __grid_constant__ Cam cam, const float* __r
     const V3 v_conic = {vp0.z, vp0.w, vp1.x};
     const V3 v_rgb = {vp1.y, vp1.z, vp1.w};
     const float v_alpha = reinterpret_cast<const float*>(vp)[8];
-    float* out_sh = v_coeffs + (size_t)g * (3 * K);
+    float* out_sh = SH_DENSE ? v_coeffs + (size_t)g * (3 * K) : nullptr;
+    if (!SH_DENSE) colour_rows[g] = make_float4(v_rgb.x, v_rgb.y, v_rgb.z, (float)visible_mask[g]);
     // Every output is linear in the nine sums, so an all-zero row (culled splat, or no contributing pixel) gives
     // exact zeros; skipping the chain also keeps 0 * inf out of the result for splats behind the camera.
     if (vp0.x == 0.f && vp0.y == 0.f && vp0.z == 0.f && vp0.w == 0.f && vp1.x == 0.f && vp1.y == 0.f &&
         vp1.z == 0.f && vp1.w == 0.f && v_alpha == 0.f) {
-        if ((3 * K) % 4 == 0) {
+        if (!SH_DENSE) {
+        } else if ((3 * K) % 4 == 0) {
 #pragma unroll
             for (int j = 0; j < (3 * K) / 4; j++) reinterpret_cast<float4*>(out_sh)[j] = make_float4(0.f, 0.f, 0.f, 0.f);
         } else {
@@ -131,6 +138,7 @@ gather_project_backward_kernel(const __grid_constant__ Cam cam, const float* __r
 
     // ---- gather_grads.wgsl:175-231 ----
     {
+        if (SH_DENSE) {
         V3 d = mean - cam.t;
         float inv = rsqrtf(dot3(d, d));
         V3 viewdir = d * inv;
@@ -147,6 +155,7 @@ gather_project_backward_kernel(const __grid_constant__ Cam cam, const float* __r
         } else {
 #pragma unroll
             for (int k = 0; k < K; k++) { out[3 * k] = b[k] * v_rgb.x; out[3 * k + 1] = b[k] * v_rgb.y; out[3 * k + 2] = b[k] * v_rgb.z; }
+        }
         }
         float sgm = 1.0f / (1.0f + __expf(-__ldg(raw_opac + g)));
         v_raw_opac[g] = v_alpha * (sgm * (1.0f - sgm));
@@ -167,18 +176,23 @@ gather_project_backward_kernel(const __grid_constant__ Cam cam, const float* __r
 void launch_gather_project_backward(const Cam& cam, uint32_t N, uint32_t K, const float* means,
                                     const float* log_scales, const float* quats, const float* raw_opac,
                                     const float* v_projected, float* v_means, float* v_xy, float* v_log_scales,
-                                    float* v_quats, float* v_coeffs, float* v_raw_opac, cudaStream_t st) {
+                                    float* v_quats, float* v_coeffs, float* v_raw_opac, float* colour_rows,
+                                    const uint8_t* visible_mask, cudaStream_t st) {
     if (N == 0) return;
     dim3 grid((N + 255) / 256), block(256);
     g_launch_count++;
 #define GB_ARGS cam, means, log_scales, quats, raw_opac, v_projected, v_means, \
-                v_xy, v_log_scales, v_quats, v_coeffs, v_raw_opac
+                v_xy, v_log_scales, v_quats, v_coeffs, v_raw_opac, (float4*)colour_rows, visible_mask
+    if (colour_rows) {  // hybrid step: no dense SH gradient (K plays no part)
+        gather_project_backward_kernel<1, false><<<grid, block, 0, st>>>(GB_ARGS);
+        return;
+    }
     switch (K) {
-        case 1: gather_project_backward_kernel<1><<<grid, block, 0, st>>>(GB_ARGS); break;
-        case 4: gather_project_backward_kernel<4><<<grid, block, 0, st>>>(GB_ARGS); break;
-        case 9: gather_project_backward_kernel<9><<<grid, block, 0, st>>>(GB_ARGS); break;
-        case 16: gather_project_backward_kernel<16><<<grid, block, 0, st>>>(GB_ARGS); break;
-        case 25: gather_project_backward_kernel<25><<<grid, block, 0, st>>>(GB_ARGS); break;
+        case 1: gather_project_backward_kernel<1, true><<<grid, block, 0, st>>>(GB_ARGS); break;
+        case 4: gather_project_backward_kernel<4, true><<<grid, block, 0, st>>>(GB_ARGS); break;
+        case 9: gather_project_backward_kernel<9, true><<<grid, block, 0, st>>>(GB_ARGS); break;
+        case 16: gather_project_backward_kernel<16, true><<<grid, block, 0, st>>>(GB_ARGS); break;
+        case 25: gather_project_backward_kernel<25, true><<<grid, block, 0, st>>>(GB_ARGS); break;
     }
 #undef GB_ARGS
 }
@@ -561,6 +575,135 @@ int launch_views_adam(const ViewsLaunch& X, uint32_t N, uint32_t K, const float*
         case 9: return launch_views_adam_k<9>(X, N, norm_quats, A, st);
         case 16: return launch_views_adam_k<16>(X, N, norm_quats, A, st);
         case 25: return launch_views_adam_k<25>(X, N, norm_quats, A, st);
+    }
+    return -1;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Hybrid view-parallel step: the SH group is 3K of the 13 + 3K gradient floats of a splat (81 % at SH
+// degree 3), but per view it is the outer product basis(viewdir) (x) v_rgb -- three floats of information.  So the
+// SH gradient is never exchanged: every rank publishes its view's colour rows (v_r, v_g, v_b, visible: 16 B per splat,
+// written by gather_project_backward_kernel<K, false>), reads every other view's rows over NVLink, rebuilds
+// sum_v basis(viewdir_v) (x) v_rgb_v for ALL splats in a fixed view order and applies Adam to its own full SH replica
+// (bit-identical on every rank, no parameter broadcast).  The eleven remaining gradient floats go through
+// dp_adam_kernel as dense sums.  Inbound NVLink bytes per splat and step: 16 (world - 1) + 44, against 237 for the
+// dense exchange at world 8 and 48 (world - 1) for the `views` exchange.
+__global__ void publish_trailer_kernel(float* __restrict__ trailer, const uint32_t* __restrict__ uniforms,
+                                       const float* __restrict__ loss) {
+    const uint32_t i = threadIdx.x;
+    if (i < 28) reinterpret_cast<uint32_t*>(trailer)[i] = uniforms[i];
+    if (i == 28) trailer[28] = loss ? *loss : 0.0f;
+}
+
+void launch_publish_colour_rows(float* rows, uint32_t N, const void* uniforms_dev, const float* loss_dev,
+                                const ViewsLaunch& X, cudaStream_t st) {
+    g_launch_count += 2;
+    publish_trailer_kernel<<<1, 32, 0, st>>>(rows + (size_t)N * RGB_STRIDE, (const uint32_t*)uniforms_dev, loss_dev);
+    ArriveLaunch L{};
+    for (int r = 0; r < X.world; r++) L.flags[r] = X.flags[r];
+    L.world = X.world; L.rank = X.rank; L.epoch = X.epoch;
+    arrive_kernel<<<1, 32, 0, st>>>(L);
+}
+
+struct ShViewsLaunch {
+    const float* means;  // the means the step's forwards rendered with (BEFORE this step's update)
+    float *sh, *m_sh, *v_sh;
+    float lr_sh_dc, lr_sh_rest, beta1, beta2, eps, inv_bc1, inv_bc2, grad_scale;
+};
+
+template <int K>
+__global__ void __launch_bounds__(256, 2)
+sh_views_adam_kernel(const __grid_constant__ ViewsLaunch X, uint32_t N, const __grid_constant__ ShViewsLaunch P) {
+    constexpr int S = (3 * K) | 1;
+    extern __shared__ float4 shv_smem[];
+    float* s_g = reinterpret_cast<float*>(shv_smem);             // [256][S] SH gradients, summed over views
+    float4* s_rows = reinterpret_cast<float4*>(s_g + 256 * S);   // [VIEW_STAGES][256] colour rows of this block, per view
+    __shared__ Cam s_cam[DP_MAX_WORLD];
+    const int world = X.world, tid = threadIdx.x;
+    if (tid < world) {
+        const uint32_t* f = X.flags[X.rank] + tid;
+        while ((int32_t)(ld_acquire_sys(f) - X.epoch) < 0) __nanosleep(64);
+    }
+    __syncthreads();
+    if (tid < world) {
+        BrushUniforms u;
+        const float* trailer = X.rows[tid] + (size_t)N * RGB_STRIDE;
+        float4* dst = reinterpret_cast<float4*>(&u);
+#pragma unroll
+        for (int j = 0; j < 7; j++) dst[j] = ld_peer_v4(trailer + 4 * j);
+        s_cam[tid] = make_cam(u);
+    }
+    if (blockIdx.x == 0 && tid == 0 && X.loss_out) {
+        float l = 0.f;
+        for (int w = 0; w < world; w++) l += ld_peer_v4(X.rows[w] + (size_t)N * RGB_STRIDE + 28).x;
+        *X.loss_out = l * P.grad_scale;
+    }
+    const uint32_t first = blockIdx.x * 256u, g = first + tid;
+    const int count = (int)min(256u, N - first);
+    auto fetch = [&](int w) {
+        if (w < world && tid < count) {
+            const float* src = X.rows[w] + ((size_t)first + tid) * RGB_STRIDE;
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(s_rows + (w % VIEW_STAGES) * 256 + tid);
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+#pragma unroll
+    for (int w = 0; w < VIEW_STAGES - 1; w++) fetch(w);
+    V3 mean_v = {0.f, 0.f, 0.f};
+    if (g < N) mean_v = {P.means[3 * (size_t)g], P.means[3 * (size_t)g + 1], P.means[3 * (size_t)g + 2]};
+#pragma unroll 4
+    for (int e = 0; e < 3 * K; e++) s_g[tid * S + e] = 0.f;
+    for (int w = 0; w < world; w++) {
+        asm volatile("cp.async.wait_group %0;" ::"n"(VIEW_STAGES - 2) : "memory");
+        __syncthreads();
+        fetch(w + VIEW_STAGES - 1);
+        if (g < N) {
+            const float4 r = s_rows[(w % VIEW_STAGES) * 256 + tid];
+            if (!(r.x == 0.f && r.y == 0.f && r.z == 0.f)) {
+                const Cam& cam = s_cam[w];
+                float b[K];
+                const V3 dv = mean_v - cam.t;
+                sh_basis<K>(cam.sh_degree, dv * rsqrtf(dot3(dv, dv)), b);
+#pragma unroll
+                for (int k = 0; k < K; k++) {
+                    s_g[tid * S + 3 * k] += b[k] * r.x;
+                    s_g[tid * S + 3 * k + 1] += b[k] * r.y;
+                    s_g[tid * S + 3 * k + 2] += b[k] * r.z;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    FusedAdamLaunch A{};
+    A.sh = P.sh; A.m_sh = P.m_sh; A.v_sh = P.v_sh;
+    A.lr_sh_dc = P.lr_sh_dc; A.lr_sh_rest = P.lr_sh_rest;
+    A.beta1 = P.beta1; A.beta2 = P.beta2; A.eps = P.eps; A.inv_bc1 = P.inv_bc1; A.inv_bc2 = P.inv_bc2;
+    A.grad_scale = P.grad_scale;
+    sh_rows_adam<K>(A, N, [&](int srow, int kk, int ch) { return s_g[srow * S + 3 * kk + ch]; });
+}
+
+template <int K>
+static int launch_sh_views_adam_k(const ViewsLaunch& X, uint32_t N, const ShViewsLaunch& P, cudaStream_t st) {
+    const size_t smem = (size_t)256 * ((3 * K) | 1) * 4 + (size_t)VIEW_STAGES * 256 * 16;
+    cudaError_t e = cudaFuncSetAttribute(sh_views_adam_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    sh_views_adam_kernel<K><<<(N + 255) / 256, 256, smem, st>>>(X, N, P);
+    return 0;
+}
+
+int launch_sh_views_adam(const ViewsLaunch& X, uint32_t N, uint32_t K, const float* means, float* sh, float* m_sh,
+                         float* v_sh, float lr_sh_dc, float lr_sh_rest, float beta1, float beta2, float eps,
+                         float inv_bc1, float inv_bc2, float grad_scale, cudaStream_t st) {
+    if (N == 0) return 0;
+    g_launch_count++;
+    const ShViewsLaunch P{means, sh, m_sh, v_sh, lr_sh_dc, lr_sh_rest, beta1, beta2, eps, inv_bc1, inv_bc2, grad_scale};
+    switch (K) {
+        case 1: return launch_sh_views_adam_k<1>(X, N, P, st);
+        case 4: return launch_sh_views_adam_k<4>(X, N, P, st);
+        case 9: return launch_sh_views_adam_k<9>(X, N, P, st);
+        case 16: return launch_sh_views_adam_k<16>(X, N, P, st);
+        case 25: return launch_sh_views_adam_k<25>(X, N, P, st);
     }
     return -1;
 }

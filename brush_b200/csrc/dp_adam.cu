@@ -23,7 +23,9 @@ namespace brush {
 __device__ __forceinline__ void wait_flags(const uint32_t* my_flags, int which, int world, uint32_t epoch) {
     if (threadIdx.x < (uint32_t)world) {
         const uint32_t* f = my_flags + which * DP_MAX_WORLD + threadIdx.x;
-        while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {}
+        // back off between polls: an overlapped exchange waits here beside the next forward's kernels, and hundreds of
+        // CTAs hammering one L2 line with system-scope loads slow those kernels down (measured: project_forward 2x)
+        while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) __nanosleep(256);
     }
     __syncthreads();
 }

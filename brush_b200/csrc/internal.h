@@ -89,7 +89,9 @@ int measure_peaks(float* out4, float* sink, cudaStream_t st);
 void launch_gather_project_backward(const Cam& cam, uint32_t N, uint32_t K, const float* means,
                                     const float* log_scales, const float* quats, const float* raw_opac,
                                     const float* v_projected, float* v_means, float* v_xy, float* v_log_scales,
-                                    float* v_quats, float* v_coeffs, float* v_raw_opac, cudaStream_t st);
+                                    float* v_quats, float* v_coeffs, float* v_raw_opac,
+                                    float* colour_rows /* hybrid step: (v_r, v_g, v_b, visible) per splat instead of v_coeffs; else null */,
+                                    const uint8_t* visible_mask, cudaStream_t st);
 
 // ---- programmatic dependent launch (PDL) ----
 // A training step is ~22 short kernels on one stream; with plain launches each boundary costs a full drain of the
@@ -166,6 +168,7 @@ void launch_visible_mask_from_list(const uint32_t* global_from_compact, const in
 // view's visibility flag; the trailer holds the view's RenderUniforms (28 words) and its loss term (word 28).
 constexpr int DP_MAX_WORLD = BRUSH_DP_MAX_WORLD;
 constexpr int VIEW_TRAILER = 32;
+constexpr uint32_t RGB_STRIDE = 4;  // hybrid step: colour rows (v_r, v_g, v_b, visible), same trailer behind them
 struct ViewsLaunch {
     int world, rank;
     const float* rows[DP_MAX_WORLD];
@@ -179,6 +182,13 @@ void launch_publish_view(float* rows, uint32_t N, const uint8_t* visible_mask, c
                          const float* loss_dev, const ViewsLaunch& X, cudaStream_t st);
 int launch_views_adam(const ViewsLaunch& X, uint32_t N, uint32_t K, const float* norm_quats, const FusedAdamLaunch& A,
                       cudaStream_t st);
+// Hybrid step: publish the trailer of this rank's colour rows + signal; then rebuild the SH gradient of every view from
+// the colour rows and apply Adam to the local SH replica.
+void launch_publish_colour_rows(float* rows, uint32_t N, const void* uniforms_dev, const float* loss_dev,
+                                const ViewsLaunch& X, cudaStream_t st);
+int launch_sh_views_adam(const ViewsLaunch& X, uint32_t N, uint32_t K, const float* means, float* sh, float* m_sh,
+                         float* v_sh, float lr_sh_dc, float lr_sh_rest, float beta1, float beta2, float eps,
+                         float inv_bc1, float inv_bc2, float grad_scale, cudaStream_t st);
 
 // ---- optim.cu ----
 // Zero-fill by a kernel on `st` (16-byte granular when aligned).  Used instead of cudaMemsetAsync everywhere in the

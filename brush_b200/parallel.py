@@ -3,12 +3,16 @@
 prescribes: every rank holds a full replica of the Gaussians, renders different camera views, and the dense
 per-Gaussian gradients are summed before the Adam step.
 
-Three exchange modes:
+Four exchange modes:
   * "views": nothing dense is exchanged.  Each rank publishes the nine per-splat sums rasterize_backwards leaves for
              its view (48-byte rows) in peer-mapped memory; every rank redoes the cheap per-splat backward for every
              view and applies Adam to its own full replica (csrc/backward.cu views_adam_kernel).  Cross-GPU traffic
              48*N*(world-1) bytes per rank and step instead of ~2*244*N, one flag barrier.
   * "nccl":  ONE all-reduce over a flat f32 buffer, then the replicated brush_adam_step (the baseline);
+  * "hybrid": the SH group (81 % of the dense gradient bytes at SH degree 3) is exchanged as the colour rows it is made
+             of (v_r, v_g, v_b, visible: 16 B per splat and view) and rebuilt + Adam-stepped on every rank
+             (csrc/backward.cu sh_views_adam_kernel); the 11 remaining floats per splat go through the "peer" kernel.
+             Inbound bytes per splat: 16 (world - 1) + 44 -- the smallest of the modes from 3 ranks up.
   * "peer":  ONE brush_dp_adam_step launch per rank over NVLink peer memory: rank r sums its 1/world slice of
              every rank's gradient buffer, applies Adam there (moments sharded), and stores the new parameters into
              every rank's replica (csrc/dp_adam.cu).  PyTorch symmetric memory is only the plumbing that maps the
@@ -155,11 +159,13 @@ class ViewBuffers:
     what lets one flag barrier per step suffice) and one flag block per rank.  group=None: plain device memory,
     world 1."""
 
-    def __init__(self, n: int, group, device):
+    def __init__(self, n: int, group, device, stride: int = VP_STRIDE):
+        """stride = floats per splat row: 12 for the `views` exchange (the nine sums of rasterize_backwards + the
+        visibility flag), 4 for the colour rows of the `hybrid` exchange (v_r, v_g, v_b, visible)."""
         from . import _lib
 
         self.n = n
-        self.block = n * VP_STRIDE + VIEW_TRAILER  # floats; 16-byte multiple
+        self.block = n * stride + VIEW_TRAILER  # floats; 16-byte multiple
         self.world = group.size() if group is not None else 1
         self.rank = group.rank() if group is not None else 0
         if self.world > _lib.DP_MAX_WORLD:

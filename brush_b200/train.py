@@ -101,15 +101,19 @@ class SplatTrainer:
         self.isect_capacity = isect_capacity
         self.optimize = optimize
         self.fused_tail = fused_tail  # single device, one view per step: backward tail + Adam in one kernel
-        if exchange not in ("nccl", "peer", "views"):
-            raise ValueError("exchange must be 'nccl', 'peer' or 'views'")
+        if exchange not in ("nccl", "peer", "views", "hybrid"):
+            raise ValueError("exchange must be 'nccl', 'peer', 'views' or 'hybrid'")
         # "peer": gradient sum + Adam + parameter broadcast as one launch over NVLink peer memory (parallel.py)
         # "views": no gradient exchange at all: 48-byte per-splat rows are published, every rank redoes the
         #          per-splat backward of every view and updates its own replica (one view per rank per step)
+        # "hybrid": SH as 16-byte colour rows rebuilt on every rank (replicated SH Adam), the 11 small floats per splat
+        #          through the "peer" kernel (one view per rank per step)
         multi = process_group is not None and process_group.size() > 1
         self.exchange = exchange if (multi or exchange == "views") else "nccl"
         self.peer: Optional[PeerBuffers] = None
         self.views: Optional[ViewBuffers] = None
+        self.colour: Optional[ViewBuffers] = None
+        self.colour_epoch = 0
         self.epoch = 0
         self._copy_stream = None
         # overlapped peer exchange (see _peer_step); BRUSH_DP_OVERLAP=0 restores the single-launch exchange
@@ -128,7 +132,7 @@ class SplatTrainer:
         self.opt_step = 0
         self.layout = FlatGradLayout(n, k)
         self.param_layout = FlatParamLayout(n, k)
-        if self.exchange == "peer":
+        if self.exchange in ("peer", "hybrid"):
             self.peer = PeerBuffers(self.layout, self.param_layout, self.pg, self.device)
             self.flat_grad = self.peer.grad
             self.peer_m = torch.zeros(self.param_layout.total, **f)
@@ -137,6 +141,8 @@ class SplatTrainer:
             self.flat_grad = self.layout.alloc(self.device)
         if self.exchange == "views":
             self.views = ViewBuffers(n, self.pg, self.device)
+        if self.exchange == "hybrid":
+            self.colour = ViewBuffers(n, self.pg, self.device, stride=4)
         (self.g_means, self.g_xy, self.g_scales, self.g_quats, self.g_sh, self.g_opac, self.stat_grad_norm,
          self.stat_visible, self.g_loss) = self.layout.views(self.flat_grad)
         self.tmp = None  # second gradient set, only for batches of more than one view per rank
@@ -228,6 +234,9 @@ class SplatTrainer:
         outs = (self.g_means, self.g_xy, self.g_scales, self.g_quats, self.g_sh, self.g_opac)
         preds, auxes = [], []
         views = self.views is not None and self.optimize and B == 1
+        hybrid = self.colour is not None
+        if hybrid and (B != 1 or not self.optimize):
+            raise ValueError("exchange='hybrid' takes one view per rank per step and needs the optimizer")
         fused = self.fused_tail and self.optimize and world == 1 and B == 1 and self.peer is None and not views
         # train.rs:361-365 (iter = the value before this step's increment)
         do_refine = (self.iter < cfg.max_refine_step and self.iter >= cfg.warmup_steps
@@ -292,6 +301,16 @@ class SplatTrainer:
                     preds.append(pred)
                     auxes.append(aux)
                     break
+                elif hybrid:
+                    # small gradients densely + this view's colour rows (16 B per splat) published to every rank
+                    self.colour_epoch += 1
+                    cx = self.colour.exchange(self.colour_epoch)
+                    caux = aux._c()
+                    ctx.check(L.brush_render_backward_hybrid(
+                        ctx.handle, self.n, self.k, p_means.data_ptr(), p_scales.data_ptr(), self.norm_rot.data_ptr(),
+                        p_opac.data_ptr(), pred.data_ptr(), self.v_out.data_ptr(), C.byref(caux), dst[0].data_ptr(),
+                        dst[1].data_ptr(), dst[2].data_ptr(), dst[3].data_ptr(), dst[5].data_ptr(),
+                        self.loss_total.data_ptr(), C.byref(cx), st))
                 else:
                     render_backward(aux, p_means, p_scales, self.norm_rot, p_sh.shape, p_opac, pred, self.v_out,
                                     ctx=ctx, out=dst)
@@ -321,7 +340,15 @@ class SplatTrainer:
                 if splats.means.data_ptr() != self.peer.param.data_ptr() + 4 * self.param_layout.offset("means"):
                     raise ValueError("peer exchange: pass the Splats returned by SplatTrainer.adopt()")
                 self.g_loss[:1].copy_(self.loss_total)
-                stat_norm, stat_vis = self._peer_step(ctx, lr_mean, grad_scale, st)
+                if hybrid:
+                    # SH: rebuilt from every view's colour rows and stepped on this rank's replica; needs the means the
+                    # forwards rendered with, so it runs BEFORE the small groups are updated
+                    m_sh, v_sh = self._adam_state("sh", splats.sh_coeffs)
+                    ctx.check(L.brush_sh_views_adam_step(
+                        ctx.handle, self.n, self.k, p_means.data_ptr(), p_sh.data_ptr(), m_sh.data_ptr(), v_sh.data_ptr(),
+                        cfg.lr_coeffs_dc, 1.0 / cfg.lr_coeffs_sh_scale, C.byref(cx), None, cfg.adam_beta1,
+                        cfg.adam_beta2, cfg.adam_eps, self.opt_step, grad_scale, st))
+                stat_norm, stat_vis = self._peer_step(ctx, lr_mean, grad_scale, st, skip_sh=hybrid)
                 loss = self.loss_buf  # grad_scale * sum over ranks, written by the exchange kernel
             else:
                 if self.pg is not None and world > 1:
@@ -404,7 +431,7 @@ class SplatTrainer:
         out = self.adopt(Splats(new[0], new[2], new[1], new[3], new[4]))
         return out, RefineStats(n_split, n_clone, alpha_pruned, scale_pruned)
 
-    def _peer_step(self, ctx, lr_mean: float, grad_scale: float, st):
+    def _peer_step(self, ctx, lr_mean: float, grad_scale: float, st, skip_sh: bool = False):
         """brush_dp_adam_step: sum of the ranks' gradients on the owned slice -> Adam (train.rs:318-359) -> new
         parameters into every replica; the refine statistics ride along as plain-sum segments.
 
@@ -443,7 +470,7 @@ class SplatTrainer:
                                                     cfg.adam_beta2, cfg.adam_eps, self.opt_step, grad_scale,
                                                     C.c_void_p(stream_ptr)))
 
-        names = list(pl.NAMES)
+        names = [n for n in pl.NAMES if not (skip_sh and n == "sh")]  # hybrid: SH never goes through this exchange
         if not self.optimize:  # gradients only: leave the parameters alone, still reduce the statistics
             names = ["grad_norm", "visible"]
         self.epoch += 1

@@ -240,6 +240,27 @@ int brush_views_adam_step(brush_ctx* ctx, uint32_t N, uint32_t K, const BrushTra
                           const BrushViewExchange* x, float* grad_norm_accum, float* visible_accum, float* loss_out,
                           float beta1, float beta2, float eps, uint32_t step, float grad_scale, void* stream);
 
+/* ---- hybrid view-parallel step (no reference counterpart) ----
+ * The SH group is 3K of the 13 + 3K gradient floats of a splat, but per view it is basis(viewdir) (x) v_rgb
+ * (gather_grads.wgsl:165-232): three floats of information.  brush_render_backward_hybrid = brush_render_backward
+ * without the dense SH gradient: the five small gradients are written densely (for brush_dp_adam_step), and the view's
+ * colour rows (v_r, v_g, v_b, visible) go to x->rows[x->rank] (f32[4 N + 32], peer-mapped, two blocks alternating
+ * by step parity like the `views` exchange; the trailer holds the view's uniforms and loss term), followed by the
+ * signal to every rank.  brush_sh_views_adam_step waits for all ranks' signals, rebuilds
+ * sum_v basis(viewdir_v) (x) v_rgb_v for ALL splats in view order from the colour rows (peer loads) and applies the
+ * SH part of brush_adam_step to this rank's full SH replica -- bit-identical on every rank.  `means` must be the
+ * means the step's forwards rendered with, so call it BEFORE the small groups are updated.  Inbound NVLink bytes
+ * per splat and step: 16 (world - 1) + 44 instead of 237 (dense, world 8) or 48 (world - 1) (`views`). */
+int brush_render_backward_hybrid(brush_ctx* ctx, uint32_t N, uint32_t K, const float* means, const float* log_scales,
+                                 const float* quats, const float* raw_opacity, const float* out_img,
+                                 const float* v_out_img, const BrushAux* aux, float* v_means, float* v_xy,
+                                 float* v_log_scales, float* v_quats, float* v_raw_opacity, const float* loss_term,
+                                 const BrushViewExchange* x, void* stream);
+int brush_sh_views_adam_step(brush_ctx* ctx, uint32_t N, uint32_t K, const float* means, float* sh_coeffs,
+                             float* m_sh_coeffs, float* v_sh_coeffs, float lr_coeffs_dc, float sh_rest_lr_scale,
+                             const BrushViewExchange* x, float* loss_out, float beta1, float beta2, float eps,
+                             uint32_t step, float grad_scale, void* stream);
+
 /* == image_to_tensor (crates/brush-dataset/src/lib.rs:11-24: u8 pixels -> f32 / 255) applied on the device after the
  * upload, so the host keeps one byte per channel and the per-step upload is 4x smaller.  n = number of channel
  * values (H*W*C); src 4-byte aligned, dst 16-byte aligned. */

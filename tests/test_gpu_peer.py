@@ -101,7 +101,7 @@ def _train_worker(rank, world, port, multimem, out):
     cams = [Camera(*ring_camera_params(w, h, j, 300)) for j in range(n_views)]
     cfg = TrainConfig(warmup_steps=0, max_refine_step=0)
     results = {}
-    for mode in ("nccl", "peer", "views"):
+    for mode in ("nccl", "peer", "views", "hybrid"):
         splats = Splats(t(sc.means), t(sc.sh_coeffs), t(sc.quats), t(sc.raw_opacity), t(sc.log_scales))
         tr = SplatTrainer(n, cfg, dev, sh_coeffs_per_channel=16, process_group=dist.group.WORLD, exchange=mode)
         splats = tr.adopt(splats)
@@ -130,7 +130,8 @@ def test_peer_exchange_matches_nccl(world, multimem):
     """world ranks train the same scene for four steps with (a) the NCCL all-reduce + replicated Adam -- the mean over
     the global batch of train.rs:229-268 done by a library collective, the oracle here: the reference is single-device
     (train.rs:216-219) -- (b) the fused peer-memory sum + Adam + broadcast (plain peer loads / stores with
-    BRUSH_DP_MULTIMEM=0, NVSwitch multimem.ld_reduce / multimem.st with 1) and (c) the `views` exchange.  Parameters,
+    BRUSH_DP_MULTIMEM=0, NVSwitch multimem.ld_reduce / multimem.st with 1), (c) the `views` exchange and (d) the
+    `hybrid` exchange (SH as colour rows rebuilt on every rank, the small groups through (b)).  Parameters,
     losses and the per-view refine statistics (train.rs:300-314) must agree; replicas must be bit-identical across
     all ranks."""
     if torch.cuda.device_count() < world:
@@ -147,12 +148,12 @@ def test_peer_exchange_matches_nccl(world, multimem):
     assert bool(r0["peer"][4]) == bool(multimem)
     names = ("means", "opacity", "sh", "rotation", "log_scales")
     for r in range(1, world):  # replicas bit-identical: one owner computes each element / same rows, same order
-        for mode in ("peer", "views", "nccl"):
+        for mode in ("peer", "views", "hybrid", "nccl"):
             for a, b in zip(r0[mode][0], out[r][mode][0]):
                 assert np.array_equal(a, b), (mode, r)
         assert np.allclose(r0["views"][1], out[r]["views"][1]) and np.allclose(r0["peer"][1], out[r]["peer"][1])
         assert np.array_equal(r0["views"][2], out[r]["views"][2]) and np.array_equal(r0["views"][3], out[r]["views"][3])
-    for mode in ("peer", "views"):
+    for mode in ("peer", "views", "hybrid"):
         for name, a, b in zip(names, r0[mode][0], r0["nccl"][0]):
             # same math; only the place of the rotation-normalisation VJP relative to the sum differs (rounding)
             close = np.isclose(a, b, rtol=2e-5, atol=2e-6)

@@ -430,6 +430,82 @@ def test_views_step_two_views_against_oracle():
         assert diff.max() <= 2.01 * lr and (diff <= 1e-5 * max(lr, 1e-3) + 1e-6).mean() > 0.995, name
 
 
+def test_hybrid_step_two_views_against_oracle():
+    """The hybrid exchange against the ORACLE, world = 2 emulated on one GPU: brush_render_backward_hybrid per "rank"
+    (small gradients dense, SH as 16-byte colour rows), then brush_sh_views_adam_step as rank 0.  The summed small
+    gradients and the SH Adam moments (= 0.1 * summed SH gradient / 2 at t = 1) must match
+    tests/helpers.py::oracle_multi_view_step within the north-star gradient tolerance."""
+    import ctypes as C
+    import sys
+
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import helpers as Hh
+    from test_parallel_gloo import _two_view_inputs
+
+    from brush_b200 import _lib, get_context
+    from brush_b200.render import make_uniforms, render_forward
+    from oracle import pyoracle as O
+
+    O.build()
+    O.set_threads(4)
+    L = _lib.lib()
+    ctx = get_context(DEV)
+    sc, cams, cam_args, v_outs, raw_rot_np, lrs, k = _two_view_inputs()
+    w, h, n = sc.width, sc.height, sc.means.shape[0]
+    ref = Hh.oracle_multi_view_step(O, sc, cam_args, raw_rot_np, v_outs, lrs, k, 0.05)
+    t = lambda a: torch.as_tensor(np.ascontiguousarray(a), device=DEV)
+    raw_rot = t(raw_rot_np)
+    norm_rot = torch.empty_like(raw_rot)
+    ctx.check(L.brush_quat_normalize(ctx.handle, raw_rot.data_ptr(), n, norm_rot.data_ptr(), None))
+    means, log_scales, sh, opac = t(sc.means), t(sc.log_scales), t(sc.sh_coeffs), t(sc.raw_opacity)
+    block = n * 4 + 32
+    rows = torch.full((2 * block,), -12345.0, device=DEV)  # poisoned: every word read must have been written
+    flags = torch.zeros(64, dtype=torch.int32, device=DEV)
+    sums, keep = None, []
+    for r, cam in enumerate(cams):
+        u = make_uniforms(cam.world_to_local(), cam.focal((w, h)), (w, h), cam.center((w, h)))
+        pred, aux = render_forward(u, means, log_scales, norm_rot, sh, opac, False, ctx=ctx)
+        keep.append((pred, aux))
+        x = _lib.BrushViewExchange()
+        x.world, x.rank, x.epoch = 2, r, 1
+        for i in range(2):
+            x.rows[i], x.flags[i] = rows.data_ptr() + 4 * block * i, flags.data_ptr()
+        g = [torch.full((n, c), -12345.0, device=DEV) for c in (3, 2, 3, 4)] + [torch.full((n,), -12345.0, device=DEV)]
+        caux = aux._c()
+        loss_term = torch.full((1,), 0.25 * (r + 1), device=DEV)
+        ctx.check(L.brush_render_backward_hybrid(
+            ctx.handle, n, k, means.data_ptr(), log_scales.data_ptr(), norm_rot.data_ptr(), opac.data_ptr(),
+            pred.data_ptr(), t(v_outs[r]).data_ptr(), C.byref(caux), g[0].data_ptr(), g[1].data_ptr(), g[2].data_ptr(),
+            g[3].data_ptr(), g[4].data_ptr(), loss_term.data_ptr(), C.byref(x), None))
+        sums = g if sums is None else [a + b for a, b in zip(sums, g)]
+    torch.cuda.synchronize()
+    vis = rows.view(2, block)[:, :n * 4].view(2, n, 4)[:, :, 3].sum(0)
+    assert np.array_equal(vis.cpu().numpy(), ref["visible"])  # the flag column of the colour rows
+    # small groups: dense per-view gradients, summed (what brush_dp_adam_step then reduces over ranks)
+    ctx.check(L.brush_quat_normalize_vjp(ctx.handle, raw_rot.data_ptr(), n, sums[3].data_ptr(), None))
+    for name, got in (("means", sums[0]), ("log_scales", sums[2]), ("rotation", sums[3]), ("raw_opacity", sums[4])):
+        a, b = got.cpu().numpy().astype(np.float64), ref["grads"][name].astype(np.float64)
+        assert (np.abs(a - b) <= 1e-3 * np.abs(b) + 2e-5 * np.abs(b).max()).all(), name
+    # SH: rebuilt from the colour rows of both views + Adam, as rank 0
+    m_sh, v_sh, loss = torch.zeros_like(sh), torch.zeros_like(sh), torch.zeros(1, device=DEV)
+    sh0 = sh.clone()
+    x = _lib.BrushViewExchange()
+    x.world, x.rank, x.epoch = 2, 0, 1
+    for i in range(2):
+        x.rows[i], x.flags[i] = rows.data_ptr() + 4 * block * i, flags.data_ptr()
+    ctx.check(L.brush_sh_views_adam_step(ctx.handle, n, k, means.data_ptr(), sh.data_ptr(), m_sh.data_ptr(),
+                                         v_sh.data_ptr(), lrs["sh_coeffs"], 0.05, C.byref(x), loss.data_ptr(), 0.9, 0.999,
+                                         1e-15, 1, 0.5, None))
+    torch.cuda.synchronize()
+    assert abs(float(loss) - 0.375) < 1e-6
+    m, rm = m_sh.cpu().numpy().astype(np.float64), ref["m"]["sh_coeffs"]
+    assert np.abs(rm).max() > 0 and (np.abs(m - rm) <= 1e-3 * np.abs(rm) + 2e-5 * np.abs(rm).max()).all()
+    step = (sh - sh0).abs()
+    lr_full = torch.full_like(step, lrs["sh_coeffs"])
+    lr_full[:, 1:, :] *= 0.05
+    assert bool((step <= lr_full * 1.01).all()) and float(step.max()) > 0.5 * lrs["sh_coeffs"]
+
+
 # (700, 40): many row segments per column strip (the seams of the row-streaming kernels); (3, 5): smaller than the
 # window; (20, 300): ten strips, the last one ragged
 @pytest.mark.parametrize("channels,h,w", [(3, 37, 53), (4, 64, 48), (3, 16, 16), (3, 700, 40), (4, 3, 5), (3, 20, 300)])
