@@ -1,6 +1,8 @@
 // Inclusive u32 prefix sum == brush_prefix_sum::prefix_sum (brush-prefix-sum/src/lib.rs:17-102, which runs
 // 2*levels+1 launches of 512-thread Hillis-Steele blocks).  Here: ONE launch, one read and one write of
 // the data (8 B/element, the algorithmic minimum), chained scan with decoupled look-back.
+#include <cstdio>
+
 #include "internal.h"
 #include "lookback.cuh"
 
@@ -108,4 +110,75 @@ void launch_inclusive_scan(const uint32_t* in, uint32_t n, uint32_t* out, uint64
     launch_k(inclusive_scan_kernel, tiles, SC_THREADS, 0, st, in, n, out, lb_status, ticket, total_out, cap, status_word);
 }
 
+// ---- the allocation-free entry point (brush_prefix_sum_u32_noalloc, include/brush_b200.h) ----
+// Same kernel, but the look-back status words and the tile ticket live in a file-scope device array instead of the
+// ctx's cudaMalloc'ed control block: callers under CUDA graph capture or in harnesses that forbid cudaMalloc get a
+// scan that allocates nothing.  Every GPU that loads the library holds the array (32 KB + 64 B) until exit.
+// Layout: word 0 = ticket (low 32 bits), words 8.. = one status word per tile (+1 spare, as scan_status_words).
+constexpr uint32_t NOALLOC_MAX_N = BRUSH_NOALLOC_SCAN_MAX_N;
+constexpr uint32_t NOALLOC_CTRL_WORDS = 8;
+constexpr uint32_t NOALLOC_WORDS = NOALLOC_CTRL_WORDS + (NOALLOC_MAX_N + SC_TILE - 1) / SC_TILE + 1;
+static __device__ __align__(256) unsigned long long g_noalloc_scan_scratch[NOALLOC_WORDS];
+
+// The array keeps the previous call's tickets and status words: clear the part this call reads, on the stream.
+__global__ void __launch_bounds__(256) noalloc_scan_clear_kernel(unsigned long long* scratch, uint32_t words) {
+    PDL_ENTER();
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < words; i += gridDim.x * blockDim.x) scratch[i] = 0ull;
+}
+
+// In host code `g_noalloc_scan_scratch` is only a handle for the runtime, never a device address: the address is
+// looked up once per device, with that device current, and cached.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static std::atomic<unsigned long long*> g_noalloc_ptr[NOALLOC_MAX_DEVICES];
+
+static cudaError_t noalloc_scratch_address(unsigned long long** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return cudaErrorInvalidDevice;
+    unsigned long long* p = g_noalloc_ptr[dev].load(std::memory_order_acquire);
+    if (!p) {
+        e = cudaGetSymbolAddress((void**)&p, g_noalloc_scan_scratch);
+        if (e != cudaSuccess) return e;
+        g_noalloc_ptr[dev].store(p, std::memory_order_release);  // racing threads store the same address
+    }
+    *out = p;
+    return cudaSuccess;
+}
+
 }  // namespace brush
+
+static int noalloc_fail(char* err_host, uint32_t err_len, int code, const char* msg, const char* detail = "") {
+    if (err_host && err_len) snprintf(err_host, err_len, "%s%s", msg, detail);
+    return code;
+}
+
+extern "C" __attribute__((visibility("default"))) int brush_prefix_sum_u32_noalloc(
+    const uint32_t* in, uint32_t n, uint32_t* out, void* stream, char* err_host, uint32_t err_len) {
+    using namespace brush;
+    if (err_host && err_len) err_host[0] = 0;
+    if (n && (!in || !out)) return noalloc_fail(err_host, err_len, BRUSH_E_INVALID, "brush_prefix_sum_u32_noalloc: null argument");
+    if (n > NOALLOC_MAX_N) {
+        char detail[96];
+        snprintf(detail, sizeof detail, "n = %u exceeds BRUSH_NOALLOC_SCAN_MAX_N = %u (static scratch)", n, NOALLOC_MAX_N);
+        return noalloc_fail(err_host, err_len, BRUSH_E_INVALID, "brush_prefix_sum_u32_noalloc: ", detail);
+    }
+    if (n == 0) return BRUSH_OK;
+    unsigned long long* scratch = nullptr;
+    cudaError_t e = noalloc_scratch_address(&scratch);
+    if (e != cudaSuccess)
+        return noalloc_fail(err_host, err_len, BRUSH_E_CUDA, "brush_prefix_sum_u32_noalloc: cudaGetSymbolAddress: ",
+                            cudaGetErrorString(e));
+    cudaStream_t st = (cudaStream_t)stream;
+    const uint32_t words = NOALLOC_CTRL_WORDS + (uint32_t)scan_status_words(n);
+    g_launch_count++;
+    e = launch_k(noalloc_scan_clear_kernel, (words + 255) / 256, 256, 0, st, scratch, words);
+    if (e == cudaSuccess) {
+        launch_inclusive_scan(in, n, out, reinterpret_cast<uint64_t*>(scratch + NOALLOC_CTRL_WORDS),
+                              reinterpret_cast<uint32_t*>(scratch), nullptr, ~0ull, nullptr, st);
+        e = cudaGetLastError();
+    }
+    if (e != cudaSuccess)
+        return noalloc_fail(err_host, err_len, BRUSH_E_CUDA, "brush_prefix_sum_u32_noalloc: launch: ", cudaGetErrorString(e));
+    return BRUSH_OK;
+}

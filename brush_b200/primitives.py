@@ -48,3 +48,24 @@ def prefix_sum(x: torch.Tensor) -> torch.Tensor:
                                              C.c_void_p(_stream_ptr(dev)))
     ctx.check(rc)
     return out
+
+
+NOALLOC_SCAN_MAX_N = 1 << 24  # BRUSH_NOALLOC_SCAN_MAX_N
+
+
+def prefix_sum_noalloc(x: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    """Inclusive scan of `x` into the caller's `out` through brush_prefix_sum_u32_noalloc: no ctx, no allocation (the
+    kernel's scratch is a static device array inside the library), at most NOALLOC_SCAN_MAX_N elements.  No
+    counterpart in the reference.  Calls on a device share the scratch: keep them on one stream or order them."""
+    for t in (x, out):
+        if not t.is_cuda or t.dtype != torch.int32 or not t.is_contiguous():
+            raise ValueError("prefix_sum_noalloc needs contiguous int32 CUDA tensors (no CPU fallback exists)")
+    if out.shape != x.shape or out.device != x.device or x.dim() != 1:
+        raise ValueError("x and out must be 1-d, of one shape, on one device")
+    err = C.create_string_buffer(256)
+    with torch.cuda.device(x.device):
+        rc = _lib.lib().brush_prefix_sum_u32_noalloc(x.data_ptr(), x.shape[0], out.data_ptr(),
+                                                     C.c_void_p(_stream_ptr(x.device)), err, len(err))
+    if rc != 0:
+        raise (ValueError if rc == -1 else RuntimeError)(err.value.decode() or f"brush error {rc}")
+    return out

@@ -148,6 +148,20 @@ int brush_radix_argsort_u64(brush_ctx* ctx, const uint64_t* keys, const uint32_t
 /* == brush_prefix_sum::prefix_sum, brush-prefix-sum/src/lib.rs:17.  Inclusive u32 scan of n elements. */
 int brush_prefix_sum_u32(brush_ctx* ctx, const uint32_t* in, uint32_t n, uint32_t* out, void* stream);
 
+/* NO COUNTERPART IN THE REFERENCE -- added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same inclusive u32
+ * scan as brush_prefix_sum_u32, with the kernel's scratch (tile ticket + look-back status words) in a file-scope
+ * `static __device__` array inside the library instead of a ctx: it takes no ctx and calls no cudaMalloc, cudaFree or
+ * allocating routine.  It runs on the CURRENT device, on `stream`; `in` / `out` are the caller's device buffers
+ * (distinct).  Limit: n <= BRUSH_NOALLOC_SCAN_MAX_N, larger sizes return BRUSH_E_INVALID.  The error text goes
+ * to the optional caller-owned host buffer err_host[err_len].  Every GPU that loads the library holds the array
+ * (32 KB + 64 B) until exit.  All calls on a device share it and it keeps the last call's contents (each call clears
+ * what it reads, on `stream`): calls that overlap on the GPU (different streams, no ordering between them) race;
+ * calls on one stream, or ordered by events, do not. */
+#define BRUSH_NOALLOC_SCAN_MAX_N 16777216u
+int brush_prefix_sum_u32_noalloc(const uint32_t* in, uint32_t n, uint32_t* out, void* stream, char* err_host,
+                                 uint32_t err_len);
+
 /* Host-staged convenience for FFI callers that hold HOST buffers (bench e2e leg, smoke tests): copies the five
  * parameter arrays H2D, renders, copies out_img (f32[H,W,4]) and the two counters back, synchronises. */
 int brush_render_forward_host(brush_ctx* ctx, const BrushUniforms* uniforms_host, uint32_t N, uint32_t K,
