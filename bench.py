@@ -378,6 +378,10 @@ def run_ours(args):
     if rank == 0:
         counts = (stats.auxes[0].read_num_visible(), stats.auxes[0].read_num_intersections())
     check = None
+    xt = None
+    if world > 1:
+        barrier()
+        xt = exchange_timing(trainer, one_step, world, rank, dev, N)
     if world > 1:
         barrier()
         check = multi_gpu_self_check(args, trainer, splats, start_params, cams, gt_dev, N, K, dev, pg, world, rank)
@@ -494,11 +498,93 @@ def run_ours(args):
     }
     if check is not None:
         out.update(check)
+    if xt is not None:
+        out["exchange_timing"] = xt
     if not args.no_cpu_baseline and world == 1:
         out["cpu_baseline"] = cpu_baseline_sample(args, sc)
     print(json.dumps(out))
     if world > 1:
         torch.distributed.destroy_process_group()
+
+
+def exchange_timing(trainer, one_step, world, rank, dev, N, reps=12):
+    """world > 1, outside every timed region: where a multi-GPU step's extra time goes.  Every step starts from a
+    barrier on all ranks; CUDA events on the step's stream bracket the exchange launch (one launch: the overlapped
+    two-launch form is switched off for these steps).  A rank that arrives early waits inside the exchange kernel for
+    the slowest rank's gradients, so per step the MINIMUM over ranks of the kernel's duration is the exchange itself and
+    the spread of the time-to-exchange over ranks is the cost of the views being unequal work (each rank renders a
+    different camera; a synchronous step lasts as long as its slowest view)."""
+    import torch
+    import torch.distributed as dist
+
+    name = "_views_step" if trainer.exchange == "views" else "_peer_step"
+    if trainer.exchange == "nccl" or not hasattr(trainer, name):
+        return None
+    orig = getattr(trainer, name)
+    saved_overlap = trainer.overlap_exchange
+    trainer.finish()
+    trainer.overlap_exchange = False
+    ev = []
+
+    def wrapped(*a, **k):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        r = orig(*a, **k)
+        e1.record()
+        ev.append((e0, e1))
+        return r
+
+    setattr(trainer, name, wrapped)
+    starts = []
+    try:
+        for s in range(reps + 2):
+            torch.cuda.synchronize(dev)
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            starts.append(e)
+            one_step(3000 + s, False)
+        torch.cuda.synchronize(dev)
+    finally:
+        setattr(trainer, name, orig)
+        trainer.overlap_exchange = saved_overlap
+    mine = torch.tensor([[starts[i].elapsed_time(ev[i][0]), ev[i][0].elapsed_time(ev[i][1])] for i in range(2, reps + 2)],
+                        device=dev)
+    every = [torch.zeros_like(mine) for _ in range(world)]
+    dist.all_gather(every, mine)
+    t = torch.stack(every).cpu()  # [rank, step, (to_exchange, exchange)]
+    to_x, x = t[..., 0], t[..., 1]
+    pure = float(x.min(dim=0).values.mean())
+    gl, pl = trainer.layout, trainer.param_layout
+    G, Pm = 4 * gl.total, 4 * pl.total
+    mode = trainer.exchange
+    if mode == "views":
+        b_in = b_out = 48 * N * (world - 1)
+    else:
+        mc = bool(trainer.peer is not None and trainer.peer.grad_mc)
+        if mode == "hybrid":  # SH leaves the flat exchange; 16-byte colour rows of every other view come in instead
+            sh = 4 * pl.padded_size("sh")
+            G, Pm = G - sh, Pm - sh
+        b_out = G * (world - 1) // world + (Pm // world if mc else Pm * (world - 1) // world)
+        b_in = (G // world if mc else G * (world - 1) // world) + Pm * (world - 1) // world
+        if mode == "hybrid":
+            b_in += 16 * N * (world - 1)
+            b_out += 16 * N * (world - 1)
+    return {
+        "mode": mode, "steps": reps, "launches_timed": name,
+        "to_exchange_ms_per_rank": [round(float(v), 4) for v in to_x.mean(dim=1)],
+        "to_exchange_ms_mean": round(float(to_x.mean()), 4),
+        "to_exchange_ms_slowest_rank_per_step": round(float(to_x.max(dim=0).values.mean()), 4),
+        "imbalance_ms": round(float((to_x.max(dim=0).values - to_x.mean(dim=0)).mean()), 4),
+        "exchange_kernel_ms_per_rank": [round(float(v), 4) for v in x.mean(dim=1)],
+        "exchange_ms": round(pure, 4),
+        "nvlink_bytes_in_per_rank": int(b_in), "nvlink_bytes_out_per_rank": int(b_out),
+        "gbs_in": round(b_in / (pure * 1e-3) / 1e9, 1), "gbs_out": round(b_out / (pure * 1e-3) / 1e9, 1),
+        "note": "exchange_ms = mean over steps of the minimum over ranks of the exchange kernel's duration (the last "
+                "rank to arrive does not wait); imbalance_ms = mean over steps of (slowest rank's time to the exchange - "
+                "mean over ranks): the part of a synchronous step that no exchange kernel can remove",
+    }
 
 
 def _checksum64(t):

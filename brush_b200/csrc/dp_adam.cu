@@ -14,6 +14,8 @@
 // Cross-GPU ordering uses two flag barriers in peer memory (release/acquire at system scope): "my gradients are
 // complete" before the first peer load, and "I have finished reading your gradients and writing your parameters"
 // before the kernel retires.
+#include <cstdlib>
+
 #include "internal.h"
 #include "peer.cuh"
 
@@ -34,7 +36,7 @@ __device__ __forceinline__ float adam_elem(float p, float g, float& m, float& v,
     return adam_update_value(p, g, m, v, lr, L.beta1, L.beta2, L.eps, L.inv_bc1, L.inv_bc2, L.grad_scale);
 }
 
-template <bool MM_LD, bool MM_ST>
+template <bool MM_LD, bool MM_ST, int U>
 __global__ void __launch_bounds__(256)
 dp_adam_kernel(const __grid_constant__ DpLaunch L) {
     const int world = L.world, rank = L.rank;
@@ -57,10 +59,9 @@ dp_adam_kernel(const __grid_constant__ DpLaunch L) {
         // owned slice [b4, e4) in units of float4 (segment offsets and counts are multiples of 4 floats)
         const uint64_t n4 = sg.count / 4;
         const uint64_t b4 = n4 * (uint64_t)rank / (uint64_t)world, e4 = n4 * (uint64_t)(rank + 1) / (uint64_t)world;
-        // two float4 per thread per iteration, all loads issued before any use: NVLink round trips are ~2 us, so the
+        // U float4 per thread per iteration, all loads issued before any use: NVLink round trips are ~2 us, so the
         // bytes in flight per SM decide the achieved bandwidth
-        for (uint64_t j = b4 + gid; j < e4; j += 2 * stride) {
-            constexpr int U = 2;
+        for (uint64_t j = b4 + gid; j < e4; j += U * stride) {
             float4 g[U], p[U], m[U], v[U];
             bool ok[U];
 #pragma unroll
@@ -153,12 +154,31 @@ void launch_dp_adam(const DpLaunch& L, cudaStream_t st) {
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     }
-    const int blocks = sms * (L.ctas_per_sm > 0 ? L.ctas_per_sm : 6);
+    int blocks = sms * (L.ctas_per_sm > 0 ? L.ctas_per_sm : 6);
+    // BRUSH_DP_SIDE_BLOCKS: grid of the side-lane (overlapped SH) launch, for A/B measurements of its SM footprint
+    static const int env_side_blocks = [] {
+        const char* e = getenv("BRUSH_DP_SIDE_BLOCKS");
+        return e ? atoi(e) : 0;
+    }();
+    if (L.lane == 1 && env_side_blocks > 0) blocks = env_side_blocks;
     const bool mm_ld = L.src_mc != nullptr, mm_st = L.dst_mc != nullptr;
-    if (mm_ld && mm_st) dp_adam_kernel<true, true><<<blocks, 256, 0, st>>>(L);
-    else if (mm_ld) dp_adam_kernel<true, false><<<blocks, 256, 0, st>>>(L);
-    else if (mm_st) dp_adam_kernel<false, true><<<blocks, 256, 0, st>>>(L);
-    else dp_adam_kernel<false, false><<<blocks, 256, 0, st>>>(L);
+    // float4s in flight per thread.  BRUSH_DP_U=2|4|8 overrides (A/B measurements).
+    static const int env_u = [] {
+        const char* e = getenv("BRUSH_DP_U");
+        return e ? atoi(e) : 0;
+    }();
+    const int u = env_u ? env_u : 2;
+#define DP_LAUNCH(LD, ST)                                                             \
+    do {                                                                              \
+        if (u >= 8) dp_adam_kernel<LD, ST, 8><<<blocks, 256, 0, st>>>(L);             \
+        else if (u >= 4) dp_adam_kernel<LD, ST, 4><<<blocks, 256, 0, st>>>(L);        \
+        else dp_adam_kernel<LD, ST, 2><<<blocks, 256, 0, st>>>(L);                    \
+    } while (0)
+    if (mm_ld && mm_st) DP_LAUNCH(true, true);
+    else if (mm_ld) DP_LAUNCH(true, false);
+    else if (mm_st) DP_LAUNCH(false, true);
+    else DP_LAUNCH(false, false);
+#undef DP_LAUNCH
 }
 
 }  // namespace brush

@@ -274,7 +274,9 @@ __device__ __forceinline__ uint32_t composite_forward(uint32_t list_addr, uint32
                                                       float& pr, float& pg, float& pb, uint32_t& groups_walked) {
     uint32_t final_a = NO_CONTRIBUTOR;
     for (uint32_t i = 0; i < n_list; i += LIST_PAD) {
+#ifndef BRUSH_COUNT_SLOW
         if (COUNT) groups_walked++;
+#endif
         const uint4 a4 = lds128u(list_addr + 4u * i);
         const uint32_t aa[4] = {a4.x, a4.y, a4.z, a4.w};
         const bool live0 = T > 0.0f;
@@ -306,6 +308,9 @@ __device__ __forceinline__ uint32_t composite_forward(uint32_t list_addr, uint32
             T = Tj[4];
             continue;
         }
+#ifdef BRUSH_COUNT_SLOW  // experiment build: count the groups that take the stop-test path instead
+        if (COUNT) groups_walked++;
+#endif
 #pragma unroll
         for (int j = 0; j < 4; j++) {  // some pixel finishes in this group (at most 32 times per warp and tile)
             const bool live = act[j] && T > 0.0f;
