@@ -205,6 +205,8 @@ def run_ours(args):
     splats = Splats(t(sc.means), t(sc.sh_coeffs), t(sc.quats), t(sc.raw_opacity), t(sc.log_scales))
     cams = view_cameras(W, H)
     ctx = get_context(dev)
+    if args.sort_mode == "fused64":
+        ctx.set_sort_mode(True)
     # Targets = the scene's own render of each view; training starts from perturbed colours and opacities.  The
     # loss gradient is dense and non-zero, but its only consistent direction is back towards the scene, so the
     # workload (visible splats, intersections, pairs) stays what BASELINE.json names for the whole run.  (Noise
@@ -485,6 +487,7 @@ def run_ours(args):
                                f"(reference default), {'fused Adam' if not args.no_optim else 'no optimizer'}, refine "
                                f"statistics accumulated every step (warmup_steps = 0), {exchange_desc}",
                    "num_visible": V, "num_intersections": I, "views": N_VIEWS, "isect_capacity": args.capacity,
+                   "sort_mode": args.sort_mode,
                    "l2": "inputs larger than L2 (236 MB of parameters + 472 MB of Adam moments per step vs 126 MB L2)"},
         "e2e": {"value": round(world * 1000.0 / ms_e2e_step, 3), "unit": UNIT, "ms_per_step": round(ms_e2e_step, 4),
                 "h2d_bytes_per_step": int(gt_host[0].numel() * gt_host.element_size() + 112), "d2h_bytes_per_step": 4},
@@ -789,6 +792,9 @@ def main():
     ap.add_argument("--capacity", type=int, default=ISECT_CAPACITY)
     ap.add_argument("--no-optim", action="store_true", help="skip Adam (pure fwd+bwd, the reference bench shape)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sort-mode", choices=["two-stage", "fused64"], default="two-stage",
+                    help="tile sort: depth sort then stable 32-bit tile-id sort (default), or ONE sort on the fused "
+                         "64-bit (tile | depth) key as render.rs:227-237 names it; identical output (A/B)")
     ap.add_argument("--profile-step", action="store_true",
                     help="run the warm-up, then ONE step between cudaProfilerStart/Stop and exit (for ncu "
                          "--profile-from-start off); prints no bench line")

@@ -4,6 +4,7 @@
 //   rasterize_backward == crates/brush-render/src/shaders/rasterize_backwards.wgsl:140-304
 // FP32/MUFU-bound stages: compiled with FMA contraction on and ex2.approx for exp(-sigma); parity is
 // the 1e-5 absolute image tolerance / 1e-3 relative gradient tolerance, not bit equality.
+#include <cstdlib>
 #include <type_traits>
 
 #include "internal.h"
@@ -77,8 +78,13 @@ void launch_tile_bins(const uint32_t* sorted_tile_ids, const uint64_t* sorted_ke
 // ld.shared so the inner loops carry one 32-bit address register and no generic->shared conversions).
 constexpr uint32_t SM_SLOTS = TILE_SIZE + 1;          // slot 256 is a dummy splat that no pixel ever sees (list padding)
 constexpr uint32_t SM_G0 = 0;                         // float4[257]: x, y, A, B
-constexpr uint32_t SM_G1 = SM_G0 + 16 * SM_SLOTS;     // float4[257]: C, L, opacity, compact gid (bits)
-constexpr uint32_t SM_COL = SM_G1 + 16 * SM_SLOTS;    // float4[257]: r, g, b, mask of the 8x4 blocks the splat reaches
+// The shared-memory data pipe is what the backward compositor runs into (ncu: l1tex data-pipe wavefronts 85 % of peak,
+// short-scoreboard the top stall) and the second limiter of the forward (62 %); a warp-uniform LDS.128 costs two
+// wavefronts, an LDS.64 one.  So each kernel lays a splat out such that its inner loop loads no word it does not use:
+//   forward  (BWD = false): G1 = C, L, opacity, tag          COL = r, g, b, mask      loop: G0.xyzw, G1.xy, COL.xyzw (5 wavefronts)
+//   backward (BWD = true):  G1 = C, L, opacity, r            COL = g, b, mask, tag    loop: G0.xyzw, G1.xyzw, COL.xy (5, was 6)
+constexpr uint32_t SM_G1 = SM_G0 + 16 * SM_SLOTS;     // float4[257]
+constexpr uint32_t SM_COL = SM_G1 + 16 * SM_SLOTS;    // float4[257]
 constexpr uint32_t SM_LIST = SM_COL + 16 * SM_SLOTS;  // u16[8][260]: per warp, LOW HALVES of the shared-window addresses of the survivors' G0 entries
 constexpr uint32_t LIST_PAD = 4;                      // lists are padded with the dummy slot to a multiple of 4
 constexpr uint32_t LIST_SLACK = 4;                    // entries past the padding that may be read (never used) by a load-ahead
@@ -87,6 +93,12 @@ constexpr uint32_t SM_BYTES = SM_LIST + LIST_STRIDE * (TILE_SIZE / 32);
 // The forward has shared memory to spare and keeps full 32-bit entries (no PRMT per entry).
 constexpr uint32_t LIST_STRIDE32 = 4 * (TILE_SIZE + LIST_PAD);
 constexpr uint32_t SM_BYTES_FWD = SM_LIST + LIST_STRIDE32 * (TILE_SIZE / 32);
+
+// Packed forward: per warp, a buffer of 16 PAIRS of survivors in pair-interleaved form (see composite_forward_packed).
+constexpr uint32_t PB_PAIR = 80;                      // bytes per pair: 5 x 16
+constexpr uint32_t PB_WARP = 16 * PB_PAIR;            // 32 survivors per chunk
+constexpr uint32_t SM_PB = SM_BYTES_FWD;              // behind the forward's lists
+constexpr uint32_t SM_BYTES_FWD_PACKED = SM_PB + (TILE_SIZE / 32) * PB_WARP;
 
 constexpr uint32_t NO_CONTRIBUTOR = 0xffffffffu;      // "no splat of this batch contributed" (never a shared-window address)
 
@@ -122,6 +134,16 @@ __device__ __forceinline__ float4 lds128_ro(uint32_t a, uint32_t token) {
 __device__ __forceinline__ uint2 lds64u_ro(uint32_t a, uint32_t token) {
     uint2 v;
     asm("ld.shared.v2.u32 {%0, %1}, [%2]; // %3" : "=r"(v.x), "=r"(v.y) : "r"(a), "r"(token));
+    return v;
+}
+__device__ __forceinline__ float2 lds64(uint32_t a) {
+    float2 v;
+    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ float2 lds64_ro(uint32_t a, uint32_t token) {
+    float2 v;
+    asm("ld.shared.v2.f32 {%0, %1}, [%2]; // %3" : "=f"(v.x), "=f"(v.y) : "r"(a), "r"(token));
     return v;
 }
 __device__ __forceinline__ uint32_t lds_u32(uint32_t a) {
@@ -203,6 +225,7 @@ __device__ __forceinline__ bool ellipse_reaches_block(const CullForm& f, float r
 // every pixel, in exact arithmetic and under rounding).  A batch of plain splats is composited by the loop variant
 // without the `sigma < 0` test and the clamp: two instructions per pair fewer, the same bits.
 constexpr float PLAIN_MAX_OPAC = 0.989f;
+template <bool BWD>
 __device__ __forceinline__ bool stage_splat(uint32_t sbase, uint32_t slot, const float* __restrict__ projected,
                                             uint32_t cg, uint32_t tag, float tile_px, float tile_py) {
     const float* p = projected + (size_t)cg * 9;
@@ -214,7 +237,8 @@ __device__ __forceinline__ bool stage_splat(uint32_t sbase, uint32_t slot, const
     f.L = __log2f(opac);
     f.h1 = -f.B * rcp_approx(2.0f * f.C); f.h2 = -f.B * rcp_approx(2.0f * f.A);
     sts128(sbase + SM_G0 + slot * 16, make_float4(x, y, f.A, f.B));
-    sts128(sbase + SM_G1 + slot * 16, make_float4(f.C, f.L, opac, __uint_as_float(tag)));
+    const float col_r = __ldg(p + 5);
+    sts128(sbase + SM_G1 + slot * 16, make_float4(f.C, f.L, opac, BWD ? col_r : __uint_as_float(tag)));
     // first stage: bounding box of the region.  sigma(d) <= t = ln(255 opac)  =>  |dx| <= sqrt(2 t cyy / det),
     // |dy| <= sqrt(2 t cxx / det); slightly inflated so that rounding can only keep a splat, never drop one.
     const float t = __logf(255.0f * opac) + 1e-3f;
@@ -233,7 +257,8 @@ __device__ __forceinline__ bool stage_splat(uint32_t sbase, uint32_t slot, const
         if (hit) hit = ellipse_reaches_block(f, rx0, rx1, ry0, ry1);
         mask |= (hit ? 1u : 0u) << b;
     }
-    sts128(sbase + SM_COL + slot * 16, make_float4(__ldg(p + 5), __ldg(p + 6), __ldg(p + 7), __uint_as_float(mask)));
+    if (BWD) sts128(sbase + SM_COL + slot * 16, make_float4(__ldg(p + 6), __ldg(p + 7), __uint_as_float(mask), __uint_as_float(tag)));
+    else sts128(sbase + SM_COL + slot * 16, make_float4(col_r, __ldg(p + 6), __ldg(p + 7), __uint_as_float(mask)));
     // |cxy| <= 0.99 sqrt(cxx cyy): sigma >= 0.01 * (cxx dx^2 + cyy dy^2) / 2, five orders above its rounding error
     return opac <= PLAIN_MAX_OPAC && cxx > 0.0f && cyy > 0.0f && cxy * cxy <= 0.98f * (cxx * cyy);
 }
@@ -242,14 +267,14 @@ __device__ __forceinline__ bool stage_splat(uint32_t sbase, uint32_t slot, const
 // addresses of the survivors' G0 entries are appended, in depth order, to the warp's list, which is then padded
 // with the dummy slot to a multiple of LIST_PAD.  Returns the list length (without padding).
 // Only slots in [t_lo, t_max) take part.
-template <bool LIST16>
+template <bool LIST16>  // LIST16 <=> the backward kernel (mask in COL.z there, COL.w in the forward)
 __device__ __forceinline__ uint32_t cull_to_list(uint32_t sbase, uint32_t list_addr, uint32_t lane, uint32_t warp,
                                                  uint32_t t_lo, uint32_t t_max) {
     uint32_t n_list = 0;
     for (uint32_t c0 = t_lo & ~31u; c0 < t_max; c0 += 32) {
         const uint32_t mine = c0 + lane;
         bool hit = false;
-        if (mine >= t_lo && mine < t_max) hit = (lds_u32(sbase + SM_COL + mine * 16u + 12u) >> warp) & 1u;
+        if (mine >= t_lo && mine < t_max) hit = (lds_u32(sbase + SM_COL + mine * 16u + (LIST16 ? 8u : 12u)) >> warp) & 1u;
         const uint32_t mask = __ballot_sync(0xffffffffu, hit);
         if (hit) {
             const uint32_t pos = n_list + __popc(mask & ((1u << lane) - 1u));
@@ -289,7 +314,7 @@ __device__ __forceinline__ uint32_t composite_forward(uint32_t list_addr, uint32
 #pragma unroll
         for (int j = 0; j < 4; j++) {
             const float4 g0 = lds128(aa[j] + SM_G0);
-            const float4 g1 = lds128(aa[j] + SM_G1);
+            const float2 g1 = lds64(aa[j] + SM_G1);  // C, L: the loop needs nothing else of G1
             const float dx = g0.x - pcx, dy = g0.y - pcy;
             const float sp = fmaf(g1.x * dy, dy, fmaf(g0.w, dy, g0.z * dx) * dx);  // -sigma * log2(e)
             const float q = sp + g1.y;                                              // log2(opac * exp(-sigma))
@@ -329,19 +354,129 @@ __device__ __forceinline__ uint32_t composite_forward(uint32_t list_addr, uint32
     return final_a;
 }
 
+// ---- packed FP32 (sm_100 FFMA2 / FMUL2 / FADD2): two IEEE-rn operations per issued instruction ----
+typedef unsigned long long f2;
+__device__ __forceinline__ f2 pack2(float lo, float hi) { f2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void unpack2(f2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) { f2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) { f2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2 add2(f2 a, f2 b) { f2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2 sub2(f2 a, f2 b) { f2 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ void lds128_f2(uint32_t a, f2& lo, f2& hi) {
+    asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(lo), "=l"(hi) : "r"(a));
+}
+
+// The same compositing loop with the per-pair geometry on packed FP32: a lane still owns one pixel, but it evaluates
+// TWO survivors per instruction.  Survivor lists are arbitrary subsets of the staged batch, so each warp first repacks
+// its next 32 survivors (one per lane) into a pair-interleaved buffer -- per pair (x1,x2,y1,y2 | A1,A2,B1,B2 |
+// C1,C2,L1,L2 | r1,r2,g1,g2 | b1,b2,addr1,addr2) -- whose 16-byte loads are then operand pairs as they stand.
+// Operation order per pixel and splat is the scalar loop's (packed operations round each half like the scalar ones),
+// so the image is bit-identical to composite_forward's.
+template <bool GENERAL, bool COUNT>
+__device__ __forceinline__ uint32_t composite_forward_packed(uint32_t list_addr, uint32_t pb, uint32_t dummy_addr, uint32_t lane,
+                                                             uint32_t n_list, float pcx, float pcy, float& T, float& pr,
+                                                             float& pg, float& pb_, uint32_t& groups_walked) {
+    uint32_t final_a = NO_CONTRIBUTOR;
+    const f2 PCX = pack2(pcx, pcx), PCY = pack2(pcy, pcy), ONE = pack2(1.0f, 1.0f);
+    const uint32_t my = pb + (lane >> 1) * PB_PAIR + (lane & 1u) * 4u;
+    for (uint32_t c0 = 0; c0 < n_list; c0 += 32) {
+        {   // repack: lane l takes survivor c0 + l (the dummy splat past the end of the list)
+            const uint32_t a = c0 + lane < n_list ? lds_u32(list_addr + 4u * (c0 + lane)) : dummy_addr;
+            const float4 g0 = lds128(a + SM_G0), g1 = lds128(a + SM_G1), col = lds128(a + SM_COL);
+            __syncwarp();  // the previous chunk has been consumed by every lane
+            sts_u32(my + 0, __float_as_uint(g0.x)); sts_u32(my + 8, __float_as_uint(g0.y));
+            sts_u32(my + 16, __float_as_uint(g0.z)); sts_u32(my + 24, __float_as_uint(g0.w));
+            sts_u32(my + 32, __float_as_uint(g1.x)); sts_u32(my + 40, __float_as_uint(g1.y));
+            sts_u32(my + 48, __float_as_uint(col.x)); sts_u32(my + 56, __float_as_uint(col.y));
+            sts_u32(my + 64, __float_as_uint(col.z)); sts_u32(my + 72, a);
+            __syncwarp();
+        }
+        const uint32_t n_chunk = min(32u, n_list - c0);
+        bool done = false;
+        for (uint32_t i = 0; i < n_chunk; i += 4) {
+            if (COUNT) groups_walked++;
+            const bool live0 = T > 0.0f;
+            const float q_min = live0 ? LOG2_INV255 : __int_as_float(0x7f800000);
+            bool act[4];
+            float alpha[4], Tj[5];
+            uint32_t aa[4];
+            f2 cr[2], cg[2];
+            float cb[4];
+            Tj[0] = T;
+#pragma unroll
+            for (int h = 0; h < 2; h++) {  // two pairs per group of four survivors
+                const uint32_t pa = pb + ((i >> 1) + h) * PB_PAIR;
+                f2 X, Y, A, B, C, L, bb, ad;
+                lds128_f2(pa, X, Y);
+                lds128_f2(pa + 16, A, B);
+                lds128_f2(pa + 32, C, L);
+                lds128_f2(pa + 48, cr[h], cg[h]);
+                lds128_f2(pa + 64, bb, ad);
+                const f2 dx = sub2(X, PCX), dy = sub2(Y, PCY);
+                const f2 sp = fma2(mul2(C, dy), dy, mul2(fma2(B, dy, mul2(A, dx)), dx));  // -sigma * log2(e)
+                const f2 q = add2(sp, L);
+                float sp0, sp1, q0, q1;
+                unpack2(sp, sp0, sp1);
+                unpack2(q, q0, q1);
+                act[2 * h] = GENERAL ? (sp0 <= 0.0f && q0 >= q_min) : (q0 >= q_min);
+                act[2 * h + 1] = GENERAL ? (sp1 <= 0.0f && q1 >= q_min) : (q1 >= q_min);
+                alpha[2 * h] = act[2 * h] ? (GENERAL ? fminf(0.999f, ex2_approx(q0)) : ex2_approx(q0)) : 0.0f;
+                alpha[2 * h + 1] = act[2 * h + 1] ? (GENERAL ? fminf(0.999f, ex2_approx(q1)) : ex2_approx(q1)) : 0.0f;
+                float o0, o1;
+                unpack2(sub2(ONE, pack2(alpha[2 * h], alpha[2 * h + 1])), o0, o1);
+                Tj[2 * h + 1] = Tj[2 * h] * o0;
+                Tj[2 * h + 2] = Tj[2 * h + 1] * o1;
+                unpack2(bb, cb[2 * h], cb[2 * h + 1]);
+                float a0, a1;
+                unpack2(ad, a0, a1);
+                aa[2 * h] = __float_as_uint(a0); aa[2 * h + 1] = __float_as_uint(a1);
+            }
+            float crr[4], cgg[4];
+            unpack2(cr[0], crr[0], crr[1]); unpack2(cr[1], crr[2], crr[3]);
+            unpack2(cg[0], cgg[0], cgg[1]); unpack2(cg[1], cgg[2], cgg[3]);
+            if (!__any_sync(0xffffffffu, live0 && Tj[4] <= 1e-4f)) {
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const float fac = alpha[j] * Tj[j];
+                    pr = fmaf(crr[j], fac, pr); pg = fmaf(cgg[j], fac, pg); pb_ = fmaf(cb[j], fac, pb_);
+                    final_a = act[j] ? aa[j] : final_a;
+                }
+                T = Tj[4];
+                continue;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) {  // some pixel finishes in this group (at most 32 times per warp and tile)
+                const bool live = act[j] && T > 0.0f;
+                const float next_T = T * (1.0f - alpha[j]);
+                const bool stop = live && next_T <= 1e-4f;
+                const bool contrib = live && !(next_T <= 1e-4f);
+                const float fac = contrib ? alpha[j] * T : 0.0f;
+                pr = fmaf(crr[j], fac, pr); pg = fmaf(cgg[j], fac, pg); pb_ = fmaf(cb[j], fac, pb_);
+                T = contrib ? next_T : T;
+                T = stop ? -T : T;
+                final_a = contrib ? aa[j] : final_a;
+            }
+            if (__all_sync(0xffffffffu, T <= 0.0f)) { done = true; break; }
+        }
+        if (done) break;
+    }
+    return final_a;
+}
+
 // COUNT: the diagnostic build of the kernel that also counts the (pixel, splat) pairs it evaluates (32 lanes x the
 // list entries each warp walks, padding included) into *pair_counter; launched only while brush_ctx_set_pair_counting
 // is on (bench.py's "pairs_evaluated", outside every timed region).
-template <bool RASTER_U32, bool COUNT>
+template <bool RASTER_U32, bool COUNT, bool PACKED>
 __global__ void __launch_bounds__(TILE_SIZE, 5)  // 48 registers: five CTAs per SM (measured best of 4 / 5 / 6)
 rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ compact_gid_from_isect,
                  const uint32_t* __restrict__ tile_bins, const float* __restrict__ projected,
                  void* __restrict__ out_img, uint32_t* __restrict__ final_index,
                  unsigned long long* __restrict__ pair_counter) {
-    __shared__ __align__(16) unsigned char smem[SM_BYTES_FWD];
+    __shared__ __align__(16) unsigned char smem[PACKED ? SM_BYTES_FWD_PACKED : SM_BYTES_FWD];
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(smem);
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t list_addr = sbase + SM_LIST + warp * LIST_STRIDE32;
+    const uint32_t pb_addr = sbase + SM_PB + warp * PB_WARP;
     const uint32_t tile_id = blockIdx.x + blockIdx.y * cam.tiles_x;
     const uint32_t bx0 = blockIdx.x * TILE_WIDTH + (warp & 1u) * 8u, by0 = blockIdx.y * TILE_WIDTH + (warp >> 1) * 4u;
     const uint32_t px = bx0 + (lane & 7u), py = by0 + (lane >> 3);
@@ -369,7 +504,7 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
         bool odd = false;
         if (tid < remaining) {
             const uint32_t cg = __ldg(compact_gid_from_isect + batch_start + tid);
-            odd = !stage_splat(sbase, tid, projected, cg, cg, (float)(blockIdx.x * TILE_WIDTH), (float)(blockIdx.y * TILE_WIDTH));
+            odd = !stage_splat<false>(sbase, tid, projected, cg, cg, (float)(blockIdx.x * TILE_WIDTH), (float)(blockIdx.y * TILE_WIDTH));
         }
         const int any_odd = __syncthreads_or(odd);
         if (__all_sync(0xffffffffu, T <= 0.0f)) continue;
@@ -382,8 +517,13 @@ rasterize_kernel(const __grid_constant__ Cam cam, const uint32_t* __restrict__ c
         // has no per-splat compare / select on the compositing state: the ALU pipe (compares, selects, min)
         // was this kernel's limiter (ncu: 61% ALU at 78% issue).  Same arithmetic in both paths, so the result
         // does not depend on which one ran.
-        const uint32_t final_a = any_odd ? composite_forward<true, COUNT>(list_addr, n_list, pcx, pcy, T, pr, pg, pb, groups_walked)
-                                         : composite_forward<false, COUNT>(list_addr, n_list, pcx, pcy, T, pr, pg, pb, groups_walked);
+        uint32_t final_a;
+        if (PACKED)
+            final_a = any_odd ? composite_forward_packed<true, COUNT>(list_addr, pb_addr, sbase + TILE_SIZE * 16u, lane, n_list, pcx, pcy, T, pr, pg, pb, groups_walked)
+                              : composite_forward_packed<false, COUNT>(list_addr, pb_addr, sbase + TILE_SIZE * 16u, lane, n_list, pcx, pcy, T, pr, pg, pb, groups_walked);
+        else
+            final_a = any_odd ? composite_forward<true, COUNT>(list_addr, n_list, pcx, pcy, T, pr, pg, pb, groups_walked)
+                              : composite_forward<false, COUNT>(list_addr, n_list, pcx, pcy, T, pr, pg, pb, groups_walked);
         if (final_a != NO_CONTRIBUTOR) final_idx = batch_start + ((final_a - sbase) >> 4);
     }
     if (COUNT && lane == 0 && groups_walked) atomicAdd(pair_counter, (unsigned long long)groups_walked * (LIST_PAD * 32u));
@@ -410,10 +550,24 @@ void launch_rasterize(const Cam& cam, const uint32_t* compact_gid_from_isect, co
     dim3 grid(cam.tiles_x, cam.tiles_y);
     g_launch_count++;
 #define RK_ARGS cam, compact_gid_from_isect, tile_bins, projected, out_img, final_index, pair_counter
-    if (raster_u32 && pair_counter) launch_k(rasterize_kernel<true, true>, grid, TILE_SIZE, 0, st, RK_ARGS);
-    else if (raster_u32) launch_k(rasterize_kernel<true, false>, grid, TILE_SIZE, 0, st, RK_ARGS);
-    else if (pair_counter) launch_k(rasterize_kernel<false, true>, grid, TILE_SIZE, 0, st, RK_ARGS);
-    else launch_k(rasterize_kernel<false, false>, grid, TILE_SIZE, 0, st, RK_ARGS);
+    // BRUSH_RASTER_PACKED=1: the packed-FP32 compositing loop (A/B).  Same bits, 24 % fewer issued instructions per
+    // group -- and the same 0.377 ms at config 4 (FFMA2 holds the FP32 pipe about as long as the two scalar
+    // instructions it replaces), so the scalar loop stays the default.
+    static const bool packed = [] {
+        const char* e = getenv("BRUSH_RASTER_PACKED");
+        return e ? atoi(e) != 0 : false;
+    }();
+    if (packed) {
+        if (raster_u32 && pair_counter) launch_k(rasterize_kernel<true, true, true>, grid, TILE_SIZE, 0, st, RK_ARGS);
+        else if (raster_u32) launch_k(rasterize_kernel<true, false, true>, grid, TILE_SIZE, 0, st, RK_ARGS);
+        else if (pair_counter) launch_k(rasterize_kernel<false, true, true>, grid, TILE_SIZE, 0, st, RK_ARGS);
+        else launch_k(rasterize_kernel<false, false, true>, grid, TILE_SIZE, 0, st, RK_ARGS);
+    } else {
+        if (raster_u32 && pair_counter) launch_k(rasterize_kernel<true, true, false>, grid, TILE_SIZE, 0, st, RK_ARGS);
+        else if (raster_u32) launch_k(rasterize_kernel<true, false, false>, grid, TILE_SIZE, 0, st, RK_ARGS);
+        else if (pair_counter) launch_k(rasterize_kernel<false, true, false>, grid, TILE_SIZE, 0, st, RK_ARGS);
+        else launch_k(rasterize_kernel<false, false, false>, grid, TILE_SIZE, 0, st, RK_ARGS);
+    }
 #undef RK_ARGS
 }
 
@@ -440,7 +594,7 @@ constexpr uint32_t BW_ROWS = 16;             // rows per warp; phase 2 gives eac
 constexpr uint32_t BW_GROUP = 4;             // survivors examined per phase-1 iteration (independent geometry => ILP)
 constexpr uint32_t BW_PAIR = SM_BYTES;
 constexpr uint32_t BW_PAIR_WARP = BW_ROWS * BW_ROW;
-constexpr uint32_t BW_PIX = BW_PAIR + (TILE_SIZE / 32u) * BW_PAIR_WARP;  // per warp float4[32]: v_out of its pixels
+constexpr uint32_t BW_PIX = BW_PAIR + (TILE_SIZE / 32u) * BW_PAIR_WARP;  // per warp float[3][32]: v_out.r / .g / .b of its pixels (512 B stride)
 constexpr uint32_t BW_BYTES = BW_PIX + (TILE_SIZE / 32u) * 512u;
 
 __device__ __forceinline__ void sts64(uint32_t a, float x, float y) {
@@ -463,9 +617,10 @@ __device__ __forceinline__ void flush_rows(uint32_t dummy_addr, uint32_t pair_ad
     bool valid = r_idx < k;
     const uint32_t a = !valid ? dummy_addr : __byte_perm(lds_u16(entries + 2u * r_idx), dummy_addr, 0x7610);
     const float4 g0 = lds128(a + SM_G0);  // x, y, A, B
-    const float4 g1 = lds128(a + SM_G1);  // C, L, opacity, compact gid
+    const float4 g1 = lds128(a + SM_G1);  // C, L, opacity, r
+    const uint32_t gid = lds_u32(a + SM_COL + 12u);  // global splat id (the row of its gradient accumulator)
     const uint32_t row = pair_addr + r_idx * BW_ROW + half * 128u;
-    const uint32_t pix = pix_addr + half * 256u;
+    const uint32_t pix = pix_addr + half * 64u;  // three planes of 32 floats: v_out.r, .g, .b of the warp's pixels
     const float by_h = by + (float)(2u * half);
     // Moments of va about the splat centre.  Along a pixel row dy is constant, so only the x-moments
     // (1, dx, dx^2) are accumulated per pixel; dy and dy^2 are applied once per row.
@@ -476,21 +631,20 @@ __device__ __forceinline__ void flush_rows(uint32_t dummy_addr, uint32_t pair_ad
     for (int py = 0; py < 2; py++) {
         float a0 = 0.f, a1 = 0.f, a2 = 0.f;
 #pragma unroll
-        for (int kx = 0; kx < 8; kx += 2) {
+        for (int kx = 0; kx < 8; kx += 4) {
             const int p = py * 8 + kx;
-            const float4 e = lds128(row + p * 8);  // va, fac of pixels p and p+1
-            const float4 o0 = lds128(pix + p * 16), o1 = lds128(pix + p * 16 + 16);
-            {
-                const float dx = dx0 - (float)kx;
-                const float t1 = e.x * dx;
-                a0 += e.x; a1 = fmaf(e.x, dx, a1); a2 = fmaf(t1, dx, a2);
-                r = fmaf(e.y, o0.x, r); g = fmaf(e.y, o0.y, g); b = fmaf(e.y, o0.z, b);
-            }
-            {
-                const float dx = dx0 - (float)(kx + 1);
-                const float t1 = e.z * dx;
-                a0 += e.z; a1 = fmaf(e.z, dx, a1); a2 = fmaf(t1, dx, a2);
-                r = fmaf(e.w, o1.x, r); g = fmaf(e.w, o1.y, g); b = fmaf(e.w, o1.z, b);
+            // four pixels per step: their (va, fac) pairs and ONE 16-byte load per colour plane (a float4 v_out per
+            // pixel cost four of these wavefront-bound loads per four pixels and carried an unused alpha)
+            const float4 e0 = lds128(row + p * 8), e1 = lds128(row + p * 8 + 16);
+            const float4 vr = lds128(pix + p * 4), vg = lds128(pix + 128u + p * 4), vb = lds128(pix + 256u + p * 4);
+            const float va_[4] = {e0.x, e0.z, e1.x, e1.z}, fac_[4] = {e0.y, e0.w, e1.y, e1.w};
+            const float cr_[4] = {vr.x, vr.y, vr.z, vr.w}, cg_[4] = {vg.x, vg.y, vg.z, vg.w}, cb_[4] = {vb.x, vb.y, vb.z, vb.w};
+#pragma unroll
+            for (int u = 0; u < 4; u++) {  // same pixel order as before: the sums are the same sums
+                const float dx = dx0 - (float)(kx + u);
+                const float t1 = va_[u] * dx;
+                a0 += va_[u]; a1 = fmaf(va_[u], dx, a1); a2 = fmaf(t1, dx, a2);
+                r = fmaf(fac_[u], cr_[u], r); g = fmaf(fac_[u], cg_[u], g); b = fmaf(fac_[u], cb_[u], b);
             }
         }
         m0[py] = a0; m1[py] = a1; m2[py] = a2;
@@ -508,7 +662,7 @@ __device__ __forceinline__ void flush_rows(uint32_t dummy_addr, uint32_t pair_ad
     if (valid) {
         // v_sigma = -opac*va; conic = -ln2 * (2A, B, 2C) in log2 form
         const float opac = g1.z, w = LN2 * opac;
-        float* dst = v_projected + (size_t)__float_as_uint(g1.w) * VP_STRIDE;
+        float* dst = v_projected + (size_t)gid * VP_STRIDE;
         if (half == 0) {
             red_add_v4(dst, w * fmaf(2.0f * g0.z, sx, g0.w * sy), w * fmaf(g0.w, sx, 2.0f * g1.x * sy),
                        -0.5f * opac * sxx, -opac * sxy);
@@ -558,7 +712,9 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
         final_isect = __ldg(final_index + pix_id);
         v_out = __ldg(reinterpret_cast<const float4*>(v_out_img) + pix_id);
     }
-    sts128(pix_addr + lane * 16u, v_out);
+    sts_u32(pix_addr + lane * 4u, __float_as_uint(v_out.x));  // colour planes for phase 2 (flush_rows)
+    sts_u32(pix_addr + 128u + lane * 4u, __float_as_uint(v_out.y));
+    sts_u32(pix_addr + 256u + lane * 4u, __float_as_uint(v_out.z));
     // Running state of the pixel (rasterize_backwards.wgsl:194-272 keeps T and the colour `buffer` behind the
     // current splat): v_alpha = ra * (dot(c, v_rgb) * T_before - dot(buffer, v_rgb) + T_final * v_a), so only
     // D = T_final * v_a - dot(buffer, v_rgb) is carried, not the three buffer channels.
@@ -587,7 +743,7 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
         bool odd = false;
         if (tid >= t_lo_tile && tid < remaining) {  // gradient rows are indexed by GLOBAL splat id, so the per-splat backward is coalesced
             const uint32_t cg = __ldg(compact_gid_from_isect + batch_end - 1u - tid);
-            odd = !stage_splat(sbase, tid, projected, cg, __ldg(global_from_compact + cg), (float)(tile_x * TILE_WIDTH),
+            odd = !stage_splat<true>(sbase, tid, projected, cg, __ldg(global_from_compact + cg), (float)(tile_x * TILE_WIDTH),
                                (float)(tile_y * TILE_WIDTH));
         }
         const int any_odd = __syncthreads_or(odd);
@@ -612,7 +768,7 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
                     if (g + BW_GROUP * u >= n_list) break;
                     const uint32_t aa[BW_GROUP] = {an[0], an[1], an[2], an[3]};
                     list_load4(list_addr + 2u * (g + BW_GROUP * (u + 1u)), sbase, an, token);
-                    float alpha[BW_GROUP], ra[BW_GROUP], visra[BW_GROUP];
+                    float alpha[BW_GROUP], ra[BW_GROUP], visra[BW_GROUP], col_r[BW_GROUP];
     #pragma unroll
                     for (int j = 0; j < (int)BW_GROUP; j++) {
                         const float4 g0 = lds128_ro(aa[j] + SM_G0, token);
@@ -627,11 +783,12 @@ rasterize_backward_kernel(const __grid_constant__ Cam cam, const uint32_t* __res
                         alpha[j] = GENERAL ? fminf(0.99f, g1.z * vis) : g1.z * vis;  // clamp 0.99 here, 0.999 forward (reference quirk)
                         ra[j] = rcp_approx(1.0f - alpha[j]);
                         visra[j] = vis * ra[j];
+                        col_r[j] = g1.w;
                     }
     #pragma unroll
                     for (int j = 0; j < (int)BW_GROUP; j++) {
-                        const float4 c = lds128_ro(aa[j] + SM_COL, token);
-                        const float uu = fmaf(c.z, v_out.z, fmaf(c.y, v_out.y, c.x * v_out.x));
+                        const float2 gb = lds64_ro(aa[j] + SM_COL, token);  // g, b (r came with G1)
+                        const float uu = fmaf(gb.y, v_out.z, fmaf(gb.x, v_out.y, col_r[j] * v_out.x));
                         const float va = visra[j] * fmaf(uu, T, D);
                         T *= ra[j];
                         const float fac = alpha[j] * T;
