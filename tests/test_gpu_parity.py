@@ -329,6 +329,44 @@ def test_deferred_colours_forward_is_bit_identical():
     assert torch.equal(img2, img3) and not torch.equal(img2, img0)
 
 
+def test_packed_forward_is_bit_identical():
+    """BRUSH_RASTER_PACKED=1 selects the packed-FP32 compositing loop of the forward rasterizer (two survivors per
+    FFMA2 / FMUL2 / FADD2; an opt-in A/B, profiles/r2p_rasterizer_experiments.md).  It performs the scalar loop's
+    operations in the scalar loop's order, so image and final_index must be the same bits -- f32 and packed-u32 output,
+    many batches per tile included.  The switch is read once per process: two child processes hash their outputs."""
+    import os
+    import subprocess
+    import sys
+
+    code = r"""
+import hashlib, sys
+import numpy as np, torch
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[1] + "/tests")
+from helpers import reference_camera
+from brush_b200 import make_uniforms, render_forward, scene
+h = lambda x: hashlib.sha256(x.contiguous().cpu().numpy().tobytes()).hexdigest()
+for n, w, hh, deg, seed in ((30_000, 320, 200, 3, 21), (6_000, 48, 32, 1, 22)):
+    sc = scene.make_scene(n, w, hh, deg, seed)
+    vm, focal, center = reference_camera(w, hh)
+    u = make_uniforms(vm, focal, (w, hh), center)
+    t = lambda a: torch.as_tensor(np.ascontiguousarray(a), device="cuda:0")
+    args = [t(sc.means), t(sc.log_scales), t(sc.quats), t(sc.sh_coeffs), t(sc.raw_opacity)]
+    img, aux = render_forward(u, *args, False)
+    img8, _ = render_forward(u, *args, True)
+    torch.cuda.synchronize()
+    print(n, aux.read_num_intersections(), h(img), h(aux.final_index), h(img8))
+"""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for packed in ("0", "1"):
+        env = dict(os.environ, BRUSH_RASTER_PACKED=packed)
+        r = subprocess.run([sys.executable, "-c", code, root], env=env, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append(r.stdout.strip().splitlines())
+    assert len(outs[0]) == 2 and outs[0] == outs[1], (outs[0], outs[1])
+    assert int(outs[0][1].split()[1]) > 48 * 32 // 256 * 600  # the small image holds several batches per tile
+
+
 def test_raster_u32(oracle):
     """Packed RGBA8 output (rasterize.wgsl:106-109): equal up to 1 LSB per channel (exp rounding)."""
     from brush_b200 import make_uniforms, render_forward, scene
