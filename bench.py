@@ -459,6 +459,12 @@ def run_ours(args):
             traffic = json.load(f).get(dom["stage"])
     except OSError:
         pass
+    limits = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "limits.json")) as f:
+            limits = json.load(f).get(dom["stage"])
+    except (OSError, ValueError):
+        pass
     if "tflops" in dom:
         roofline = {"kernel": dom["stage"], "bound": "fp32", "achieved": dom["tflops"], "peak": round(fp32_peak, 2),
                     "unit": "TFLOP/s", "frac": dom["frac_fp32"], "frac_executed": dom.get("frac_executed"),
@@ -468,6 +474,9 @@ def run_ours(args):
                     "mufu_peak_tops": round(mufu_peak_measured, 3), "frac_mufu": dom.get("frac_mufu"),
                     "pairs_reference": dom["pairs_reference"], "pairs_evaluated": dom["pairs_evaluated"],
                     "culled_pair_ratio": dom["culled_pair_ratio"],
+                    # pipe utilisations of the kernel from the committed ncu --set full capture (profiles/limits.json):
+                    # which unit binds first (for rasterize_backwards: the shared-memory data pipe, not the FP32 pipe)
+                    "ncu_limits": limits,
                     # the same kernel against the HBM roofline, in the base contract's shape
                     "hbm_view": {"bound": "hbm", "achieved": dom["gbs"], "peak": peak, "unit": "GB/s",
                                  "frac": dom["frac_hbm"], "traffic": traffic, "peak_source": peak_src},
