@@ -129,171 +129,27 @@ radix_hist_kernel(const KeyT* __restrict__ keys, const int32_t* __restrict__ n_d
 }
 
 // ---- one onesweep pass ----
+// Two kernels with ONE body (onesweep_body.inc) that differ only in their launch bounds:
+//   onesweep_kernel      100 registers, two CTAs per SM -- fastest while a pass is a single wave of tiles (its time is
+//                        then ONE tile's latency: the 1 M-key depth sort);
+//   onesweep_kernel_occ3 80 registers (no spills), three CTAs per SM -- faster as soon as a pass is many waves, where the
+//                        serial phases of a tile overlap only across CTAs (76.7 M keys: 1.94 -> 1.59 ms; 64 registers /
+//                        four CTAs spill and gain nothing more).
+// (A shared __device__ function changed the register allocation of the first: the body is textually included.)
 template <typename KeyT, int ITEMS>
 __global__ void __launch_bounds__(RS_THREADS)
 onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, KeyT* __restrict__ keys_out,
                 uint32_t* __restrict__ vals_out, const int32_t* __restrict__ n_dev, uint32_t max_n, uint32_t shift,
                 uint32_t mask, const uint32_t* __restrict__ hist, uint32_t* lb, uint32_t* ticket) {
-    constexpr int TILE = RS_THREADS * ITEMS;
-    __shared__ KeyT s_keys[TILE];
-    __shared__ uint32_t s_vals[TILE];
-    __shared__ uint32_t s_whist[RS_WARPS][RS_RADIX];
-    __shared__ uint32_t s_local_base[RS_RADIX];  // exclusive digit offsets inside the tile
-    __shared__ uint32_t s_goff[RS_RADIX];        // global destination of the tile's first key of each digit
-    __shared__ uint32_t s_scan[RS_WARPS];
-    __shared__ uint32_t s_tile;
+#include "onesweep_body.inc"
+}
 
-    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-    PDL_ENTER();
-    // The grid is sized for max_n (the count lives on the device).  CTAs beyond the tiles *n_dev needs leave at once
-    // -- no ticket, no shared-memory set-up: at 3 M intersections in a 16 M-entry buffer that is 3300 of 4096 CTAs --
-    // and the others draw tickets 0 .. tiles-1 in start order, so a tile never waits on one that has not started.
-    const uint32_t n = min((uint32_t)max(*n_dev, 0), max_n);
-    if ((uint64_t)blockIdx.x * TILE >= n) return;
-#pragma unroll
-    for (int w = 0; w < RS_WARPS; w++) s_whist[w][tid] = 0;
-    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
-    __syncthreads();
-    const uint32_t tile = s_tile;
-    const uint64_t tile_start = (uint64_t)tile * TILE;
-    const uint32_t count = (uint32_t)min((uint64_t)TILE, (uint64_t)n - tile_start);
-
-    PROF_MARK(0);
-    // global exclusive digit base = exclusive scan of this pass's histogram (thread d <-> digit d)
-    uint32_t bin_base;
-    {
-        uint32_t h = hist[tid];
-        uint32_t incl = h;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= (uint32_t)o) incl += t;
-        }
-        if (lane == 31) s_scan[warp] = incl;
-        __syncthreads();
-        uint32_t woff = 0;
-#pragma unroll
-        for (int w = 0; w < RS_WARPS; w++) woff += (w < (int)warp) ? s_scan[w] : 0u;
-        bin_base = woff + incl - h;
-    }
-
-    // warp-striped load: warp w owns [w*ITEMS*32, (w+1)*ITEMS*32), item i of lane l = chunk[i*32 + l]
-    KeyT key[ITEMS];
-    uint32_t val[ITEMS];  // loaded with the keys: a load issued at scatter time sat on the tile's critical path (1.8 us)
-    uint32_t rank[ITEMS];
-    const uint32_t chunk = warp * (ITEMS * 32);
-#pragma unroll
-    for (int i = 0; i < ITEMS; i++) {
-        uint32_t idx = chunk + i * 32 + lane;
-        key[i] = idx < count ? keys_in[tile_start + idx] : (KeyT)0;
-    }
-#pragma unroll
-    for (int i = 0; i < ITEMS; i++) {
-        uint32_t idx = chunk + i * 32 + lane;
-        val[i] = idx < count ? vals_in[tile_start + idx] : 0u;
-    }
-    PROF_MARK(1);
-    // stable per-warp multisplit: match_any groups equal digits, the group leader bumps the warp counter
-#pragma unroll
-    for (int i = 0; i < ITEMS; i++) {
-        const bool valid = chunk + i * 32 + lane < count;
-        const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
-        const uint32_t peers = match_digit(d, valid) | (1u << lane);  // an invalid lane is its own (unused) group
-        const uint32_t leader = 31 - __clz(peers);
-        uint32_t pre = 0;
-        if (valid && lane == leader) {
-            pre = s_whist[warp][d];
-            s_whist[warp][d] = pre + __popc(peers);
-        }
-        pre = __shfl_sync(0xffffffffu, pre, leader);
-        rank[i] = pre + __popc(peers & ((1u << lane) - 1u));
-        __syncwarp();
-    }
-    __syncthreads();
-
-    PROF_MARK(2);
-    // thread d: exclusive scan of digit d's count over the warps -> tile count of digit d
-    uint32_t tile_count = 0;
-#pragma unroll
-    for (int w = 0; w < RS_WARPS; w++) {
-        uint32_t t = s_whist[w][tid];
-        s_whist[w][tid] = tile_count;
-        tile_count += t;
-    }
-    PROF_MARK(3);
-    // decoupled look-back per digit: status word = flag[31:30] | count[29:0]
-    {
-        volatile uint32_t* vlb = lb;
-        const uint32_t me = tile * RS_RADIX + tid;
-        uint32_t excl = 0;
-        if (tile == 0) {
-            vlb[me] = (2u << 30) | tile_count;
-        } else {
-            vlb[me] = (1u << 30) | tile_count;
-            // Walk back over the predecessors LB_WINDOW at a time: the status loads of a window are independent,
-            // so a walk of d tiles costs about d/LB_WINDOW L2 round trips instead of d (when a whole pass fits in
-            // one wave of CTAs nothing is inclusive yet and every tile walks all the way back).
-            int t = (int)tile - 1;
-            bool found = false;
-            while (!found) {
-                uint32_t w[LB_WINDOW];
-#pragma unroll
-                for (int u = 0; u < LB_WINDOW; u++) w[u] = t - u >= 0 ? vlb[(uint32_t)(t - u) * RS_RADIX + tid] : (2u << 30);
-#pragma unroll
-                for (int u = 0; u < LB_WINDOW; u++) {
-                    if (found) break;
-                    uint32_t sv = w[u];
-                    while ((sv >> 30) == 0u) sv = vlb[(uint32_t)(t - u) * RS_RADIX + tid];
-                    excl += sv & 0x3fffffffu;
-                    found = (sv >> 30) == 2u;
-                }
-                t -= LB_WINDOW;
-            }
-            vlb[me] = (2u << 30) | (excl + tile_count);
-        }
-        s_goff[tid] = bin_base + excl;
-    }
-    PROF_MARK(4);
-    // exclusive scan of tile_count over digits -> position of each digit's run inside the tile
-    {
-        uint32_t incl = tile_count;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= (uint32_t)o) incl += t;
-        }
-        __syncthreads();  // s_scan reuse
-        if (lane == 31) s_scan[warp] = incl;
-        __syncthreads();
-        uint32_t woff = 0;
-#pragma unroll
-        for (int w = 0; w < RS_WARPS; w++) woff += (w < (int)warp) ? s_scan[w] : 0u;
-        s_local_base[tid] = woff + incl - tile_count;
-    }
-    __syncthreads();
-
-    PROF_MARK(5);
-    // scatter into shared memory in sorted order, then stream out digit runs (coalesced)
-#pragma unroll
-    for (int i = 0; i < ITEMS; i++) {
-        uint32_t idx = chunk + i * 32 + lane;
-        if (idx < count) {
-            const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
-            const uint32_t pos = s_local_base[d] + s_whist[warp][d] + rank[i];
-            s_keys[pos] = key[i];
-            s_vals[pos] = val[i];
-        }
-    }
-    __syncthreads();
-    PROF_MARK(6);
-    for (uint32_t j = tid; j < count; j += RS_THREADS) {
-        const KeyT k = s_keys[j];
-        const uint32_t d = (uint32_t)(k >> shift) & mask;
-        const uint32_t dst = s_goff[d] + (j - s_local_base[d]);
-        keys_out[dst] = k;
-        vals_out[dst] = s_vals[j];
-    }
-    PROF_MARK(7);
+template <typename KeyT, int ITEMS>
+__global__ void __launch_bounds__(RS_THREADS, 3)
+onesweep_kernel_occ3(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, KeyT* __restrict__ keys_out,
+                uint32_t* __restrict__ vals_out, const int32_t* __restrict__ n_dev, uint32_t max_n, uint32_t shift,
+                uint32_t mask, const uint32_t* __restrict__ hist, uint32_t* lb, uint32_t* ticket) {
+#include "onesweep_body.inc"
 }
 
 template <typename KeyT>
@@ -347,10 +203,17 @@ static void radix_sort_impl(const KeyT* keys, const uint32_t* vals, const int32_
             launch_k(onesweep_kernel<KeyT, 8>, tiles, RS_THREADS, 0, st, src_k, src_v, dst_k, dst_v, n_dev, max_n,
                      plan.shift[p], plan.mask[p], (const uint32_t*)(s.hist + p * RS_RADIX),
                      s.lb + (size_t)p * tiles * RS_RADIX, s.tickets + p);
-        else if constexpr (sizeof(KeyT) == 4)
-            launch_k(onesweep_kernel<KeyT, 16>, tiles, RS_THREADS, 0, st, src_k, src_v, dst_k, dst_v, n_dev, max_n,
-                     plan.shift[p], plan.mask[p], (const uint32_t*)(s.hist + p * RS_RADIX),
-                     s.lb + (size_t)p * tiles * RS_RADIX, s.tickets + p);
+        else if constexpr (sizeof(KeyT) == 4) {
+            // more tiles than two CTAs per SM hold at once?  The buffer's size decides: the count lives on the device.
+            if (tiles > 2u * 148u)
+                launch_k(onesweep_kernel_occ3<KeyT, 16>, tiles, RS_THREADS, 0, st, src_k, src_v, dst_k, dst_v, n_dev, max_n,
+                         plan.shift[p], plan.mask[p], (const uint32_t*)(s.hist + p * RS_RADIX),
+                         s.lb + (size_t)p * tiles * RS_RADIX, s.tickets + p);
+            else
+                launch_k(onesweep_kernel<KeyT, 16>, tiles, RS_THREADS, 0, st, src_k, src_v, dst_k, dst_v, n_dev, max_n,
+                         plan.shift[p], plan.mask[p], (const uint32_t*)(s.hist + p * RS_RADIX),
+                         s.lb + (size_t)p * tiles * RS_RADIX, s.tickets + p);
+        }
         src_k = dst_k;
         src_v = dst_v;
     }
