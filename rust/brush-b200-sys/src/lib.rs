@@ -5,8 +5,12 @@
 //! `RenderBackwards::backward` (render.rs:465-626).
 //!
 //! Source only -- never compiled here (no Rust toolchain in the build image).  The Burn-facing glue that calls this
-//! crate is `rust/brush-render-b200/render_b200.rs`.
+//! crate is `rust/brush-render-b200/render_b200.rs`.  [`train`] wraps the train-step entry points (image loss, fused
+//! backward + Adam, refine), [`dist`] the view-parallel ones; between the three modules every entry point of the header has
+//! a safe wrapper (tests/test_abi_host.py checks that).
+pub mod dist;
 pub mod ffi;
+pub mod train;
 
 use std::ffi::CStr;
 use std::os::raw::{c_int, c_void};

@@ -118,6 +118,32 @@ def test_rust_ffi_block_matches_the_header():
         cls = getattr(_lib, cname)
         assert [f[0] for f in cls._fields_] == [f[0] for f in by_name[cname]], cname
         assert issubclass(cls, ctypes.Structure)
+    # every entry point of the header has a safe wrapper in the sys crate (lib.rs: render path and primitives, train.rs:
+    # the train step, dist.rs: the view-parallel step), called with as many arguments as the header declares
+    crate = os.path.join(ROOT, "rust", "brush-b200-sys", "src")
+    wrapped = {}
+    for fname in ("lib.rs", "train.rs", "dist.rs"):
+        src = open(os.path.join(crate, fname)).read()
+        for m in re.finditer(r"ffi::(brush_[a-z0-9_]+)\(", src):
+            i, depth = m.end(), 1
+            j = i
+            while depth:
+                depth += {"(": 1, ")": -1}.get(src[j], 0)
+                j += 1
+            parts, d, cur = [], 0, ""
+            for ch in src[i:j - 1]:
+                d += {"(": 1, "[": 1, "{": 1, ")": -1, "]": -1, "}": -1}.get(ch, 0)
+                if ch == "," and d == 0:
+                    parts.append(cur)
+                    cur = ""
+                else:
+                    cur += ch
+            parts.append(cur)
+            wrapped[m.group(1)] = len([x for x in parts if x.strip()])
+    n_params = {name: len(params) for name, params, _ in funcs}
+    assert set(wrapped) == declared, sorted(declared - set(wrapped))
+    for name, n_args in wrapped.items():
+        assert n_args == n_params[name], f"safe wrapper of {name} passes {n_args} arguments, the header declares {n_params[name]}"
     # the Burn-facing glue names every call it makes through the safe wrappers of the sys crate
     glue = open(os.path.join(ROOT, "rust", "brush-render-b200", "render_b200.rs")).read()
     sys_lib = open(os.path.join(ROOT, "rust", "brush-b200-sys", "src", "lib.rs")).read()
