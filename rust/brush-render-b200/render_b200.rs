@@ -35,7 +35,7 @@ use crate::{Backend, RenderAux};
 pub type CudaBackend = JitBackend<CudaRuntime, f32, i32>;
 
 /// One library context per CUDA device (the analogue of the per-device cubecl client, render.rs:91).
-fn ctx_for(device: &CudaDevice) -> &'static Mutex<Ctx> {
+pub fn ctx_for(device: &CudaDevice) -> &'static Mutex<Ctx> {
     static CTXS: OnceLock<Mutex<Vec<(usize, &'static Mutex<Ctx>)>>> = OnceLock::new();
     let mut all = CTXS.get_or_init(|| Mutex::new(Vec::new())).lock().unwrap();
     if let Some((_, c)) = all.iter().find(|(i, _)| *i == device.index) {
@@ -51,7 +51,7 @@ fn ctx_for(device: &CudaDevice) -> &'static Mutex<Ctx> {
 /// `CudaResource { ptr: CUdeviceptr, .. }`) already offset to the tensor's first element.  Tensors handed to the
 /// operator are contiguous (`into_contiguous` below), as the reference's kernels assume (render.rs binds
 /// `handle.binding()` directly).
-fn dptr<E>(t: &JitTensor<CudaRuntime, E>) -> *mut c_void {
+pub fn dptr<E>(t: &JitTensor<CudaRuntime, E>) -> *mut c_void {
     let res = t.client.get_resource(t.handle.clone().binding());
     res.resource().ptr as *mut c_void
 }
@@ -61,11 +61,11 @@ fn dptr<E>(t: &JitTensor<CudaRuntime, E>) -> *mut c_void {
 /// default stream, wait for it.  With the accessor (`feature = "cubecl-stream"`) every call is enqueue-and-return,
 /// like the reference's `client.execute_unchecked`.
 #[cfg(feature = "cubecl-stream")]
-fn stream_of(t: &JitTensor<CudaRuntime, f32>) -> *mut c_void {
+pub fn stream_of(t: &JitTensor<CudaRuntime, f32>) -> *mut c_void {
     t.client.cuda_stream() as *mut c_void
 }
 #[cfg(not(feature = "cubecl-stream"))]
-fn stream_of(t: &JitTensor<CudaRuntime, f32>) -> *mut c_void {
+pub fn stream_of(t: &JitTensor<CudaRuntime, f32>) -> *mut c_void {
     t.client.sync(); // cubecl's pending work is complete before the library touches the buffers
     std::ptr::null_mut()
 }
@@ -79,6 +79,24 @@ fn int_empty(shape: &[usize], device: &CudaDevice) -> JitTensor<CudaRuntime, i32
     // create_tensor (crates/brush-kernel/src/lib.rs:125-147): uninitialised; the library zero-fills what the
     // reference's int_zeros calls zero (render.rs:124,165,241) in its own single init launch.
     CudaBackend::int_empty(shape.to_vec().into(), device)
+}
+
+/// The C view of a forward's auxiliary tensors (`RenderAux`, lib.rs:20-33) for the backward entry points; also used by
+/// the trainer glue (`brush-train-b200/train_b200.rs`).
+pub fn aux_of(aux: &RenderAux<CudaBackend>) -> BrushAux {
+    BrushAux {
+        projected_splats: dptr(&aux.projected_splats) as *mut f32,
+        uniforms_buffer: dptr(&aux.uniforms_buffer) as *mut i32,
+        num_intersections: dptr(&aux.num_intersections) as *mut i32,
+        num_visible: dptr(&aux.num_visible) as *mut i32,
+        final_index: dptr(&aux.final_index) as *mut i32,
+        cum_tiles_hit: dptr(&aux.cum_tiles_hit) as *mut i32,
+        tile_bins: dptr(&aux.tile_bins) as *mut i32,
+        compact_gid_from_isect: dptr(&aux.compact_gid_from_isect) as *mut i32,
+        global_from_compact_gid: dptr(&aux.global_from_compact_gid) as *mut i32,
+        tile_id_from_isect: std::ptr::null_mut(),
+        isect_capacity: aux.compact_gid_from_isect.shape.dims[0] as u64,
+    }
 }
 
 /// == render_forward, crates/brush-render/src/render.rs:55-323.
@@ -359,19 +377,7 @@ impl Backward<CudaBackend, 6> for RenderBackwardsB200 {
         let v_coeffs = CudaBackend::float_empty([num_points, k, 3].into(), &device);
         let v_opacities = CudaBackend::float_empty([num_points].into(), &device);
 
-        let aux_ffi = BrushAux {
-            projected_splats: dptr(&aux.projected_splats) as *mut f32,
-            uniforms_buffer: dptr(&aux.uniforms_buffer) as *mut i32,
-            num_intersections: dptr(&aux.num_intersections) as *mut i32,
-            num_visible: dptr(&aux.num_visible) as *mut i32,
-            final_index: dptr(&aux.final_index) as *mut i32,
-            cum_tiles_hit: dptr(&aux.cum_tiles_hit) as *mut i32,
-            tile_bins: dptr(&aux.tile_bins) as *mut i32,
-            compact_gid_from_isect: dptr(&aux.compact_gid_from_isect) as *mut i32,
-            global_from_compact_gid: dptr(&aux.global_from_compact_gid) as *mut i32,
-            tile_id_from_isect: std::ptr::null_mut(),
-            isect_capacity: aux.compact_gid_from_isect.shape.dims[0] as u64,
-        };
+        let aux_ffi = aux_of(&aux);
         let ptrs = SplatPtrs {
             means: dptr(&means) as *const f32,
             log_scales: dptr(&log_scales) as *const f32,
