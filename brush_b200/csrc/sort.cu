@@ -130,7 +130,7 @@ radix_hist_kernel(const KeyT* __restrict__ keys, const int32_t* __restrict__ n_d
 
 // ---- one onesweep pass ----
 // Two kernels with ONE body (onesweep_body.inc) that differ only in their launch bounds:
-//   onesweep_kernel      100 registers, two CTAs per SM -- fastest while a pass is a single wave of tiles (its time is
+//   onesweep_kernel      128 registers, two CTAs per SM -- fastest while a pass is a single wave of tiles (its time is
 //                        then ONE tile's latency: the 1 M-key depth sort);
 //   onesweep_kernel_occ3 80 registers (no spills), three CTAs per SM -- faster as soon as a pass is many waves, where the
 //                        serial phases of a tile overlap only across CTAs (76.7 M keys: 1.94 -> 1.59 ms; 64 registers /
